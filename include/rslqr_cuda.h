@@ -1,0 +1,134 @@
+/* rslqr_cuda.h -- the C-ABI boundary between the C host layer and the sm_100a kernels.
+ *
+ * Plain C: opaque handle, ints, doubles and raw pointers only; no C++ or torch types. The
+ * reference has no FFI layer (it is one C library, reference src/ndlqr.h); these entry points are
+ * what its public functions bind to in this build:
+ *
+ *   ndlqr_NewNdLqrSolver            (reference src/solver.c:61)   -> rslqr_cuda_create
+ *   ndlqr_InitializeWithLQRProblem  (reference src/solver.c:122)  -> rslqr_cuda_upload (+ _pack_rhs)
+ *   ndlqr_ResetSolver / ResetNdData (reference src/solver.c:98)   -> rslqr_cuda_reset
+ *   ndlqr_Solve                     (reference src/solve.c:38)    -> rslqr_cuda_solve
+ *   ndlqr_SolveLeaf ... UpdateShurFactor (reference src/nested_dissection.c:10-171)
+ *                                                                 -> rslqr_cuda_stage
+ *   ndlqr_GetSolution / CopySolution (reference src/solve.c:192,197) -> rslqr_cuda_download_solution
+ *   solver->fact mirror             (reference src/nddata.c:82)   -> rslqr_cuda_download_fact
+ *   cholinfo->success               (reference src/linalg.c:84)   -> rslqr_cuda_download_status
+ *   NdLqrProfile                    (reference src/solve.c:15-25) -> rslqr_cuda_get_profile
+ *
+ * A handle owns `batch` independent problems of identical shape (n, m, N); the single-solver
+ * API uses batch = 1. Inputs are "flat knot blocks": per problem N blocks of
+ * rslqr_cuda_knot_stride(n,m) doubles in the LQRData order  Q(n) R(m) q(n) r(m) c A(n*n) B(n*m)
+ * d(n)  (reference src/lqr_data.c:25-36) plus x0(n). Outputs per problem: the solution vector of
+ * N*(2n+m) doubles [lambda_k, x_k, u_k]_k (reference src/solve.h:47-53) and optionally the factor
+ * array `fact` of log2(N)*N*(2n+m)*n doubles in the reference's NdData order.
+ *
+ * Every function returns 0 on success and a negative RSLQR_E_* code otherwise;
+ * rslqr_cuda_last_error() gives the message. All calls are synchronous with respect to the host
+ * unless stated. There is no CPU fallback: without a usable CUDA device create() fails. */
+#ifndef RSLQR_CUDA_H
+#define RSLQR_CUDA_H
+#include <stddef.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rslqr_cuda_solver rslqr_cuda_solver;
+
+enum {
+  RSLQR_OK = 0,
+  RSLQR_E_ARG = -1,      /* bad argument (NULL, non power-of-two horizon, range) */
+  RSLQR_E_NODEVICE = -2, /* no CUDA device / driver */
+  RSLQR_E_CUDA = -3,     /* a CUDA call failed */
+  RSLQR_E_NOMEM = -4,    /* device or pinned allocation failed */
+  RSLQR_E_UNSUPPORTED = -5
+};
+
+/* create() flags */
+enum {
+  RSLQR_KEEP_FACT = 1u << 0, /* allocate the dense `fact` array (needed by staged mode, stage
+                                calls and download_fact); without it only the fused kernel runs */
+  RSLQR_PROFILE = 1u << 1    /* record CUDA events around each phase in staged mode */
+};
+
+/* solve modes */
+enum {
+  RSLQR_MODE_AUTO = 0,   /* fused cluster kernel when the shape fits on chip, else staged */
+  RSLQR_MODE_STAGED = 1, /* one launch per phase per level (leaf, products, Cholesky, solves, Schur, rhs) */
+  RSLQR_MODE_FUSED = 2   /* whole solve of a problem inside one thread-block cluster */
+};
+
+/* stages for rslqr_cuda_stage(); `level`, `item`, `col` select one task, -1 = all tasks of the phase */
+enum {
+  RSLQR_STAGE_PACK_RHS = 0,    /* build the negated rhs from the flat problem (solver.c:138-190) */
+  RSLQR_STAGE_LEAVES = 1,      /* ndlqr_SolveLeaf, item = knot                                   */
+  RSLQR_STAGE_PRODUCTS = 2,    /* ndlqr_FactorInnerProduct, item = leaf, col = fact level        */
+  RSLQR_STAGE_CHOLESKY = 3,    /* separator Cholesky, item = leaf                                */
+  RSLQR_STAGE_SOLVES = 4,      /* ndlqr_SolveCholeskyFactor, item = leaf, col = upper level      */
+  RSLQR_STAGE_SCHUR = 5,       /* ndlqr_UpdateShurFactor, item = knot, col = upper level         */
+  RSLQR_STAGE_RHS_PRODUCTS = 6,
+  RSLQR_STAGE_RHS_SOLVES = 7,
+  RSLQR_STAGE_RHS_SCHUR = 8
+};
+
+int rslqr_cuda_device_count(void);
+const char* rslqr_cuda_last_error(void);
+int rslqr_cuda_knot_stride(int nstates, int ninputs);
+
+int rslqr_cuda_create(int nstates, int ninputs, int nhorizon, int batch, int device,
+                      unsigned flags, rslqr_cuda_solver** out);
+int rslqr_cuda_destroy(rslqr_cuda_solver* h);
+
+/* host -> device: problems [first, first+count). `knots` = count*N*stride doubles, `x0` = count*n. */
+int rslqr_cuda_upload(rslqr_cuda_solver* h, const double* knots, const double* x0, int first,
+                      int count);
+/* host -> device: overwrite the rhs / solution vector of problems [first, first+count) */
+int rslqr_cuda_upload_rhs(rslqr_cuda_solver* h, const double* soln, int first, int count);
+
+int rslqr_cuda_reset(rslqr_cuda_solver* h);            /* zero fact, soln and status           */
+int rslqr_cuda_set_mode(rslqr_cuda_solver* h, int mode);
+int rslqr_cuda_get_mode(rslqr_cuda_solver* h);         /* the mode solve() will actually use   */
+
+/* Whole solve for all problems of the handle: pack rhs (if `pack_rhs`), leaves, K factor levels,
+ * K rhs levels. Blocks until the result is on the device. */
+int rslqr_cuda_solve(rslqr_cuda_solver* h, int pack_rhs);
+/* Same, but only enqueues on the handle's stream (for overlap with copies); pair with _sync. */
+int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs);
+int rslqr_cuda_sync(rslqr_cuda_solver* h);
+
+/* One phase (or one task of it) in staged mode; needs RSLQR_KEEP_FACT. `problem` -1 = all. */
+int rslqr_cuda_stage(rslqr_cuda_solver* h, int stage, int level, int item, int col, int problem);
+/* ndlqr_UpdateShurFactor with an explicit calc_lambda (the reference lets the caller choose). */
+int rslqr_cuda_schur_task(rslqr_cuda_solver* h, int index, int knot, int level, int upper_level,
+                          int calc_lambda, int use_rhs, int problem);
+
+/* device -> host */
+int rslqr_cuda_download_solution(rslqr_cuda_solver* h, double* soln, int first, int count);
+int rslqr_cuda_download_fact(rslqr_cuda_solver* h, double* fact, int problem);
+/* per problem: 3N-1 status words in NdLqrCholeskyFactors slot order, 0 = ok, -1 = pivot <= 0 */
+int rslqr_cuda_download_status(rslqr_cuda_solver* h, int* status, int problem);
+/* per problem summary: 0 = every factorization succeeded */
+int rslqr_cuda_download_flags(rslqr_cuda_solver* h, int* flags, int first, int count);
+/* sqrt(diag Q_k), sqrt(diag R_k): the leaf Cholesky factors, [N][n+m] per problem */
+int rslqr_cuda_download_leaf_factors(rslqr_cuda_solver* h, double* out, int problem);
+
+/* ms: [0] total [1] leaves [2] products [3] cholesky [4] solves [5] schur [6] rhs; staged+PROFILE */
+int rslqr_cuda_get_profile(rslqr_cuda_solver* h, double ms[7]);
+
+/* raw device pointers for callers that keep data resident (benchmarks, other CUDA code).
+ * Layouts as for upload / download. `fact` is NULL without RSLQR_KEEP_FACT. */
+int rslqr_cuda_device_pointers(rslqr_cuda_solver* h, double** knots, double** x0, double** soln,
+                               double** fact);
+void* rslqr_cuda_stream(rslqr_cuda_solver* h);          /* cudaStream_t the handle launches on */
+int rslqr_cuda_kernel_launches(rslqr_cuda_solver* h);   /* kernels launched by the last solve  */
+/* average device time (ms) of the dominant kernel over the launches since the last call with
+ * reset != 0; measured with CUDA events on the handle's stream when enabled by enable != 0 */
+int rslqr_cuda_kernel_timing(rslqr_cuda_solver* h, int enable, int reset, double* avg_ms, int* launches);
+
+/* pinned host memory helpers so that callers can stage uploads at full PCIe rate */
+void* rslqr_cuda_host_alloc(size_t bytes);
+void rslqr_cuda_host_free(void* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

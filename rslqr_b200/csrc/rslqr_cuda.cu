@@ -1,0 +1,455 @@
+// rslqr_cuda.cu -- implementation of the C-ABI in include/rslqr_cuda.h: device memory, copies,
+// kernel launches. No arithmetic happens on the host in this file.
+#include "rslqr_cuda.h"
+
+#include <cuda_runtime.h>
+
+#include <chrono>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "kernels_fused.cuh"
+#include "kernels_staged.cuh"
+
+using namespace rslqr;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+#define CU(call)                                                                         \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess)                                                               \
+      return fail(e_ == cudaErrorMemoryAllocation ? RSLQR_E_NOMEM : RSLQR_E_CUDA,        \
+                  std::string(#call) + ": " + cudaGetErrorString(e_));                   \
+  } while (0)
+
+struct PhaseSpan { int phase; cudaEvent_t t0, t1; };
+
+struct rslqr_cuda_solver {
+  Shape s;
+  Bufs b;
+  int batch, device;
+  unsigned flags;
+  int mode;            // requested
+  cudaStream_t stream;
+  double* d_knots; double* d_x0;
+  int launches;
+  // staged-mode profile
+  std::vector<PhaseSpan> spans;
+  std::vector<cudaEvent_t> evpool; size_t evused;
+  double prof[7];
+  // dominant-kernel timing
+  bool ktime_on; std::vector<std::pair<cudaEvent_t, cudaEvent_t>> kspans; double k_ms; int k_n;
+  FusedPlan fused;
+};
+
+extern "C" const char* rslqr_cuda_last_error(void) { return g_err.c_str(); }
+
+extern "C" int rslqr_cuda_device_count(void) {
+  int c = 0;
+  if (cudaGetDeviceCount(&c) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return c;
+}
+
+extern "C" int rslqr_cuda_knot_stride(int n, int m) { return 2 * n + 2 * m + 1 + n * n + n * m + n; }
+
+static Shape make_shape(int n, int m, int N) {
+  Shape s;
+  s.n = n; s.m = m; s.N = N; s.K = rs_log2(N);
+  s.fs = (2 * n + m) * n; s.zs = 2 * n + m;
+  s.stride = rslqr_cuda_knot_stride(n, m);
+  s.oQ = 0; s.oR = n; s.oq = n + m; s.orr = 2 * n + m; s.oA = 2 * n + 2 * m + 1;
+  s.oB = s.oA + n * n; s.od = s.oB + n * m;
+  return s;
+}
+
+extern "C" int rslqr_cuda_create(int n, int m, int N, int batch, int device, unsigned flags,
+                                 rslqr_cuda_solver** out) {
+  if (!out) return fail(RSLQR_E_ARG, "out is NULL");
+  *out = nullptr;
+  if (n <= 0 || m <= 0 || N < 2 || (N & (N - 1)) || batch <= 0)
+    return fail(RSLQR_E_ARG, "need n,m,batch > 0 and a power-of-two horizon >= 2");
+  int ndev = rslqr_cuda_device_count();
+  if (ndev <= 0) return fail(RSLQR_E_NODEVICE, "no CUDA device available (there is no CPU fallback)");
+  if (device < 0 || device >= ndev) return fail(RSLQR_E_ARG, "device index out of range");
+  CU(cudaSetDevice(device));
+  rslqr_cuda_solver* h = new rslqr_cuda_solver();
+  h->s = make_shape(n, m, N);
+  h->batch = batch; h->device = device; h->flags = flags; h->mode = RSLQR_MODE_AUTO;
+  h->launches = 0; h->evused = 0; h->ktime_on = false; h->k_ms = 0; h->k_n = 0;
+  memset(h->prof, 0, sizeof(h->prof));
+  memset(&h->b, 0, sizeof(h->b));
+  h->d_knots = h->d_x0 = nullptr;
+  const Shape& s = h->s;
+  cudaError_t e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking);
+  if (e != cudaSuccess) { delete h; return fail(RSLQR_E_CUDA, cudaGetErrorString(e)); }
+  auto alloc = [&](void** p, size_t bytes) { return cudaMalloc(p, bytes); };
+  bool ok = true;
+  ok &= alloc((void**)&h->d_knots, sizeof(double) * (size_t)batch * N * s.stride) == cudaSuccess;
+  ok &= alloc((void**)&h->d_x0, sizeof(double) * (size_t)batch * n) == cudaSuccess;
+  ok &= alloc((void**)&h->b.soln, sizeof(double) * (size_t)batch * N * s.zs) == cudaSuccess;
+  ok &= alloc((void**)&h->b.status, sizeof(int) * (size_t)batch * 3 * N) == cudaSuccess;
+  ok &= alloc((void**)&h->b.flags, sizeof(int) * (size_t)batch) == cudaSuccess;
+  ok &= alloc((void**)&h->b.leafd, sizeof(double) * (size_t)batch * N * (n + m)) == cudaSuccess;
+  if (ok && (flags & RSLQR_KEEP_FACT))
+    ok &= alloc((void**)&h->b.fact, sizeof(double) * (size_t)batch * s.K * N * s.fs) == cudaSuccess;
+  if (!ok) {
+    cudaGetLastError();
+    rslqr_cuda_destroy(h);
+    return fail(RSLQR_E_NOMEM, "device allocation failed");
+  }
+  h->b.knots = h->d_knots; h->b.x0 = h->d_x0;
+  fused_plan(h->s, h->batch, h->device, &h->fused);
+  *out = h;
+  int rc = rslqr_cuda_reset(h);
+  if (rc) { rslqr_cuda_destroy(h); *out = nullptr; }
+  return rc;
+}
+
+extern "C" int rslqr_cuda_destroy(rslqr_cuda_solver* h) {
+  if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
+  cudaSetDevice(h->device);
+  cudaStreamSynchronize(h->stream);
+  cudaFree(h->d_knots); cudaFree(h->d_x0); cudaFree(h->b.soln); cudaFree(h->b.fact);
+  cudaFree(h->b.status); cudaFree(h->b.flags); cudaFree(h->b.leafd);
+  for (auto ev : h->evpool) cudaEventDestroy(ev);
+  for (auto& pr : h->kspans) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+  cudaStreamDestroy(h->stream);
+  delete h;
+  return RSLQR_OK;
+}
+
+static bool range_ok(const rslqr_cuda_solver* h, int first, int count) {
+  return first >= 0 && count >= 0 && first + count <= h->batch;
+}
+
+extern "C" int rslqr_cuda_upload(rslqr_cuda_solver* h, const double* knots, const double* x0,
+                                 int first, int count) {
+  if (!h || !knots || !x0 || !range_ok(h, first, count)) return fail(RSLQR_E_ARG, "upload: bad argument");
+  CU(cudaSetDevice(h->device));
+  const Shape& s = h->s;
+  const size_t per = (size_t)s.N * s.stride;
+  CU(cudaMemcpyAsync(h->d_knots + first * per, knots, sizeof(double) * per * count, cudaMemcpyHostToDevice, h->stream));
+  CU(cudaMemcpyAsync(h->d_x0 + (size_t)first * s.n, x0, sizeof(double) * (size_t)s.n * count, cudaMemcpyHostToDevice, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_upload_rhs(rslqr_cuda_solver* h, const double* soln, int first, int count) {
+  if (!h || !soln || !range_ok(h, first, count)) return fail(RSLQR_E_ARG, "upload_rhs: bad argument");
+  CU(cudaSetDevice(h->device));
+  const size_t per = (size_t)h->s.N * h->s.zs;
+  CU(cudaMemcpyAsync(h->b.soln + first * per, soln, sizeof(double) * per * count, cudaMemcpyHostToDevice, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_reset(rslqr_cuda_solver* h) {
+  if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
+  CU(cudaSetDevice(h->device));
+  const Shape& s = h->s;
+  if (h->b.fact) CU(cudaMemsetAsync(h->b.fact, 0, sizeof(double) * (size_t)h->batch * s.K * s.N * s.fs, h->stream));
+  CU(cudaMemsetAsync(h->b.soln, 0, sizeof(double) * (size_t)h->batch * s.N * s.zs, h->stream));
+  CU(cudaMemsetAsync(h->b.status, 0, sizeof(int) * (size_t)h->batch * 3 * s.N, h->stream));
+  CU(cudaMemsetAsync(h->b.flags, 0, sizeof(int) * (size_t)h->batch, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_set_mode(rslqr_cuda_solver* h, int mode) {
+  if (!h || mode < RSLQR_MODE_AUTO || mode > RSLQR_MODE_FUSED) return fail(RSLQR_E_ARG, "set_mode: bad argument");
+  if (mode == RSLQR_MODE_STAGED && !h->b.fact) return fail(RSLQR_E_UNSUPPORTED, "staged mode needs RSLQR_KEEP_FACT");
+  if (mode == RSLQR_MODE_FUSED && !h->fused.available) return fail(RSLQR_E_UNSUPPORTED, "shape does not fit the fused cluster kernel");
+  h->mode = mode;
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_get_mode(rslqr_cuda_solver* h) {
+  if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
+  if (h->mode != RSLQR_MODE_AUTO) return h->mode;
+  if (h->fused.available) return RSLQR_MODE_FUSED;
+  return RSLQR_MODE_STAGED;
+}
+
+// ------------------------------------------------------------------ staged launches
+static inline int round32(int x) { return ((x + 31) / 32) * 32; }
+static inline int clampi(int x, int lo, int hi) { return x < lo ? lo : (x > hi ? hi : x); }
+
+static int launch_stage(rslqr_cuda_solver* h, int stage, int level, Sel sel) {
+  const Shape& s = h->s;
+  const int n = s.n, nn = n * n;
+  if (sel.np <= 0 || sel.nitems <= 0) return RSLQR_OK;
+  const long long tasks = (long long)sel.np * sel.nitems;
+  cudaStream_t st = h->stream;
+  switch (stage) {
+    case RSLQR_STAGE_PACK_RHS: {
+      sel.item0 = 0; sel.nitems = s.N;
+      const long long tot = (long long)sel.np * s.N * s.zs;
+      pack_rhs_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(s, h->b, sel);
+      break;
+    }
+    case RSLQR_STAGE_LEAVES:
+      leaf_kernel<<<(unsigned)tasks, clampi(round32(nn), 32, 256), 0, st>>>(s, h->b, sel);
+      break;
+    case RSLQR_STAGE_PRODUCTS:
+      products_kernel<<<(unsigned)(tasks * (sel.col < 0 ? 3 : 1)), clampi(round32(nn), 32, 256), 0, st>>>(s, h->b, sel, level);
+      break;
+    case RSLQR_STAGE_CHOLESKY:
+      cholesky_kernel<<<(unsigned)tasks, clampi(round32(n), 32, 256), sizeof(double) * nn, st>>>(s, h->b, sel, level);
+      break;
+    case RSLQR_STAGE_SOLVES:
+      solves_kernel<<<(unsigned)(tasks * (sel.col < 0 ? 2 : 1)), clampi(round32(nn), 32, 256), sizeof(double) * 2 * nn, st>>>(s, h->b, sel, level);
+      break;
+    case RSLQR_STAGE_SCHUR:
+      schur_kernel<<<(unsigned)(tasks * (sel.col < 0 ? 2 : 1)), clampi(round32(s.fs), 32, 256), sizeof(double) * nn, st>>>(s, h->b, sel, level);
+      break;
+    case RSLQR_STAGE_RHS_PRODUCTS:
+      rhs_products_kernel<<<(unsigned)((tasks * n + 127) / 128), 128, 0, st>>>(s, h->b, sel, level);
+      break;
+    case RSLQR_STAGE_RHS_SOLVES:
+      rhs_solves_kernel<<<(unsigned)tasks, clampi(round32(n), 32, 256), sizeof(double) * (nn + n), st>>>(s, h->b, sel, level);
+      break;
+    case RSLQR_STAGE_RHS_SCHUR:
+      rhs_schur_kernel<<<(unsigned)((tasks * s.zs + 127) / 128), 128, 0, st>>>(s, h->b, sel, level);
+      break;
+    default:
+      return fail(RSLQR_E_ARG, "unknown stage");
+  }
+  CU(cudaGetLastError());
+  ++h->launches;
+  return RSLQR_OK;
+}
+
+static cudaEvent_t take_event(rslqr_cuda_solver* h) {
+  if (h->evused == h->evpool.size()) {
+    cudaEvent_t ev;
+    cudaEventCreate(&ev);
+    h->evpool.push_back(ev);
+  }
+  return h->evpool[h->evused++];
+}
+
+static int timed_stage(rslqr_cuda_solver* h, int phase, int stage, int level, const Sel& sel) {
+  const bool prof = (h->flags & RSLQR_PROFILE) != 0;
+  PhaseSpan sp;
+  if (prof) { sp.phase = phase; sp.t0 = take_event(h); sp.t1 = take_event(h); cudaEventRecord(sp.t0, h->stream); }
+  int rc = launch_stage(h, stage, level, sel);
+  if (prof) { cudaEventRecord(sp.t1, h->stream); h->spans.push_back(sp); }
+  return rc;
+}
+
+static Sel all_items(const rslqr_cuda_solver* h, int nitems) {
+  Sel sel;
+  sel.p0 = 0; sel.np = h->batch; sel.item0 = 0; sel.nitems = nitems; sel.col = -1;
+  sel.calc_lambda = -1; sel.index = -1;
+  return sel;
+}
+
+static int solve_staged(rslqr_cuda_solver* h, int pack_rhs) {
+  const Shape& s = h->s;
+  if (!h->b.fact) return fail(RSLQR_E_UNSUPPORTED, "staged mode needs RSLQR_KEEP_FACT");
+  int rc = 0;
+  if (s.n * s.n * 2 * sizeof(double) > 48 * 1024) {
+    CU(cudaFuncSetAttribute(solves_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(s.n * s.n * 2 * sizeof(double))));
+  }
+  if (pack_rhs) rc |= timed_stage(h, 6, RSLQR_STAGE_PACK_RHS, 0, all_items(h, s.N));
+  rc |= timed_stage(h, 1, RSLQR_STAGE_LEAVES, 0, all_items(h, s.N));
+  for (int level = 0; level < s.K && !rc; ++level) {
+    const int leaves = 1 << (s.K - level - 1);
+    rc |= timed_stage(h, 2, RSLQR_STAGE_PRODUCTS, level, all_items(h, leaves));
+    rc |= timed_stage(h, 3, RSLQR_STAGE_CHOLESKY, level, all_items(h, leaves));
+    if (level < s.K - 1) {
+      rc |= timed_stage(h, 4, RSLQR_STAGE_SOLVES, level, all_items(h, leaves));
+      rc |= timed_stage(h, 5, RSLQR_STAGE_SCHUR, level, all_items(h, s.N));
+    }
+  }
+  for (int level = 0; level < s.K && !rc; ++level) {
+    const int leaves = 1 << (s.K - level - 1);
+    rc |= timed_stage(h, 6, RSLQR_STAGE_RHS_PRODUCTS, level, all_items(h, leaves));
+    rc |= timed_stage(h, 6, RSLQR_STAGE_RHS_SOLVES, level, all_items(h, leaves));
+    rc |= timed_stage(h, 6, RSLQR_STAGE_RHS_SCHUR, level, all_items(h, s.N));
+  }
+  return rc;
+}
+
+extern "C" int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs) {
+  if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
+  CU(cudaSetDevice(h->device));
+  h->launches = 0;
+  h->spans.clear();
+  h->evused = 0;
+  const int mode = rslqr_cuda_get_mode(h);
+  if (mode == RSLQR_MODE_FUSED) {
+    std::pair<cudaEvent_t, cudaEvent_t> kt;
+    if (h->ktime_on) {
+      cudaEventCreate(&kt.first); cudaEventCreate(&kt.second);
+      cudaEventRecord(kt.first, h->stream);
+    }
+    int rc = fused_launch(h->fused, h->s, h->b, h->batch, pack_rhs, h->stream, g_err);
+    if (h->ktime_on) { cudaEventRecord(kt.second, h->stream); h->kspans.push_back(kt); }
+    if (rc) return rc;
+    h->launches = 1;
+    return RSLQR_OK;
+  }
+  return solve_staged(h, pack_rhs);
+}
+
+extern "C" int rslqr_cuda_sync(rslqr_cuda_solver* h) {
+  if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
+  CU(cudaSetDevice(h->device));
+  CU(cudaStreamSynchronize(h->stream));
+  if (!h->spans.empty()) {
+    memset(h->prof, 0, sizeof(h->prof));
+    for (auto& sp : h->spans) {
+      float ms = 0;
+      cudaEventElapsedTime(&ms, sp.t0, sp.t1);
+      h->prof[sp.phase] += ms;
+      h->prof[0] += ms;
+    }
+    h->spans.clear();
+  }
+  for (auto& pr : h->kspans) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, pr.first, pr.second) == cudaSuccess) { h->k_ms += ms; ++h->k_n; }
+    cudaEventDestroy(pr.first); cudaEventDestroy(pr.second);
+  }
+  h->kspans.clear();
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_solve(rslqr_cuda_solver* h, int pack_rhs) {
+  int rc = rslqr_cuda_solve_async(h, pack_rhs);
+  if (rc) return rc;
+  return rslqr_cuda_sync(h);
+}
+
+extern "C" int rslqr_cuda_stage(rslqr_cuda_solver* h, int stage, int level, int item, int col, int problem) {
+  if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
+  if (!h->b.fact) return fail(RSLQR_E_UNSUPPORTED, "stage calls need RSLQR_KEEP_FACT");
+  const Shape& s = h->s;
+  if (level < 0 || level >= s.K || problem >= h->batch) return fail(RSLQR_E_ARG, "stage: level/problem out of range");
+  CU(cudaSetDevice(h->device));
+  const bool per_knot = stage == RSLQR_STAGE_LEAVES || stage == RSLQR_STAGE_SCHUR ||
+                        stage == RSLQR_STAGE_RHS_SCHUR || stage == RSLQR_STAGE_PACK_RHS;
+  const int nall = per_knot ? s.N : (1 << (s.K - level - 1));
+  if (item >= nall || col >= s.K) return fail(RSLQR_E_ARG, "stage: item/col out of range");
+  Sel sel = all_items(h, nall);
+  if (problem >= 0) { sel.p0 = problem; sel.np = 1; }
+  if (item >= 0) { sel.item0 = item; sel.nitems = 1; }
+  sel.col = col;
+  if (s.n * s.n * 2 * sizeof(double) > 48 * 1024)
+    CU(cudaFuncSetAttribute(solves_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(s.n * s.n * 2 * sizeof(double))));
+  int rc = launch_stage(h, stage, level, sel);
+  if (rc) return rc;
+  CU(cudaStreamSynchronize(h->stream));
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_schur_task(rslqr_cuda_solver* h, int index, int knot, int level, int upper_level,
+                                     int calc_lambda, int use_rhs, int problem) {
+  if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
+  if (!h->b.fact) return fail(RSLQR_E_UNSUPPORTED, "stage calls need RSLQR_KEEP_FACT");
+  const Shape& s = h->s;
+  if (level < 0 || level >= s.K || upper_level < 0 || upper_level >= s.K || knot < 0 || knot >= s.N ||
+      index < 0 || index >= s.N - 1 || problem >= h->batch)
+    return fail(RSLQR_E_ARG, "schur_task: argument out of range");
+  CU(cudaSetDevice(h->device));
+  Sel sel = all_items(h, 1);
+  if (problem >= 0) { sel.p0 = problem; sel.np = 1; }
+  sel.item0 = knot; sel.col = upper_level; sel.calc_lambda = calc_lambda ? 1 : 0; sel.index = index;
+  int rc = launch_stage(h, use_rhs ? RSLQR_STAGE_RHS_SCHUR : RSLQR_STAGE_SCHUR, level, sel);
+  if (rc) return rc;
+  CU(cudaStreamSynchronize(h->stream));
+  return RSLQR_OK;
+}
+
+// ------------------------------------------------------------------ device -> host
+extern "C" int rslqr_cuda_download_solution(rslqr_cuda_solver* h, double* soln, int first, int count) {
+  if (!h || !soln || !range_ok(h, first, count)) return fail(RSLQR_E_ARG, "download_solution: bad argument");
+  CU(cudaSetDevice(h->device));
+  const size_t per = (size_t)h->s.N * h->s.zs;
+  CU(cudaMemcpyAsync(soln, h->b.soln + first * per, sizeof(double) * per * count, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_download_fact(rslqr_cuda_solver* h, double* fact, int problem) {
+  if (!h || !fact || problem < 0 || problem >= h->batch) return fail(RSLQR_E_ARG, "download_fact: bad argument");
+  if (!h->b.fact) return fail(RSLQR_E_UNSUPPORTED, "download_fact needs RSLQR_KEEP_FACT");
+  CU(cudaSetDevice(h->device));
+  const size_t per = (size_t)h->s.K * h->s.N * h->s.fs;
+  CU(cudaMemcpyAsync(fact, h->b.fact + problem * per, sizeof(double) * per, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_download_status(rslqr_cuda_solver* h, int* status, int problem) {
+  if (!h || !status || problem < 0 || problem >= h->batch) return fail(RSLQR_E_ARG, "download_status: bad argument");
+  CU(cudaSetDevice(h->device));
+  const size_t per = (size_t)3 * h->s.N;
+  CU(cudaMemcpyAsync(status, h->b.status + problem * per, sizeof(int) * (per - 1), cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_download_flags(rslqr_cuda_solver* h, int* flags, int first, int count) {
+  if (!h || !flags || !range_ok(h, first, count)) return fail(RSLQR_E_ARG, "download_flags: bad argument");
+  CU(cudaSetDevice(h->device));
+  CU(cudaMemcpyAsync(flags, h->b.flags + first, sizeof(int) * count, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_download_leaf_factors(rslqr_cuda_solver* h, double* out, int problem) {
+  if (!h || !out || problem < 0 || problem >= h->batch) return fail(RSLQR_E_ARG, "download_leaf_factors: bad argument");
+  CU(cudaSetDevice(h->device));
+  const size_t per = (size_t)h->s.N * (h->s.n + h->s.m);
+  CU(cudaMemcpyAsync(out, h->b.leafd + problem * per, sizeof(double) * per, cudaMemcpyDeviceToHost, h->stream));
+  CU(cudaStreamSynchronize(h->stream));
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_get_profile(rslqr_cuda_solver* h, double ms[7]) {
+  if (!h || !ms) return fail(RSLQR_E_ARG, "get_profile: bad argument");
+  memcpy(ms, h->prof, sizeof(h->prof));
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_device_pointers(rslqr_cuda_solver* h, double** knots, double** x0, double** soln, double** fact) {
+  if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
+  if (knots) *knots = h->d_knots;
+  if (x0) *x0 = h->d_x0;
+  if (soln) *soln = h->b.soln;
+  if (fact) *fact = h->b.fact;
+  return RSLQR_OK;
+}
+
+extern "C" void* rslqr_cuda_stream(rslqr_cuda_solver* h) { return h ? (void*)h->stream : nullptr; }
+extern "C" int rslqr_cuda_kernel_launches(rslqr_cuda_solver* h) { return h ? h->launches : RSLQR_E_ARG; }
+
+extern "C" int rslqr_cuda_kernel_timing(rslqr_cuda_solver* h, int enable, int reset, double* avg_ms, int* launches) {
+  if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
+  if (avg_ms) *avg_ms = h->k_n ? h->k_ms / h->k_n : 0.0;
+  if (launches) *launches = h->k_n;
+  if (reset) { h->k_ms = 0; h->k_n = 0; }
+  h->ktime_on = enable != 0;
+  return RSLQR_OK;
+}
+
+extern "C" void* rslqr_cuda_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cudaHostAlloc(&p, bytes, cudaHostAllocDefault) != cudaSuccess) {
+    cudaGetLastError();
+    g_err = "cudaHostAlloc failed";
+    return nullptr;
+  }
+  return p;
+}
+extern "C" void rslqr_cuda_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}

@@ -1,0 +1,435 @@
+"""ctypes binding of librslqr.so (include/rslqr_cuda.h, include/solver.h, include/solve.h, ...).
+
+Mirrors the reference's operator surface for the solve path: ``NdLqrSolver`` wraps
+ndlqr_NewNdLqrSolver / ndlqr_InitializeWithLQRProblem / ndlqr_Solve / ndlqr_GetSolution
+(reference src/solver.h:131-157, src/solve.h:37-72) and ``CudaSolver`` wraps the batched C-ABI.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "librslqr.so")
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+        "(make -C rslqr_b200/csrc). There is no Python or CPU fallback for the solve path.")
+LIB = C.CDLL(LIB_PATH)
+
+MODE_AUTO, MODE_STAGED, MODE_FUSED = 0, 1, 2
+KEEP_FACT, PROFILE = 1, 2
+STAGE = dict(PACK_RHS=0, LEAVES=1, PRODUCTS=2, CHOLESKY=3, SOLVES=4, SCHUR=5,
+             RHS_PRODUCTS=6, RHS_SOLVES=7, RHS_SCHUR=8)
+
+c_dp = C.POINTER(C.c_double)
+c_ip = C.POINTER(C.c_int)
+
+
+class RslqrError(RuntimeError):
+    pass
+
+
+def _sig(name, restype, *argtypes):
+    fn = getattr(LIB, name)
+    fn.restype = restype
+    fn.argtypes = list(argtypes)
+    return fn
+
+
+_sig("rslqr_cuda_last_error", C.c_char_p)
+_sig("rslqr_cuda_device_count", C.c_int)
+_sig("rslqr_cuda_knot_stride", C.c_int, C.c_int, C.c_int)
+_sig("rslqr_cuda_create", C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint, C.POINTER(C.c_void_p))
+_sig("rslqr_cuda_destroy", C.c_int, C.c_void_p)
+_sig("rslqr_cuda_upload", C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int)
+_sig("rslqr_cuda_upload_rhs", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int)
+_sig("rslqr_cuda_reset", C.c_int, C.c_void_p)
+_sig("rslqr_cuda_set_mode", C.c_int, C.c_void_p, C.c_int)
+_sig("rslqr_cuda_get_mode", C.c_int, C.c_void_p)
+_sig("rslqr_cuda_solve", C.c_int, C.c_void_p, C.c_int)
+_sig("rslqr_cuda_solve_async", C.c_int, C.c_void_p, C.c_int)
+_sig("rslqr_cuda_sync", C.c_int, C.c_void_p)
+_sig("rslqr_cuda_stage", C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int)
+_sig("rslqr_cuda_schur_task", C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int)
+_sig("rslqr_cuda_download_solution", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int)
+_sig("rslqr_cuda_download_fact", C.c_int, C.c_void_p, C.c_void_p, C.c_int)
+_sig("rslqr_cuda_download_status", C.c_int, C.c_void_p, C.c_void_p, C.c_int)
+_sig("rslqr_cuda_download_flags", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int)
+_sig("rslqr_cuda_download_leaf_factors", C.c_int, C.c_void_p, C.c_void_p, C.c_int)
+_sig("rslqr_cuda_get_profile", C.c_int, C.c_void_p, c_dp)
+_sig("rslqr_cuda_device_pointers", C.c_int, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+     C.POINTER(C.c_void_p), C.POINTER(C.c_void_p))
+_sig("rslqr_cuda_stream", C.c_void_p, C.c_void_p)
+_sig("rslqr_cuda_kernel_launches", C.c_int, C.c_void_p)
+_sig("rslqr_cuda_kernel_timing", C.c_int, C.c_void_p, C.c_int, C.c_int, c_dp, c_ip)
+_sig("rslqr_cuda_host_alloc", C.c_void_p, C.c_size_t)
+_sig("rslqr_cuda_host_free", None, C.c_void_p)
+_sig("rslqr_synth_fill", C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.c_void_p)
+
+
+def knot_stride(n, m):
+    return LIB.rslqr_cuda_knot_stride(n, m)
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise RslqrError(f"{what} failed ({rc}): {LIB.rslqr_cuda_last_error().decode()}")
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def pinned_array(shape, dtype=np.float64):
+    """numpy array over cudaHostAlloc'ed memory (freed when the array's base is collected)."""
+    count = int(np.prod(shape))
+    nbytes = max(count * np.dtype(dtype).itemsize, 8)
+    p = LIB.rslqr_cuda_host_alloc(nbytes)
+    if not p:
+        raise RslqrError("pinned allocation failed: " + LIB.rslqr_cuda_last_error().decode())
+    buf = (C.c_char * nbytes).from_address(p)
+    arr = np.frombuffer(buf, dtype=dtype, count=count).reshape(shape)
+    _PINNED[id(buf)] = (buf, p)
+    return arr
+
+
+_PINNED = {}
+
+
+class CudaSolver:
+    """Batched device solver: one handle = `batch` problems of shape (n, m, N) on one GPU."""
+
+    def __init__(self, n, m, N, batch=1, device=0, flags=KEEP_FACT):
+        self.n, self.m, self.N, self.batch, self.device = n, m, N, batch, device
+        self.K = N.bit_length() - 1
+        self.fs, self.zs, self.stride = (2 * n + m) * n, 2 * n + m, knot_stride(n, m)
+        self.h = C.c_void_p()
+        _check(LIB.rslqr_cuda_create(n, m, N, batch, device, flags, C.byref(self.h)), "rslqr_cuda_create")
+
+    def close(self):
+        if self.h:
+            LIB.rslqr_cuda_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # -- data movement
+    def upload(self, knots, x0, first=0):
+        knots = np.ascontiguousarray(knots, dtype=np.float64)
+        x0 = np.ascontiguousarray(x0, dtype=np.float64)
+        count = x0.size // self.n
+        assert knots.size == count * self.N * self.stride, "knots must be [count][N][stride]"
+        _check(LIB.rslqr_cuda_upload(self.h, _ptr(knots), _ptr(x0), first, count), "upload")
+
+    def upload_rhs(self, soln, first=0):
+        soln = np.ascontiguousarray(soln, dtype=np.float64)
+        _check(LIB.rslqr_cuda_upload_rhs(self.h, _ptr(soln), first, soln.size // (self.N * self.zs)), "upload_rhs")
+
+    def reset(self):
+        _check(LIB.rslqr_cuda_reset(self.h), "reset")
+
+    def set_mode(self, mode):
+        _check(LIB.rslqr_cuda_set_mode(self.h, mode), "set_mode")
+
+    @property
+    def mode(self):
+        return LIB.rslqr_cuda_get_mode(self.h)
+
+    # -- compute
+    def solve(self, pack_rhs=True):
+        _check(LIB.rslqr_cuda_solve(self.h, int(pack_rhs)), "solve")
+
+    def solve_async(self, pack_rhs=True):
+        _check(LIB.rslqr_cuda_solve_async(self.h, int(pack_rhs)), "solve_async")
+
+    def sync(self):
+        _check(LIB.rslqr_cuda_sync(self.h), "sync")
+
+    def stage(self, name, level=0, item=-1, col=-1, problem=-1):
+        _check(LIB.rslqr_cuda_stage(self.h, STAGE[name], level, item, col, problem), "stage " + name)
+
+    def schur_task(self, index, knot, level, upper_level, calc_lambda, use_rhs=False, problem=-1):
+        _check(LIB.rslqr_cuda_schur_task(self.h, index, knot, level, upper_level, int(calc_lambda),
+                                         int(use_rhs), problem), "schur_task")
+
+    # -- results
+    def solution(self, first=0, count=None, out=None):
+        count = self.batch - first if count is None else count
+        if out is None:
+            out = np.empty((count, self.N * self.zs))
+        _check(LIB.rslqr_cuda_download_solution(self.h, _ptr(out), first, count), "download_solution")
+        return out
+
+    def fact(self, problem=0):
+        out = np.empty((self.K, self.N, self.fs))
+        _check(LIB.rslqr_cuda_download_fact(self.h, _ptr(out), problem), "download_fact")
+        return out
+
+    def status(self, problem=0):
+        out = np.zeros(3 * self.N - 1, dtype=np.int32)
+        _check(LIB.rslqr_cuda_download_status(self.h, _ptr(out), problem), "download_status")
+        return out
+
+    def flags(self):
+        out = np.zeros(self.batch, dtype=np.int32)
+        _check(LIB.rslqr_cuda_download_flags(self.h, _ptr(out), 0, self.batch), "download_flags")
+        return out
+
+    def leaf_factors(self, problem=0):
+        out = np.empty((self.N, self.n + self.m))
+        _check(LIB.rslqr_cuda_download_leaf_factors(self.h, _ptr(out), problem), "download_leaf_factors")
+        return out
+
+    def profile(self):
+        ms = (C.c_double * 7)()
+        _check(LIB.rslqr_cuda_get_profile(self.h, ms), "get_profile")
+        return dict(zip(("total", "leaves", "products", "cholesky", "solves", "schur", "rhs"), list(ms)))
+
+    def device_pointers(self):
+        p = [C.c_void_p() for _ in range(4)]
+        _check(LIB.rslqr_cuda_device_pointers(self.h, *[C.byref(x) for x in p]), "device_pointers")
+        return dict(zip(("knots", "x0", "soln", "fact"), [x.value for x in p]))
+
+    @property
+    def stream(self):
+        return LIB.rslqr_cuda_stream(self.h)
+
+    @property
+    def launches(self):
+        return LIB.rslqr_cuda_kernel_launches(self.h)
+
+    def kernel_timing(self, enable=True, reset=False):
+        ms, cnt = C.c_double(), C.c_int()
+        _check(LIB.rslqr_cuda_kernel_timing(self.h, int(enable), int(reset), C.byref(ms), C.byref(cnt)), "kernel_timing")
+        return ms.value, cnt.value
+
+
+def synth_problems(n, m, N, seed, first_id, count, knots=None, x0=None):
+    """Flat synthetic problems: returns (knots[count,N,stride], x0[count,n])."""
+    st = knot_stride(n, m)
+    if knots is None:
+        knots = np.empty((count, N, st))
+    if x0 is None:
+        x0 = np.empty((count, n))
+    rc = LIB.rslqr_synth_fill(n, m, N, seed, first_id, count, _ptr(knots), _ptr(x0))
+    if rc != 0:
+        raise RslqrError("rslqr_synth_fill failed")
+    return knots, x0
+
+
+# ---------------------------------------------------------------------------------------------
+# C host API (struct layouts of include/*.h == the reference's public structs)
+# ---------------------------------------------------------------------------------------------
+class Matrix(C.Structure):
+    _fields_ = [("rows", C.c_int), ("cols", C.c_int), ("data", c_dp)]
+
+
+class LQRData(C.Structure):
+    _fields_ = [("nstates", C.c_int), ("ninputs", C.c_int)] + [(k, c_dp) for k in "QRqrcABd"]
+
+
+class LQRProblem(C.Structure):
+    _fields_ = [("nhorizon", C.c_int), ("x0", c_dp), ("lqrdata", C.POINTER(C.POINTER(LQRData)))]
+
+
+class NdFactor(C.Structure):
+    _fields_ = [("lambda_", Matrix), ("state", Matrix), ("input", Matrix)]
+
+
+class NdData(C.Structure):
+    _fields_ = [("nstates", C.c_int), ("ninputs", C.c_int), ("nsegments", C.c_int), ("depth", C.c_int),
+                ("width", C.c_int), ("data", c_dp), ("factors", C.POINTER(NdFactor))]
+
+
+class CholeskyInfo(C.Structure):
+    _fields_ = [("uplo", C.c_char), ("success", C.c_int), ("lib", C.c_char), ("fact", C.c_void_p),
+                ("is_freed", C.c_int)]
+
+
+class NdLqrCholeskyFactors(C.Structure):
+    _fields_ = [("depth", C.c_int), ("nhorizon", C.c_int), ("cholinfo", C.POINTER(CholeskyInfo)),
+                ("numfacts", C.c_int)]
+
+
+class UnitRange(C.Structure):
+    _fields_ = [("start", C.c_int), ("stop", C.c_int)]
+
+
+class BinaryNode(C.Structure):
+    pass
+
+
+BinaryNode._fields_ = [("idx", C.c_int), ("level", C.c_int), ("levelidx", C.c_int), ("left_inds", UnitRange),
+                       ("right_inds", UnitRange), ("parent", C.POINTER(BinaryNode)),
+                       ("left_child", C.POINTER(BinaryNode)), ("right_child", C.POINTER(BinaryNode))]
+
+
+class OrderedBinaryTree(C.Structure):
+    _fields_ = [("root", C.POINTER(BinaryNode)), ("node_list", C.POINTER(BinaryNode)),
+                ("num_elements", C.c_int), ("depth", C.c_int)]
+
+
+class NdLqrProfile(C.Structure):
+    _fields_ = [(k, C.c_double) for k in ("t_total_ms", "t_leaves_ms", "t_products_ms", "t_cholesky_ms",
+                                           "t_cholsolve_ms", "t_shur_ms")] + [("num_threads", C.c_int)]
+
+
+_REF_SOLVER_FIELDS = [
+    ("nstates", C.c_int), ("ninputs", C.c_int), ("nhorizon", C.c_int), ("depth", C.c_int), ("nvars", C.c_int),
+    ("tree", OrderedBinaryTree), ("diagonals", C.POINTER(Matrix)), ("data", C.POINTER(NdData)),
+    ("fact", C.POINTER(NdData)), ("soln", C.POINTER(NdData)), ("cholfacts", C.POINTER(NdLqrCholeskyFactors)),
+    ("solve_time_ms", C.c_double), ("linalg_time_ms", C.c_double), ("profile", NdLqrProfile),
+    ("num_threads", C.c_int)]
+
+
+class RefSolverStruct(C.Structure):  # layout of the reference's NdLqrSolver (src/solver.h:114-130)
+    _fields_ = _REF_SOLVER_FIELDS
+
+
+class SolverStruct(C.Structure):  # this build: same prefix + appended fields (include/solver.h)
+    _fields_ = _REF_SOLVER_FIELDS + [("device", C.c_void_p), ("flat_knots", c_dp), ("flat_x0", c_dp),
+                                     ("mirror_fact", C.c_int)]
+
+
+def bind_host_api(lib, solver_struct):
+    """Declare the prototypes of the public C API on `lib` (used for librslqr.so and, in the tests,
+    for the compiled reference, which exports the same names)."""
+    def sig(name, restype, *argtypes):
+        try:
+            fn = getattr(lib, name)
+        except AttributeError:
+            return
+        fn.restype = restype
+        fn.argtypes = list(argtypes)
+    SP = C.POINTER(solver_struct)
+    PP = C.POINTER(LQRProblem)
+    DP = C.POINTER(LQRData)
+    NP = C.POINTER(NdData)
+    sig("ndlqr_NewLQRData", DP, C.c_int, C.c_int)
+    sig("ndlqr_FreeLQRData", C.c_int, DP)
+    sig("ndlqr_InitializeLQRData", C.c_int, DP, c_dp, c_dp, c_dp, c_dp, C.c_double, c_dp, c_dp, c_dp)
+    sig("ndlqr_CopyLQRData", C.c_int, DP, DP)
+    sig("ndlqr_NewLQRProblem", PP, C.c_int, C.c_int, C.c_int)
+    sig("ndlqr_InitializeLQRProblem", C.c_int, PP, c_dp, C.POINTER(DP))
+    sig("ndlqr_FreeLQRProblem", C.c_int, PP)
+    sig("ndlqr_ReadLQRProblemJSONFile", PP, C.c_char_p)
+    sig("ndlqr_ReadLQRDataJSONFile", DP, C.c_char_p)
+    sig("ReadMatrixJSONFile", Matrix, C.c_char_p, C.c_char_p)
+    sig("FreeMatrix", C.c_int, C.POINTER(Matrix))
+    sig("ndlqr_NewNdLqrSolver", SP, C.c_int, C.c_int, C.c_int)
+    sig("ndlqr_FreeNdLqrSolver", C.c_int, SP)
+    sig("ndlqr_InitializeWithLQRProblem", C.c_int, PP, SP)
+    sig("ndlqr_ResetSolver", None, SP)
+    sig("ndlqr_Solve", C.c_int, SP)
+    sig("ndlqr_SolveLQRProblem", C.c_int, PP, SP)
+    sig("ndlqr_GetSolution", Matrix, SP)
+    sig("ndlqr_CopySolution", C.c_int, SP, c_dp)
+    sig("ndlqr_GetNumVars", C.c_int, SP)
+    sig("ndlqr_SetNumThreads", C.c_int, SP, C.c_int)
+    sig("ndlqr_GetNumThreads", C.c_int, SP)
+    sig("ndlqr_GetProfile", NdLqrProfile, SP)
+    sig("ndlqr_SolveLeaf", C.c_int, SP, C.c_int)
+    sig("ndlqr_SolveLeaves", C.c_int, SP)
+    sig("ndlqr_FactorInnerProduct", C.c_int, NP, NP, C.c_int, C.c_int, C.c_int)
+    sig("ndlqr_SolveCholeskyFactor", C.c_int, NP, C.POINTER(CholeskyInfo), C.c_int, C.c_int, C.c_int)
+    sig("ndlqr_UpdateShurFactor", C.c_int, NP, NP, C.c_int, C.c_int, C.c_int, C.c_int, C.c_bool)
+    sig("ndlqr_ShouldCalcLambda", C.c_bool, C.POINTER(OrderedBinaryTree), C.c_int, C.c_int)
+    sig("ndlqr_ComputeShurCompliment", C.c_int, SP, C.c_int, C.c_int, C.c_int)
+    sig("ndlqr_SolverFactorCholesky", C.c_int, SP, C.c_int, C.c_int)
+    sig("ndlqr_NewNdData", NP, C.c_int, C.c_int, C.c_int, C.c_int)
+    sig("ndlqr_FreeNdData", C.c_int, NP)
+    sig("ndlqr_GetNdFactor", C.c_int, NP, C.c_int, C.c_int, C.POINTER(C.POINTER(NdFactor)))
+    sig("ndlqr_ResetNdData", None, NP)
+    sig("ndlqr_BuildTree", OrderedBinaryTree, C.c_int)
+    sig("ndlqr_FreeTree", C.c_int, C.POINTER(OrderedBinaryTree))
+    sig("ndlqr_GetIndexFromLeaf", C.c_int, C.POINTER(OrderedBinaryTree), C.c_int, C.c_int)
+    sig("ndlqr_GetIndexLevel", C.c_int, C.POINTER(OrderedBinaryTree), C.c_int)
+    sig("ndlqr_GetIndexAtLevel", C.c_int, C.POINTER(OrderedBinaryTree), C.c_int, C.c_int)
+    sig("ndlqr_NewCholeskyFactors", C.POINTER(NdLqrCholeskyFactors), C.c_int, C.c_int)
+    sig("ndlqr_FreeCholeskyFactors", C.c_int, C.POINTER(NdLqrCholeskyFactors))
+    sig("ndlqr_GetQFactorizon", C.c_int, C.POINTER(NdLqrCholeskyFactors), C.c_int, C.POINTER(C.POINTER(CholeskyInfo)))
+    sig("ndlqr_GetRFactorizon", C.c_int, C.POINTER(NdLqrCholeskyFactors), C.c_int, C.POINTER(C.POINTER(CholeskyInfo)))
+    sig("ndlqr_GetSFactorization", C.c_int, C.POINTER(NdLqrCholeskyFactors), C.c_int, C.c_int,
+        C.POINTER(C.POINTER(CholeskyInfo)))
+    sig("rslqr_synth_problem", PP, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_int)
+    sig("ndlqr_LQRDataBlockSize", C.c_int, C.c_int, C.c_int)
+    return lib
+
+
+bind_host_api(LIB, SolverStruct)
+
+
+def problem_to_flat(prob_ptr, n, m):
+    """(knots[N,stride], x0[n]) numpy copies of an LQRProblem* (either library's)."""
+    pr = prob_ptr.contents
+    N, st = pr.nhorizon, 2 * n + 2 * m + 1 + n * n + n * m + n
+    knots = np.empty((N, st))
+    for k in range(N):
+        knots[k] = np.ctypeslib.as_array(pr.lqrdata[k].contents.Q, shape=(st,))
+    x0 = np.ctypeslib.as_array(pr.x0, shape=(n,)).copy()
+    return knots, x0
+
+
+def load_problem_json(path):
+    """Read a reference-format problem file through the library's JSON loader.
+    Returns (n, m, N, knots[N,stride], x0[n])."""
+    pp = LIB.ndlqr_ReadLQRProblemJSONFile(os.fsencode(path))
+    if not pp:
+        raise RslqrError(f"could not read LQR problem from {path}")
+    try:
+        n, m = pp.contents.lqrdata[0].contents.nstates, pp.contents.lqrdata[0].contents.ninputs
+        knots, x0 = problem_to_flat(pp, n, m)
+        return n, m, pp.contents.nhorizon, knots, x0
+    finally:
+        LIB.ndlqr_FreeLQRProblem(pp)
+
+
+class NdLqrSolver:
+    """The reference's single-problem flow (reference src/solver.h:84-96) through the C host API."""
+
+    def __init__(self, n, m, N, lib=LIB):
+        self.lib = lib
+        self.p = lib.ndlqr_NewNdLqrSolver(n, m, N)
+        if not self.p:
+            raise RslqrError("ndlqr_NewNdLqrSolver returned NULL")
+        self.n, self.m, self.N = n, m, N
+
+    @property
+    def c(self):
+        return self.p.contents
+
+    def initialize(self, prob_ptr):
+        return self.lib.ndlqr_InitializeWithLQRProblem(prob_ptr, self.p)
+
+    def reset(self):
+        self.lib.ndlqr_ResetSolver(self.p)
+
+    def solve(self):
+        return self.lib.ndlqr_Solve(self.p)
+
+    def solution(self):
+        mat = self.lib.ndlqr_GetSolution(self.p)
+        return np.ctypeslib.as_array(mat.data, shape=(mat.rows,)).copy()
+
+    def soln_array(self):
+        return np.ctypeslib.as_array(self.c.soln.contents.data, shape=(self.N * (2 * self.n + self.m),))
+
+    def nddata_array(self, which):
+        nd = getattr(self.c, which).contents
+        K = nd.depth
+        return np.ctypeslib.as_array(nd.data, shape=(K, self.N, (2 * self.n + self.m) * nd.width))
+
+    def close(self):
+        if self.p:
+            self.lib.ndlqr_FreeNdLqrSolver(self.p)
+            self.p = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
