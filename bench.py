@@ -1,0 +1,340 @@
+#!/usr/bin/env python
+"""bench.py -- LQR solves/sec for the batched quadrotor configuration (BASELINE.json configs[2]:
+n=12, m=4, N=256, batch 4096 per GPU, synthetic generator of SURVEY App. D, seed 2024).
+
+One "step" = one pass of the hot path (pack rhs + leaves + K factor levels + rhs propagation) over
+the whole batch. `value` is measured with the problems already resident in HBM; `e2e` goes through
+the C-ABI with HOST buffers (pinned), host->device copy of every problem and device->host copy of
+every solution inside the timed region.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--batch B] [--mode auto|staged|fused]
+
+Under torchrun (N > 1) every rank owns one GPU and its own shard of `batch` problems (weak scaling,
+no data-path collective); timing is bracketed by barriers and reduced with MAX over ranks.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+N_STATES, N_INPUTS, HORIZON, SEED = 12, 4, 256, 2024
+METRIC = "LQR solves/sec (n=12,m=4,N=256 batched)"
+WORKLOAD = "batched quadrotor LQR n=12 m=4 N=256 (BASELINE configs[2])"
+
+
+# ------------------------------------------------------------------------------------------
+def flop_model(n, m, N):
+    """Structurally non-zero FLOPs of one solve."""
+    K = N.bit_length() - 1
+    t_ch = N - 1
+    t_cs = 2 * N - 2 * K - 2
+    t_ip = t_cs + (N - 1)
+    t_sc = 2 * N * (K - 1) - (2 ** (K + 1) - 4)
+    t_scl = 0
+    for j in range(K - 1):
+        size = 2 ** (j + 1)
+        for leaf in range(N // size):
+            a, b = leaf * size, leaf * size + size - 1
+            cols = (a > 0) + (b < N - 1)
+            t_scl += cols * (size - 2 + (1 if a == 0 else 0))
+    leaf = N * (4 * n ** 3 + n ** 3 / 3 + m ** 3 / 3 + 2 * m * m * n)
+    return (t_ip * (4 * n ** 3 + 4 * m * n * n) + t_ch * n ** 3 / 3 + t_cs * 2 * n ** 3 +
+            t_sc * (2 * n ** 3 + 2 * m * n * n) + t_scl * 2 * n ** 3 + leaf)
+
+
+def schur_bytes_model(n, m, N, batch):
+    """Algorithmic HBM bytes of the staged Schur launches, averaged per launch: every active task
+    (knot, boundary column) reads F(k,level) and reads+writes F(k,column) (SURVEY 8d streaming model)."""
+    K = N.bit_length() - 1
+    fs = (2 * n + m) * n
+    tot = 0
+    for j in range(K - 1):
+        size = 2 ** (j + 1)
+        for leaf in range(N // size):
+            a, b = leaf * size, leaf * size + size - 1
+            cols = (a > 0) + (b < N - 1)
+            tot += size * (fs * (1 if cols else 0) + 2 * fs * cols) * 8
+    return tot * batch / (K - 1)
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, gpu):
+        super().__init__(daemon=True)
+        self.gpu, self.rows, self.stop_flag = gpu, [], False
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.gpu)],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        self.stop_flag = True
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        sm = sorted(float(r[0]) for r in self.rows if r[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [nm for i, nm in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows if len(r) >= 6)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.rows[0][1]), "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p)), "measured"
+    return {"hbm_gbs": 6650.0}, "fallback"
+
+
+# ------------------------------------------------------------------------------------------
+# CPU side: the reference's own ndlqr_Solve (oracle/_ref, unmodified sources) on the host cores
+# ------------------------------------------------------------------------------------------
+def cpu_reference_rate(n, m, N, knots, x0, budget_s=12.0, cores=None):
+    """Solves/sec of the reference on this host: one problem per core, num_threads = 1 each
+    (the strongest CPU configuration for a batch). Runs a bounded sample."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as O
+    cores = cores or max(1, len(os.sched_getaffinity(0)))
+    kind = "reference" if O.REF is not None else "port"
+    nprob = knots.shape[0]
+    done = [0] * cores
+    t_end = [0.0]
+    start_evt = threading.Event()
+
+    def worker(tid):
+        if kind == "reference":
+            pp = [O.ref_problem_from_flat(n, m, N, knots[(tid + i * cores) % nprob], x0[(tid + i * cores) % nprob])
+                  for i in range(2)]
+            sp = O.REF.ndlqr_NewNdLqrSolver(n, m, N)
+            O.REF.ndlqr_SetNumThreads(sp, 1)
+        else:
+            ps = O.PortSolver(n, m, N)
+        start_evt.wait()
+        i = 0
+        while time.perf_counter() < t_end[0]:
+            if kind == "reference":
+                O.REF.ndlqr_ResetSolver(sp)
+                O.REF.ndlqr_InitializeWithLQRProblem(pp[i % 2], sp)
+                O.REF.ndlqr_Solve(sp)
+            else:
+                j = (tid + i * cores) % nprob
+                ps.init(knots[j], x0[j])
+                ps.solve(1)
+            i += 1
+            done[tid] = i
+
+    th = [threading.Thread(target=worker, args=(t,)) for t in range(cores)]
+    for t in th:
+        t.start()
+    time.sleep(0.5)  # setup
+    t0 = time.perf_counter()
+    t_end[0] = t0 + budget_s
+    start_evt.set()
+    for t in th:
+        t.join()
+    dt = time.perf_counter() - t0
+    total = sum(done)
+    return {"value": total / dt, "unit": "solves/s", "cores": cores, "kind": kind,
+            "sample": f"{total} solves of the same n={n},m={m},N={N} problems in {dt:.1f}s, one problem per core, "
+                      f"num_threads=1 per solve (ndlqr_Solve only + reset/init)"}
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    n, m, N = N_STATES, N_INPUTS, HORIZON
+    import rslqr_b200 as R  # generator only (host C); the solve below is the reference's CPU code
+    cores = max(1, len(os.sched_getaffinity(0)))
+    knots, x0 = R.synth_problems(n, m, N, SEED, 0, min(args.batch, 4 * cores))
+    per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
+    for _ in range(args.warmup):
+        cpu_reference_rate(n, m, N, knots, x0, budget_s=min(2.0, per_step), cores=cores)
+    rates = [cpu_reference_rate(n, m, N, knots, x0, budget_s=per_step, cores=cores) for _ in range(args.steps)]
+    val = float(np.mean([r["value"] for r in rates]))
+    base = rates[-1]
+    base["value"] = val
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "solves/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "batch_per_gpu": args.batch, "seed": SEED,
+                       "note": "reference ndlqr_Solve (OpenMP/C, unmodified sources compiled by oracle/Makefile) on host cores"},
+            "cpu_baseline": base,
+            "e2e": {"value": val, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------
+# GPU side
+# ------------------------------------------------------------------------------------------
+def run_ours(args, rank, world, local_rank):
+    import rslqr_b200 as R
+    from rslqr_b200.lib import pinned_array
+    n, m, N, B = N_STATES, N_INPUTS, HORIZON, args.batch
+    dist = None
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+
+    def allmax(x):
+        if dist is None:
+            return x
+        import torch
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    mode = {"auto": R.MODE_AUTO, "staged": R.MODE_STAGED, "fused": R.MODE_FUSED}[args.mode]
+    flags = R.KEEP_FACT | R.PROFILE if mode == R.MODE_STAGED else 0
+    s = R.CudaSolver(n, m, N, batch=B, device=local_rank, flags=flags)
+    if mode != R.MODE_AUTO:
+        s.set_mode(mode)
+    if s.mode == R.MODE_STAGED and not (flags & R.KEEP_FACT):
+        s.close()
+        flags = R.KEEP_FACT | R.PROFILE
+        s = R.CudaSolver(n, m, N, batch=B, device=local_rank, flags=flags)
+    staged = s.mode == R.MODE_STAGED
+    st, zs = s.stride, s.zs
+    # synthetic inputs, generated into pinned host memory (ids rank*B .. rank*B+B-1)
+    h_knots = pinned_array((B, N, st))
+    h_x0 = pinned_array((B, n))
+    h_soln = pinned_array((B, N * zs))
+    nthreads = min(16, max(1, len(os.sched_getaffinity(0))))
+    chunks = np.array_split(np.arange(B), nthreads)
+
+    def gen(ids):
+        if len(ids):
+            R.synth_problems(n, m, N, SEED, rank * B + int(ids[0]), len(ids), h_knots[ids[0]:ids[-1] + 1], h_x0[ids[0]:ids[-1] + 1])
+    th = [threading.Thread(target=gen, args=(c,)) for c in chunks]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    s.upload(h_knots, h_x0)
+
+    def step_resident():
+        if staged:
+            s.reset()          # the staged kernels accumulate into a zeroed factor array (reference contract)
+        s.solve_async(True)
+
+    def step_e2e():
+        s.upload_async(h_knots, h_x0)
+        if staged:
+            s.reset()
+        s.solve_async(True)
+        s.solution_async(h_soln)
+        s.sync()
+
+    for _ in range(args.warmup):
+        step_resident()
+        s.sync()
+    launches_per_step = s.launches + (4 if staged else 0)
+    s.kernel_timing(enable=True, reset=True)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    barrier(); s.sync()
+    s.mark(0)
+    for _ in range(args.steps):
+        step_resident()
+    s.mark(1)
+    ms_total = s.elapsed_ms(0, 1)
+    s.sync(); barrier()
+    ms_total = allmax(ms_total)
+    k_ms, k_n = s.kernel_timing(enable=False, reset=True)
+    prof = s.profile() if staged else None
+    assert not s.flags().any(), "a Cholesky factorization failed"
+    # end-to-end: host buffers in, host solutions out, copies inside the timed region
+    for _ in range(min(2, args.warmup)):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    e2e_s = allmax(time.perf_counter() - t0)
+    clocks = sampler.summary()
+    barrier()
+
+    ms_per_step = ms_total / args.steps
+    value = world * B / (ms_per_step * 1e-3)
+    pk, pk_kind = peaks()
+    if staged:
+        bytes_launch = schur_bytes_model(n, m, N, B)
+        k_avg_ms = prof["schur"] / (s.K - 1) if prof and prof["schur"] > 0 else None
+        ach = bytes_launch / (k_avg_ms * 1e-3) / 1e9 if k_avg_ms else None
+        roof = {"kernel": "schur_kernel (staged, per level)", "bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"],
+                "unit": "GB/s", "frac": ach / pk["hbm_gbs"] if ach else None, "traffic": None, "peak_kind": pk_kind,
+                "algorithmic_bytes_per_launch": bytes_launch, "avg_launch_ms": k_avg_ms}
+    else:
+        fl = flop_model(n, m, N) * B
+        k_avg_ms = k_ms if k_n else ms_per_step
+        ach = fl / (k_avg_ms * 1e-3) / 1e12
+        fp64_peak = float(os.environ.get("RSLQR_FP64_PEAK_TFLOPS", "37.3"))
+        roof = {"kernel": "fused_solve_kernel (whole solve in one cluster launch)", "bound": "tensor", "achieved": ach,
+                "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach / fp64_peak, "traffic": None,
+                "peak_kind": "fp64 DFMA, 148 SM x 64 FMA/clk x 1.965 GHz (MEASURED_PEAKS.json has no fp64 entry; see DESIGN.md)",
+                "algorithmic_flops_per_launch": fl, "avg_launch_ms": k_avg_ms}
+    line = {"metric": METRIC, "value": value, "unit": "solves/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "batch_per_gpu": B, "global_batch": B * world, "seed": SEED,
+                       "mode": "staged" if staged else "fused", "parallelism": f"batch-shard x{world}, no collective",
+                       "l2": "inputs (%.2f GB/GPU) larger than L2; no explicit flush" % (B * N * st * 8 / 1e9)},
+            "clocks": clocks,
+            "e2e": {"value": world * B * args.steps / e2e_s, "unit": "solves/s",
+                    "h2d_bytes_per_step": int(h_knots.nbytes + h_x0.nbytes), "d2h_bytes_per_step": int(h_soln.nbytes)},
+            "gpu_launches": int(launches_per_step * args.steps),
+            "roofline": roof}
+    if staged and prof:
+        line["phase_ms"] = prof
+    if rank == 0 and world == 1 and not args.no_cpu:
+        line["cpu_baseline"] = cpu_reference_rate(n, m, N, h_knots[:64].copy(), h_x0[:64].copy(), budget_s=args.cpu_seconds)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    s.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=4096)
+    ap.add_argument("--mode", default="auto", choices=["auto", "staged", "fused"])
+    ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -124,6 +124,14 @@ int rslqr_cuda_kernel_launches(rslqr_cuda_solver* h);   /* kernels launched by t
  * reset != 0; measured with CUDA events on the handle's stream when enabled by enable != 0 */
 int rslqr_cuda_kernel_timing(rslqr_cuda_solver* h, int enable, int reset, double* avg_ms, int* launches);
 
+/* CUDA-event stopwatch on the handle's stream: mark(slot) records event `slot` (0..7) after the work
+ * enqueued so far; elapsed_ms(a,b) synchronises on b and returns the device time between them (<0 on error) */
+int rslqr_cuda_mark(rslqr_cuda_solver* h, int slot);
+double rslqr_cuda_elapsed_ms(rslqr_cuda_solver* h, int slot_a, int slot_b);
+/* asynchronous copies on the handle's stream (host buffers should be pinned); pair with _sync */
+int rslqr_cuda_upload_async(rslqr_cuda_solver* h, const double* knots, const double* x0, int first, int count);
+int rslqr_cuda_download_solution_async(rslqr_cuda_solver* h, double* soln, int first, int count);
+
 /* pinned host memory helpers so that callers can stage uploads at full PCIe rate */
 void* rslqr_cuda_host_alloc(size_t bytes);
 void rslqr_cuda_host_free(void* p);

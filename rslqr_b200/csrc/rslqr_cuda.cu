@@ -46,6 +46,7 @@ struct rslqr_cuda_solver {
   // dominant-kernel timing
   bool ktime_on; std::vector<std::pair<cudaEvent_t, cudaEvent_t>> kspans; double k_ms; int k_n;
   FusedPlan fused;
+  cudaEvent_t marks[8]; bool marks_made;
 };
 
 extern "C" const char* rslqr_cuda_last_error(void) { return g_err.c_str(); }
@@ -81,6 +82,7 @@ extern "C" int rslqr_cuda_create(int n, int m, int N, int batch, int device, uns
   rslqr_cuda_solver* h = new rslqr_cuda_solver();
   h->s = make_shape(n, m, N);
   h->batch = batch; h->device = device; h->flags = flags; h->mode = RSLQR_MODE_AUTO;
+  h->marks_made = false;
   h->launches = 0; h->evused = 0; h->ktime_on = false; h->k_ms = 0; h->k_n = 0;
   memset(h->prof, 0, sizeof(h->prof));
   memset(&h->b, 0, sizeof(h->b));
@@ -119,6 +121,7 @@ extern "C" int rslqr_cuda_destroy(rslqr_cuda_solver* h) {
   cudaFree(h->b.status); cudaFree(h->b.flags); cudaFree(h->b.leafd);
   for (auto ev : h->evpool) cudaEventDestroy(ev);
   for (auto& pr : h->kspans) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+  if (h->marks_made) for (auto ev : h->marks) cudaEventDestroy(ev);
   cudaStreamDestroy(h->stream);
   delete h;
   return RSLQR_OK;
@@ -452,4 +455,42 @@ extern "C" void* rslqr_cuda_host_alloc(size_t bytes) {
 }
 extern "C" void rslqr_cuda_host_free(void* p) {
   if (p) cudaFreeHost(p);
+}
+
+extern "C" int rslqr_cuda_mark(rslqr_cuda_solver* h, int slot) {
+  if (!h || slot < 0 || slot >= 8) return fail(RSLQR_E_ARG, "mark: bad argument");
+  CU(cudaSetDevice(h->device));
+  if (!h->marks_made) {
+    for (auto& ev : h->marks) CU(cudaEventCreate(&ev));
+    h->marks_made = true;
+  }
+  CU(cudaEventRecord(h->marks[slot], h->stream));
+  return RSLQR_OK;
+}
+
+extern "C" double rslqr_cuda_elapsed_ms(rslqr_cuda_solver* h, int a, int b) {
+  if (!h || !h->marks_made || a < 0 || a >= 8 || b < 0 || b >= 8) return -1.0;
+  cudaSetDevice(h->device);
+  if (cudaEventSynchronize(h->marks[b]) != cudaSuccess) return -1.0;
+  float ms = 0;
+  if (cudaEventElapsedTime(&ms, h->marks[a], h->marks[b]) != cudaSuccess) return -1.0;
+  return ms;
+}
+
+extern "C" int rslqr_cuda_upload_async(rslqr_cuda_solver* h, const double* knots, const double* x0, int first, int count) {
+  if (!h || !knots || !x0 || !range_ok(h, first, count)) return fail(RSLQR_E_ARG, "upload_async: bad argument");
+  CU(cudaSetDevice(h->device));
+  const Shape& s = h->s;
+  const size_t per = (size_t)s.N * s.stride;
+  CU(cudaMemcpyAsync(h->d_knots + first * per, knots, sizeof(double) * per * count, cudaMemcpyHostToDevice, h->stream));
+  CU(cudaMemcpyAsync(h->d_x0 + (size_t)first * s.n, x0, sizeof(double) * (size_t)s.n * count, cudaMemcpyHostToDevice, h->stream));
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_download_solution_async(rslqr_cuda_solver* h, double* soln, int first, int count) {
+  if (!h || !soln || !range_ok(h, first, count)) return fail(RSLQR_E_ARG, "download_solution_async: bad argument");
+  CU(cudaSetDevice(h->device));
+  const size_t per = (size_t)h->s.N * h->s.zs;
+  CU(cudaMemcpyAsync(soln, h->b.soln + first * per, sizeof(double) * per * count, cudaMemcpyDeviceToHost, h->stream));
+  return RSLQR_OK;
 }

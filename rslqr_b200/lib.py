@@ -62,6 +62,10 @@ _sig("rslqr_cuda_device_pointers", C.c_int, C.c_void_p, C.POINTER(C.c_void_p), C
 _sig("rslqr_cuda_stream", C.c_void_p, C.c_void_p)
 _sig("rslqr_cuda_kernel_launches", C.c_int, C.c_void_p)
 _sig("rslqr_cuda_kernel_timing", C.c_int, C.c_void_p, C.c_int, C.c_int, c_dp, c_ip)
+_sig("rslqr_cuda_mark", C.c_int, C.c_void_p, C.c_int)
+_sig("rslqr_cuda_elapsed_ms", C.c_double, C.c_void_p, C.c_int, C.c_int)
+_sig("rslqr_cuda_upload_async", C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int)
+_sig("rslqr_cuda_download_solution_async", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int)
 _sig("rslqr_cuda_host_alloc", C.c_void_p, C.c_size_t)
 _sig("rslqr_cuda_host_free", None, C.c_void_p)
 _sig("rslqr_synth_fill", C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.c_void_p)
@@ -193,6 +197,23 @@ class CudaSolver:
         p = [C.c_void_p() for _ in range(4)]
         _check(LIB.rslqr_cuda_device_pointers(self.h, *[C.byref(x) for x in p]), "device_pointers")
         return dict(zip(("knots", "x0", "soln", "fact"), [x.value for x in p]))
+
+    def mark(self, slot):
+        _check(LIB.rslqr_cuda_mark(self.h, slot), "mark")
+
+    def elapsed_ms(self, a, b):
+        ms = LIB.rslqr_cuda_elapsed_ms(self.h, a, b)
+        if ms < 0:
+            raise RslqrError("elapsed_ms failed")
+        return ms
+
+    def upload_async(self, knots, x0, first=0):
+        count = x0.size // self.n
+        _check(LIB.rslqr_cuda_upload_async(self.h, _ptr(knots), _ptr(x0), first, count), "upload_async")
+
+    def solution_async(self, out, first=0, count=None):
+        count = self.batch - first if count is None else count
+        _check(LIB.rslqr_cuda_download_solution_async(self.h, _ptr(out), first, count), "download_solution_async")
 
     @property
     def stream(self):
