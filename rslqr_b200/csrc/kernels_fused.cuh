@@ -1,13 +1,675 @@
-// kernels_fused.cuh -- placeholder plan for the fused cluster kernel (filled in below in later commits)
+// kernels_fused.cuh -- "tiered" device path: the bottom levels of the nested dissection stay on chip.
+//
+// The reference walks the binary tree level by level over ALL knots of a problem (reference
+// src/solve.c:68-182), streaming the whole factor array through memory once per level. Here a CTA owns
+// a group of G = 2^g consecutive knots and runs the leaf stage and the first g levels for that group out of
+// shared memory (tier 0); the few remaining levels only ever need the first and the last knot of each group,
+// so they run on compact "boundary entries" (tiers >= 1); a top-down pass turns the separator solves of those
+// upper levels into final multipliers, and one streaming kernel applies them to every knot.
+//
+// State kept per knot k (replaces the K columns F(k,0..K-1) of the reference's NdData, src/nddata.h:83-93):
+//   L(k), R(k) : (2n+m) x n blocks = the two structurally non-zero "boundary" columns of the subtree that
+//                currently contains k: L couples to the separator on the left of the
+//                subtree (lambda_a), R to the one on its right (lambda_{b+1}); rows = [Lambda | X | U].
+//   z(k)       : the right-hand side / solution column (the rhs rides along as a 25th column instead of the
+//                reference's second pass over `fact`, src/solve.c:137-182; the reference notes this option
+//                itself, src/nddata.h:72-75).
+// After the leaves L(k) = F(k, lev(k-1)) and R(k) = F(k, lev(k)). Merging the sibling subtrees [a,i] and
+// [i+1,b] at level j (separator variable lambda_{i+1}) is, in the reference's terms:
+//   ndlqr_FactorInnerProduct (src/nested_dissection.c:114):
+//        S   = A_i X_R(i) + B_i U_R(i) - X_L(i+1)             (own column j)
+//        S_L = A_i X_L(i) + B_i U_L(i)                         (column p_L; F(i+1,p_L) is still zero)
+//        S_R = -X_R(i+1)                                        (column p_R; F(i,p_R) is still zero)
+//        s   = A_i z_x(i) + B_i z_u(i) - z_x(i+1) - z_lambda(i+1)
+//   Cholesky + ndlqr_SolveCholeskyFactor (src/solve.c:87-98, src/nested_dissection.c:136):
+//        [f_L f_R zs] = S^{-1} [S_L S_R s]
+//   ndlqr_UpdateShurFactor (src/nested_dissection.c:154) for every knot k of [a,b], own = R(k) if k <= i else L(k):
+//        L(k) <- (k <= i ? L(k) : 0) - own f_L ;  R(k) <- (k <= i ? 0 : R(k)) - own f_R ;  z(k) -= own zs
+//        (the Lambda rows the reference skips via ndlqr_ShouldCalcLambda are exactly the rows where own is zero)
+//   and F(i+1,.).Lambda <- f_. : Lambda rows of knot i+1 become (f_L, f_R, zs).
+// All arithmetic is IEEE fp64. Shapes are compile-time (n, m) so blocks live in registers / fragments.
 #pragma once
 #include <cuda_runtime.h>
+#include <cstring>
 #include <string>
 #include "kernels_staged.cuh"
+
 namespace rslqr {
-struct FusedPlan { bool available; };
-inline void fused_plan(const Shape&, int, int, FusedPlan* p) { p->available = false; }
-inline int fused_launch(const FusedPlan&, const Shape&, const Bufs&, int, int, cudaStream_t, std::string& err) {
-  err = "fused kernel not built";
-  return -5;
+
+struct FusedBufs {
+  double* stL;     // [batch][N*ZS][NS]   state after tier 0, row-major rows
+  double* stR;     // [batch][N*ZS][NS]
+  double* stz;     // [batch][N*ZS]
+  double* ent[8];  // per tier t >= 1 input entries: [batch][M_{t-1}][ENT]
+  double* sep;     // [batch][M0][(2NS+1)*NS]  upper separators: [f_L | f_R | zs], slot q = (i+1)/G0
+  double* lamhat;  // [batch][M0+1][NS]        final multipliers of the upper separators (slots 0 and M0 = 0)
+};
+
+template <int NS, int NI>
+struct Dim {
+  static constexpr int ZS = 2 * NS + NI;         // rows per knot
+  static constexpr int XU = NS + NI;             // X and U rows
+  static constexpr int W = 2 * NS + 1;           // columns [L | R | z]
+  static constexpr int WSZ = W * NS;             // one separator record [f_L | f_R | zs], column-major ld NS
+  static constexpr int SLOT = ZS * NS;           // one block, row-major [ZS][NS]
+  static constexpr int ENT = 2 * SLOT + ZS + NS; // boundary entry: L rows, R rows, z, lambda-rhs of the first knot
+};
+
+__device__ __forceinline__ double fast_rcp(double d) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+  double e = fma(-d, r, 1.0);
+  r = fma(r, e, r);
+  e = fma(-d, r, 1.0);
+  r = fma(r, e, r);
+  return r;
 }
+
+__device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+
+// ---------------------------------------------------------------------------------------------------------
+// One separator, one warp: inner products -> factorization -> solves. Lane roles:
+//   lanes [0,NS)      : column c of S  (then, for the solves, column c of S_R -> f_R)
+//   lanes [NS,2NS)    : column c of S_L -> f_L
+//   lane  2NS         : s -> zs
+// S is symmetric, so "lane c holds column c" doubles as "lane c holds row c" for the row-per-lane
+// factorization. The factorization is S = Lt D Lt^T (unit lower Lt): same factor as the reference's
+// Cholesky (src/linalg_custom.c:88) up to the diagonal scaling L = Lt sqrt(D), without a square root or a
+// division on the dependent chain; the solves are Lt^{-T} D^{-1} Lt^{-1}.
+//   AB    : global, A_i (NS x NS column-major) followed by B_i (NS x NI column-major)
+//   LXi/RXi : X rows of knot i in its L / R block (row-major, ld NS), the U rows follow directly
+//   zxi   : z_x(i) followed by z_u(i)
+//   LXn/RXn : X rows of knot i+1; zxn = z_x(i+1); zln = z_lambda(i+1)
+//   Lsm   : NS*NS doubles of scratch for Lt (row-major); Wout: [f_L | f_R | zs] column-major ld NS
+// Returns non-zero (warp-uniform) when a pivot is <= 0 (reference: clap_CholeskyFactorize fails).
+// ---------------------------------------------------------------------------------------------------------
+template <int NS, int NI>
+__device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const double* LXi, const double* RXi,
+                                           const double* zxi, const double* LXn, const double* RXn,
+                                           const double* zxn, const double* zln, double* Lsm, double* Wout) {
+  static_assert(2 * NS + 1 <= 32, "one warp per separator needs 2n+1 <= 32");
+  const int lane = threadIdx.x & 31;
+  const int c = lane < NS ? lane : (lane < 2 * NS ? lane - NS : 0);
+  const double* src;
+  int ss;
+  if (lane < NS) { src = RXi + c; ss = NS; }
+  else if (lane < 2 * NS) { src = LXi + c; ss = NS; }
+  else { src = zxi; ss = 1; }  // lanes > 2NS compute a harmless copy of the rhs column
+  double acc[NS];
+#pragma unroll
+  for (int r = 0; r < NS; ++r) acc[r] = 0.0;
+#pragma unroll 4
+  for (int l = 0; l < NS + NI; ++l) {
+    const double x = src[l * ss];
+    const double* col = AB + l * NS;  // column l of [A | B] (B follows A, both have NS rows)
+#pragma unroll
+    for (int r = 0; r < NS; ++r) acc[r] = fma(__ldg(col + r), x, acc[r]);
+  }
+  if (lane < NS) {
+#pragma unroll
+    for (int r = 0; r < NS; ++r) acc[r] -= LXn[r * NS + c];
+  } else if (lane >= 2 * NS) {
+#pragma unroll
+    for (int r = 0; r < NS; ++r) acc[r] = acc[r] - zxn[r] - zln[r];
+  }
+  // ---- factorization, lane i < NS holds row i of S in a[] ----
+  int bad = 0;
+  {
+    double a[NS];
+#pragma unroll
+    for (int r = 0; r < NS; ++r) a[r] = acc[r];
+#pragma unroll
+    for (int j = 0; j < NS; ++j) {
+      const double d = shfl_d(a[j], j);
+      if (!(d > 0.0)) bad = 1;
+      const double dinv = fast_rcp(d);
+      const double lij = a[j] * dinv;  // Lt(i,j) for lane i > j
+#pragma unroll
+      for (int k = j + 1; k < NS; ++k) {
+        const double pk = shfl_d(a[k], j);  // pivot row element S'(j,k) = S'(k,j)
+        a[k] = fma(-lij, pk, a[k]);
+      }
+      a[j] = lane == j ? dinv : lij;  // the diagonal slot of Lt carries 1/D(j)
+    }
+    if (lane < NS) {
+#pragma unroll
+      for (int k = 0; k < NS; ++k) Lsm[lane * NS + k] = a[k];
+    }
+  }
+  __syncwarp();
+  // ---- solves: lanes < NS take over the S_R columns ----
+  if (lane < NS) {
+#pragma unroll
+    for (int r = 0; r < NS; ++r) acc[r] = -RXn[r * NS + c];
+  }
+#pragma unroll
+  for (int j = 0; j < NS; ++j) {
+#pragma unroll
+    for (int i = j + 1; i < NS; ++i) acc[i] = fma(-Lsm[i * NS + j], acc[j], acc[i]);
+  }
+#pragma unroll
+  for (int j = 0; j < NS; ++j) acc[j] *= Lsm[j * NS + j];
+#pragma unroll
+  for (int j = NS - 1; j >= 0; --j) {
+#pragma unroll
+    for (int i = 0; i < j; ++i) acc[i] = fma(-Lsm[j * NS + i], acc[j], acc[i]);
+  }
+  if (lane <= 2 * NS) {
+    const int wc = lane < NS ? NS + lane : (lane < 2 * NS ? lane - NS : 2 * NS);
+#pragma unroll
+    for (int r = 0; r < NS; ++r) Wout[wc * NS + r] = acc[r];
+  }
+  __syncwarp();
+  return bad;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Schur update of a whole group at level j (ndlqr_UpdateShurFactor over every knot of the group).
+// Two implementations with identical results up to summation order:
+//   schur_dmma : fp64 tensor cores, mma.sync m8n8k4. A knot pair is 2*ZS rows = an integer number of 8-row
+//                tiles (needs 2*ZS % 8 == 0, NS % 4 == 0); warp w owns knot pair w, so all of its tiles see the
+//                same separator and the B fragments [-f_L | -f_R] are loaded once per level.
+//   schur_dfma : plain DFMA, one thread per row (any shape).
+// Ls/Rs: [G*ZS][NS] row-major, zv: [G*ZS], W: per separator [f_L | f_R | zs] column-major ld NS.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+               : "+d"(d0), "+d"(d1)
+               : "d"(a), "d"(b));
+}
+
+template <int NS, int NI>
+__device__ __forceinline__ void schur_dmma(double* Ls, double* Rs, double* zv, const double* W, int j) {
+  using D = Dim<NS, NI>;
+  constexpr int ZS = D::ZS, KS = NS / 4, NT = 2 * NS / 8, TILES = 2 * ZS / 8;
+  static_assert((2 * ZS) % 8 == 0 && NS % 4 == 0, "tile shapes");
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q = lane & 3, rr = lane >> 2;
+  const int s = warp >> j;  // separator (local) of knot pair `warp` at level j
+  const double* Wf = W + s * D::WSZ;
+  double bneg[KS][NT], zq[KS];
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) bneg[ks][nt] = -Wf[(8 * nt + rr) * NS + 4 * ks + q];
+    zq[ks] = Wf[2 * NS * NS + 4 * ks + q];
+  }
+  const int ksep = (2 * s + 1) << j;  // local knot i+1: its Lambda rows receive (f_L, f_R, zs)
+#pragma unroll 1
+  for (int t = 0; t < TILES; ++t) {
+    const int R = warp * 2 * ZS + 8 * t + rr;
+    const int kn = 2 * warp + (8 * t + rr >= ZS ? 1 : 0);
+    const int row = R - kn * ZS;
+    const int side = (kn >> j) & 1;  // 0: left child (own = R block), 1: right child (own = L block)
+    const double* own = side ? Ls : Rs;
+    double a[KS];
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) a[ks] = own[R * NS + 4 * ks + q];
+    double c[NT][2];
+    double* dst[NT];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      const int n = 8 * nt + 2 * q;
+      const bool inL = n < NS;
+      dst[nt] = (inL ? Ls : Rs) + R * NS + (inL ? n : n - NS);
+      const bool isown = inL == (side == 1);
+      const double2 v = *reinterpret_cast<const double2*>(dst[nt]);
+      c[nt][0] = isown ? 0.0 : v.x;
+      c[nt][1] = isown ? 0.0 : v.y;
+    }
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks)
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) dmma884(c[nt][0], c[nt][1], a[ks], bneg[ks][nt]);
+    double part = 0.0;
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) part = fma(a[ks], zq[ks], part);
+    part += __shfl_xor_sync(0xffffffffu, part, 1);
+    part += __shfl_xor_sync(0xffffffffu, part, 2);
+    const bool special = (kn == ksep) && (row < NS);
+    if (special) {
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        c[nt][0] = Wf[(8 * nt + 2 * q) * NS + row];
+        c[nt][1] = Wf[(8 * nt + 2 * q + 1) * NS + row];
+      }
+    }
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) *reinterpret_cast<double2*>(dst[nt]) = make_double2(c[nt][0], c[nt][1]);
+    if (q == 0) zv[R] = special ? Wf[2 * NS * NS + row] : zv[R] - part;
+  }
+}
+
+// one row: [L R z](R) <- keep - own * [f_L f_R zs]; `side` selects own (0: R block, 1: L block)
+template <int NS>
+__device__ __forceinline__ void schur_row(double* Lrow, double* Rrow, double* zr, const double* Wf, int side,
+                                          bool special, int row) {
+  double o[NS];
+  const double* own = side ? Lrow : Rrow;
+#pragma unroll
+  for (int k = 0; k < NS; ++k) o[k] = own[k];
+#pragma unroll 2
+  for (int c = 0; c < NS; ++c) {
+    double aL = side ? 0.0 : Lrow[c];
+    double aR = side ? Rrow[c] : 0.0;
+#pragma unroll
+    for (int k = 0; k < NS; ++k) {
+      aL = fma(-o[k], Wf[c * NS + k], aL);
+      aR = fma(-o[k], Wf[(NS + c) * NS + k], aR);
+    }
+    if (special) { aL = Wf[c * NS + row]; aR = Wf[(NS + c) * NS + row]; }
+    Lrow[c] = aL;
+    Rrow[c] = aR;
+  }
+  double az = *zr;
+#pragma unroll
+  for (int k = 0; k < NS; ++k) az = fma(-o[k], Wf[2 * NS * NS + k], az);
+  if (special) az = Wf[2 * NS * NS + row];
+  *zr = az;
+}
+
+template <int NS, int NI, int G>
+__device__ __forceinline__ void schur_dfma(double* Ls, double* Rs, double* zv, const double* W, int j) {
+  using D = Dim<NS, NI>;
+  constexpr int ZS = D::ZS;
+  for (int R = threadIdx.x; R < G * ZS; R += blockDim.x) {
+    const int kn = R / ZS, row = R - kn * ZS;
+    const int side = (kn >> j) & 1;
+    const int s = kn >> (j + 1);
+    const bool special = (kn == ((2 * s + 1) << j)) && (row < NS);
+    schur_row<NS>(Ls + R * NS, Rs + R * NS, zv + R, W + s * D::WSZ, side, special, row);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Tier 0: one CTA = (problem, group of G consecutive knots). Leaves (ndlqr_SolveLeaf, reference
+// src/nested_dissection.c:10-105, with the rhs built on the fly like src/solver.c:138-190 when pack_rhs != 0)
+// and levels 0 .. log2(G)-1, all in shared memory. G/2 warps: warp w is the spine warp of separator w and
+// owns knot pair w in the Schur update.
+// Output: the group's state (L, R, z) to fb.stL/stR/stz and its boundary entry to fb.ent[0]; when the group
+// is the whole problem (N == G) the solution goes straight to b.soln.
+// dynamic smem: (2*G*SLOT + G*ZS + (G/2)*WSZ) doubles.
+// ---------------------------------------------------------------------------------------------------------
+template <int NS, int NI, int G>
+constexpr int tier0_smem_doubles() {
+  using D = Dim<NS, NI>;
+  return 2 * G * D::SLOT + G * D::ZS + (G / 2) * D::WSZ;
+}
+
+template <int NS, int NI, int G, bool DMMA>
+__global__ void __launch_bounds__(16 * G, 512 / (16 * G)) tier0_kernel(Shape s, Bufs b, FusedBufs fb, int pack_rhs, int M0) {
+  using D = Dim<NS, NI>;
+  constexpr int ZS = D::ZS, SLOT = D::SLOT, WSZ = D::WSZ;
+  extern __shared__ double sm[];
+  double* Ls = sm;
+  double* Rs = Ls + G * SLOT;
+  double* zv = Rs + G * SLOT;
+  double* W = zv + G * ZS;
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int prob = blockIdx.x / M0, grp = blockIdx.x % M0;
+  const int k0 = grp * G;
+  const int N = s.N;
+
+  // ---- leaves: L(k) = F(k, lev(k-1)), R(k) = F(k, lev(k)) ----
+  for (int idx = tid; idx < G * SLOT; idx += nthr) {
+    const int kl = idx / SLOT, e = idx - kl * SLOT;
+    const int row = e / NS, c = e - row * NS;
+    const int k = k0 + kl;
+    const double* kn = knot_ptr(s, b, prob, k);
+    double l = 0.0, r = 0.0;
+    if (row < NS) {
+      if (k == 0) r = -kn[s.oA + row * NS + c];  // F(0,0).Lambda = -A0^T (nested_dissection.c:31-36)
+    } else if (row < 2 * NS) {
+      const int i = row - NS;
+      const double qi = kn[s.oQ + i];
+      if (k > 0 && c == i) l = -1.0 / qi;                         // Q \ (-I)   (:96-102)
+      if (k > 0 && k < N - 1) r = kn[s.oA + i * NS + c] / qi;     // Q \ A^T    (:75-79)
+    } else {
+      const int i = row - 2 * NS;
+      if (k < N - 1) r = kn[s.oB + i * NS + c] / kn[s.oR + i];    // R \ B^T    (:40-44, :80-84)
+    }
+    Ls[idx] = l;
+    Rs[idx] = r;
+  }
+  for (int idx = tid; idx < G * ZS; idx += nthr) {
+    const int kl = idx / ZS, row = idx - kl * ZS;
+    const int k = k0 + kl;
+    const double* kn = knot_ptr(s, b, prob, k);
+    auto raw = [&](int rw) -> double {  // entry rw of the (negated) rhs of knot k
+      if (!pack_rhs) return soln_ptr(s, b, prob, k)[rw];
+      double v;
+      if (rw < NS) v = (k == 0) ? b.x0[(size_t)prob * NS + rw] : knot_ptr(s, b, prob, k - 1)[s.od + rw];
+      else if (rw < 2 * NS) v = kn[s.oq + rw - NS];
+      else v = (k < N - 1) ? kn[s.orr + rw - 2 * NS] : 0.0;
+      return -v;
+    };
+    double v;
+    if (k == 0) {  // nested_dissection.c:45-59
+      if (row < NS) v = -kn[s.oQ + row] * raw(row) - raw(NS + row);
+      else if (row < 2 * NS) v = -raw(row - NS);
+      else v = raw(row) / kn[s.oR + row - 2 * NS];
+    } else {
+      if (row < NS) v = raw(row);
+      else if (row < 2 * NS) v = raw(row) / kn[s.oQ + row - NS];
+      else v = (k < N - 1) ? raw(row) / kn[s.oR + row - 2 * NS] : raw(row);
+    }
+    zv[idx] = v;
+  }
+  // leaf "Cholesky" status: Q_k, R_k diagonal, factorization fails on an entry <= 0
+  for (int idx = tid; idx < G * (NS + NI); idx += nthr) {
+    const int kl = idx / (NS + NI), i = idx - kl * (NS + NI);
+    const int k = k0 + kl;
+    if (i >= NS && k == N - 1) continue;
+    const double d = knot_ptr(s, b, prob, k)[i < NS ? s.oQ + i : s.oR + i - NS];
+    if (!(d > 0.0)) {
+      b.status[(size_t)prob * 3 * N + (i < NS ? rs_slot_Q(k) : rs_slot_R(k))] = -1;
+      b.flags[prob] = 1;
+    }
+  }
+
+  // ---- levels ----
+  int g = 0;
+  while ((1 << g) < G) ++g;
+  for (int j = 0; j < g; ++j) {
+    __syncthreads();
+    const int nsep = G >> (j + 1);
+    if (warp < nsep) {
+      const int il = ((2 * warp + 1) << j) - 1;  // local index of the separator knot i
+      const double* AB = knot_ptr(s, b, prob, k0 + il) + s.oA;
+      double* Lsm = Ls + (il + 1) * SLOT;  // Lambda rows of knot i+1: still zero, used as scratch
+      const int bad = spine_merge<NS, NI>(AB, Ls + il * SLOT + NS * NS, Rs + il * SLOT + NS * NS, zv + il * ZS + NS,
+                                          Ls + (il + 1) * SLOT + NS * NS, Rs + (il + 1) * SLOT + NS * NS,
+                                          zv + (il + 1) * ZS + NS, zv + (il + 1) * ZS, Lsm, W + warp * WSZ);
+      for (int e = lane; e < NS * NS; e += 32) Lsm[e] = 0.0;
+      if (bad && lane == 0) {
+        const int i = k0 + il;
+        b.status[(size_t)prob * 3 * N + rs_slot_S(i >> (j + 1), j, N)] = -1;
+        b.flags[prob] = 1;
+      }
+    }
+    __syncthreads();
+    if constexpr (DMMA) schur_dmma<NS, NI>(Ls, Rs, zv, W, j);
+    else schur_dfma<NS, NI, G>(Ls, Rs, zv, W, j);
+  }
+  __syncthreads();
+
+  // ---- output ----
+  if (M0 == 1) {
+    double* out = soln_ptr(s, b, prob, 0);
+    for (int idx = tid; idx < G * ZS; idx += nthr) out[idx] = zv[idx];
+    return;
+  }
+  {
+    const size_t base = ((size_t)prob * N + k0) * ZS;
+    double2* oL = reinterpret_cast<double2*>(fb.stL + base * NS);
+    double2* oR = reinterpret_cast<double2*>(fb.stR + base * NS);
+    const double2* iL = reinterpret_cast<const double2*>(Ls);
+    const double2* iR = reinterpret_cast<const double2*>(Rs);
+    for (int idx = tid; idx < G * SLOT / 2; idx += nthr) { oL[idx] = iL[idx]; oR[idx] = iR[idx]; }
+    for (int idx = tid; idx < G * ZS; idx += nthr) fb.stz[base + idx] = zv[idx];
+    // boundary entry: rows [X(first knot) | X,U(last knot)] of L, R, z and the lambda-rhs of the first knot
+    double* en = fb.ent[0] + ((size_t)prob * M0 + grp) * D::ENT;
+    for (int idx = tid; idx < SLOT; idx += nthr) {
+      const int er = idx / NS, c = idx - er * NS;
+      const int lr = er < NS ? NS + er : (G - 1) * ZS + er;
+      en[idx] = Ls[lr * NS + c];
+      en[SLOT + idx] = Rs[lr * NS + c];
+    }
+    for (int er = tid; er < ZS; er += nthr) en[2 * SLOT + er] = zv[er < NS ? NS + er : (G - 1) * ZS + er];
+    for (int c = tid; c < NS; c += nthr) en[2 * SLOT + ZS + c] = zv[c];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Tiers >= 1: one CTA = (problem, `ecount` consecutive boundary entries); runs log2(ecount) more levels.
+// An entry stands for a subtree [a,b] already merged below: rows [X(a) | X(b) | U(b)] of L, R and z (the only
+// rows a later ndlqr_FactorInnerProduct reads) plus z_lambda(a). Merging entries e_l (left subtree ends there)
+// and e_l+1: spine_merge on knot i = last knot of e_l, then the Schur update of just the rows that stay
+// boundary rows: X(a) of the left subtree's first entry (own = R) and X,U(b) of the right subtree's last entry
+// (own = L). The separator record [f_L | f_R | zs] goes to fb.sep for the top-down pass.
+// `span` = knots per input entry; warps = max(1, ecount/2).
+// dynamic smem: (ecount*ENT + warps*(WSZ + NS*NS)) doubles.
+// ---------------------------------------------------------------------------------------------------------
+template <int NS, int NI>
+__global__ void tier_kernel(Shape s, Bufs b, FusedBufs fb, int tier, int Min, int ecount, int span, int G0) {
+  using D = Dim<NS, NI>;
+  constexpr int ZS = D::ZS, SLOT = D::SLOT, WSZ = D::WSZ, ENT = D::ENT;
+  static_assert(ZS <= 32, "lean Schur update maps one row per lane");
+  extern __shared__ double sm[];
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const int warp = tid >> 5, lane = tid & 31, nwarp = nthr >> 5;
+  const int ncta = Min / ecount;
+  const int prob = blockIdx.x / ncta, sg = blockIdx.x % ncta;
+  const int M0 = s.N / G0;
+  double* ents = sm;
+  double* Wall = ents + ecount * ENT;
+  double* Lall = Wall + nwarp * WSZ;
+  const double* in = fb.ent[tier - 1] + ((size_t)prob * Min + (size_t)sg * ecount) * ENT;
+  for (int idx = tid; idx < ecount * ENT; idx += nthr) ents[idx] = in[idx];
+  int levels = 0;
+  while ((1 << levels) < ecount) ++levels;
+  for (int l = 0; l < levels; ++l) {
+    __syncthreads();
+    const int nsep = ecount >> (l + 1);
+    if (warp < nsep) {
+      const int el = ((2 * warp + 1) << l) - 1, er = el + 1;
+      const int ea = (2 * warp) << l, eb = er + (1 << l) - 1;
+      const int i = (sg * ecount + el + 1) * span - 1;  // global knot index of the separator
+      const double* AB = knot_ptr(s, b, prob, i) + s.oA;
+      double* El = ents + el * ENT;
+      double* Er = ents + er * ENT;
+      double* Wf = Wall + warp * WSZ;
+      const int bad = spine_merge<NS, NI>(AB, El + NS * NS, El + SLOT + NS * NS, El + 2 * SLOT + NS, Er, Er + SLOT,
+                                          Er + 2 * SLOT, Er + 2 * SLOT + ZS, Lall + warp * NS * NS, Wf);
+      double* rec = fb.sep + ((size_t)prob * M0 + (i + 1) / G0) * WSZ;
+      for (int e = lane; e < WSZ; e += 32) rec[e] = Wf[e];
+      if (bad && lane == 0) {
+        int lev = 0;
+        while ((i >> lev) & 1) ++lev;
+        b.status[(size_t)prob * 3 * s.N + rs_slot_S(i >> (lev + 1), lev, s.N)] = -1;
+        b.flags[prob] = 1;
+      }
+      if (lane < ZS) {
+        double* E = ents + (lane < NS ? ea : eb) * ENT;
+        schur_row<NS>(E + lane * NS, E + SLOT + lane * NS, E + 2 * SLOT + lane, Wf, lane < NS ? 0 : 1, false, 0);
+      }
+    }
+  }
+  __syncthreads();
+  if (ncta > 1) {  // not the top tier: hand the merged entry up
+    double* out = fb.ent[tier] + ((size_t)prob * ncta + sg) * ENT;
+    const double* E0 = ents;
+    const double* E1 = ents + (ecount - 1) * ENT;
+    for (int idx = tid; idx < SLOT; idx += nthr) {
+      const double* E = idx < NS * NS ? E0 : E1;
+      out[idx] = E[idx];
+      out[SLOT + idx] = E[SLOT + idx];
+    }
+    for (int r = tid; r < ZS; r += nthr) out[2 * SLOT + r] = (r < NS ? E0 : E1)[2 * SLOT + r];
+    for (int c = tid; c < NS; c += nthr) out[2 * SLOT + ZS + c] = E0[2 * SLOT + ZS + c];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Top-down: final multiplier of every upper separator, from the top level down:
+//   lambda(q) = zs(q) - f_L(q) lambda(q - h) - f_R(q) lambda(q + h),  h = 2^ctz(q)
+// (this is what the reference's remaining Schur updates do to the Lambda rows of knot i+1, telescoped).
+// Slots 0 and M0 of fb.lamhat hold zeros (no separator outside the horizon). One CTA per problem.
+// ---------------------------------------------------------------------------------------------------------
+template <int NS>
+__global__ void topdown_kernel(FusedBufs fb, int M0) {
+  constexpr int WSZ = (2 * NS + 1) * NS;
+  const int prob = blockIdx.x;
+  double* lam = fb.lamhat + (size_t)prob * (M0 + 1) * NS;
+  const double* sep = fb.sep + (size_t)prob * M0 * WSZ;
+  if (threadIdx.x < NS) { lam[threadIdx.x] = 0.0; lam[M0 * NS + threadIdx.x] = 0.0; }
+  int T = 0;
+  while ((1 << T) < M0) ++T;
+  for (int t = T - 1; t >= 0; --t) {
+    __syncthreads();
+    const int cnt = M0 >> (t + 1), h = 1 << t;
+    for (int idx = threadIdx.x; idx < cnt * NS; idx += blockDim.x) {
+      const int u = idx / NS, r = idx - u * NS;
+      const int q = (2 * u + 1) << t;
+      const double* rec = sep + (size_t)q * WSZ;
+      const double* la = lam + (q - h) * NS;
+      const double* lb = lam + (q + h) * NS;
+      double v = rec[2 * NS * NS + r];
+#pragma unroll
+      for (int c = 0; c < NS; ++c) v = fma(-rec[c * NS + r], la[c], fma(-rec[(NS + c) * NS + r], lb[c], v));
+      lam[q * NS + r] = v;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Finalize (the rhs propagation of all upper levels in one pass, reference src/solve.c:175-180):
+//   soln(k) = z(k) - L(k) lambda_a - R(k) lambda_{b+1},  [a,b] = the tier-0 group of k;
+// the Lambda rows of the first knot of a group are the separator multiplier itself. One thread per row.
+// ---------------------------------------------------------------------------------------------------------
+template <int NS, int NI>
+__global__ void finalize_kernel(Shape s, Bufs b, FusedBufs fb, int G0, int M0, long long rows_total) {
+  constexpr int ZS = 2 * NS + NI;
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= rows_total) return;
+  const long long per = (long long)s.N * ZS;
+  const int prob = (int)(gid / per);
+  const int R = (int)(gid - prob * per);
+  const int k = R / ZS, row = R - k * ZS;
+  const int grp = k / G0;
+  const double* la = fb.lamhat + ((size_t)prob * (M0 + 1) + grp) * NS;
+  const double* lb = la + NS;
+  const double2* pl = reinterpret_cast<const double2*>(fb.stL + gid * NS);
+  const double2* pr = reinterpret_cast<const double2*>(fb.stR + gid * NS);
+  double v = fb.stz[gid];
+#pragma unroll
+  for (int c = 0; c < NS / 2; ++c) {
+    const double2 l2 = pl[c], r2 = pr[c];
+    v = fma(-l2.x, la[2 * c], v);
+    v = fma(-l2.y, la[2 * c + 1], v);
+    v = fma(-r2.x, lb[2 * c], v);
+    v = fma(-r2.y, lb[2 * c + 1], v);
+  }
+  if (row < NS && k > 0 && k == grp * G0) v = la[row];
+  b.soln[gid] = v;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// host side: plan, buffers, launches
+// ---------------------------------------------------------------------------------------------------------
+struct FusedTier { int Min, ecount, span; };
+struct FusedPlan {
+  bool available;
+  int ns, ni, G0, M0, ntiers, use_dmma;
+  FusedTier tiers[8];
+  FusedBufs fb;
+  size_t bytes;
+  int launches;
+};
+
+inline bool fused_shape_ok(int n, int m) { return (n == 12 && m == 4) || (n == 6 && m == 3); }
+
+// Decides the tiling for (n, m, N) and allocates the device buffers of the tiered path. Leaves
+// plan->available = false (and no allocation) when the shape is not covered; the caller then uses the staged path.
+inline int fused_plan(const Shape& s, int batch, int g0_pref, FusedPlan* p, std::string& err) {
+  memset(p, 0, sizeof(*p));
+  if (!fused_shape_ok(s.n, s.m) || s.N < 8) return 0;
+  p->ns = s.n; p->ni = s.m;
+  p->G0 = (g0_pref == 16 && s.N >= 16) ? 16 : 8;
+  p->M0 = s.N / p->G0;
+  p->use_dmma = (s.n == 12);
+  int M = p->M0, span = p->G0;
+  while (M > 1) {
+    if (p->ntiers == 8) return 0;
+    const int e = M < 8 ? M : 8;
+    p->tiers[p->ntiers++] = FusedTier{M, e, span};
+    M /= e; span *= e;
+  }
+  if (p->M0 > 1) {
+    const size_t zs = s.zs, n = s.n;
+    const size_t ent = 2 * zs * n + zs + n, wsz = (2 * n + 1) * n;
+    auto alloc = [&](double** ptr, size_t cnt) {
+      p->bytes += cnt * sizeof(double);
+      return cudaMalloc((void**)ptr, cnt * sizeof(double)) == cudaSuccess;
+    };
+    bool ok = alloc(&p->fb.stL, (size_t)batch * s.N * zs * n) && alloc(&p->fb.stR, (size_t)batch * s.N * zs * n) &&
+              alloc(&p->fb.stz, (size_t)batch * s.N * zs) && alloc(&p->fb.sep, (size_t)batch * p->M0 * wsz) &&
+              alloc(&p->fb.lamhat, (size_t)batch * (p->M0 + 1) * n);
+    for (int t = 0; ok && t < p->ntiers; ++t) ok = alloc(&p->fb.ent[t], (size_t)batch * p->tiers[t].Min * ent);
+    if (!ok) {
+      cudaGetLastError();
+      err = "device allocation for the tiered path failed";
+      return -4;
+    }
+  }
+  p->available = true;
+  return 0;
+}
+
+inline void fused_free(FusedPlan* p) {
+  cudaFree(p->fb.stL); cudaFree(p->fb.stR); cudaFree(p->fb.stz); cudaFree(p->fb.sep); cudaFree(p->fb.lamhat);
+  for (int t = 0; t < 8; ++t) cudaFree(p->fb.ent[t]);
+  memset(p, 0, sizeof(*p));
+}
+
+template <int NS, int NI, int G, bool DMMA>
+inline cudaError_t launch_tier0(const FusedPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st) {
+  constexpr int smem = tier0_smem_doubles<NS, NI, G>() * (int)sizeof(double);
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(tier0_kernel<NS, NI, G, DMMA>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    attr_done = true;
+  }
+  tier0_kernel<NS, NI, G, DMMA><<<(unsigned)((size_t)batch * p.M0), 16 * G, smem, st>>>(s, b, p.fb, pack_rhs, p.M0);
+  return cudaGetLastError();
+}
+
+template <int NS, int NI>
+inline cudaError_t launch_upper(FusedPlan& p, const Shape& s, const Bufs& b, int batch, cudaStream_t st) {
+  using D = Dim<NS, NI>;
+  for (int t = 0; t < p.ntiers; ++t) {
+    const FusedTier& T = p.tiers[t];
+    const int warps = T.ecount / 2 > 0 ? T.ecount / 2 : 1;
+    const int smem = (T.ecount * D::ENT + warps * (D::WSZ + NS * NS)) * (int)sizeof(double);
+    static bool attr_done = false;
+    if (!attr_done) {
+      cudaError_t e = cudaFuncSetAttribute(tier_kernel<NS, NI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (8 * D::ENT + 4 * (D::WSZ + NS * NS)) * (int)sizeof(double));
+      if (e != cudaSuccess) return e;
+      attr_done = true;
+    }
+    tier_kernel<NS, NI><<<(unsigned)((size_t)batch * (T.Min / T.ecount)), 32 * warps, smem, st>>>(
+        s, b, p.fb, t + 1, T.Min, T.ecount, T.span, p.G0);
+    ++p.launches;
+  }
+  topdown_kernel<NS><<<batch, 128, 0, st>>>(p.fb, p.M0);
+  ++p.launches;
+  const long long rows = (long long)batch * s.N * D::ZS;
+  finalize_kernel<NS, NI><<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(s, b, p.fb, p.G0, p.M0, rows);
+  ++p.launches;
+  return cudaGetLastError();
+}
+
+// Whole solve of `batch` problems on stream `st`. force_dfma != 0 selects the DFMA Schur update for A/B tests.
+inline int fused_launch(FusedPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, int force_dfma,
+                        cudaStream_t st, std::string& err) {
+  if (!p.available) { err = "shape not covered by the tiered kernels"; return -5; }
+  p.launches = 1;
+  cudaError_t e;
+  const bool dm = p.use_dmma && !force_dfma;
+  if (s.n == 12) {
+    if (p.G0 == 16) e = dm ? launch_tier0<12, 4, 16, true>(p, s, b, batch, pack_rhs, st) : launch_tier0<12, 4, 16, false>(p, s, b, batch, pack_rhs, st);
+    else e = dm ? launch_tier0<12, 4, 8, true>(p, s, b, batch, pack_rhs, st) : launch_tier0<12, 4, 8, false>(p, s, b, batch, pack_rhs, st);
+    if (e == cudaSuccess && p.M0 > 1) e = launch_upper<12, 4>(p, s, b, batch, st);
+  } else {
+    if (p.G0 == 16) e = launch_tier0<6, 3, 16, false>(p, s, b, batch, pack_rhs, st);
+    else e = launch_tier0<6, 3, 8, false>(p, s, b, batch, pack_rhs, st);
+    if (e == cudaSuccess && p.M0 > 1) e = launch_upper<6, 3>(p, s, b, batch, st);
+  }
+  if (e != cudaSuccess) { err = std::string("tiered launch: ") + cudaGetErrorString(e); return -3; }
+  return 0;
+}
+
 }  // namespace rslqr

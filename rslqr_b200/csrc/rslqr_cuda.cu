@@ -6,6 +6,7 @@
 
 #include <chrono>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -45,7 +46,7 @@ struct rslqr_cuda_solver {
   double prof[7];
   // dominant-kernel timing
   bool ktime_on; std::vector<std::pair<cudaEvent_t, cudaEvent_t>> kspans; double k_ms; int k_n;
-  FusedPlan fused;
+  FusedPlan fused; int force_dfma;
   cudaEvent_t marks[8]; bool marks_made;
 };
 
@@ -106,7 +107,15 @@ extern "C" int rslqr_cuda_create(int n, int m, int N, int batch, int device, uns
     return fail(RSLQR_E_NOMEM, "device allocation failed");
   }
   h->b.knots = h->d_knots; h->b.x0 = h->d_x0;
-  fused_plan(h->s, h->batch, h->device, &h->fused);
+  {
+    const char* g0 = getenv("RSLQR_G0");
+    const char* fd = getenv("RSLQR_FORCE_DFMA");
+    h->force_dfma = fd ? atoi(fd) : 0;
+    if (fused_plan(h->s, h->batch, g0 ? atoi(g0) : 8, &h->fused, g_err)) {
+      rslqr_cuda_destroy(h);
+      return RSLQR_E_NOMEM;
+    }
+  }
   *out = h;
   int rc = rslqr_cuda_reset(h);
   if (rc) { rslqr_cuda_destroy(h); *out = nullptr; }
@@ -119,6 +128,7 @@ extern "C" int rslqr_cuda_destroy(rslqr_cuda_solver* h) {
   cudaStreamSynchronize(h->stream);
   cudaFree(h->d_knots); cudaFree(h->d_x0); cudaFree(h->b.soln); cudaFree(h->b.fact);
   cudaFree(h->b.status); cudaFree(h->b.flags); cudaFree(h->b.leafd);
+  fused_free(&h->fused);
   for (auto ev : h->evpool) cudaEventDestroy(ev);
   for (auto& pr : h->kspans) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
   if (h->marks_made) for (auto ev : h->marks) cudaEventDestroy(ev);
@@ -167,7 +177,7 @@ extern "C" int rslqr_cuda_reset(rslqr_cuda_solver* h) {
 extern "C" int rslqr_cuda_set_mode(rslqr_cuda_solver* h, int mode) {
   if (!h || mode < RSLQR_MODE_AUTO || mode > RSLQR_MODE_FUSED) return fail(RSLQR_E_ARG, "set_mode: bad argument");
   if (mode == RSLQR_MODE_STAGED && !h->b.fact) return fail(RSLQR_E_UNSUPPORTED, "staged mode needs RSLQR_KEEP_FACT");
-  if (mode == RSLQR_MODE_FUSED && !h->fused.available) return fail(RSLQR_E_UNSUPPORTED, "shape does not fit the fused cluster kernel");
+  if (mode == RSLQR_MODE_FUSED && !h->fused.available) return fail(RSLQR_E_UNSUPPORTED, "shape is not covered by the tiered (fused) kernels");
   h->mode = mode;
   return RSLQR_OK;
 }
@@ -293,10 +303,10 @@ extern "C" int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs) {
       cudaEventCreate(&kt.first); cudaEventCreate(&kt.second);
       cudaEventRecord(kt.first, h->stream);
     }
-    int rc = fused_launch(h->fused, h->s, h->b, h->batch, pack_rhs, h->stream, g_err);
+    int rc = fused_launch(h->fused, h->s, h->b, h->batch, pack_rhs, h->force_dfma, h->stream, g_err);
     if (h->ktime_on) { cudaEventRecord(kt.second, h->stream); h->kspans.push_back(kt); }
     if (rc) return rc;
-    h->launches = 1;
+    h->launches = h->fused.launches;
     return RSLQR_OK;
   }
   return solve_staged(h, pack_rhs);

@@ -153,6 +153,44 @@ def test_edge_shapes(shape):
             assert max(rel_err_classes(z[p], want, n, m, N)) < TOL, (shape, mode, p)
 
 
+@pytest.mark.parametrize("g0", [8, 16])
+@pytest.mark.parametrize("dfma", [0, 1])
+@pytest.mark.parametrize("shape", [(12, 4, 8), (12, 4, 16), (12, 4, 32), (12, 4, 128), (12, 4, 256), (12, 4, 4096),
+                                   (6, 3, 8), (6, 3, 64), (6, 3, 512)])
+def test_tiered_path_variants(shape, g0, dfma, monkeypatch):
+    # the tiered (fused) path for both group sizes and both Schur-update implementations (DMMA / DFMA),
+    # from one group (N == G) to four tiers (N = 4096), against the oracle
+    n, m, N = shape
+    monkeypatch.setenv("RSLQR_G0", str(g0))
+    monkeypatch.setenv("RSLQR_FORCE_DFMA", str(dfma))
+    B = 5
+    kn, x0 = R.synth_problems(n, m, N, 77, 0, B)
+    s = R.CudaSolver(n, m, N, batch=B, flags=0)
+    s.set_mode(R.MODE_FUSED)
+    s.upload(kn, x0)
+    s.solve()
+    z = s.solution()
+    assert not s.flags().any()
+    for p in range(B):
+        want, _ = O.port_solve(n, m, N, kn[p], x0[p], threads=2)
+        assert max(rel_err_classes(z[p], want, n, m, N)) < TOL, (shape, g0, dfma, p)
+    s.close()
+
+
+def test_tiered_path_reports_cholesky_failure():
+    n, m, N = 12, 4, 64
+    kn, x0 = R.synth_problems(n, m, N, 1, 0, 3)
+    kn[1, 3, 2] = -1.0      # Q[2] of knot 3 of problem 1: leaf factorization fails
+    s = R.CudaSolver(n, m, N, batch=3, flags=0)
+    s.set_mode(R.MODE_FUSED)
+    s.upload(kn, x0)
+    s.solve()
+    fl = s.flags()
+    assert fl[0] == 0 and fl[1] == 1
+    assert s.status(1)[2 * 3] == -1 and s.status(0).sum() == 0
+    s.close()
+
+
 def test_batch_quadrotor_properties():
     # BASELINE configs[2] shape (n=12,m=4,N=256) at a batch the CPU checks in seconds: sample vs oracle,
     # KKT residual of EVERY problem, and independence of problems from their batch position.
