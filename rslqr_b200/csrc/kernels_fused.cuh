@@ -65,6 +65,12 @@ __device__ __forceinline__ double fast_rcp(double d) {
   return r;
 }
 
+__device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+               : "+d"(d0), "+d"(d1)
+               : "d"(a), "d"(b));
+}
+
 __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -96,51 +102,100 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
   else if (lane < 2 * NS) { src = LXi + c; ss = NS; }
   else { src = zxi; ss = 1; }  // lanes > 2NS compute a harmless copy of the rhs column
   double acc[NS];
+  constexpr bool MMA_P1 = ((NS + NI) % 4 == 0) && (NS > 8) && (NS <= 16) && (2 * NS + 1 > 24);
+  if constexpr (MMA_P1) {
+    // [A_i | B_i] (NS x (NS+NI), padded to 16 rows) times [X_R;U_R | X_L;U_L | z_x;z_u](i) ((NS+NI) x (2NS+1),
+    // padded to 32 columns) on the fp64 tensor cores: 2 x 4 tiles, (NS+NI)/4 k-steps; the 8x8 result fragments
+    // are dropped into Wout (column-major, ld NS) and picked up again one column per lane.
+    constexpr int KS = (NS + NI) / 4;
+    const int q = lane & 3, rr = lane >> 2;
+    double d[2][4][2];
 #pragma unroll
-  for (int r = 0; r < NS; ++r) acc[r] = 0.0;
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) d[mt][nt][0] = d[mt][nt][1] = 0.0;
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+      const int l = 4 * ks + q;
+      const double a0 = __ldg(AB + l * NS + rr);
+      const double a1 = (8 + rr < NS) ? __ldg(AB + l * NS + 8 + rr) : 0.0;
+      double bf[4];
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        const int n = 8 * nt + rr;
+        bf[nt] = n < NS ? RXi[l * NS + n] : (n < 2 * NS ? LXi[l * NS + n - NS] : (n == 2 * NS ? zxi[l] : 0.0));
+      }
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        dmma884(d[0][nt][0], d[0][nt][1], a0, bf[nt]);
+        dmma884(d[1][nt][0], d[1][nt][1], a1, bf[nt]);
+      }
+    }
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int row = 8 * mt + rr, col = 8 * nt + 2 * q + h;
+          if (row < NS && col <= 2 * NS) Wout[col * NS + row] = d[mt][nt][h];
+        }
+    __syncwarp();
+    const int mc = lane <= 2 * NS ? lane : 2 * NS;
+#pragma unroll
+    for (int r = 0; r < NS; ++r) acc[r] = Wout[mc * NS + r];
+    __syncwarp();
+  } else {
+#pragma unroll
+    for (int r = 0; r < NS; ++r) acc[r] = 0.0;
 #pragma unroll 4
-  for (int l = 0; l < NS + NI; ++l) {
-    const double x = src[l * ss];
-    const double* col = AB + l * NS;  // column l of [A | B] (B follows A, both have NS rows)
+    for (int l = 0; l < NS + NI; ++l) {
+      const double x = src[l * ss];
+      const double* col = AB + l * NS;  // column l of [A | B] (B follows A, both have NS rows)
 #pragma unroll
-    for (int r = 0; r < NS; ++r) acc[r] = fma(__ldg(col + r), x, acc[r]);
+      for (int r = 0; r < NS; ++r) acc[r] = fma(__ldg(col + r), x, acc[r]);
+    }
   }
+  const int mycol = lane <= 2 * NS ? lane : 2 * NS;
   if (lane < NS) {
 #pragma unroll
     for (int r = 0; r < NS; ++r) acc[r] -= LXn[r * NS + c];
-  } else if (lane >= 2 * NS) {
+  } else {
+    if (lane >= 2 * NS) {
 #pragma unroll
-    for (int r = 0; r < NS; ++r) acc[r] = acc[r] - zxn[r] - zln[r];
+      for (int r = 0; r < NS; ++r) acc[r] = acc[r] - zxn[r] - zln[r];
+    }
+    // park the rhs columns in Wout so that only one register array is live during the factorization
+#pragma unroll
+    for (int r = 0; r < NS; ++r) Wout[mycol * NS + r] = acc[r];
   }
-  // ---- factorization, lane i < NS holds row i of S in a[] ----
+  // ---- factorization, lane i < NS holds row i of S in acc[] (the other lanes run along on junk) ----
   int bad = 0;
-  {
-    double a[NS];
 #pragma unroll
-    for (int r = 0; r < NS; ++r) a[r] = acc[r];
+  for (int j = 0; j < NS; ++j) {
+    const double d = shfl_d(acc[j], j);
+    if (!(d > 0.0)) bad = 1;
+    const double dinv = fast_rcp(d);
+    const double lij = acc[j] * dinv;  // Lt(i,j) for lane i > j
 #pragma unroll
-    for (int j = 0; j < NS; ++j) {
-      const double d = shfl_d(a[j], j);
-      if (!(d > 0.0)) bad = 1;
-      const double dinv = fast_rcp(d);
-      const double lij = a[j] * dinv;  // Lt(i,j) for lane i > j
-#pragma unroll
-      for (int k = j + 1; k < NS; ++k) {
-        const double pk = shfl_d(a[k], j);  // pivot row element S'(j,k) = S'(k,j)
-        a[k] = fma(-lij, pk, a[k]);
-      }
-      a[j] = lane == j ? dinv : lij;  // the diagonal slot of Lt carries 1/D(j)
+    for (int k = j + 1; k < NS; ++k) {
+      const double pk = shfl_d(acc[k], j);  // pivot row element S'(j,k) = S'(k,j)
+      acc[k] = fma(-lij, pk, acc[k]);
     }
-    if (lane < NS) {
+    acc[j] = lane == j ? dinv : lij;  // the diagonal slot of Lt carries 1/D(j)
+  }
+  if (lane < NS) {
 #pragma unroll
-      for (int k = 0; k < NS; ++k) Lsm[lane * NS + k] = a[k];
-    }
+    for (int k = 0; k < NS; ++k) Lsm[lane * NS + k] = acc[k];
   }
   __syncwarp();
-  // ---- solves: lanes < NS take over the S_R columns ----
+  // ---- solves: lanes < NS take the S_R columns, the others pick their parked column up again ----
   if (lane < NS) {
 #pragma unroll
     for (int r = 0; r < NS; ++r) acc[r] = -RXn[r * NS + c];
+  } else {
+#pragma unroll
+    for (int r = 0; r < NS; ++r) acc[r] = Wout[mycol * NS + r];
   }
 #pragma unroll
   for (int j = 0; j < NS; ++j) {
@@ -154,6 +209,7 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
 #pragma unroll
     for (int i = 0; i < j; ++i) acc[i] = fma(-Lsm[j * NS + i], acc[j], acc[i]);
   }
+  __syncwarp();
   if (lane <= 2 * NS) {
     const int wc = lane < NS ? NS + lane : (lane < 2 * NS ? lane - NS : 2 * NS);
 #pragma unroll
@@ -172,17 +228,12 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
 //   schur_dfma : plain DFMA, one thread per row (any shape).
 // Ls/Rs: [G*ZS][NS] row-major, zv: [G*ZS], W: per separator [f_L | f_R | zs] column-major ld NS.
 // ---------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double b) {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
-               : "+d"(d0), "+d"(d1)
-               : "d"(a), "d"(b));
-}
 
-template <int NS, int NI>
-__device__ __forceinline__ void schur_dmma(double* Ls, double* Rs, double* zv, const double* W, int j) {
+template <int NS, int NI, bool LEVEL0>
+__device__ __forceinline__ void schur_dmma_level(double* Ls, double* Rs, double* zv, const double* W, int j) {
   using D = Dim<NS, NI>;
   constexpr int ZS = D::ZS, KS = NS / 4, NT = 2 * NS / 8, TILES = 2 * ZS / 8;
-  static_assert((2 * ZS) % 8 == 0 && NS % 4 == 0, "tile shapes");
+  static_assert((2 * ZS) % 8 == 0 && NS % 4 == 0 && NS % 2 == 0, "tile shapes");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q = lane & 3, rr = lane >> 2;
   const int s = warp >> j;  // separator (local) of knot pair `warp` at level j
@@ -194,28 +245,37 @@ __device__ __forceinline__ void schur_dmma(double* Ls, double* Rs, double* zv, c
     for (int nt = 0; nt < NT; ++nt) bneg[ks][nt] = -Wf[(8 * nt + rr) * NS + 4 * ks + q];
     zq[ks] = Wf[2 * NS * NS + 4 * ks + q];
   }
-  const int ksep = (2 * s + 1) << j;  // local knot i+1: its Lambda rows receive (f_L, f_R, zs)
-#pragma unroll 1
+  // per-lane bases: row (8t + rr) of the pair, A fragment column q, C fragment columns 2q, 2q+1
+  const int rowbase = (warp * 2 * ZS + rr) * NS;
+  // side of the pair above level 0: 0 = left child (own = R block), 1 = right child (own = L block);
+  // at level 0 the first knot of the pair is a left child and the second a right child
+  const int pside = LEVEL0 ? 0 : (warp >> (j - 1)) & 1;
+  // which block column pair (8nt + 2q, +1) lives in: L for n < NS
+  bool inL[NT];
+  int coff[NT];
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt) {
+    const int n = 8 * nt + 2 * q;
+    inL[nt] = n < NS;
+    coff[nt] = inL[nt] ? n : n - NS;
+  }
+#pragma unroll
   for (int t = 0; t < TILES; ++t) {
-    const int R = warp * 2 * ZS + 8 * t + rr;
-    const int kn = 2 * warp + (8 * t + rr >= ZS ? 1 : 0);
-    const int row = R - kn * ZS;
-    const int side = (kn >> j) & 1;  // 0: left child (own = R block), 1: right child (own = L block)
-    const double* own = side ? Ls : Rs;
+    int side;
+    if (LEVEL0) side = (8 * t + 7 < ZS) ? 0 : ((8 * t >= ZS) ? 1 : (8 * t + rr >= ZS ? 1 : 0));
+    else side = pside;
+    const double* own = (side ? Ls : Rs) + rowbase + t * 8 * NS + q;
     double a[KS];
 #pragma unroll
-    for (int ks = 0; ks < KS; ++ks) a[ks] = own[R * NS + 4 * ks + q];
+    for (int ks = 0; ks < KS; ++ks) a[ks] = own[4 * ks];
     double c[NT][2];
     double* dst[NT];
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
-      const int n = 8 * nt + 2 * q;
-      const bool inL = n < NS;
-      dst[nt] = (inL ? Ls : Rs) + R * NS + (inL ? n : n - NS);
-      const bool isown = inL == (side == 1);
-      const double2 v = *reinterpret_cast<const double2*>(dst[nt]);
-      c[nt][0] = isown ? 0.0 : v.x;
-      c[nt][1] = isown ? 0.0 : v.y;
+      dst[nt] = (inL[nt] ? Ls : Rs) + rowbase + t * 8 * NS + coff[nt];
+      const bool isown = inL[nt] == (side == 1);
+      if (isown) { c[nt][0] = 0.0; c[nt][1] = 0.0; }
+      else { const double2 v = *reinterpret_cast<const double2*>(dst[nt]); c[nt][0] = v.x; c[nt][1] = v.y; }
     }
 #pragma unroll
     for (int ks = 0; ks < KS; ++ks)
@@ -226,18 +286,29 @@ __device__ __forceinline__ void schur_dmma(double* Ls, double* Rs, double* zv, c
     for (int ks = 0; ks < KS; ++ks) part = fma(a[ks], zq[ks], part);
     part += __shfl_xor_sync(0xffffffffu, part, 1);
     part += __shfl_xor_sync(0xffffffffu, part, 2);
-    const bool special = (kn == ksep) && (row < NS);
-    if (special) {
-#pragma unroll
-      for (int nt = 0; nt < NT; ++nt) {
-        c[nt][0] = Wf[(8 * nt + 2 * q) * NS + row];
-        c[nt][1] = Wf[(8 * nt + 2 * q + 1) * NS + row];
-      }
-    }
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) *reinterpret_cast<double2*>(dst[nt]) = make_double2(c[nt][0], c[nt][1]);
-    if (q == 0) zv[R] = special ? Wf[2 * NS * NS + row] : zv[R] - part;
+    if (q == 0) zv[warp * 2 * ZS + 8 * t + rr] -= part;
   }
+  // F(i+1, .).Lambda <- (f_L, f_R, zs): the Lambda rows of local knot (2s+1) << j, owned by this warp if it
+  // lies in its pair (own was zero there, so the update above left keep - 0 behind)
+  const int ksep = (2 * s + 1) << j;
+  if ((ksep >> 1) == warp) {
+    __syncwarp();
+    for (int e = lane; e < D::W * NS; e += 32) {
+      const int col = e / NS, row = e - col * NS;
+      const double v = Wf[e];
+      if (col < NS) Ls[(ksep * ZS + row) * NS + col] = v;
+      else if (col < 2 * NS) Rs[(ksep * ZS + row) * NS + col - NS] = v;
+      else zv[ksep * ZS + row] = v;
+    }
+  }
+}
+
+template <int NS, int NI>
+__device__ __forceinline__ void schur_dmma(double* Ls, double* Rs, double* zv, const double* W, int j) {
+  if (j == 0) schur_dmma_level<NS, NI, true>(Ls, Rs, zv, W, 0);
+  else schur_dmma_level<NS, NI, false>(Ls, Rs, zv, W, j);
 }
 
 // one row: [L R z](R) <- keep - own * [f_L f_R zs]; `side` selects own (0: R block, 1: L block)
@@ -312,60 +383,85 @@ __global__ void __launch_bounds__(16 * G, 512 / (16 * G)) tier0_kernel(Shape s, 
   const int N = s.N;
 
   // ---- leaves: L(k) = F(k, lev(k-1)), R(k) = F(k, lev(k)) ----
-  for (int idx = tid; idx < G * SLOT; idx += nthr) {
-    const int kl = idx / SLOT, e = idx - kl * SLOT;
-    const int row = e / NS, c = e - row * NS;
-    const int k = k0 + kl;
-    const double* kn = knot_ptr(s, b, prob, k);
-    double l = 0.0, r = 0.0;
-    if (row < NS) {
-      if (k == 0) r = -kn[s.oA + row * NS + c];  // F(0,0).Lambda = -A0^T (nested_dissection.c:31-36)
-    } else if (row < 2 * NS) {
-      const int i = row - NS;
-      const double qi = kn[s.oQ + i];
-      if (k > 0 && c == i) l = -1.0 / qi;                         // Q \ (-I)   (:96-102)
-      if (k > 0 && k < N - 1) r = kn[s.oA + i * NS + c] / qi;     // Q \ A^T    (:75-79)
-    } else {
-      const int i = row - 2 * NS;
-      if (k < N - 1) r = kn[s.oB + i * NS + c] / kn[s.oR + i];    // R \ B^T    (:40-44, :80-84)
-    }
-    Ls[idx] = l;
-    Rs[idx] = r;
+  // pass A: straight coalesced copies. [A_k | B_k] column-major is exactly [X rows | U rows] of A^T, B^T
+  // row-major, so it lands in R(k) unscaled; the small vectors Q,R,q,r,d go to a staging area inside W.
+  constexpr int VEC = 2 * NS + 2 * NI, STG = VEC + NS, AB = NS * (NS + NI);
+  static_assert(G * STG + NS <= (G / 2) * WSZ, "staging area must fit into W");
+  double* stg = W;               // [G][Q(NS) R(NI) q(NS) r(NI) d(NS)]
+  double* prevd = W + G * STG;   // d_{k0-1} (or x0 for the first group)
+  const double* kn0 = knot_ptr(s, b, prob, k0);
+  for (int idx = tid; idx < G * AB; idx += nthr) {
+    const int kl = idx / AB, e = idx - kl * AB;
+    Rs[kl * SLOT + NS * NS + e] = kn0[(size_t)kl * s.stride + s.oA + e];
   }
+  for (int idx = tid; idx < G * VEC; idx += nthr) {
+    const int kl = idx / VEC, e = idx - kl * VEC;
+    stg[kl * STG + e] = kn0[(size_t)kl * s.stride + e];
+  }
+  for (int idx = tid; idx < G * NS; idx += nthr) {
+    const int kl = idx / NS, e = idx - kl * NS;
+    stg[kl * STG + VEC + e] = kn0[(size_t)kl * s.stride + s.od + e];
+  }
+  if (tid < NS) prevd[tid] = (k0 == 0) ? b.x0[(size_t)prob * NS + tid] : (kn0 - s.stride)[s.od + tid];
+  for (int idx = tid; idx < G * SLOT; idx += nthr) Ls[idx] = 0.0;
+  for (int idx = tid; idx < G * NS * NS; idx += nthr) {
+    const int kl = idx / (NS * NS), e = idx - kl * NS * NS;
+    Rs[kl * SLOT + e] = 0.0;
+  }
+  const double* zin = soln_ptr(s, b, prob, k0);
+  __syncthreads();
+  // pass B: rhs (needs the raw Q of knot 0), then Q, R -> 1/Q, 1/R with the leaf "Cholesky" status
+  // (Q_k, R_k are diagonal: the factorization fails on an entry <= 0, reference src/linalg_custom.c:88)
   for (int idx = tid; idx < G * ZS; idx += nthr) {
     const int kl = idx / ZS, row = idx - kl * ZS;
     const int k = k0 + kl;
-    const double* kn = knot_ptr(s, b, prob, k);
-    auto raw = [&](int rw) -> double {  // entry rw of the (negated) rhs of knot k
-      if (!pack_rhs) return soln_ptr(s, b, prob, k)[rw];
-      double v;
-      if (rw < NS) v = (k == 0) ? b.x0[(size_t)prob * NS + rw] : knot_ptr(s, b, prob, k - 1)[s.od + rw];
-      else if (rw < 2 * NS) v = kn[s.oq + rw - NS];
-      else v = (k < N - 1) ? kn[s.orr + rw - 2 * NS] : 0.0;
-      return -v;
+    const double* sv = stg + kl * STG;
+    auto raw = [&](int rw) -> double {  // entry rw of the negated rhs of knot k (reference src/solver.c:138-190)
+      if (!pack_rhs) return zin[kl * ZS + rw];
+      if (rw < NS) return -(kl == 0 ? prevd[rw] : sv[rw - STG + VEC]);
+      if (rw < 2 * NS) return -sv[NS + NI + rw - NS];
+      return (k < N - 1) ? -sv[2 * NS + NI + rw - 2 * NS] : 0.0;
     };
     double v;
     if (k == 0) {  // nested_dissection.c:45-59
-      if (row < NS) v = -kn[s.oQ + row] * raw(row) - raw(NS + row);
+      if (row < NS) v = -sv[row] * raw(row) - raw(NS + row);
       else if (row < 2 * NS) v = -raw(row - NS);
-      else v = raw(row) / kn[s.oR + row - 2 * NS];
+      else v = raw(row) / sv[NS + row - 2 * NS];
     } else {
       if (row < NS) v = raw(row);
-      else if (row < 2 * NS) v = raw(row) / kn[s.oQ + row - NS];
-      else v = (k < N - 1) ? raw(row) / kn[s.oR + row - 2 * NS] : raw(row);
+      else if (row < 2 * NS) v = raw(row) / sv[row - NS];
+      else v = (k < N - 1) ? raw(row) / sv[NS + row - 2 * NS] : raw(row);
     }
     zv[idx] = v;
   }
-  // leaf "Cholesky" status: Q_k, R_k diagonal, factorization fails on an entry <= 0
+  __syncthreads();
   for (int idx = tid; idx < G * (NS + NI); idx += nthr) {
     const int kl = idx / (NS + NI), i = idx - kl * (NS + NI);
     const int k = k0 + kl;
-    if (i >= NS && k == N - 1) continue;
-    const double d = knot_ptr(s, b, prob, k)[i < NS ? s.oQ + i : s.oR + i - NS];
-    if (!(d > 0.0)) {
+    const double d = stg[kl * STG + i];
+    if (!(d > 0.0) && !(i >= NS && k == N - 1)) {
       b.status[(size_t)prob * 3 * N + (i < NS ? rs_slot_Q(k) : rs_slot_R(k))] = -1;
       b.flags[prob] = 1;
     }
+    stg[kl * STG + i] = 1.0 / d;
+  }
+  __syncthreads();
+  // pass C: row scalings. R(k): X = Q \ A^T, U = R \ B^T (nested_dissection.c:75-84); L(k): X = Q \ (-I) (:96-102);
+  // knot 0: Lambda = -A0^T, X = 0 (:31-36); last knot: R(k) = 0.
+  for (int idx = tid; idx < G * AB; idx += nthr) {
+    const int kl = idx / AB, e = idx - kl * AB;
+    const int row = e / NS;  // 0..NS+NI-1: X rows then U rows; stg holds 1/Q then 1/R in the same order
+    const int k = k0 + kl;
+    double* p = Rs + kl * SLOT + NS * NS + e;
+    const double rawv = *p;
+    double v = rawv * stg[kl * STG + row];
+    if (k == N - 1) v = 0.0;
+    if (k == 0 && row < NS) { Rs[kl * SLOT + e] = -rawv; v = 0.0; }
+    *p = v;
+  }
+  for (int idx = tid; idx < G * NS; idx += nthr) {
+    const int kl = idx / NS, i = idx - kl * NS;
+    if (k0 + kl > 0) Ls[kl * SLOT + (NS + i) * NS + i] = -stg[kl * STG + i];
   }
 
   // ---- levels ----
@@ -432,7 +528,7 @@ __global__ void __launch_bounds__(16 * G, 512 / (16 * G)) tier0_kernel(Shape s, 
 // dynamic smem: (ecount*ENT + warps*(WSZ + NS*NS)) doubles.
 // ---------------------------------------------------------------------------------------------------------
 template <int NS, int NI>
-__global__ void tier_kernel(Shape s, Bufs b, FusedBufs fb, int tier, int Min, int ecount, int span, int G0) {
+__global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, FusedBufs fb, int tier, int Min, int ecount, int span, int G0) {
   using D = Dim<NS, NI>;
   constexpr int ZS = D::ZS, SLOT = D::SLOT, WSZ = D::WSZ, ENT = D::ENT;
   static_assert(ZS <= 32, "lean Schur update maps one row per lane");
