@@ -345,3 +345,13 @@ def test_batch_host_api():
     LIB.ndlqr_FreeBatchSolver(bs)
     for p in probs:
         LIB.ndlqr_FreeLQRProblem(p)
+
+
+def test_c_consumer_flow_runs(tmp_path):
+    # the compiled C consumer (tests/c/consumer_flow.c) solves the shipped problems on the GPU and matches "soln"
+    import subprocess
+    from test_host_api import _compile_consumer
+    exe = _compile_consumer(os.path.join(os.path.dirname(GOLDEN), "c", "consumer_flow.c"), str(tmp_path / "consumer"))
+    for name in ("lqr_prob.json", "lqr_prob_256.json"):
+        r = subprocess.run([exe, os.path.join(GOLDEN, name)], capture_output=True, text=True)
+        assert r.returncode == 0, (name, r.returncode, r.stdout, r.stderr)

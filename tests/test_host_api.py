@@ -209,3 +209,24 @@ def test_synth_generator_is_reproducible():
     kk, xx = L.problem_to_flat(pp, 12, 4)
     assert np.array_equal(kk, k1[0]) and np.array_equal(xx, x1[0])
     LIB.ndlqr_FreeLQRProblem(pp)
+
+
+def _compile_consumer(src, out, extra=()):
+    import subprocess
+    libdir = os.path.join(ROOT, "rslqr_b200")
+    cmd = ["/usr/bin/gcc", "-std=c11", "-O1", "-I" + os.path.join(ROOT, "include"), *extra, src, "-L" + libdir, "-lrslqr",
+           "-Wl,-rpath," + libdir, "-lm", "-o", out]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    return out
+
+
+def test_reference_example_compiles_and_links(tmp_path):
+    # drop-in at link level: a consumer written against the reference's headers builds
+    # against include/ + librslqr.so; when the reference tree is mounted, its own example is built UNMODIFIED
+    exe = _compile_consumer(os.path.join(ROOT, "tests", "c", "consumer_flow.c"), str(tmp_path / "consumer"))
+    assert os.path.exists(exe)
+    ref_example = "/root/reference/examples/installexample/main.c"
+    if os.path.exists(ref_example):
+        prob = os.path.join(GOLDEN, "lqr_prob.json")
+        _compile_consumer(ref_example, str(tmp_path / "ref_example"), extra=[f'-DLQRPROBFILE="{prob}"'])
