@@ -238,11 +238,8 @@ def run_ours(args, rank, world, local_rank):
         s.solve_async(True)
 
     def step_e2e():
-        s.upload_async(h_knots, h_x0)
-        if staged:
-            s.reset()
-        s.solve_async(True)
-        s.solution_async(h_soln)
+        # the user-facing call: host problems in, host solutions out (chunked, copies overlap the kernels)
+        s.solve_host(h_knots, h_x0, h_soln, chunk=args.chunk)
         s.sync()
 
     for _ in range(args.warmup):
@@ -324,6 +321,7 @@ def main():
     ap.add_argument("--batch", type=int, default=4096)
     ap.add_argument("--mode", default="auto", choices=["auto", "staged", "fused"])
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--chunk", type=int, default=0, help="problems per pipeline chunk of the e2e call (0 = automatic)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -94,6 +94,12 @@ int rslqr_cuda_solve(rslqr_cuda_solver* h, int pack_rhs);
 /* Same, but only enqueues on the handle's stream (for overlap with copies); pair with _sync. */
 int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs);
 int rslqr_cuda_sync(rslqr_cuda_solver* h);
+/* End to end from HOST buffers (pinned for full PCIe rate): upload `count` problems, solve them (rhs packed from
+ * the problem data, as ndlqr_InitializeWithLQRProblem + ndlqr_Solve do, reference src/solver.c:122, src/solve.c:38)
+ * and copy the solutions back, in chunks of `chunk` problems (<= 0: automatic) pipelined over three streams so
+ * that copies and kernels overlap. Asynchronous: pair with rslqr_cuda_sync. */
+int rslqr_cuda_solve_host(rslqr_cuda_solver* h, const double* knots, const double* x0, double* soln, int count,
+                          int chunk);
 
 /* One phase (or one task of it) in staged mode; needs RSLQR_KEEP_FACT. `problem` -1 = all. */
 int rslqr_cuda_stage(rslqr_cuda_solver* h, int stage, int level, int item, int col, int problem);

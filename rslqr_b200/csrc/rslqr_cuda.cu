@@ -47,6 +47,8 @@ struct rslqr_cuda_solver {
   // dominant-kernel timing
   bool ktime_on; std::vector<std::pair<cudaEvent_t, cudaEvent_t>> kspans; double k_ms; int k_n;
   FusedPlan fused; int force_dfma;
+  int r_first, r_count;            // problem range the next enqueue covers (whole batch by default)
+  cudaStream_t s_h2d, s_d2h; bool pipe_made; std::vector<cudaEvent_t> ev_up, ev_done; cudaEvent_t ev_join;
   cudaEvent_t marks[8]; bool marks_made;
 };
 
@@ -83,7 +85,7 @@ extern "C" int rslqr_cuda_create(int n, int m, int N, int batch, int device, uns
   rslqr_cuda_solver* h = new rslqr_cuda_solver();
   h->s = make_shape(n, m, N);
   h->batch = batch; h->device = device; h->flags = flags; h->mode = RSLQR_MODE_AUTO;
-  h->marks_made = false;
+  h->marks_made = false; h->pipe_made = false; h->r_first = 0; h->r_count = batch;
   h->launches = 0; h->evused = 0; h->ktime_on = false; h->k_ms = 0; h->k_n = 0;
   memset(h->prof, 0, sizeof(h->prof));
   memset(&h->b, 0, sizeof(h->b));
@@ -132,6 +134,11 @@ extern "C" int rslqr_cuda_destroy(rslqr_cuda_solver* h) {
   for (auto ev : h->evpool) cudaEventDestroy(ev);
   for (auto& pr : h->kspans) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
   if (h->marks_made) for (auto ev : h->marks) cudaEventDestroy(ev);
+  if (h->pipe_made) {
+    for (auto ev : h->ev_up) cudaEventDestroy(ev);
+    for (auto ev : h->ev_done) cudaEventDestroy(ev);
+    cudaEventDestroy(h->ev_join); cudaStreamDestroy(h->s_h2d); cudaStreamDestroy(h->s_d2h);
+  }
   cudaStreamDestroy(h->stream);
   delete h;
   return RSLQR_OK;
@@ -258,7 +265,7 @@ static int timed_stage(rslqr_cuda_solver* h, int phase, int stage, int level, co
 
 static Sel all_items(const rslqr_cuda_solver* h, int nitems) {
   Sel sel;
-  sel.p0 = 0; sel.np = h->batch; sel.item0 = 0; sel.nitems = nitems; sel.col = -1;
+  sel.p0 = h->r_first; sel.np = h->r_count; sel.item0 = 0; sel.nitems = nitems; sel.col = -1;
   sel.calc_lambda = -1; sel.index = -1;
   return sel;
 }
@@ -303,13 +310,85 @@ extern "C" int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs) {
       cudaEventCreate(&kt.first); cudaEventCreate(&kt.second);
       cudaEventRecord(kt.first, h->stream);
     }
-    int rc = fused_launch(h->fused, h->s, h->b, h->batch, pack_rhs, h->force_dfma, h->stream, g_err);
+    // the kernels index problems from 0: hand them views that start at the first problem of the range
+    const Shape& s = h->s;
+    const size_t f = (size_t)h->r_first;
+    Bufs b = h->b;
+    b.knots += f * s.N * s.stride; b.x0 += f * s.n; b.soln += f * s.N * s.zs;
+    b.status += f * 3 * s.N; b.flags += f; b.leafd += f * s.N * (s.n + s.m);
+    FusedPlan q = h->fused;
+    if (q.M0 > 1) {
+      const size_t ent = 2 * (size_t)s.zs * s.n + s.zs + s.n, wsz = (2 * (size_t)s.n + 1) * s.n;
+      q.fb.stL += f * s.N * s.zs * s.n; q.fb.stR += f * s.N * s.zs * s.n; q.fb.stz += f * s.N * s.zs;
+      q.fb.sep += f * q.M0 * wsz; q.fb.lamhat += f * (q.M0 + 1) * s.n;
+      for (int t = 0; t < q.ntiers; ++t) q.fb.ent[t] += f * q.tiers[t].Min * ent;
+    }
+    int rc = fused_launch(q, s, b, h->r_count, pack_rhs, h->force_dfma, h->stream, g_err);
     if (h->ktime_on) { cudaEventRecord(kt.second, h->stream); h->kspans.push_back(kt); }
     if (rc) return rc;
-    h->launches = h->fused.launches;
+    h->launches = q.launches;
     return RSLQR_OK;
   }
   return solve_staged(h, pack_rhs);
+}
+
+// Host buffers in, host solutions out: uploads, solves and downloads are cut into chunks of problems and
+// overlapped on three streams (copy-in, compute, copy-out), so the PCIe transfers hide the kernels.
+extern "C" int rslqr_cuda_solve_host(rslqr_cuda_solver* h, const double* knots, const double* x0, double* soln,
+                                     int count, int chunk) {
+  if (!h || !knots || !x0 || !soln || count <= 0 || count > h->batch) return fail(RSLQR_E_ARG, "solve_host: bad argument");
+  CU(cudaSetDevice(h->device));
+  const Shape& s = h->s;
+  if (chunk <= 0) {
+    // ~64 MB of input per chunk keeps the first upload (which nothing overlaps) short
+    const size_t per = sizeof(double) * (size_t)s.N * s.stride;
+    chunk = (int)((64u << 20) / per);
+    if (chunk < 1) chunk = 1;
+  }
+  if (chunk > count) chunk = count;
+  const int nch = (count + chunk - 1) / chunk;
+  if (!h->pipe_made) {
+    CU(cudaStreamCreateWithFlags(&h->s_h2d, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&h->s_d2h, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
+    h->pipe_made = true;
+  }
+  while ((int)h->ev_up.size() < nch) {
+    cudaEvent_t a, b2;
+    CU(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&b2, cudaEventDisableTiming));
+    h->ev_up.push_back(a); h->ev_done.push_back(b2);
+  }
+  // the copy-in must not overtake work already queued on the compute stream that still reads the inputs
+  CU(cudaEventRecord(h->ev_join, h->stream));
+  CU(cudaStreamWaitEvent(h->s_h2d, h->ev_join, 0));
+  CU(cudaStreamWaitEvent(h->s_d2h, h->ev_join, 0));
+  const size_t kper = (size_t)s.N * s.stride, zper = (size_t)s.N * s.zs;
+  const int staged = rslqr_cuda_get_mode(h) == RSLQR_MODE_STAGED;
+  int launches = 0, rc = 0;
+  for (int c = 0; c < nch && !rc; ++c) {
+    const int first = c * chunk, cnt = (first + chunk <= count) ? chunk : count - first;
+    CU(cudaMemcpyAsync(h->d_knots + first * kper, knots + first * kper, sizeof(double) * kper * cnt, cudaMemcpyHostToDevice, h->s_h2d));
+    CU(cudaMemcpyAsync(h->d_x0 + (size_t)first * s.n, x0 + (size_t)first * s.n, sizeof(double) * (size_t)s.n * cnt, cudaMemcpyHostToDevice, h->s_h2d));
+    CU(cudaEventRecord(h->ev_up[c], h->s_h2d));
+    CU(cudaStreamWaitEvent(h->stream, h->ev_up[c], 0));
+    if (staged) {  // the staged kernels accumulate into a zeroed factor array (reference contract, src/solve.h:28-32)
+      CU(cudaMemsetAsync(h->b.fact + (size_t)first * s.K * s.N * s.fs, 0, sizeof(double) * (size_t)cnt * s.K * s.N * s.fs, h->stream));
+    }
+    h->r_first = first; h->r_count = cnt;
+    rc = rslqr_cuda_solve_async(h, 1);
+    launches += h->launches;
+    h->r_first = 0; h->r_count = h->batch;
+    if (rc) break;
+    CU(cudaEventRecord(h->ev_done[c], h->stream));
+    CU(cudaStreamWaitEvent(h->s_d2h, h->ev_done[c], 0));
+    CU(cudaMemcpyAsync(soln + first * zper, h->b.soln + first * zper, sizeof(double) * zper * cnt, cudaMemcpyDeviceToHost, h->s_d2h));
+  }
+  h->launches = launches;
+  if (rc) return rc;
+  CU(cudaEventRecord(h->ev_join, h->s_d2h));
+  CU(cudaStreamWaitEvent(h->stream, h->ev_join, 0));
+  return RSLQR_OK;
 }
 
 extern "C" int rslqr_cuda_sync(rslqr_cuda_solver* h) {

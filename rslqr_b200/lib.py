@@ -49,6 +49,7 @@ _sig("rslqr_cuda_get_mode", C.c_int, C.c_void_p)
 _sig("rslqr_cuda_solve", C.c_int, C.c_void_p, C.c_int)
 _sig("rslqr_cuda_solve_async", C.c_int, C.c_void_p, C.c_int)
 _sig("rslqr_cuda_sync", C.c_int, C.c_void_p)
+_sig("rslqr_cuda_solve_host", C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int)
 _sig("rslqr_cuda_stage", C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int)
 _sig("rslqr_cuda_schur_task", C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int)
 _sig("rslqr_cuda_download_solution", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int)
@@ -152,6 +153,14 @@ class CudaSolver:
 
     def sync(self):
         _check(LIB.rslqr_cuda_sync(self.h), "sync")
+
+    def solve_host(self, knots, x0, soln, count=None, chunk=0):
+        """host buffers in, host solutions out, copies and kernels pipelined; asynchronous (call sync())"""
+        count = self.batch if count is None else count
+        for a in (knots, x0, soln):
+            assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"]
+        assert knots.size >= count * self.N * self.stride and x0.size >= count * self.n and soln.size >= count * self.N * self.zs
+        _check(LIB.rslqr_cuda_solve_host(self.h, _ptr(knots), _ptr(x0), _ptr(soln), count, chunk), "solve_host")
 
     def stage(self, name, level=0, item=-1, col=-1, problem=-1):
         _check(LIB.rslqr_cuda_stage(self.h, STAGE[name], level, item, col, problem), "stage " + name)

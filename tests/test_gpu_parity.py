@@ -355,3 +355,28 @@ def test_c_consumer_flow_runs(tmp_path):
     for name in ("lqr_prob.json", "lqr_prob_256.json"):
         r = subprocess.run([exe, os.path.join(GOLDEN, name)], capture_output=True, text=True)
         assert r.returncode == 0, (name, r.returncode, r.stdout, r.stderr)
+
+
+@pytest.mark.parametrize("mode", [R.MODE_FUSED, R.MODE_STAGED])
+def test_solve_host_pipeline_matches_resident_solve(mode):
+    # the chunked host-to-host call (copies overlapped with kernels) returns bit-identical solutions
+    n, m, N, B = 12, 4, 64, 37
+    kn, x0 = R.synth_problems(n, m, N, 5, 0, B)
+    s = R.CudaSolver(n, m, N, batch=B, flags=R.KEEP_FACT)
+    s.set_mode(mode)
+    s.upload(kn, x0)
+    s.reset()
+    s.solve()
+    want = s.solution().copy()
+    for chunk in (0, 1, 8, 37, 100):
+        out = np.zeros((B, N * s.zs))
+        s.upload(np.zeros_like(kn), np.zeros_like(x0))   # make sure the call really uploads
+        s.solve_host(kn, x0, out, chunk=chunk)
+        s.sync()
+        assert np.array_equal(out, want), (mode, chunk)
+    # a partial count leaves the rest untouched
+    out = np.full((B, N * s.zs), 7.0)
+    s.solve_host(kn, x0, out, count=5, chunk=2)
+    s.sync()
+    assert np.array_equal(out[:5], want[:5]) and (out[5:] == 7.0).all()
+    s.close()
