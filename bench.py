@@ -49,6 +49,32 @@ def flop_model(n, m, N):
             t_sc * (2 * n ** 3 + 2 * m * n * n) + t_scl * 2 * n ** 3 + leaf)
 
 
+def tier0_flops_per_group(n, m, G):
+    """FLOPs tier0_kernel executes for one group of G knots: dense Schur update of every
+    knot at each of the log2(G) levels (rows 2n+m, columns [L|R|z] = 2n+1, inner dimension n) plus per separator
+    the inner products [A|B](n x (n+m)) x (n+m x 2n+1), the LDL^T factorization (n^3/6) and 2n+1 solves (n^2 each)."""
+    g = G.bit_length() - 1
+    zs, w = 2 * n + m, 2 * n + 1
+    schur = g * G * zs * w * n
+    spine = (G - 1) * (n * (n + m) * w + n ** 3 / 6 + w * n * n)
+    return 2.0 * (schur + spine)
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum of tier0_kernel per problem, from the committed ncu --set full capture
+# (profiles/r01_ncu_tier0_v1.md: 0.995 GB + 4.060 GB at batch 2048)
+TIER0_TRAFFIC_BYTES_PER_PROBLEM = (0.995207936e9 + 4.060259e9) / 2048
+
+
+def fp64_peak():
+    """fp64 tensor (DMMA m8n8k4) peak measured on this pool's B200 by tools/fp64_peak.cu (MEASURED_PEAKS.json has
+    no fp64 entry)."""
+    p = os.path.join(ROOT, "profiles", "r01_fp64_peak.json")
+    try:
+        return {"tflops": float(json.load(open(p))["dmma_m8n8k4_tflops"]), "kind": "measured (tools/fp64_peak.cu, profiles/r01_fp64_peak.json)"}
+    except Exception:
+        return {"tflops": 37.2, "kind": "fallback: 148 SM x 64 FMA/clk x 1.965 GHz"}
+
+
 def schur_bytes_model(n, m, N, batch):
     """Algorithmic HBM bytes of the staged Schur launches, averaged per launch: every active task
     (knot, boundary column) reads F(k,level) and reads+writes F(k,column) (SURVEY 8d streaming model)."""
@@ -282,14 +308,24 @@ def run_ours(args, rank, world, local_rank):
                 "unit": "GB/s", "frac": ach / pk["hbm_gbs"] if ach else None, "traffic": None, "peak_kind": pk_kind,
                 "algorithmic_bytes_per_launch": bytes_launch, "avg_launch_ms": k_avg_ms}
     else:
-        fl = flop_model(n, m, N) * B
+        # dominant kernel of the tiered path: tier0_kernel (leaves + the first log2(G) levels on chip), one launch
+        # per step, timed with CUDA events on the launching stream by the C-ABI (rslqr_cuda_kernel_timing)
+        G0 = int(os.environ.get("RSLQR_G0", "8"))
+        G0 = 16 if G0 == 16 else 8
+        fl_group = tier0_flops_per_group(n, m, G0)
+        fl = fl_group * (N // G0) * B
         k_avg_ms = k_ms if k_n else ms_per_step
         ach = fl / (k_avg_ms * 1e-3) / 1e12
-        fp64_peak = float(os.environ.get("RSLQR_FP64_PEAK_TFLOPS", "37.3"))
-        roof = {"kernel": "fused_solve_kernel (whole solve in one cluster launch)", "bound": "tensor", "achieved": ach,
-                "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach / fp64_peak, "traffic": None,
-                "peak_kind": "fp64 DFMA, 148 SM x 64 FMA/clk x 1.965 GHz (MEASURED_PEAKS.json has no fp64 entry; see DESIGN.md)",
-                "algorithmic_flops_per_launch": fl, "avg_launch_ms": k_avg_ms}
+        fp64 = fp64_peak()
+        roof = {"kernel": f"tier0_kernel<{n},{m},G={G0}> (leaves + levels 0..{G0.bit_length() - 2} on chip, DMMA Schur update)",
+                "bound": "tensor", "achieved": ach, "peak": fp64["tflops"], "unit": "TFLOP/s", "frac": ach / fp64["tflops"],
+                "traffic": TIER0_TRAFFIC_BYTES_PER_PROBLEM * B if (n, m, N, G0) == (12, 4, 256, 8) else None,
+                "peak_kind": fp64["kind"],
+                "flops_per_launch": fl, "flops_per_group": fl_group, "avg_launch_ms": k_avg_ms, "kernel_launches_timed": k_n,
+                "kernel_share_of_step": k_avg_ms / ms_per_step,
+                "reference_count_tflops_whole_step": flop_model(n, m, N) * B / (ms_per_step * 1e-3) / 1e12,
+                "note": "achieved = FLOPs tier0 executes (DESIGN.md section 5) / its CUDA-event time; "
+                        "reference_count = SURVEY 8d figure (32.2 MFLOP/solve as the reference executes it) over the whole step"}
     line = {"metric": METRIC, "value": value, "unit": "solves/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",

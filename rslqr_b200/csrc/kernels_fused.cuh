@@ -750,18 +750,21 @@ inline cudaError_t launch_upper(FusedPlan& p, const Shape& s, const Bufs& b, int
 
 // Whole solve of `batch` problems on stream `st`. force_dfma != 0 selects the DFMA Schur update for A/B tests.
 inline int fused_launch(FusedPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, int force_dfma,
-                        cudaStream_t st, std::string& err) {
+                        cudaStream_t st, std::string& err, cudaEvent_t k0 = nullptr, cudaEvent_t k1 = nullptr) {
   if (!p.available) { err = "shape not covered by the tiered kernels"; return -5; }
   p.launches = 1;
   cudaError_t e;
   const bool dm = p.use_dmma && !force_dfma;
+  if (k0) cudaEventRecord(k0, st);  // k0..k1 bracket the dominant kernel (tier 0) only
   if (s.n == 12) {
     if (p.G0 == 16) e = dm ? launch_tier0<12, 4, 16, true>(p, s, b, batch, pack_rhs, st) : launch_tier0<12, 4, 16, false>(p, s, b, batch, pack_rhs, st);
     else e = dm ? launch_tier0<12, 4, 8, true>(p, s, b, batch, pack_rhs, st) : launch_tier0<12, 4, 8, false>(p, s, b, batch, pack_rhs, st);
+    if (k1) cudaEventRecord(k1, st);
     if (e == cudaSuccess && p.M0 > 1) e = launch_upper<12, 4>(p, s, b, batch, st);
   } else {
     if (p.G0 == 16) e = launch_tier0<6, 3, 16, false>(p, s, b, batch, pack_rhs, st);
     else e = launch_tier0<6, 3, 8, false>(p, s, b, batch, pack_rhs, st);
+    if (k1) cudaEventRecord(k1, st);
     if (e == cudaSuccess && p.M0 > 1) e = launch_upper<6, 3>(p, s, b, batch, st);
   }
   if (e != cudaSuccess) { err = std::string("tiered launch: ") + cudaGetErrorString(e); return -3; }

@@ -306,10 +306,7 @@ extern "C" int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs) {
   const int mode = rslqr_cuda_get_mode(h);
   if (mode == RSLQR_MODE_FUSED) {
     std::pair<cudaEvent_t, cudaEvent_t> kt;
-    if (h->ktime_on) {
-      cudaEventCreate(&kt.first); cudaEventCreate(&kt.second);
-      cudaEventRecord(kt.first, h->stream);
-    }
+    if (h->ktime_on) { cudaEventCreate(&kt.first); cudaEventCreate(&kt.second); }
     // the kernels index problems from 0: hand them views that start at the first problem of the range
     const Shape& s = h->s;
     const size_t f = (size_t)h->r_first;
@@ -323,8 +320,9 @@ extern "C" int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs) {
       q.fb.sep += f * q.M0 * wsz; q.fb.lamhat += f * (q.M0 + 1) * s.n;
       for (int t = 0; t < q.ntiers; ++t) q.fb.ent[t] += f * q.tiers[t].Min * ent;
     }
-    int rc = fused_launch(q, s, b, h->r_count, pack_rhs, h->force_dfma, h->stream, g_err);
-    if (h->ktime_on) { cudaEventRecord(kt.second, h->stream); h->kspans.push_back(kt); }
+    int rc = fused_launch(q, s, b, h->r_count, pack_rhs, h->force_dfma, h->stream, g_err,
+                          h->ktime_on ? kt.first : nullptr, h->ktime_on ? kt.second : nullptr);
+    if (h->ktime_on) h->kspans.push_back(kt);
     if (rc) return rc;
     h->launches = q.launches;
     return RSLQR_OK;
