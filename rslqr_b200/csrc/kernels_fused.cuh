@@ -36,6 +36,8 @@
 
 namespace rslqr {
 
+inline size_t fused_ent_doubles(int n, int m) { return ((size_t)2 * (2 * n + m) * n + (2 * n + m) + n + 1) & ~(size_t)1; }
+
 struct FusedBufs {
   double* stL;     // [batch][N*ZS][NS]   state after tier 0, row-major rows
   double* stR;     // [batch][N*ZS][NS]
@@ -52,8 +54,47 @@ struct Dim {
   static constexpr int W = 2 * NS + 1;           // columns [L | R | z]
   static constexpr int WSZ = W * NS;             // one separator record [f_L | f_R | zs], column-major ld NS
   static constexpr int SLOT = ZS * NS;           // one block, row-major [ZS][NS]
-  static constexpr int ENT = 2 * SLOT + ZS + NS; // boundary entry: L rows, R rows, z, lambda-rhs of the first knot
+  // boundary entry: L rows, R rows, z, lambda-rhs of the first knot; padded to an even count so that entries stay
+  // 16-byte aligned for the TMA bulk copies
+  static constexpr int ENT = (2 * SLOT + ZS + NS + 1) & ~1;
 };
+
+// ---- TMA 1-D bulk copies (cp.async.bulk) and the mbarrier that tracks them ----
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, int bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, int parity) {
+  unsigned ok;
+  do {
+    asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(ok)
+                 : "r"(smem_u32(bar)), "r"(parity)
+                 : "memory");
+  } while (!ok);
+}
+// global -> shared, completion counted in bytes on `bar`; 16-byte aligned addresses, size a multiple of 16
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, int bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+// shared -> global as part of the thread's current bulk group
+__device__ __forceinline__ void bulk_s2g(void* dst, const void* src, int bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+// make generic-proxy writes to shared memory visible to the async proxy (TMA) before a bulk store
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 __device__ __forceinline__ double fast_rcp(double d) {
   double r;
@@ -237,7 +278,7 @@ __device__ __forceinline__ void schur_dmma_level(double* Ls, double* Rs, double*
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q = lane & 3, rr = lane >> 2;
   const int s = warp >> j;  // separator (local) of knot pair `warp` at level j
-  const double* Wf = W + s * D::WSZ;
+  const double* Wf = W + (s << j) * D::WSZ;  // records are indexed by the first warp of the subtree
   double bneg[KS][NT], zq[KS];
 #pragma unroll
   for (int ks = 0; ks < KS; ++ks) {
@@ -348,7 +389,7 @@ __device__ __forceinline__ void schur_dfma(double* Ls, double* Rs, double* zv, c
     const int side = (kn >> j) & 1;
     const int s = kn >> (j + 1);
     const bool special = (kn == ((2 * s + 1) << j)) && (row < NS);
-    schur_row<NS>(Ls + R * NS, Rs + R * NS, zv + R, W + s * D::WSZ, side, special, row);
+    schur_row<NS>(Ls + R * NS, Rs + R * NS, zv + R, W + (s << j) * D::WSZ, side, special, row);
   }
 }
 
@@ -371,8 +412,8 @@ template <int NS, int NI, int G, bool DMMA>
 __global__ void __launch_bounds__(16 * G, 512 / (16 * G)) tier0_kernel(Shape s, Bufs b, FusedBufs fb, int pack_rhs, int M0) {
   using D = Dim<NS, NI>;
   constexpr int ZS = D::ZS, SLOT = D::SLOT, WSZ = D::WSZ;
-  extern __shared__ double sm[];
-  double* Ls = sm;
+  extern __shared__ __align__(16) double smf[];
+  double* Ls = smf;
   double* Rs = Ls + G * SLOT;
   double* zv = Rs + G * SLOT;
   double* W = zv + G * ZS;
@@ -383,100 +424,117 @@ __global__ void __launch_bounds__(16 * G, 512 / (16 * G)) tier0_kernel(Shape s, 
   const int N = s.N;
 
   // ---- leaves: L(k) = F(k, lev(k-1)), R(k) = F(k, lev(k)) ----
-  // pass A: straight coalesced copies. [A_k | B_k] column-major is exactly [X rows | U rows] of A^T, B^T
-  // row-major, so it lands in R(k) unscaled; the small vectors Q,R,q,r,d go to a staging area inside W.
-  constexpr int VEC = 2 * NS + 2 * NI, STG = VEC + NS, AB = NS * (NS + NI);
-  static_assert(G * STG + NS <= (G / 2) * WSZ, "staging area must fit into W");
-  double* stg = W;               // [G][Q(NS) R(NI) q(NS) r(NI) d(NS)]
-  double* prevd = W + G * STG;   // d_{k0-1} (or x0 for the first group)
+  // pass A: one TMA bulk copy brings the group's G flat knot blocks (contiguous in HBM) into the L area,
+  // which is only needed (zeroed) after the leaves. [A_k | B_k] column-major is exactly [X rows | U rows] of
+  // (A_k^T, B_k^T) row-major, so R(k) is a row-scaled copy of it.
+  constexpr int VEC = 2 * NS + 2 * NI, AB = NS * (NS + NI);
+  constexpr int STRIDE = VEC + 1 + AB + NS;          // doubles per flat knot block (reference src/lqr_data.c:25-36)
+  constexpr int OA = VEC + 1, OD = OA + AB;
+  static_assert(STRIDE <= SLOT && (G * STRIDE) % 2 == 0, "raw knot blocks are staged in the L area");
+  static_assert(G * (NS + NI) + NS <= (G / 2) * WSZ, "reciprocals are staged in W");
+  __shared__ __align__(8) unsigned long long mbar;
+  double* raw = Ls;                    // [G][STRIDE]
+  double* inv = W;                     // [G][NS+NI]  1/Q, 1/R
+  double* prevd = W + G * (NS + NI);   // d_{k0-1} (or x0 for the first group)
   const double* kn0 = knot_ptr(s, b, prob, k0);
-  for (int idx = tid; idx < G * AB; idx += nthr) {
-    const int kl = idx / AB, e = idx - kl * AB;
-    Rs[kl * SLOT + NS * NS + e] = kn0[(size_t)kl * s.stride + s.oA + e];
+  if (tid == 0) {
+    mbar_init(&mbar, 1);
+    fence_mbar_init();
   }
-  for (int idx = tid; idx < G * VEC; idx += nthr) {
-    const int kl = idx / VEC, e = idx - kl * VEC;
-    stg[kl * STG + e] = kn0[(size_t)kl * s.stride + e];
+  __syncthreads();
+  if (tid == 0) {
+    mbar_expect_tx(&mbar, G * STRIDE * (int)sizeof(double));
+    bulk_g2s(raw, kn0, G * STRIDE * (int)sizeof(double), &mbar);
   }
-  for (int idx = tid; idx < G * NS; idx += nthr) {
-    const int kl = idx / NS, e = idx - kl * NS;
-    stg[kl * STG + VEC + e] = kn0[(size_t)kl * s.stride + s.od + e];
-  }
-  if (tid < NS) prevd[tid] = (k0 == 0) ? b.x0[(size_t)prob * NS + tid] : (kn0 - s.stride)[s.od + tid];
-  for (int idx = tid; idx < G * SLOT; idx += nthr) Ls[idx] = 0.0;
+  if (tid < NS) prevd[tid] = (k0 == 0) ? b.x0[(size_t)prob * NS + tid] : (kn0 - STRIDE)[OD + tid];
   for (int idx = tid; idx < G * NS * NS; idx += nthr) {
     const int kl = idx / (NS * NS), e = idx - kl * NS * NS;
     Rs[kl * SLOT + e] = 0.0;
   }
   const double* zin = soln_ptr(s, b, prob, k0);
-  __syncthreads();
-  // pass B: rhs (needs the raw Q of knot 0), then Q, R -> 1/Q, 1/R with the leaf "Cholesky" status
-  // (Q_k, R_k are diagonal: the factorization fails on an entry <= 0, reference src/linalg_custom.c:88)
+  mbar_wait(&mbar, 0);
+  __syncthreads();  // prevd
+  // pass B: rhs of the leaves (reference src/solver.c:138-190 for the packing, src/nested_dissection.c:45-59,
+  // 87-95 for the leaf solves) and 1/Q, 1/R with the leaf "Cholesky" status (Q_k, R_k are diagonal: the
+  // factorization fails on an entry <= 0, reference src/linalg_custom.c:88)
   for (int idx = tid; idx < G * ZS; idx += nthr) {
     const int kl = idx / ZS, row = idx - kl * ZS;
     const int k = k0 + kl;
-    const double* sv = stg + kl * STG;
-    auto raw = [&](int rw) -> double {  // entry rw of the negated rhs of knot k (reference src/solver.c:138-190)
+    const double* sv = raw + kl * STRIDE;
+    auto rhs = [&](int rw) -> double {  // entry rw of the negated rhs of knot k
       if (!pack_rhs) return zin[kl * ZS + rw];
-      if (rw < NS) return -(kl == 0 ? prevd[rw] : sv[rw - STG + VEC]);
+      if (rw < NS) return -(kl == 0 ? prevd[rw] : sv[rw - STRIDE + OD]);
       if (rw < 2 * NS) return -sv[NS + NI + rw - NS];
       return (k < N - 1) ? -sv[2 * NS + NI + rw - 2 * NS] : 0.0;
     };
     double v;
-    if (k == 0) {  // nested_dissection.c:45-59
-      if (row < NS) v = -sv[row] * raw(row) - raw(NS + row);
-      else if (row < 2 * NS) v = -raw(row - NS);
-      else v = raw(row) / sv[NS + row - 2 * NS];
+    if (k == 0) {
+      if (row < NS) v = -sv[row] * rhs(row) - rhs(NS + row);
+      else if (row < 2 * NS) v = -rhs(row - NS);
+      else v = rhs(row) / sv[NS + row - 2 * NS];
     } else {
-      if (row < NS) v = raw(row);
-      else if (row < 2 * NS) v = raw(row) / sv[row - NS];
-      else v = (k < N - 1) ? raw(row) / sv[NS + row - 2 * NS] : raw(row);
+      if (row < NS) v = rhs(row);
+      else if (row < 2 * NS) v = rhs(row) / sv[row - NS];
+      else v = (k < N - 1) ? rhs(row) / sv[NS + row - 2 * NS] : rhs(row);
     }
     zv[idx] = v;
   }
-  __syncthreads();
   for (int idx = tid; idx < G * (NS + NI); idx += nthr) {
     const int kl = idx / (NS + NI), i = idx - kl * (NS + NI);
     const int k = k0 + kl;
-    const double d = stg[kl * STG + i];
+    const double d = raw[kl * STRIDE + i];
     if (!(d > 0.0) && !(i >= NS && k == N - 1)) {
       b.status[(size_t)prob * 3 * N + (i < NS ? rs_slot_Q(k) : rs_slot_R(k))] = -1;
       b.flags[prob] = 1;
     }
-    stg[kl * STG + i] = 1.0 / d;
+    inv[idx] = 1.0 / d;
   }
   __syncthreads();
-  // pass C: row scalings. R(k): X = Q \ A^T, U = R \ B^T (nested_dissection.c:75-84); L(k): X = Q \ (-I) (:96-102);
-  // knot 0: Lambda = -A0^T, X = 0 (:31-36); last knot: R(k) = 0.
+  // pass C: R(k): X = Q \ A^T, U = R \ B^T (nested_dissection.c:75-84); knot 0: Lambda = -A0^T, X = 0 (:31-36);
+  // last knot: R(k) = 0
   for (int idx = tid; idx < G * AB; idx += nthr) {
     const int kl = idx / AB, e = idx - kl * AB;
-    const int row = e / NS;  // 0..NS+NI-1: X rows then U rows; stg holds 1/Q then 1/R in the same order
+    const int row = e / NS;  // 0..NS+NI-1: X rows then U rows, inv[] holds 1/Q then 1/R in the same order
     const int k = k0 + kl;
-    double* p = Rs + kl * SLOT + NS * NS + e;
-    const double rawv = *p;
-    double v = rawv * stg[kl * STG + row];
+    const double rawv = raw[kl * STRIDE + OA + e];
+    double v = rawv * inv[kl * (NS + NI) + row];
     if (k == N - 1) v = 0.0;
     if (k == 0 && row < NS) { Rs[kl * SLOT + e] = -rawv; v = 0.0; }
-    *p = v;
+    Rs[kl * SLOT + NS * NS + e] = v;
   }
+  __syncthreads();
+  // pass D: L(k): X = Q \ (-I) (:96-102), everything else zero (this also retires the raw staging)
+  for (int idx = tid; idx < G * SLOT / 2; idx += nthr) reinterpret_cast<double2*>(Ls)[idx] = make_double2(0.0, 0.0);
+  __syncthreads();
   for (int idx = tid; idx < G * NS; idx += nthr) {
     const int kl = idx / NS, i = idx - kl * NS;
-    if (k0 + kl > 0) Ls[kl * SLOT + (NS + i) * NS + i] = -stg[kl * STG + i];
+    if (k0 + kl > 0) Ls[kl * SLOT + (NS + i) * NS + i] = -inv[kl * (NS + NI) + i];
   }
 
   // ---- levels ----
+  // The level-j merge of subtree t only involves the 2^j warps that own its knot pairs, so (DMMA path, where a
+  // warp owns a knot pair) the warps of a subtree meet on their own named barrier instead of the CTA barrier;
+  // level 0 needs none at all (warp w runs the spine of separator w and then updates its own pair).
+  // The spine warp of a subtree is its first warp, and W is indexed by that warp.
   int g = 0;
   while ((1 << g) < G) ++g;
+  __syncthreads();
+  int barid = 1;
   for (int j = 0; j < g; ++j) {
-    __syncthreads();
-    const int nsep = G >> (j + 1);
-    if (warp < nsep) {
-      const int il = ((2 * warp + 1) << j) - 1;  // local index of the separator knot i
+    const int t = warp >> j;                 // subtree of this warp at level j
+    const int w0 = t << j;                   // its first warp = spine warp
+    const int nsub = (G / 2) >> j;           // subtrees at this level
+    const bool local = DMMA && (nsub > 1);   // barrier scope: subtree (named) or CTA
+    if (j > 0) {
+      if (local) bar_sync(barid + t, 32 << j); else __syncthreads();
+    }
+    if (warp == w0) {
+      const int il = ((2 * t + 1) << j) - 1;  // local index of the separator knot i
       const double* AB = knot_ptr(s, b, prob, k0 + il) + s.oA;
       double* Lsm = Ls + (il + 1) * SLOT;  // Lambda rows of knot i+1: still zero, used as scratch
       const int bad = spine_merge<NS, NI>(AB, Ls + il * SLOT + NS * NS, Rs + il * SLOT + NS * NS, zv + il * ZS + NS,
                                           Ls + (il + 1) * SLOT + NS * NS, Rs + (il + 1) * SLOT + NS * NS,
-                                          zv + (il + 1) * ZS + NS, zv + (il + 1) * ZS, Lsm, W + warp * WSZ);
+                                          zv + (il + 1) * ZS + NS, zv + (il + 1) * ZS, Lsm, W + w0 * WSZ);
       for (int e = lane; e < NS * NS; e += 32) Lsm[e] = 0.0;
       if (bad && lane == 0) {
         const int i = k0 + il;
@@ -484,28 +542,26 @@ __global__ void __launch_bounds__(16 * G, 512 / (16 * G)) tier0_kernel(Shape s, 
         b.flags[prob] = 1;
       }
     }
-    __syncthreads();
+    if (j == 0 && DMMA) __syncwarp();
+    else if (local) bar_sync(barid + t, 32 << j);
+    else __syncthreads();
+    if (j > 0) barid += nsub;  // ids are unique per (level, subtree): a warp may run ahead into the next level
     if constexpr (DMMA) schur_dmma<NS, NI>(Ls, Rs, zv, W, j);
     else schur_dfma<NS, NI, G>(Ls, Rs, zv, W, j);
   }
   __syncthreads();
 
-  // ---- output ----
+  // ---- output: TMA bulk stores straight out of shared memory ----
   if (M0 == 1) {
     double* out = soln_ptr(s, b, prob, 0);
     for (int idx = tid; idx < G * ZS; idx += nthr) out[idx] = zv[idx];
     return;
   }
   {
-    const size_t base = ((size_t)prob * N + k0) * ZS;
-    double2* oL = reinterpret_cast<double2*>(fb.stL + base * NS);
-    double2* oR = reinterpret_cast<double2*>(fb.stR + base * NS);
-    const double2* iL = reinterpret_cast<const double2*>(Ls);
-    const double2* iR = reinterpret_cast<const double2*>(Rs);
-    for (int idx = tid; idx < G * SLOT / 2; idx += nthr) { oL[idx] = iL[idx]; oR[idx] = iR[idx]; }
-    for (int idx = tid; idx < G * ZS; idx += nthr) fb.stz[base + idx] = zv[idx];
-    // boundary entry: rows [X(first knot) | X,U(last knot)] of L, R, z and the lambda-rhs of the first knot
-    double* en = fb.ent[0] + ((size_t)prob * M0 + grp) * D::ENT;
+    // boundary entry: rows [X(first knot) | X,U(last knot)] of L, R, z and the lambda-rhs of the first knot,
+    // gathered into W (free after the last level)
+    static_assert(D::ENT <= (G / 2) * WSZ, "entry is staged in W");
+    double* en = W;
     for (int idx = tid; idx < SLOT; idx += nthr) {
       const int er = idx / NS, c = idx - er * NS;
       const int lr = er < NS ? NS + er : (G - 1) * ZS + er;
@@ -514,6 +570,17 @@ __global__ void __launch_bounds__(16 * G, 512 / (16 * G)) tier0_kernel(Shape s, 
     }
     for (int er = tid; er < ZS; er += nthr) en[2 * SLOT + er] = zv[er < NS ? NS + er : (G - 1) * ZS + er];
     for (int c = tid; c < NS; c += nthr) en[2 * SLOT + ZS + c] = zv[c];
+    fence_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      const size_t base = ((size_t)prob * N + k0) * ZS;
+      bulk_s2g(fb.stL + base * NS, Ls, G * SLOT * (int)sizeof(double));
+      bulk_s2g(fb.stR + base * NS, Rs, G * SLOT * (int)sizeof(double));
+      bulk_s2g(fb.stz + base, zv, G * ZS * (int)sizeof(double));
+      bulk_s2g(fb.ent[0] + ((size_t)prob * M0 + grp) * D::ENT, en, D::ENT * (int)sizeof(double));
+      bulk_commit();
+      bulk_wait_read0();  // shared memory must stay valid until the copy engine has read it
+    }
   }
 }
 
@@ -532,7 +599,8 @@ __global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, FusedBufs
   using D = Dim<NS, NI>;
   constexpr int ZS = D::ZS, SLOT = D::SLOT, WSZ = D::WSZ, ENT = D::ENT;
   static_assert(ZS <= 32, "lean Schur update maps one row per lane");
-  extern __shared__ double sm[];
+  extern __shared__ __align__(16) double smf[];
+  double* sm = smf;
   const int tid = threadIdx.x, nthr = blockDim.x;
   const int warp = tid >> 5, lane = tid & 31, nwarp = nthr >> 5;
   const int ncta = Min / ecount;
@@ -542,7 +610,17 @@ __global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, FusedBufs
   double* Wall = ents + ecount * ENT;
   double* Lall = Wall + nwarp * WSZ;
   const double* in = fb.ent[tier - 1] + ((size_t)prob * Min + (size_t)sg * ecount) * ENT;
-  for (int idx = tid; idx < ecount * ENT; idx += nthr) ents[idx] = in[idx];
+  __shared__ __align__(8) unsigned long long mbar;
+  if (tid == 0) {
+    mbar_init(&mbar, 1);
+    fence_mbar_init();
+  }
+  __syncthreads();
+  if (tid == 0) {  // one TMA bulk copy: the CTA's entries are contiguous in HBM
+    mbar_expect_tx(&mbar, ecount * ENT * (int)sizeof(double));
+    bulk_g2s(ents, in, ecount * ENT * (int)sizeof(double), &mbar);
+  }
+  mbar_wait(&mbar, 0);
   int levels = 0;
   while ((1 << levels) < ecount) ++levels;
   for (int l = 0; l < levels; ++l) {
@@ -684,7 +762,7 @@ inline int fused_plan(const Shape& s, int batch, int g0_pref, FusedPlan* p, std:
   }
   if (p->M0 > 1) {
     const size_t zs = s.zs, n = s.n;
-    const size_t ent = 2 * zs * n + zs + n, wsz = (2 * n + 1) * n;
+    const size_t ent = fused_ent_doubles(s.n, s.m), wsz = (2 * n + 1) * n;
     auto alloc = [&](double** ptr, size_t cnt) {
       p->bytes += cnt * sizeof(double);
       return cudaMalloc((void**)ptr, cnt * sizeof(double)) == cudaSuccess;

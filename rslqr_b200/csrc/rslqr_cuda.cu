@@ -315,7 +315,7 @@ extern "C" int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs) {
     b.status += f * 3 * s.N; b.flags += f; b.leafd += f * s.N * (s.n + s.m);
     FusedPlan q = h->fused;
     if (q.M0 > 1) {
-      const size_t ent = 2 * (size_t)s.zs * s.n + s.zs + s.n, wsz = (2 * (size_t)s.n + 1) * s.n;
+      const size_t ent = fused_ent_doubles(s.n, s.m), wsz = (2 * (size_t)s.n + 1) * s.n;
       q.fb.stL += f * s.N * s.zs * s.n; q.fb.stR += f * s.N * s.zs * s.n; q.fb.stz += f * s.N * s.zs;
       q.fb.sep += f * q.M0 * wsz; q.fb.lamhat += f * (q.M0 + 1) * s.n;
       for (int t = 0; t < q.ntiers; ++t) q.fb.ent[t] += f * q.tiers[t].Min * ent;
