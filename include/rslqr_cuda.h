@@ -138,6 +138,22 @@ double rslqr_cuda_elapsed_ms(rslqr_cuda_solver* h, int slot_a, int slot_b);
 int rslqr_cuda_upload_async(rslqr_cuda_solver* h, const double* knots, const double* x0, int first, int count);
 int rslqr_cuda_download_solution_async(rslqr_cuda_solver* h, double* soln, int first, int count);
 
+/* ---- one long horizon split over GPUs (BASELINE configs[3]): shard r owns knots [first_knot, first_knot+shard_knots)
+ * of a horizon of `nhorizon` knots. Upload as usual (knots = the shard's knot blocks, x0 = x0 for the first shard, else
+ * d of the knot before the shard). Solve = shard_reduce (leaves + all local levels -> one boundary entry + [A|B] of the
+ * last knot in d_payload) ; all-gather of the payloads over NVLink (NCCL by the caller, or rslqr_cuda_shard_exchange
+ * within one process) ; shard_finish (the top log2(nranks) separator levels on the gathered entries, redundantly on
+ * every rank, then the local top-down pass and rhs propagation). All asynchronous on the handle's stream.
+ * Replaces the top levels of the reference's loop, src/solve.c:68-182, which has no distributed form. */
+int rslqr_cuda_create_shard(int nstates, int ninputs, int nhorizon, int first_knot, int shard_knots, int device,
+                            unsigned flags, rslqr_cuda_solver** out);
+size_t rslqr_cuda_shard_payload_doubles(rslqr_cuda_solver* h);
+int rslqr_cuda_shard_reduce(rslqr_cuda_solver* h, double* d_payload);
+int rslqr_cuda_shard_finish(rslqr_cuda_solver* h, const double* d_gathered, int rank, int nranks);
+int rslqr_cuda_shard_exchange(rslqr_cuda_solver** hs, int nranks, double** d_payload, double** d_gathered);
+/* enqueue on a caller-owned cudaStream_t (e.g. the stream NCCL collectives are ordered on) */
+int rslqr_cuda_set_stream(rslqr_cuda_solver* h, void* stream);
+
 /* pinned host memory helpers so that callers can stage uploads at full PCIe rate */
 void* rslqr_cuda_host_alloc(size_t bytes);
 void rslqr_cuda_host_free(void* p);

@@ -421,7 +421,7 @@ __global__ void __launch_bounds__(16 * G, 512 / (16 * G)) tier0_kernel(Shape s, 
   const int warp = tid >> 5, lane = tid & 31;
   const int prob = blockIdx.x / M0, grp = blockIdx.x % M0;
   const int k0 = grp * G;
-  const int N = s.N;
+  const int N = s.N, Ng = s.Ng;
 
   // ---- leaves: L(k) = F(k, lev(k-1)), R(k) = F(k, lev(k)) ----
   // pass A: one TMA bulk copy brings the group's G flat knot blocks (contiguous in HBM) into the L area,
@@ -446,6 +446,7 @@ __global__ void __launch_bounds__(16 * G, 512 / (16 * G)) tier0_kernel(Shape s, 
     mbar_expect_tx(&mbar, G * STRIDE * (int)sizeof(double));
     bulk_g2s(raw, kn0, G * STRIDE * (int)sizeof(double), &mbar);
   }
+  // lambda-rhs of the group's first knot: x0 (or, for a shard, d of the knot before it) travels in b.x0
   if (tid < NS) prevd[tid] = (k0 == 0) ? b.x0[(size_t)prob * NS + tid] : (kn0 - STRIDE)[OD + tid];
   for (int idx = tid; idx < G * NS * NS; idx += nthr) {
     const int kl = idx / (NS * NS), e = idx - kl * NS * NS;
@@ -460,30 +461,32 @@ __global__ void __launch_bounds__(16 * G, 512 / (16 * G)) tier0_kernel(Shape s, 
   for (int idx = tid; idx < G * ZS; idx += nthr) {
     const int kl = idx / ZS, row = idx - kl * ZS;
     const int k = k0 + kl;
+    const int kg = s.kofs + k;  // global knot index (shards)
     const double* sv = raw + kl * STRIDE;
     auto rhs = [&](int rw) -> double {  // entry rw of the negated rhs of knot k
       if (!pack_rhs) return zin[kl * ZS + rw];
       if (rw < NS) return -(kl == 0 ? prevd[rw] : sv[rw - STRIDE + OD]);
       if (rw < 2 * NS) return -sv[NS + NI + rw - NS];
-      return (k < N - 1) ? -sv[2 * NS + NI + rw - 2 * NS] : 0.0;
+      return (kg < Ng - 1) ? -sv[2 * NS + NI + rw - 2 * NS] : 0.0;
     };
     double v;
-    if (k == 0) {
+    if (kg == 0) {
       if (row < NS) v = -sv[row] * rhs(row) - rhs(NS + row);
       else if (row < 2 * NS) v = -rhs(row - NS);
       else v = rhs(row) / sv[NS + row - 2 * NS];
     } else {
       if (row < NS) v = rhs(row);
       else if (row < 2 * NS) v = rhs(row) / sv[row - NS];
-      else v = (k < N - 1) ? rhs(row) / sv[NS + row - 2 * NS] : rhs(row);
+      else v = (kg < Ng - 1) ? rhs(row) / sv[NS + row - 2 * NS] : rhs(row);
     }
     zv[idx] = v;
   }
   for (int idx = tid; idx < G * (NS + NI); idx += nthr) {
     const int kl = idx / (NS + NI), i = idx - kl * (NS + NI);
     const int k = k0 + kl;
+    const int kg = s.kofs + k;  // global knot index (shards)
     const double d = raw[kl * STRIDE + i];
-    if (!(d > 0.0) && !(i >= NS && k == N - 1)) {
+    if (!(d > 0.0) && !(i >= NS && kg == Ng - 1)) {
       b.status[(size_t)prob * 3 * N + (i < NS ? rs_slot_Q(k) : rs_slot_R(k))] = -1;
       b.flags[prob] = 1;
     }
@@ -496,10 +499,11 @@ __global__ void __launch_bounds__(16 * G, 512 / (16 * G)) tier0_kernel(Shape s, 
     const int kl = idx / AB, e = idx - kl * AB;
     const int row = e / NS;  // 0..NS+NI-1: X rows then U rows, inv[] holds 1/Q then 1/R in the same order
     const int k = k0 + kl;
+    const int kg = s.kofs + k;  // global knot index (shards)
     const double rawv = raw[kl * STRIDE + OA + e];
     double v = rawv * inv[kl * (NS + NI) + row];
-    if (k == N - 1) v = 0.0;
-    if (k == 0 && row < NS) { Rs[kl * SLOT + e] = -rawv; v = 0.0; }
+    if (kg == Ng - 1) v = 0.0;
+    if (kg == 0 && row < NS) { Rs[kl * SLOT + e] = -rawv; v = 0.0; }
     Rs[kl * SLOT + NS * NS + e] = v;
   }
   __syncthreads();
@@ -508,7 +512,7 @@ __global__ void __launch_bounds__(16 * G, 512 / (16 * G)) tier0_kernel(Shape s, 
   __syncthreads();
   for (int idx = tid; idx < G * NS; idx += nthr) {
     const int kl = idx / NS, i = idx - kl * NS;
-    if (k0 + kl > 0) Ls[kl * SLOT + (NS + i) * NS + i] = -inv[kl * (NS + NI) + i];
+    if (s.kofs + k0 + kl > 0) Ls[kl * SLOT + (NS + i) * NS + i] = -inv[kl * (NS + NI) + i];
   }
 
   // ---- levels ----
@@ -594,8 +598,25 @@ __global__ void __launch_bounds__(16 * G, 512 / (16 * G)) tier0_kernel(Shape s, 
 // `span` = knots per input entry; warps = max(1, ecount/2).
 // dynamic smem: (ecount*ENT + warps*(WSZ + NS*NS)) doubles.
 // ---------------------------------------------------------------------------------------------------------
+// Where a tier reads and writes; lets the same kernel run the local tiers of a problem, the last local tier of
+// a shard (merged entry goes to the exchange payload) and the cross-GPU tier (entries, [A|B] blocks and records
+// live in the gathered payload buffer).
+struct TierArgs {
+  const double* in;        // entry e of problem p: in + (p*Min + e)*in_stride
+  long long in_stride;
+  const double* ab;        // [A|B] of the last knot of entry e: ab + p*ab_pstride + e*ab_stride
+  long long ab_stride, ab_pstride;
+  double* sep;             // record of the separator between entries e and e+1: sep + p*sep_pstride + (e+1)*sep_mul*WSZ
+  long long sep_pstride;
+  int sep_mul;
+  double* out;             // merged entry of CTA c of problem p: out + (p*ncta + c)*out_stride; nullptr = none
+  long long out_stride;
+  int Min, ecount;
+  int span;                // knots per input entry (status words only; 0 = cross-GPU tier, flags only)
+};
+
 template <int NS, int NI>
-__global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, FusedBufs fb, int tier, int Min, int ecount, int span, int G0) {
+__global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, TierArgs a) {
   using D = Dim<NS, NI>;
   constexpr int ZS = D::ZS, SLOT = D::SLOT, WSZ = D::WSZ, ENT = D::ENT;
   static_assert(ZS <= 32, "lean Schur update maps one row per lane");
@@ -603,22 +624,24 @@ __global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, FusedBufs
   double* sm = smf;
   const int tid = threadIdx.x, nthr = blockDim.x;
   const int warp = tid >> 5, lane = tid & 31, nwarp = nthr >> 5;
-  const int ncta = Min / ecount;
+  const int ecount = a.ecount;
+  const int ncta = a.Min / ecount;
   const int prob = blockIdx.x / ncta, sg = blockIdx.x % ncta;
-  const int M0 = s.N / G0;
   double* ents = sm;
   double* Wall = ents + ecount * ENT;
   double* Lall = Wall + nwarp * WSZ;
-  const double* in = fb.ent[tier - 1] + ((size_t)prob * Min + (size_t)sg * ecount) * ENT;
+  const double* in = a.in + ((size_t)prob * a.Min + (size_t)sg * ecount) * a.in_stride;
   __shared__ __align__(8) unsigned long long mbar;
   if (tid == 0) {
     mbar_init(&mbar, 1);
     fence_mbar_init();
   }
   __syncthreads();
-  if (tid == 0) {  // one TMA bulk copy: the CTA's entries are contiguous in HBM
+  if (tid == 0) {  // TMA bulk copies (one when the CTA's entries are contiguous in HBM)
     mbar_expect_tx(&mbar, ecount * ENT * (int)sizeof(double));
-    bulk_g2s(ents, in, ecount * ENT * (int)sizeof(double), &mbar);
+    if (a.in_stride == ENT) bulk_g2s(ents, in, ecount * ENT * (int)sizeof(double), &mbar);
+    else
+      for (int e = 0; e < ecount; ++e) bulk_g2s(ents + e * ENT, in + e * a.in_stride, ENT * (int)sizeof(double), &mbar);
   }
   mbar_wait(&mbar, 0);
   int levels = 0;
@@ -629,19 +652,22 @@ __global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, FusedBufs
     if (warp < nsep) {
       const int el = ((2 * warp + 1) << l) - 1, er = el + 1;
       const int ea = (2 * warp) << l, eb = er + (1 << l) - 1;
-      const int i = (sg * ecount + el + 1) * span - 1;  // global knot index of the separator
-      const double* AB = knot_ptr(s, b, prob, i) + s.oA;
+      const int ge = sg * ecount + el;  // entry index within the problem; the separator sits right after it
+      const double* AB = a.ab + (size_t)prob * a.ab_pstride + (size_t)ge * a.ab_stride;
       double* El = ents + el * ENT;
       double* Er = ents + er * ENT;
       double* Wf = Wall + warp * WSZ;
       const int bad = spine_merge<NS, NI>(AB, El + NS * NS, El + SLOT + NS * NS, El + 2 * SLOT + NS, Er, Er + SLOT,
                                           Er + 2 * SLOT, Er + 2 * SLOT + ZS, Lall + warp * NS * NS, Wf);
-      double* rec = fb.sep + ((size_t)prob * M0 + (i + 1) / G0) * WSZ;
+      double* rec = a.sep + (size_t)prob * a.sep_pstride + (size_t)(ge + 1) * a.sep_mul * WSZ;
       for (int e = lane; e < WSZ; e += 32) rec[e] = Wf[e];
       if (bad && lane == 0) {
-        int lev = 0;
-        while ((i >> lev) & 1) ++lev;
-        b.status[(size_t)prob * 3 * s.N + rs_slot_S(i >> (lev + 1), lev, s.N)] = -1;
+        if (a.span > 0) {
+          const int i = (ge + 1) * a.span - 1;  // local knot index of the separator
+          int lev = 0;
+          while ((i >> lev) & 1) ++lev;
+          b.status[(size_t)prob * 3 * s.N + rs_slot_S(i >> (lev + 1), lev, s.N)] = -1;
+        }
         b.flags[prob] = 1;
       }
       if (lane < ZS) {
@@ -651,8 +677,8 @@ __global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, FusedBufs
     }
   }
   __syncthreads();
-  if (ncta > 1) {  // not the top tier: hand the merged entry up
-    double* out = fb.ent[tier] + ((size_t)prob * ncta + sg) * ENT;
+  if (a.out) {  // hand the merged entry up: rows X(a) from the first entry, X,U(b) from the last
+    double* out = a.out + ((size_t)prob * ncta + sg) * a.out_stride;
     const double* E0 = ents;
     const double* E1 = ents + (ecount - 1) * ENT;
     for (int idx = tid; idx < SLOT; idx += nthr) {
@@ -672,12 +698,16 @@ __global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, FusedBufs
 // Slots 0 and M0 of fb.lamhat hold zeros (no separator outside the horizon). One CTA per problem.
 // ---------------------------------------------------------------------------------------------------------
 template <int NS>
-__global__ void topdown_kernel(FusedBufs fb, int M0) {
+__global__ void topdown_kernel(const double* sep_all, double* lam_all, int M0, const double* left, const double* right) {
+  // left/right: multipliers of the separators bounding the range (a shard's neighbours), nullptr = none
   constexpr int WSZ = (2 * NS + 1) * NS;
   const int prob = blockIdx.x;
-  double* lam = fb.lamhat + (size_t)prob * (M0 + 1) * NS;
-  const double* sep = fb.sep + (size_t)prob * M0 * WSZ;
-  if (threadIdx.x < NS) { lam[threadIdx.x] = 0.0; lam[M0 * NS + threadIdx.x] = 0.0; }
+  double* lam = lam_all + (size_t)prob * (M0 + 1) * NS;
+  const double* sep = sep_all + (size_t)prob * M0 * WSZ;
+  if (threadIdx.x < NS) {
+    lam[threadIdx.x] = left ? left[(size_t)prob * NS + threadIdx.x] : 0.0;
+    lam[M0 * NS + threadIdx.x] = right ? right[(size_t)prob * NS + threadIdx.x] : 0.0;
+  }
   int T = 0;
   while ((1 << T) < M0) ++T;
   for (int t = T - 1; t >= 0; --t) {
@@ -725,7 +755,7 @@ __global__ void finalize_kernel(Shape s, Bufs b, FusedBufs fb, int G0, int M0, l
     v = fma(-r2.x, lb[2 * c], v);
     v = fma(-r2.y, lb[2 * c + 1], v);
   }
-  if (row < NS && k > 0 && k == grp * G0) v = la[row];
+  if (row < NS && s.kofs + k > 0 && k == grp * G0) v = la[row];
   b.soln[gid] = v;
 }
 
@@ -738,6 +768,8 @@ struct FusedPlan {
   int ns, ni, G0, M0, ntiers, use_dmma;
   FusedTier tiers[8];
   FusedBufs fb;
+  double* xsep;   // [8][WSZ]  records of the cross-GPU separators (shards)
+  double* xlam;   // [9][NS]   their final multipliers, slots 0 and G zero
   size_t bytes;
   int launches;
 };
@@ -771,6 +803,7 @@ inline int fused_plan(const Shape& s, int batch, int g0_pref, FusedPlan* p, std:
               alloc(&p->fb.stz, (size_t)batch * s.N * zs) && alloc(&p->fb.sep, (size_t)batch * p->M0 * wsz) &&
               alloc(&p->fb.lamhat, (size_t)batch * (p->M0 + 1) * n);
     for (int t = 0; ok && t < p->ntiers; ++t) ok = alloc(&p->fb.ent[t], (size_t)batch * p->tiers[t].Min * ent);
+    ok = ok && alloc(&p->xsep, 8 * wsz) && alloc(&p->xlam, 9 * n);
     if (!ok) {
       cudaGetLastError();
       err = "device allocation for the tiered path failed";
@@ -784,6 +817,7 @@ inline int fused_plan(const Shape& s, int batch, int g0_pref, FusedPlan* p, std:
 inline void fused_free(FusedPlan* p) {
   cudaFree(p->fb.stL); cudaFree(p->fb.stR); cudaFree(p->fb.stz); cudaFree(p->fb.sep); cudaFree(p->fb.lamhat);
   for (int t = 0; t < 8; ++t) cudaFree(p->fb.ent[t]);
+  cudaFree(p->xsep); cudaFree(p->xlam);
   memset(p, 0, sizeof(*p));
 }
 
@@ -801,29 +835,66 @@ inline cudaError_t launch_tier0(const FusedPlan& p, const Shape& s, const Bufs& 
 }
 
 template <int NS, int NI>
-inline cudaError_t launch_upper(FusedPlan& p, const Shape& s, const Bufs& b, int batch, cudaStream_t st) {
+inline cudaError_t tier_attr() {
   using D = Dim<NS, NI>;
+  static bool attr_done = false;
+  if (attr_done) return cudaSuccess;
+  cudaError_t e = cudaFuncSetAttribute(tier_kernel<NS, NI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (8 * D::ENT + 4 * (D::WSZ + NS * NS)) * (int)sizeof(double));
+  if (e == cudaSuccess) attr_done = true;
+  return e;
+}
+
+template <int NS, int NI>
+inline void launch_tier(const Shape& s, const Bufs& b, const TierArgs& a, int batch, cudaStream_t st) {
+  using D = Dim<NS, NI>;
+  const int warps = a.ecount / 2 > 0 ? a.ecount / 2 : 1;
+  const int smem = (a.ecount * D::ENT + warps * (D::WSZ + NS * NS)) * (int)sizeof(double);
+  tier_kernel<NS, NI><<<(unsigned)((size_t)batch * (a.Min / a.ecount)), 32 * warps, smem, st>>>(s, b, a);
+}
+
+// tiers >= 1 of the local tree. `last_out`: where the last tier puts its merged entry (shards), nullptr = nowhere.
+template <int NS, int NI>
+inline cudaError_t launch_tiers(FusedPlan& p, const Shape& s, const Bufs& b, int batch, cudaStream_t st,
+                                double* last_out, long long last_out_stride) {
+  using D = Dim<NS, NI>;
+  cudaError_t e = tier_attr<NS, NI>();
+  if (e != cudaSuccess) return e;
   for (int t = 0; t < p.ntiers; ++t) {
     const FusedTier& T = p.tiers[t];
-    const int warps = T.ecount / 2 > 0 ? T.ecount / 2 : 1;
-    const int smem = (T.ecount * D::ENT + warps * (D::WSZ + NS * NS)) * (int)sizeof(double);
-    static bool attr_done = false;
-    if (!attr_done) {
-      cudaError_t e = cudaFuncSetAttribute(tier_kernel<NS, NI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (8 * D::ENT + 4 * (D::WSZ + NS * NS)) * (int)sizeof(double));
-      if (e != cudaSuccess) return e;
-      attr_done = true;
-    }
-    tier_kernel<NS, NI><<<(unsigned)((size_t)batch * (T.Min / T.ecount)), 32 * warps, smem, st>>>(
-        s, b, p.fb, t + 1, T.Min, T.ecount, T.span, p.G0);
+    TierArgs a;
+    a.in = p.fb.ent[t]; a.in_stride = D::ENT;
+    a.ab = b.knots + (size_t)(T.span - 1) * s.stride + s.oA; a.ab_stride = (long long)T.span * s.stride;
+    a.ab_pstride = (long long)s.N * s.stride;
+    a.sep = p.fb.sep; a.sep_pstride = (long long)p.M0 * D::WSZ; a.sep_mul = T.span / p.G0;
+    const bool last = t == p.ntiers - 1;
+    a.out = last ? last_out : p.fb.ent[t + 1];
+    a.out_stride = last ? last_out_stride : D::ENT;
+    a.Min = T.Min; a.ecount = T.ecount; a.span = T.span;
+    launch_tier<NS, NI>(s, b, a, batch, st);
     ++p.launches;
   }
-  topdown_kernel<NS><<<batch, 128, 0, st>>>(p.fb, p.M0);
+  return cudaGetLastError();
+}
+
+// top-down over the local upper separators + finalize. left/right: multipliers of the neighbouring separators.
+template <int NS, int NI>
+inline cudaError_t launch_down(FusedPlan& p, const Shape& s, const Bufs& b, int batch, cudaStream_t st,
+                               const double* left, const double* right) {
+  using D = Dim<NS, NI>;
+  topdown_kernel<NS><<<batch, 128, 0, st>>>(p.fb.sep, p.fb.lamhat, p.M0, left, right);
   ++p.launches;
   const long long rows = (long long)batch * s.N * D::ZS;
   finalize_kernel<NS, NI><<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(s, b, p.fb, p.G0, p.M0, rows);
   ++p.launches;
   return cudaGetLastError();
+}
+
+template <int NS, int NI>
+inline cudaError_t launch_upper(FusedPlan& p, const Shape& s, const Bufs& b, int batch, cudaStream_t st) {
+  cudaError_t e = launch_tiers<NS, NI>(p, s, b, batch, st, nullptr, 0);
+  if (e != cudaSuccess) return e;
+  return launch_down<NS, NI>(p, s, b, batch, st, nullptr, nullptr);
 }
 
 // Whole solve of `batch` problems on stream `st`. force_dfma != 0 selects the DFMA Schur update for A/B tests.
@@ -846,6 +917,72 @@ inline int fused_launch(FusedPlan& p, const Shape& s, const Bufs& b, int batch, 
     if (e == cudaSuccess && p.M0 > 1) e = launch_upper<6, 3>(p, s, b, batch, st);
   }
   if (e != cudaSuccess) { err = std::string("tiered launch: ") + cudaGetErrorString(e); return -3; }
+  return 0;
+}
+
+// ---- shards of one long horizon (one per GPU): reduce -> exchange (caller) -> finish ----
+inline size_t fused_payload_doubles(int n, int m) { return fused_ent_doubles(n, m) + (((size_t)n * (n + m) + 1) & ~(size_t)1); }
+
+template <int NS, int NI>
+inline cudaError_t shard_reduce_t(FusedPlan& p, const Shape& s, const Bufs& b, int pack_rhs, int force_dfma, cudaStream_t st,
+                                  double* payload) {
+  using D = Dim<NS, NI>;
+  const bool dm = p.use_dmma && !force_dfma;
+  cudaError_t e;
+  if constexpr (NS == 12) {
+    if (p.G0 == 16) e = dm ? launch_tier0<NS, NI, 16, true>(p, s, b, 1, pack_rhs, st) : launch_tier0<NS, NI, 16, false>(p, s, b, 1, pack_rhs, st);
+    else e = dm ? launch_tier0<NS, NI, 8, true>(p, s, b, 1, pack_rhs, st) : launch_tier0<NS, NI, 8, false>(p, s, b, 1, pack_rhs, st);
+  } else {
+    e = p.G0 == 16 ? launch_tier0<NS, NI, 16, false>(p, s, b, 1, pack_rhs, st) : launch_tier0<NS, NI, 8, false>(p, s, b, 1, pack_rhs, st);
+  }
+  if (e != cudaSuccess) return e;
+  p.launches = 1;
+  e = launch_tiers<NS, NI>(p, s, b, 1, st, payload, (long long)fused_payload_doubles(NS, NI));
+  if (e != cudaSuccess) return e;
+  // [A|B] of the shard's last knot rides along: the neighbour's merge needs it (ndlqr_FactorInnerProduct)
+  return cudaMemcpyAsync(payload + D::ENT, b.knots + (size_t)(s.N - 1) * s.stride + s.oA, sizeof(double) * NS * (NS + NI),
+                         cudaMemcpyDeviceToDevice, st);
+}
+
+template <int NS, int NI>
+inline cudaError_t shard_finish_t(FusedPlan& p, const Shape& s, const Bufs& b, cudaStream_t st, const double* gathered,
+                                  int rank, int nranks) {
+  using D = Dim<NS, NI>;
+  const double *left = nullptr, *right = nullptr;
+  if (nranks > 1) {
+    cudaError_t e = tier_attr<NS, NI>();
+    if (e != cudaSuccess) return e;
+    TierArgs a;
+    const long long pay = (long long)fused_payload_doubles(NS, NI);
+    a.in = gathered; a.in_stride = pay;
+    a.ab = gathered + D::ENT; a.ab_stride = pay; a.ab_pstride = 0;
+    a.sep = p.xsep; a.sep_pstride = 0; a.sep_mul = 1;
+    a.out = nullptr; a.out_stride = 0;
+    a.Min = nranks; a.ecount = nranks; a.span = 0;
+    launch_tier<NS, NI>(s, b, a, 1, st);  // every rank runs the top log2(nranks) levels redundantly, bit-identically
+    topdown_kernel<NS><<<1, 128, 0, st>>>(p.xsep, p.xlam, nranks, nullptr, nullptr);
+    p.launches += 2;
+    left = p.xlam + (size_t)rank * NS;
+    right = p.xlam + (size_t)(rank + 1) * NS;
+  }
+  return launch_down<NS, NI>(p, s, b, 1, st, left, right);
+}
+
+inline int fused_shard_reduce(FusedPlan& p, const Shape& s, const Bufs& b, int pack_rhs, int force_dfma, cudaStream_t st,
+                              double* payload, std::string& err) {
+  if (!p.available || p.ntiers < 1) { err = "shard needs the tiered kernels and at least two groups of knots"; return -5; }
+  cudaError_t e = s.n == 12 ? shard_reduce_t<12, 4>(p, s, b, pack_rhs, force_dfma, st, payload)
+                            : shard_reduce_t<6, 3>(p, s, b, pack_rhs, force_dfma, st, payload);
+  if (e != cudaSuccess) { err = std::string("shard reduce: ") + cudaGetErrorString(e); return -3; }
+  return 0;
+}
+
+inline int fused_shard_finish(FusedPlan& p, const Shape& s, const Bufs& b, cudaStream_t st, const double* gathered, int rank,
+                              int nranks, std::string& err) {
+  if (!p.available || p.ntiers < 1) { err = "shard needs the tiered kernels"; return -5; }
+  cudaError_t e = s.n == 12 ? shard_finish_t<12, 4>(p, s, b, st, gathered, rank, nranks)
+                            : shard_finish_t<6, 3>(p, s, b, st, gathered, rank, nranks);
+  if (e != cudaSuccess) { err = std::string("shard finish: ") + cudaGetErrorString(e); return -3; }
   return 0;
 }
 

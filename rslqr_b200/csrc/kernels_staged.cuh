@@ -21,6 +21,7 @@ struct Shape {
   int zs;      // 2n+m
   int stride;  // doubles per flat knot block
   int oQ, oR, oq, orr, oA, oB, od;  // offsets inside a knot block
+  int kofs, Ng;  // shard of a longer horizon (tiered path only): global index of local knot 0, global horizon
 };
 
 struct Bufs {

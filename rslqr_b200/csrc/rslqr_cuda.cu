@@ -47,6 +47,7 @@ struct rslqr_cuda_solver {
   // dominant-kernel timing
   bool ktime_on; std::vector<std::pair<cudaEvent_t, cudaEvent_t>> kspans; double k_ms; int k_n;
   FusedPlan fused; int force_dfma;
+  bool shard; bool own_stream;
   int r_first, r_count;            // problem range the next enqueue covers (whole batch by default)
   cudaStream_t s_h2d, s_d2h; bool pipe_made; std::vector<cudaEvent_t> ev_up, ev_done; cudaEvent_t ev_join;
   cudaEvent_t marks[8]; bool marks_made;
@@ -69,6 +70,7 @@ static Shape make_shape(int n, int m, int N) {
   s.stride = rslqr_cuda_knot_stride(n, m);
   s.oQ = 0; s.oR = n; s.oq = n + m; s.orr = 2 * n + m; s.oA = 2 * n + 2 * m + 1;
   s.oB = s.oA + n * n; s.od = s.oB + n * m;
+  s.kofs = 0; s.Ng = N;
   return s;
 }
 
@@ -85,6 +87,7 @@ extern "C" int rslqr_cuda_create(int n, int m, int N, int batch, int device, uns
   rslqr_cuda_solver* h = new rslqr_cuda_solver();
   h->s = make_shape(n, m, N);
   h->batch = batch; h->device = device; h->flags = flags; h->mode = RSLQR_MODE_AUTO;
+  h->shard = false; h->own_stream = true;
   h->marks_made = false; h->pipe_made = false; h->r_first = 0; h->r_count = batch;
   h->launches = 0; h->evused = 0; h->ktime_on = false; h->k_ms = 0; h->k_n = 0;
   memset(h->prof, 0, sizeof(h->prof));
@@ -139,7 +142,7 @@ extern "C" int rslqr_cuda_destroy(rslqr_cuda_solver* h) {
     for (auto ev : h->ev_done) cudaEventDestroy(ev);
     cudaEventDestroy(h->ev_join); cudaStreamDestroy(h->s_h2d); cudaStreamDestroy(h->s_d2h);
   }
-  cudaStreamDestroy(h->stream);
+  if (h->own_stream) cudaStreamDestroy(h->stream);
   delete h;
   return RSLQR_OK;
 }
@@ -299,6 +302,7 @@ static int solve_staged(rslqr_cuda_solver* h, int pack_rhs) {
 
 extern "C" int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs) {
   if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
+  if (h->shard) return fail(RSLQR_E_UNSUPPORTED, "a shard is solved with shard_reduce / exchange / shard_finish");
   CU(cudaSetDevice(h->device));
   h->launches = 0;
   h->spans.clear();
@@ -579,5 +583,78 @@ extern "C" int rslqr_cuda_download_solution_async(rslqr_cuda_solver* h, double* 
   CU(cudaSetDevice(h->device));
   const size_t per = (size_t)h->s.N * h->s.zs;
   CU(cudaMemcpyAsync(soln, h->b.soln + first * per, sizeof(double) * per * count, cudaMemcpyDeviceToHost, h->stream));
+  return RSLQR_OK;
+}
+
+// ------------------------------------------------------------------ shards of one long horizon
+extern "C" int rslqr_cuda_create_shard(int n, int m, int nhorizon, int first_knot, int shard_knots, int device,
+                                       unsigned flags, rslqr_cuda_solver** out) {
+  if (!out) return fail(RSLQR_E_ARG, "out is NULL");
+  *out = nullptr;
+  if (nhorizon < 2 || (nhorizon & (nhorizon - 1)) || shard_knots < 16 || (shard_knots & (shard_knots - 1)) ||
+      first_knot < 0 || first_knot % shard_knots || first_knot + shard_knots > nhorizon)
+    return fail(RSLQR_E_ARG, "shard: need power-of-two horizon and shard size (>= 16), first_knot a multiple of the shard size");
+  int rc = rslqr_cuda_create(n, m, shard_knots, 1, device, flags & ~RSLQR_KEEP_FACT, out);
+  if (rc) return rc;
+  rslqr_cuda_solver* h = *out;
+  if (!h->fused.available || h->fused.ntiers < 1) {
+    rslqr_cuda_destroy(h);
+    *out = nullptr;
+    return fail(RSLQR_E_UNSUPPORTED, "shards need a shape covered by the tiered kernels");
+  }
+  h->shard = true;
+  h->s.kofs = first_knot;
+  h->s.Ng = nhorizon;
+  return RSLQR_OK;
+}
+
+extern "C" size_t rslqr_cuda_shard_payload_doubles(rslqr_cuda_solver* h) {
+  return h ? fused_payload_doubles(h->s.n, h->s.m) : 0;
+}
+
+extern "C" int rslqr_cuda_shard_reduce(rslqr_cuda_solver* h, double* d_payload) {
+  if (!h || !d_payload || !h->shard) return fail(RSLQR_E_ARG, "shard_reduce: bad argument");
+  CU(cudaSetDevice(h->device));
+  int rc = fused_shard_reduce(h->fused, h->s, h->b, 1, h->force_dfma, h->stream, d_payload, g_err);
+  h->launches = h->fused.launches;
+  return rc;
+}
+
+extern "C" int rslqr_cuda_shard_finish(rslqr_cuda_solver* h, const double* d_gathered, int rank, int nranks) {
+  if (!h || !h->shard || nranks < 1 || nranks > 8 || (nranks & (nranks - 1)) || rank < 0 || rank >= nranks ||
+      (nranks > 1 && !d_gathered) || h->s.kofs != rank * h->s.N || h->s.Ng != nranks * h->s.N)
+    return fail(RSLQR_E_ARG, "shard_finish: bad argument (rank / nranks must match the shard's position; nranks <= 8)");
+  CU(cudaSetDevice(h->device));
+  int rc = fused_shard_finish(h->fused, h->s, h->b, h->stream, d_gathered, rank, nranks, g_err);
+  h->launches = h->fused.launches;
+  return rc;
+}
+
+// Enqueue on a caller-owned stream (e.g. the one NCCL collectives are ordered on) instead of the handle's own.
+extern "C" int rslqr_cuda_set_stream(rslqr_cuda_solver* h, void* stream) {
+  if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
+  CU(cudaSetDevice(h->device));
+  CU(cudaStreamSynchronize(h->stream));
+  if (h->own_stream) cudaStreamDestroy(h->stream);
+  h->stream = (cudaStream_t)stream;
+  h->own_stream = false;
+  return RSLQR_OK;
+}
+
+// Single-process exchange for `nranks` shard handles (any devices): the all-gather of the payloads as peer copies.
+// d_payload[r] / d_gathered[r] are device buffers on shard r's device (payload / nranks * payload doubles).
+extern "C" int rslqr_cuda_shard_exchange(rslqr_cuda_solver** hs, int nranks, double** d_payload, double** d_gathered) {
+  if (!hs || !d_payload || !d_gathered || nranks < 1) return fail(RSLQR_E_ARG, "shard_exchange: bad argument");
+  const size_t pay = rslqr_cuda_shard_payload_doubles(hs[0]);
+  for (int r = 0; r < nranks; ++r) {  // payloads complete
+    CU(cudaSetDevice(hs[r]->device));
+    CU(cudaStreamSynchronize(hs[r]->stream));
+  }
+  for (int dst = 0; dst < nranks; ++dst) {
+    CU(cudaSetDevice(hs[dst]->device));
+    for (int src = 0; src < nranks; ++src)
+      CU(cudaMemcpyPeerAsync(d_gathered[dst] + src * pay, hs[dst]->device, d_payload[src], hs[src]->device,
+                             sizeof(double) * pay, hs[dst]->stream));
+  }
   return RSLQR_OK;
 }

@@ -69,6 +69,12 @@ _sig("rslqr_cuda_upload_async", C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c
 _sig("rslqr_cuda_download_solution_async", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int)
 _sig("rslqr_cuda_host_alloc", C.c_void_p, C.c_size_t)
 _sig("rslqr_cuda_host_free", None, C.c_void_p)
+_sig("rslqr_cuda_create_shard", C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint, C.POINTER(C.c_void_p))
+_sig("rslqr_cuda_shard_payload_doubles", C.c_size_t, C.c_void_p)
+_sig("rslqr_cuda_shard_reduce", C.c_int, C.c_void_p, C.c_void_p)
+_sig("rslqr_cuda_shard_finish", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int)
+_sig("rslqr_cuda_shard_exchange", C.c_int, C.POINTER(C.c_void_p), C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p))
+_sig("rslqr_cuda_set_stream", C.c_int, C.c_void_p, C.c_void_p)
 _sig("rslqr_synth_fill", C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.c_void_p)
 
 
@@ -463,3 +469,42 @@ class NdLqrSolver:
             self.close()
         except Exception:
             pass
+
+
+class ShardSolver(CudaSolver):
+    """One shard (knots [rank*shard_knots, (rank+1)*shard_knots)) of a single long-horizon problem on one GPU."""
+
+    def __init__(self, n, m, N, rank, nranks, device=0):
+        assert N % nranks == 0
+        Nl = N // nranks
+        self.n, self.m, self.N, self.batch, self.device = n, m, Nl, 1, device
+        self.Nglobal, self.rank, self.nranks = N, rank, nranks
+        self.K = Nl.bit_length() - 1
+        self.fs, self.zs, self.stride = (2 * n + m) * n, 2 * n + m, knot_stride(n, m)
+        self.h = C.c_void_p()
+        _check(LIB.rslqr_cuda_create_shard(n, m, N, rank * Nl, Nl, device, 0, C.byref(self.h)), "rslqr_cuda_create_shard")
+        self.payload_doubles = LIB.rslqr_cuda_shard_payload_doubles(self.h)
+
+    def upload_shard(self, knots_full, x0):
+        """knots_full: [N, stride] of the whole problem; takes this shard's slice and its boundary vector"""
+        lo = self.rank * self.N
+        head = x0 if self.rank == 0 else knots_full[lo - 1, -self.n:]
+        self.upload(np.ascontiguousarray(knots_full[lo:lo + self.N])[None], np.ascontiguousarray(head)[None])
+
+    def reduce(self, d_payload_ptr):
+        _check(LIB.rslqr_cuda_shard_reduce(self.h, C.c_void_p(d_payload_ptr)), "shard_reduce")
+
+    def finish(self, d_gathered_ptr):
+        _check(LIB.rslqr_cuda_shard_finish(self.h, C.c_void_p(d_gathered_ptr), self.rank, self.nranks), "shard_finish")
+
+    def set_stream(self, stream_ptr):
+        _check(LIB.rslqr_cuda_set_stream(self.h, C.c_void_p(stream_ptr)), "set_stream")
+
+
+def shard_exchange(shards, payload_ptrs, gathered_ptrs):
+    """single-process all-gather of the shard payloads (peer copies)"""
+    n = len(shards)
+    hs = (C.c_void_p * n)(*[s.h for s in shards])
+    pp = (C.c_void_p * n)(*payload_ptrs)
+    gp = (C.c_void_p * n)(*gathered_ptrs)
+    _check(LIB.rslqr_cuda_shard_exchange(hs, n, pp, gp), "shard_exchange")
