@@ -90,6 +90,32 @@ def schur_bytes_model(n, m, N, batch):
     return tot * batch / (K - 1)
 
 
+class stdout_to_stderr:
+    """NCCL prints its version banner on fd 1 at the first collective; keep stdout = the one JSON line."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+
+    def __exit__(self, *exc):
+        sys.stdout.flush()
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+
+
+def init_nccl(local_rank):
+    import torch
+    import torch.distributed as dist
+    torch.cuda.set_device(local_rank)
+    with stdout_to_stderr():
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        t = torch.zeros(1, device="cuda")
+        dist.all_reduce(t)          # first collective: communicator set-up (and the banner) happen here
+        torch.cuda.synchronize()
+    return dist
+
+
 class ClockSampler(threading.Thread):
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
 
@@ -215,10 +241,7 @@ def run_ours(args, rank, world, local_rank):
     n, m, N, B = N_STATES, N_INPUTS, HORIZON, args.batch
     dist = None
     if world > 1:
-        import torch
-        import torch.distributed as dist
-        torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist = init_nccl(local_rank)
 
     def barrier():
         if dist is not None:
@@ -348,6 +371,76 @@ def run_ours(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def run_long(args, rank, world, local_rank):
+    """BASELINE configs[3]: ONE long-horizon problem (n=12, m=4, N=16384) split into `world` subtrees, one per GPU;
+    the only exchange is one all-gather of the 7.2 KB per-shard payloads over NVLink (NCCL). Reports latency."""
+    import torch
+    import rslqr_b200 as R
+    from rslqr_b200.dist import LongHorizon
+    n, m, N = N_STATES, N_INPUTS, args.horizon
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        dist = init_nccl(local_rank)
+    knots, x0 = R.synth_problems(n, m, N, SEED, 0, 1)
+    lh = LongHorizon(n, m, N, rank, world, local_rank)
+    lh.upload(knots[0], x0[0])
+    for _ in range(max(args.warmup, 3)):
+        lh.solve_async()
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(args.steps):
+        lh.solve_async()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    if dist is not None:
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    # end to end: upload of the shard from host memory + solve + download of the shard's solution
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        lh.upload(knots[0], x0[0])
+        lh.solve_async()
+        z = lh.solution()
+    e2e_ms = (time.perf_counter() - t0) / args.steps * 1e3
+    if dist is not None:
+        t = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_ms = float(t.item())
+    clocks = sampler.summary()
+    assert not lh.shard.flags().any() and np.isfinite(z).all()
+    line = {"metric": f"single long-horizon LQR solve latency (n={n},m={m},N={N})", "value": ms, "unit": "ms", "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": False, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"single long-horizon LQR n={n} m={m} N={N} (BASELINE configs[3])", "seed": SEED,
+                       "parallelism": f"{world} subtrees of {N // world} knots, one all-gather of {lh.shard.payload_doubles * 8} B per rank",
+                       "l2": "working set (state 92 MB + inputs 31 MB over all ranks) vs 126 MB L2 per GPU; no explicit flush"},
+            "clocks": clocks,
+            "e2e": {"value": e2e_ms, "unit": "ms", "h2d_bytes_per_step": int(knots.nbytes // world), "d2h_bytes_per_step": int(z.nbytes)},
+            "gpu_launches": int(lh.shard.launches * args.steps)}
+    if rank == 0 and args.cpu_long:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import oracle_lib as O
+        cores = max(1, len(os.sched_getaffinity(0)))
+        t0 = time.perf_counter()
+        O.port_solve(n, m, N, knots[0], x0[0], threads=cores)
+        line["cpu_baseline"] = {"value": (time.perf_counter() - t0) * 1e3, "unit": "ms", "cores": cores, "kind": "port",
+                                "sample": "one solve of the same problem, oracle C port with OpenMP over all host cores (includes init)"}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    lh.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -356,6 +449,10 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=4096)
     ap.add_argument("--mode", default="auto", choices=["auto", "staged", "fused"])
+    ap.add_argument("--workload", default="batch", choices=["batch", "long"],
+                    help="batch = BASELINE configs[2] (default, the headline metric); long = configs[3] single long horizon")
+    ap.add_argument("--horizon", type=int, default=16384, help="horizon of the long workload")
+    ap.add_argument("--cpu-long", action="store_true", help="long workload: also time one CPU solve (takes ~10-60 s)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--chunk", type=int, default=0, help="problems per pipeline chunk of the e2e call (0 = automatic)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
@@ -366,6 +463,8 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
         run_reference(args, rank, world)
+    elif args.workload == "long":
+        run_long(args, rank, world, local_rank)
     else:
         run_ours(args, rank, world, local_rank)
 

@@ -417,3 +417,32 @@ def test_long_horizon_shards_emulated_on_one_gpu(shape, nranks):
     one.close()
     for s in shards:
         s.close()
+
+
+def test_long_horizon_16384_eight_shards_kkt():
+    # BASELINE configs[3] at full size: n=12, m=4, N=16384 as 8 subtrees of 2048 knots (ranks emulated on one device).
+    # Size-independent checks: KKT residual and agreement with the single-handle tiered solve.
+    import torch
+    n, m, N, G = 12, 4, 16384, 8
+    kn, x0 = R.synth_problems(n, m, N, 2024, 0, 1)
+    shards = [R.ShardSolver(n, m, N, r, G, device=0) for r in range(G)]
+    pay = shards[0].payload_doubles
+    d_pay = [torch.zeros(pay, dtype=torch.float64, device="cuda:0") for _ in range(G)]
+    d_gat = [torch.zeros(pay * G, dtype=torch.float64, device="cuda:0") for _ in range(G)]
+    for s in shards:
+        s.upload_shard(kn[0], x0[0])
+    for s, p in zip(shards, d_pay):
+        s.reduce(p.data_ptr())
+    R.shard_exchange(shards, [p.data_ptr() for p in d_pay], [g.data_ptr() for g in d_gat])
+    for s, g in zip(shards, d_gat):
+        s.finish(g.data_ptr())
+    z = np.concatenate([(s.sync(), s.solution()[0])[1] for s in shards])
+    res = O.kkt_residual(n, m, N, kn[0], x0[0], z)
+    assert res < 1e-10 * np.linalg.norm(z), res
+    one = R.CudaSolver(n, m, N, batch=1, flags=0)
+    one.upload(kn, x0)
+    one.solve()
+    assert np.linalg.norm(one.solution()[0] - z) <= 1e-11 * np.linalg.norm(z)
+    one.close()
+    for s in shards:
+        s.close()
