@@ -13,6 +13,7 @@
 
 #include "kernels_fused.cuh"
 #include "kernels_staged.cuh"
+#include "kernels_staged_mma.cuh"
 
 using namespace rslqr;
 
@@ -220,15 +221,34 @@ static int launch_stage(rslqr_cuda_solver* h, int stage, int level, Sel sel) {
       leaf_kernel<<<(unsigned)tasks, clampi(round32(nn), 32, 256), 0, st>>>(s, h->b, sel);
       break;
     case RSLQR_STAGE_PRODUCTS:
+      if (n == 64 && s.m == 16 && !getenv("RSLQR_NO_MMA_STAGED")) {
+        constexpr int smem = 64 * (80 + 4) * (int)sizeof(double);
+        products_mma_kernel<64, 16><<<(unsigned)(tasks * (sel.col < 0 ? 3 : 1)), 128, smem, st>>>(s, h->b, sel, level);
+      } else if (n == 16 && s.m == 16 && !getenv("RSLQR_NO_MMA_STAGED")) {
+        products_mma_kernel<16, 16><<<(unsigned)(tasks * (sel.col < 0 ? 3 : 1)), 32, 16 * 36 * sizeof(double), st>>>(s, h->b, sel, level);
+      } else
       products_kernel<<<(unsigned)(tasks * (sel.col < 0 ? 3 : 1)), clampi(round32(nn), 32, 256), 0, st>>>(s, h->b, sel, level);
       break;
     case RSLQR_STAGE_CHOLESKY:
       cholesky_kernel<<<(unsigned)tasks, clampi(round32(n), 32, 256), sizeof(double) * nn, st>>>(s, h->b, sel, level);
       break;
     case RSLQR_STAGE_SOLVES:
+      if (n == 64 && s.m == 16 && !getenv("RSLQR_NO_MMA_STAGED")) {
+        constexpr int smem = (64 * 66 + 64 * 65 + 64) * (int)sizeof(double);
+        static bool attr = false;
+        if (!attr) { CU(cudaFuncSetAttribute(solves_cols_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = true; }
+        solves_cols_kernel<64><<<(unsigned)(tasks * (sel.col < 0 ? 2 : 1)), 64, smem, st>>>(s, h->b, sel, level);
+      } else if (n == 16 && s.m == 16 && !getenv("RSLQR_NO_MMA_STAGED")) {
+        solves_cols_kernel<16><<<(unsigned)(tasks * (sel.col < 0 ? 2 : 1)), 16, (16 * 18 + 16 * 17 + 16) * sizeof(double), st>>>(s, h->b, sel, level);
+      } else
       solves_kernel<<<(unsigned)(tasks * (sel.col < 0 ? 2 : 1)), clampi(round32(nn), 32, 256), sizeof(double) * 2 * nn, st>>>(s, h->b, sel, level);
       break;
     case RSLQR_STAGE_SCHUR:
+      if (n == 64 && s.m == 16 && !getenv("RSLQR_NO_MMA_STAGED"))
+        schur_mma_kernel<64, 16><<<(unsigned)(tasks * (sel.col < 0 ? 2 : 1)), 32 * 9, sizeof(double) * 68 * 64, st>>>(s, h->b, sel, level);
+      else if (n == 16 && s.m == 16 && !getenv("RSLQR_NO_MMA_STAGED"))
+        schur_mma_kernel<16, 16><<<(unsigned)(tasks * (sel.col < 0 ? 2 : 1)), 32 * 3, sizeof(double) * 20 * 16, st>>>(s, h->b, sel, level);
+      else
       schur_kernel<<<(unsigned)(tasks * (sel.col < 0 ? 2 : 1)), clampi(round32(s.fs), 32, 256), sizeof(double) * nn, st>>>(s, h->b, sel, level);
       break;
     case RSLQR_STAGE_RHS_PRODUCTS:

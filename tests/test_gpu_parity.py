@@ -142,7 +142,7 @@ def test_vs_compiled_reference_live():
                     assert np.allclose(s.fact(p), rfact, rtol=1e-8, atol=1e-11)
 
 
-@pytest.mark.parametrize("shape", [(12, 4, 2), (1, 1, 2), (1, 1, 8), (2, 3, 4), (7, 2, 64), (12, 4, 1024), (33, 9, 8), (64, 16, 16)])
+@pytest.mark.parametrize("shape", [(12, 4, 2), (1, 1, 2), (1, 1, 8), (2, 3, 4), (7, 2, 64), (12, 4, 1024), (33, 9, 8), (64, 16, 16), (16, 16, 32), (64, 16, 128)])
 def test_edge_shapes(shape):
     # minimum horizon, scalar systems, m > n, non-multiple-of-warp sizes, long horizon, large state
     n, m, N = shape
