@@ -60,6 +60,27 @@ def tier0_flops_per_group(n, m, G):
     return 2.0 * (schur + spine)
 
 
+def scan_leaf_flops_per_subtree(n, m):
+    """FLOPs scan_leaf_kernel executes for one 4-knot subtree: two level-0 merges formed from the
+    flat knot blocks (S = [A B] D [A B]^T, s, S_L; LDL^T; 2n+1 solves; A^T [f_L f_R zs]; row scalings) and one general
+    merge (inner products [A|B] x (n+m x 2n+1), LDL^T, 2n+1 solves, lean Schur update of the 2n+m boundary rows)."""
+    w, zs = 2 * n + 1, 2 * n + m
+    raw = n * n * (n + m) + n * (n + m) + n * n + n ** 3 / 6 + w * n * n + n * n * w + (n + m) * w
+    gen = n * (n + m) * w + n ** 3 / 6 + w * n * n + zs * w * n
+    return 2.0 * (2 * raw + gen)
+
+
+def scan_leaf_bytes_per_subtree(n, m):
+    """Algorithmic HBM bytes of scan_leaf_kernel per 4-knot subtree: 4 flat knot blocks read; one boundary entry and
+    three separator records [f_L | f_R | zs] written."""
+    stride = 2 * n + 2 * m + 1 + n * n + n * m + n
+    ent = (2 * (2 * n + m) * n + (2 * n + m) + n + 1) & ~1
+    return 8 * (4 * stride + ent + 3 * (2 * n + 1) * n)
+
+
+# dram bytes of scan_leaf_kernel per problem from the committed ncu --set full capture (None until captured)
+SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM = None
+
 # dram__bytes_read.sum + dram__bytes_write.sum of tier0_kernel per problem, from the committed ncu --set full capture
 # (profiles/r01_ncu_tier0_v1.md: 0.995 GB + 4.060 GB at batch 2048)
 TIER0_TRAFFIC_BYTES_PER_PROBLEM = (0.995207936e9 + 4.060259e9) / 2048
@@ -255,7 +276,7 @@ def run_ours(args, rank, world, local_rank):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    mode = {"auto": R.MODE_AUTO, "staged": R.MODE_STAGED, "fused": R.MODE_FUSED}[args.mode]
+    mode = {"auto": R.MODE_AUTO, "staged": R.MODE_STAGED, "fused": R.MODE_FUSED, "scan": R.MODE_SCAN}[args.mode]
     flags = R.KEEP_FACT | R.PROFILE if mode == R.MODE_STAGED else 0
     s = R.CudaSolver(n, m, N, batch=B, device=local_rank, flags=flags)
     if mode != R.MODE_AUTO:
@@ -330,6 +351,26 @@ def run_ours(args, rank, world, local_rank):
         roof = {"kernel": "schur_kernel (staged, per level)", "bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"],
                 "unit": "GB/s", "frac": ach / pk["hbm_gbs"] if ach else None, "traffic": None, "peak_kind": pk_kind,
                 "algorithmic_bytes_per_launch": bytes_launch, "avg_launch_ms": k_avg_ms}
+    elif s.mode == R.MODE_SCAN:
+        # dominant kernel of the scan path: scan_leaf_kernel (levels 0 and 1 = 3/4 of all separators), one launch per
+        # step, timed with CUDA events on the launching stream by the C-ABI (rslqr_cuda_kernel_timing)
+        nsub = B * (N // 4)
+        by_sub = scan_leaf_bytes_per_subtree(n, m)
+        fl_sub = scan_leaf_flops_per_subtree(n, m)
+        k_avg_ms = k_ms if k_n else ms_per_step
+        ach = nsub * by_sub / (k_avg_ms * 1e-3) / 1e9
+        fp64 = fp64_peak()
+        roof = {"kernel": f"scan_leaf_kernel<{n},{m}> (one warp per 4-knot subtree: leaf factors + levels 0..1 on boundary entries)",
+                "bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ach / pk["hbm_gbs"],
+                "traffic": SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM * B if SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM and (n, m, N) == (12, 4, 256) else None,
+                "peak_kind": pk_kind, "algorithmic_bytes_per_launch": nsub * by_sub, "bytes_per_subtree": by_sub,
+                "avg_launch_ms": k_avg_ms, "kernel_launches_timed": k_n, "kernel_share_of_step": k_avg_ms / ms_per_step,
+                "fp64_tflops_executed": nsub * fl_sub / (k_avg_ms * 1e-3) / 1e12, "fp64_frac_of_dmma_peak": nsub * fl_sub / (k_avg_ms * 1e-3) / 1e12 / fp64["tflops"],
+                "flops_per_subtree": fl_sub,
+                "reference_count_tflops_whole_step": flop_model(n, m, N) * B / (ms_per_step * 1e-3) / 1e12,
+                "note": "achieved = algorithmic HBM bytes of the leaf kernel (4 flat knot blocks in, 1 boundary entry + 3 separator "
+                        "records out per subtree, DESIGN.md section 5) / its CUDA-event time; its arithmetic intensity (3.7 flop/B) is "
+                        "below the fp64 ridge (5.7 flop/B), so HBM is the bounding roofline; fp64_* report the executed FLOPs beside it"}
     else:
         # dominant kernel of the tiered path: tier0_kernel (leaves + the first log2(G) levels on chip), one launch
         # per step, timed with CUDA events on the launching stream by the C-ABI (rslqr_cuda_kernel_timing)
@@ -353,7 +394,7 @@ def run_ours(args, rank, world, local_rank):
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": WORKLOAD, "batch_per_gpu": B, "global_batch": B * world, "seed": SEED,
-                       "mode": "staged" if staged else "fused", "parallelism": f"batch-shard x{world}, no collective",
+                       "mode": {R.MODE_STAGED: "staged", R.MODE_FUSED: "fused (tiered)", R.MODE_SCAN: "scan"}[s.mode], "parallelism": f"batch-shard x{world}, no collective",
                        "l2": "inputs (%.2f GB/GPU) larger than L2; no explicit flush" % (B * N * st * 8 / 1e9)},
             "clocks": clocks,
             "e2e": {"value": world * B * args.steps / e2e_s, "unit": "solves/s",
@@ -448,7 +489,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=4096)
-    ap.add_argument("--mode", default="auto", choices=["auto", "staged", "fused"])
+    ap.add_argument("--mode", default="auto", choices=["auto", "staged", "fused", "scan"])
     ap.add_argument("--workload", default="batch", choices=["batch", "long"],
                     help="batch = BASELINE configs[2] (default, the headline metric); long = configs[3] single long horizon")
     ap.add_argument("--horizon", type=int, default=16384, help="horizon of the long workload")

@@ -52,9 +52,10 @@ enum {
 
 /* solve modes */
 enum {
-  RSLQR_MODE_AUTO = 0,   /* fused cluster kernel when the shape fits on chip, else staged */
+  RSLQR_MODE_AUTO = 0,   /* scan kernels when the shape is covered, else tiered, else staged */
   RSLQR_MODE_STAGED = 1, /* one launch per phase per level (leaf, products, Cholesky, solves, Schur, rhs) */
-  RSLQR_MODE_FUSED = 2   /* whole solve of a problem inside one thread-block cluster */
+  RSLQR_MODE_FUSED = 2,  /* tiered: a CTA keeps a group of knots in shared memory for the first levels */
+  RSLQR_MODE_SCAN = 3    /* every level on boundary entries, one warp per subtree (kernels_scan.cuh) */
 };
 
 /* stages for rslqr_cuda_stage(); `level`, `item`, `col` select one task, -1 = all tasks of the phase */

@@ -7,5 +7,5 @@ library raises.
 """
 from .lib import (  # noqa: F401
     LIB, LIB_PATH, RslqrError, CudaSolver, NdLqrSolver, load_problem_json, synth_problems,
-    knot_stride, ShardSolver, shard_exchange, MODE_AUTO, MODE_STAGED, MODE_FUSED, KEEP_FACT, PROFILE, STAGE,
+    knot_stride, ShardSolver, shard_exchange, MODE_AUTO, MODE_STAGED, MODE_FUSED, MODE_SCAN, KEEP_FACT, PROFILE, STAGE,
 )

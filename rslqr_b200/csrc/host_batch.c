@@ -34,7 +34,7 @@ NdLqrBatchSolver* ndlqr_NewBatchSolver(int n, int m, int N, int batch, int devic
       free(bs);
       return NULL;
     }
-  } else if (rslqr_cuda_get_mode(bs->dev) != RSLQR_MODE_FUSED) {
+  } else if (rslqr_cuda_get_mode(bs->dev) == RSLQR_MODE_STAGED) {
     rslqr_cuda_destroy(bs->dev);
     if (rslqr_cuda_create(n, m, N, batch, device, RSLQR_KEEP_FACT, &bs->dev) != RSLQR_OK) {
       fprintf(stderr, "ERROR: ndlqr_NewBatchSolver: %s\n", rslqr_cuda_last_error());

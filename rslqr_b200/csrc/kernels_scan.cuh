@@ -1,0 +1,576 @@
+// kernels_scan.cuh -- "scan" device path: the whole nested dissection on boundary entries, one warp per merge.
+//
+// The tiered path (kernels_fused.cuh) keeps the dense state (L, R, z) of every knot for its first levels and
+// a CTA cooperates on a group of knots, so most of its warps wait at the level barriers while one warp per
+// separator runs the serial factorization chain. Here EVERY level works on boundary entries only -- the rows
+// [X(a) | X(b) | U(b)] of the two boundary columns of a subtree [a,b], all a later ndlqr_FactorInnerProduct
+// (reference src/nested_dissection.c:114) ever reads -- and a warp owns a subtree outright:
+//
+//   scan_leaf_kernel : one warp = 4 consecutive knots. The two level-0 merges are formed straight from the
+//                      flat knot blocks (the leaf factors of ndlqr_SolveLeaf, src/nested_dissection.c:10-105,
+//                      are diagonal scalings, so S = A Q^-1 A^T + B R^-1 B^T + Q^-1 and the Schur update of a
+//                      leaf pair is one 12x12x24 product), the level-1 merge is the general one. No CTA barrier.
+//   tier_kernel      : (kernels_fused.cuh) the remaining levels, 8 entries per CTA.
+//   topdown_kernel   : (kernels_fused.cuh) multipliers of the separators above the 4-knot subtrees.
+//   scan_down_kernel : one warp = 4 knots: multipliers of its three interior separators from the stored records
+//                      [f_L | f_R | zs], then x_k, u_k from the leaf equations (the reference's rhs propagation
+//                      src/solve.c:175-180 telescoped: soln(k) = z(k) - L(k) lambda_k - R(k) lambda_{k+1} with the
+//                      LEAF blocks L(k) = [0; -Q^-1; 0], R(k) = [0; Q^-1 A^T; R^-1 B^T]).
+//
+// Nothing but entries (5.7 KB per subtree) and separator records (2.4 KB each) is written to HBM.
+// Arithmetic: IEEE fp64; inner products and Schur updates on mma.sync.m8n8k4.f64 (DMMA).
+#pragma once
+#include "kernels_fused.cuh"
+
+namespace rslqr {
+
+// the spine after the inner products: lanes < NS hold column c of S in acc[]; the right-hand-side columns
+// S_L (lanes NS..2NS-1) and s (lane 2NS) are parked in Wout[lane*NS + r]; load_sr(r, c) yields S_R(r, c).
+// Same factorization / solves as spine_merge (kernels_fused.cuh).
+template <int NS, class LoadSR>
+__device__ __forceinline__ int spine_factor_solve(double (&acc)[NS], double* Lsm, double* Wout, LoadSR load_sr) {
+  const int lane = threadIdx.x & 31;
+  const int c = lane < NS ? lane : 0;
+  const int mycol = lane <= 2 * NS ? lane : 2 * NS;
+  int bad = 0;
+#pragma unroll
+  for (int j = 0; j < NS; ++j) {
+    const double d = shfl_d(acc[j], j);
+    if (!(d > 0.0)) bad = 1;
+    const double dinv = fast_rcp(d);
+    const double lij = acc[j] * dinv;
+#pragma unroll
+    for (int k = j + 1; k < NS; ++k) {
+      const double pk = shfl_d(acc[k], j);
+      acc[k] = fma(-lij, pk, acc[k]);
+    }
+    acc[j] = lane == j ? dinv : lij;
+  }
+  if (lane < NS) {
+#pragma unroll
+    for (int k = 0; k < NS; ++k) Lsm[lane * NS + k] = acc[k];
+  }
+  __syncwarp();
+#pragma unroll
+  for (int r = 0; r < NS; ++r) {
+    const double sr = load_sr(r, c);  // warp-uniform control flow inside (may shuffle)
+    acc[r] = lane < NS ? sr : Wout[mycol * NS + r];
+  }
+#pragma unroll
+  for (int j = 0; j < NS; ++j) {
+#pragma unroll
+    for (int i = j + 1; i < NS; ++i) acc[i] = fma(-Lsm[i * NS + j], acc[j], acc[i]);
+  }
+#pragma unroll
+  for (int j = 0; j < NS; ++j) acc[j] *= Lsm[j * NS + j];
+#pragma unroll
+  for (int j = NS - 1; j >= 0; --j) {
+#pragma unroll
+    for (int i = 0; i < j; ++i) acc[i] = fma(-Lsm[j * NS + i], acc[j], acc[i]);
+  }
+  __syncwarp();
+  if (lane <= 2 * NS) {
+    const int wc = lane < NS ? NS + lane : (lane < 2 * NS ? lane - NS : 2 * NS);
+#pragma unroll
+    for (int r = 0; r < NS; ++r) Wout[wc * NS + r] = acc[r];
+  }
+  __syncwarp();
+  return bad;
+}
+
+// entry `rw` of the negated right-hand side of local knot k (reference src/solver.c:138-190), either packed on the
+// fly from the flat knot blocks or read from the soln buffer (pack_rhs == 0: the caller uploaded its own rhs)
+__device__ __forceinline__ double scan_rhs(const Shape& s, const Bufs& b, int prob, int k, int rw, int pack_rhs) {
+  if (!pack_rhs) return soln_ptr(s, b, prob, k)[rw];
+  const double* kn = knot_ptr(s, b, prob, k);
+  if (rw < s.n) return -(k == 0 ? b.x0[(size_t)prob * s.n + rw] : (kn - s.stride)[s.od + rw]);
+  if (rw < 2 * s.n) return -kn[s.oq + rw - s.n];
+  return (s.kofs + k < s.Ng - 1) ? -kn[s.orr + rw - 2 * s.n] : 0.0;
+}
+
+// Per-lane leaf quantities of one knot (ndlqr_SolveLeaf on diagonal Q, R): lane l < NS+NI holds
+//   dinv = 1/Q[l] (l < NS) or 1/R[l-NS];  zi = entry l of the leaf-solved (z_x | z_u);  zl = z_lambda[l] (l < NS)
+struct LeafLane { double dinv, zi, zl; };
+
+template <int NS, int NI>
+__device__ __forceinline__ LeafLane leaf_lane(const Shape& s, const Bufs& b, int prob, int k, int pack_rhs, bool check) {
+  const int lane = threadIdx.x & 31;
+  LeafLane o;
+  o.dinv = 0.0; o.zi = 0.0; o.zl = 0.0;
+  const int kg = s.kofs + k;
+  const bool last = kg == s.Ng - 1;
+  if (lane < NS + NI) {
+    const double* kn = knot_ptr(s, b, prob, k);
+    const double d = __ldg(kn + lane);  // Q then R are the first NS+NI doubles of the block
+    const bool isR = lane >= NS;
+    if (check && !(d > 0.0) && !(isR && last)) {
+      b.status[(size_t)prob * 3 * s.N + (isR ? rs_slot_R(k) : rs_slot_Q(k))] = -1;
+      b.flags[prob] = 1;
+    }
+    o.dinv = (isR && last) ? 0.0 : 1.0 / d;
+    const double rx = scan_rhs(s, b, prob, k, NS + lane, pack_rhs);  // rhs of the x / u row
+    if (kg == 0) {
+      const double rl = lane < NS ? scan_rhs(s, b, prob, k, lane, pack_rhs) : 0.0;
+      if (lane < NS) { o.zi = -rl; o.zl = -d * rl - rx; }
+      else o.zi = rx * o.dinv;
+    } else {
+      if (lane < NS) { o.zi = rx * o.dinv; o.zl = scan_rhs(s, b, prob, k, lane, pack_rhs); }
+      else o.zi = last ? rx : rx * o.dinv;
+    }
+  }
+  return o;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Level-0 merge of two single knots i (left) and i+1 (right), straight from their flat blocks:
+//   S   = A_i Q_i^-1 A_i^T + B_i R_i^-1 B_i^T + Q_{i+1}^-1      (ndlqr_FactorInnerProduct on the leaf factors)
+//   S_L = -A_i Q_i^-1,   S_R = -Q_{i+1}^-1 A_{i+1}^T,   s = A_i z_x(i) + B_i z_u(i) - z_x(i+1) - z_lambda(i+1)
+//   [f_L f_R zs] = S^-1 [S_L S_R s]                               (Cholesky + ndlqr_SolveCholeskyFactor)
+//   entry rows X(i)   : -Q_i^-1 ([I|0] + A_i^T [f_L f_R]),  z_x(i) - Q_i^-1 A_i^T zs        (ndlqr_UpdateShurFactor)
+//         rows X(i+1) :  Q_{i+1}^-1 ([0|A_{i+1}^T] + [f_L f_R]),  z_x(i+1) + Q_{i+1}^-1 zs
+//         rows U(i+1) :  [0 | R_{i+1}^-1 B_{i+1}^T],  z_u(i+1)                              (unchanged)
+// Knot 0 has X_R = 0 and Lambda = -A_0^T (src/nested_dissection.c:24-59): its X rows stay (0, 0, x0).
+// The last knot of the horizon has R(k) = 0. ABl / ABr: [A|B] of the two knots (column-major, NS rows).
+// E: output entry (Dim::ENT layout), Wf: [f_L | f_R | zs] on return, Lsm: NS*NS scratch.
+// ---------------------------------------------------------------------------------------------------------
+template <int NS, int NI>
+__device__ __forceinline__ int merge_raw(const double* __restrict__ ABl, const double* __restrict__ ABr, const LeafLane& ll,
+                                         const LeafLane& lr, bool first0, bool lastR, double* E, double* Lsm, double* Wf) {
+  using D = Dim<NS, NI>;
+  constexpr int ZS = D::ZS, SLOT = D::SLOT;
+  constexpr int KS = (NS + NI) / 4, KA = NS / 4;
+  static_assert(NS % 4 == 0 && (NS + NI) % 4 == 0 && NS > 8 && NS <= 16 && ((NS + NI) * 2 * NS) % 32 == 0, "tile shapes");
+  const int lane = threadIdx.x & 31, q = lane & 3, rr = lane >> 2;
+  const bool r1 = 8 + rr < NS;  // second row tile is partial
+  double acc[NS];
+  {
+    double a0[KS], a1[KS];
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+      const int l = 4 * ks + q;
+      a0[ks] = __ldg(ABl + l * NS + rr);
+      a1[ks] = r1 ? __ldg(ABl + l * NS + 8 + rr) : 0.0;
+    }
+    double d[2][2][2];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < 2; ++nt) d[mt][nt][0] = d[mt][nt][1] = 0.0;
+    double p0 = 0.0, p1 = 0.0;
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+      double dk = shfl_d(ll.dinv, 4 * ks + q);
+      if (first0 && ks < KA) dk = 0.0;  // X_R(0) = 0
+      const double zk = shfl_d(ll.zi, 4 * ks + q);
+      const double b0 = a0[ks] * dk, b1 = a1[ks] * dk;
+      dmma884(d[0][0][0], d[0][0][1], a0[ks], b0);
+      dmma884(d[0][1][0], d[0][1][1], a0[ks], b1);
+      dmma884(d[1][0][0], d[1][0][1], a1[ks], b0);
+      dmma884(d[1][1][0], d[1][1][1], a1[ks], b1);
+      p0 = fma(a0[ks], zk, p0);
+      p1 = fma(a1[ks], zk, p1);
+    }
+    p0 += __shfl_xor_sync(0xffffffffu, p0, 1);
+    p0 += __shfl_xor_sync(0xffffffffu, p0, 2);
+    p1 += __shfl_xor_sync(0xffffffffu, p1, 1);
+    p1 += __shfl_xor_sync(0xffffffffu, p1, 2);
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt) {
+      const int row = 8 * mt + rr, rs = row < NS ? row : 0;
+      const double dr = shfl_d(lr.dinv, rs);
+      const double t = shfl_d(lr.zi, rs) + shfl_d(lr.zl, rs);
+#pragma unroll
+      for (int nt = 0; nt < 2; ++nt)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int col = 8 * nt + 2 * q + h;
+          if (row < NS && col < NS) Wf[col * NS + row] = d[mt][nt][h] + (col == row ? dr : 0.0);
+        }
+      if (q == 0 && row < NS) Wf[2 * NS * NS + row] = (mt ? p1 : p0) - t;
+    }
+    const int cl = (lane >= NS && lane < 2 * NS) ? lane - NS : 0;
+    const double dcs = shfl_d(ll.dinv, cl);
+    if (lane >= NS && lane < 2 * NS) {
+#pragma unroll
+      for (int r = 0; r < NS; ++r) Wf[lane * NS + r] = first0 ? 0.0 : -__ldg(ABl + cl * NS + r) * dcs;
+    }
+    __syncwarp();
+    const int mc = lane < NS ? lane : 0;
+#pragma unroll
+    for (int r = 0; r < NS; ++r) acc[r] = Wf[mc * NS + r];
+    __syncwarp();
+  }
+  const int bad = spine_factor_solve<NS>(acc, Lsm, Wf, [&](int r, int c) -> double {
+    const double dr = shfl_d(lr.dinv, r);
+    return lastR ? 0.0 : -__ldg(ABr + r * NS + c) * dr;
+  });
+  // ---- entry rows X(i): A_i^T [f_L f_R] on DMMA ----
+  {
+    double bf[KA][3], zq[KA];
+#pragma unroll
+    for (int ks = 0; ks < KA; ++ks) {
+#pragma unroll
+      for (int nt = 0; nt < 3; ++nt) bf[ks][nt] = Wf[(8 * nt + rr) * NS + 4 * ks + q];
+      zq[ks] = Wf[2 * NS * NS + 4 * ks + q];
+    }
+    static_assert(2 * NS == 24, "three column tiles");
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt) {
+      const int row = 8 * mt + rr, rs = row < NS ? row : 0;
+      double at[KA];
+#pragma unroll
+      for (int ks = 0; ks < KA; ++ks) at[ks] = row < NS ? __ldg(ABl + row * NS + 4 * ks + q) : 0.0;
+      double c[3][2];
+#pragma unroll
+      for (int nt = 0; nt < 3; ++nt) c[nt][0] = c[nt][1] = 0.0;
+      double part = 0.0;
+#pragma unroll
+      for (int ks = 0; ks < KA; ++ks) {
+#pragma unroll
+        for (int nt = 0; nt < 3; ++nt) dmma884(c[nt][0], c[nt][1], at[ks], bf[ks][nt]);
+        part = fma(at[ks], zq[ks], part);
+      }
+      part += __shfl_xor_sync(0xffffffffu, part, 1);
+      part += __shfl_xor_sync(0xffffffffu, part, 2);
+      const double dl = first0 ? 0.0 : shfl_d(ll.dinv, rs);
+      const double zrow = shfl_d(ll.zi, rs);
+      if (row < NS) {
+#pragma unroll
+        for (int nt = 0; nt < 3; ++nt) {
+          const int col = 8 * nt + 2 * q;
+          const double v0 = -dl * ((col == row ? 1.0 : 0.0) + c[nt][0]);
+          const double v1 = -dl * ((col + 1 == row ? 1.0 : 0.0) + c[nt][1]);
+          double* dst = col < NS ? E + row * NS + col : E + SLOT + row * NS + col - NS;
+          *reinterpret_cast<double2*>(dst) = make_double2(v0, v1);
+        }
+        if (q == 0) E[2 * SLOT + row] = zrow - dl * part;
+      }
+    }
+  }
+  // ---- entry rows X(i+1), U(i+1): row scalings ----
+#pragma unroll 4
+  for (int e = lane; e < (NS + NI) * 2 * NS; e += 32) {
+    const int row = e / (2 * NS), col = e - row * 2 * NS;
+    const double dr = shfl_d(lr.dinv, row);
+    const double a = (col >= NS && !lastR) ? __ldg(ABr + row * NS + col - NS) : 0.0;  // A_{i+1}(c,r) / B_{i+1}(c,r-NS)
+    const double f = row < NS ? Wf[col * NS + row] : 0.0;
+    double* dst = col < NS ? E + (NS + row) * NS + col : E + SLOT + (NS + row) * NS + col - NS;
+    *dst = dr * (f + a);
+  }
+  {
+    const int rs = lane < NS ? lane : 0;
+    const double zs = Wf[2 * NS * NS + rs];
+    if (lane < NS + NI) E[2 * SLOT + NS + lane] = lane < NS ? fma(lr.dinv, zs, lr.zi) : lr.zi;
+    if (lane < NS) E[2 * SLOT + ZS + lane] = ll.zl;
+  }
+  __syncwarp();
+  return bad;
+}
+
+// one row of the lean Schur update with separate source and destination (the right subtree's rows move into
+// the merged entry): dst <- keep - own * [f_L f_R zs]; side 0: own = R block (keep L), side 1: own = L block
+template <int NS>
+__device__ __forceinline__ void schur_row_io(const double* sL, const double* sR, const double* sz, double* dL, double* dR,
+                                             double* dz, const double* Wf, int side) {
+  double o[NS], kp[NS];
+  const double* own = side ? sL : sR;
+  const double* keep = side ? sR : sL;
+#pragma unroll
+  for (int k = 0; k < NS; ++k) { o[k] = own[k]; kp[k] = keep[k]; }
+  const double z0 = *sz;
+#pragma unroll 2
+  for (int c = 0; c < NS; ++c) {
+    double aL = side ? 0.0 : kp[c];
+    double aR = side ? kp[c] : 0.0;
+#pragma unroll
+    for (int k = 0; k < NS; ++k) {
+      aL = fma(-o[k], Wf[c * NS + k], aL);
+      aR = fma(-o[k], Wf[(NS + c) * NS + k], aR);
+    }
+    dL[c] = aL;
+    dR[c] = aR;
+  }
+  double az = z0;
+#pragma unroll
+  for (int k = 0; k < NS; ++k) az = fma(-o[k], Wf[2 * NS * NS + k], az);
+  *dz = az;
+}
+
+struct ScanBufs {
+  double* ent0;    // [batch][M0][ENT]   entries of the 4-knot subtrees (input of the first tier)
+  double* sep_in;  // [batch][M0][3][WSZ] records of the interior separators of a subtree: local knots 1, 2, 3
+};
+
+constexpr int SCAN_LEAF = 4;   // knots per warp in the leaf kernel
+constexpr int SCAN_WPC = 5;    // warps per CTA (independent of each other; sized for shared memory)
+
+template <int NS, int NI>
+constexpr int scan_leaf_smem_doubles() {
+  using D = Dim<NS, NI>;
+  return SCAN_WPC * (2 * D::ENT + D::WSZ + NS * NS);
+}
+
+template <int NS, int NI>
+__global__ void __launch_bounds__(32 * SCAN_WPC, 3) scan_leaf_kernel(Shape s, Bufs b, ScanBufs sb, int pack_rhs, int M0,
+                                                                      long long nsub) {
+  using D = Dim<NS, NI>;
+  constexpr int ZS = D::ZS, SLOT = D::SLOT, WSZ = D::WSZ, ENT = D::ENT;
+  extern __shared__ __align__(16) double smf[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long sub = (long long)blockIdx.x * SCAN_WPC + warp;
+  if (sub >= nsub) return;
+  double* E0 = smf + warp * (2 * ENT + WSZ + NS * NS);
+  double* E1 = E0 + ENT;
+  double* Wf = E1 + ENT;
+  double* Lsm = Wf + WSZ;
+  const int prob = (int)(sub / M0), grp = (int)(sub - (long long)prob * M0);
+  const int k0 = grp * SCAN_LEAF;
+  const int N = s.N;
+  double* rec = sb.sep_in + ((size_t)prob * M0 + grp) * 3 * WSZ;
+  int bad;
+  // ---- level 0: (k0, k0+1) -> E0, (k0+2, k0+3) -> E1 ----
+#pragma unroll 1
+  for (int h = 0; h < 2; ++h) {
+    const int k = k0 + 2 * h;
+    const LeafLane ll = leaf_lane<NS, NI>(s, b, prob, k, pack_rhs, true);
+    const LeafLane lr = leaf_lane<NS, NI>(s, b, prob, k + 1, pack_rhs, true);
+    const double* kl = knot_ptr(s, b, prob, k);
+    bad = merge_raw<NS, NI>(kl + s.oA, kl + s.stride + s.oA, ll, lr, s.kofs + k == 0, s.kofs + k + 1 == s.Ng - 1,
+                            h ? E1 : E0, Lsm, Wf);
+    for (int e = lane; e < WSZ; e += 32) rec[(2 * h) * WSZ + e] = Wf[e];
+    if (bad && lane == 0) {
+      b.status[(size_t)prob * 3 * N + rs_slot_S(k >> 1, 0, N)] = -1;
+      b.flags[prob] = 1;
+    }
+    __syncwarp();
+  }
+  // ---- level 1: E0 + E1 -> E0 (separator after knot k0+1) ----
+  bad = spine_merge<NS, NI>(knot_ptr(s, b, prob, k0 + 1) + s.oA, E0 + NS * NS, E0 + SLOT + NS * NS, E0 + 2 * SLOT + NS, E1,
+                            E1 + SLOT, E1 + 2 * SLOT, E1 + 2 * SLOT + ZS, Lsm, Wf);
+  for (int e = lane; e < WSZ; e += 32) rec[WSZ + e] = Wf[e];
+  if (bad && lane == 0) {
+    b.status[(size_t)prob * 3 * N + rs_slot_S(k0 >> 2, 1, N)] = -1;
+    b.flags[prob] = 1;
+  }
+  if (M0 == 1) return;  // a single subtree is the whole problem: only the records are needed
+  if (lane < ZS) {
+    const double* S = lane < NS ? E0 : E1;
+    schur_row_io<NS>(S + lane * NS, S + SLOT + lane * NS, S + 2 * SLOT + lane, E0 + lane * NS, E0 + SLOT + lane * NS,
+                     E0 + 2 * SLOT + lane, Wf, lane < NS ? 0 : 1);
+  }
+  fence_async_smem();
+  __syncwarp();
+  if (lane == 0) {
+    bulk_s2g(sb.ent0 + ((size_t)prob * M0 + grp) * ENT, E0, ENT * (int)sizeof(double));
+    bulk_commit();
+    bulk_wait_read0();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Down: one warp = one 4-knot subtree [4g, 4g+3]. lam[g], lam[g+1] are the multipliers of the separators
+// bounding it. Interior multipliers from the records (rec 0/1/2 = separators at local knots 1/2/3):
+//   l2 = zs1 - fL1 la - fR1 lb;  l1 = zs0 - fL0 la - fR0 l2;  l3 = zs2 - fL2 l2 - fR2 lb
+// then for every knot k (lk = its own multiplier, ln = the next one):
+//   x_k = Q_k^-1 (rhs_x + lk - A_k^T ln),  u_k = R_k^-1 (rhs_u - B_k^T ln),  lambda_k = lk
+//   knot 0: x_0 = -rhs_lambda (= x0), lambda_0 = -Q_0 rhs_lambda - rhs_x + A_0^T l_1   (src/nested_dissection.c:24-59)
+//   last knot: u slot = rhs_u (no input there)
+// Two knots at a time: lanes 0..15 take the rows of one, lanes 16..31 of the next.
+// ---------------------------------------------------------------------------------------------------------
+template <int NS, int NI>
+__global__ void __launch_bounds__(128) scan_down_kernel(Shape s, Bufs b, ScanBufs sb, const double* lam_all, int pack_rhs,
+                                                         int M0, long long nsub) {
+  using D = Dim<NS, NI>;
+  constexpr int ZS = D::ZS, WSZ = D::WSZ;
+  static_assert(NS + NI <= 16 && NS <= 16, "two knots per warp pass");
+  const int lane = threadIdx.x & 31;
+  const long long sub = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (sub >= nsub) return;
+  const int prob = (int)(sub / M0), grp = (int)(sub - (long long)prob * M0);
+  const double* la_p = lam_all + ((size_t)prob * (M0 + 1) + grp) * NS;
+  const double* rec = sb.sep_in + ((size_t)prob * M0 + grp) * 3 * WSZ;
+  const int half = lane >> 4, r = lane & 15;
+  const int rc = r < NS ? r : 0;
+  // multipliers, one entry per lane r < NS (both halves hold copies)
+  const double la = la_p[rc], lb = la_p[NS + rc];
+  auto sepmul = [&](const double* R, double left, double right) -> double {
+    double v = R[2 * NS * NS + rc];
+#pragma unroll
+    for (int c = 0; c < NS; ++c) {
+      const double lc = __shfl_sync(0xffffffffu, left, (lane & 16) + c);
+      const double rcv = __shfl_sync(0xffffffffu, right, (lane & 16) + c);
+      v = fma(-R[c * NS + rc], lc, fma(-R[(NS + c) * NS + rc], rcv, v));
+    }
+    return v;
+  };
+  const double l2 = sepmul(rec + WSZ, la, lb);
+  // half 0 computes l1 (record 0: la | l2), half 1 computes l3 (record 2: l2 | lb)
+  const double l13 = sepmul(rec + (half ? 2 * WSZ : 0), half ? l2 : la, half ? lb : l2);
+  const double l1 = __shfl_sync(0xffffffffu, l13, rc), l3 = __shfl_sync(0xffffffffu, l13, 16 + rc);
+#pragma unroll 1
+  for (int pass = 0; pass < 2; ++pass) {
+    const int j = 2 * pass + half;  // local knot of this half-warp
+    const int k = grp * SCAN_LEAF + j;
+    const int kg = s.kofs + k;
+    const double lk = j == 0 ? la : (j == 1 ? l1 : (j == 2 ? l2 : l3));
+    const double ln = j == 0 ? l1 : (j == 1 ? l2 : (j == 2 ? l3 : lb));
+    const double* kn = knot_ptr(s, b, prob, k);
+    double* out = soln_ptr(s, b, prob, k);
+    const bool last = kg == s.Ng - 1;
+    double acc = 0.0;  // row r of [A|B]^T ln
+    const double* col = kn + s.oA + (r < NS + NI ? r : 0) * NS;
+#pragma unroll
+    for (int c = 0; c < NS; ++c) {
+      const double lc = __shfl_sync(0xffffffffu, ln, (lane & 16) + c);
+      acc = fma(last ? 0.0 : __ldg(col + c), lc, acc);
+    }
+    if (r < NS + NI) {
+      const double d = __ldg(kn + r);
+      const double rx = scan_rhs(s, b, prob, k, NS + r, pack_rhs);
+      if (r < NS) {
+        const double rl = kg == 0 ? scan_rhs(s, b, prob, k, r, pack_rhs) : 0.0;
+        double xv, lv;
+        if (kg == 0) { xv = -rl; lv = -d * rl - rx + acc; }
+        else { xv = (rx + lk - acc) / d; lv = lk; }
+        // all reads of the rhs (possibly aliasing soln) of this row are done before the writes below
+        out[r] = lv;
+        out[NS + r] = xv;
+      } else {
+        out[NS + r] = last ? rx : (rx - acc) / d;
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------------
+struct ScanPlan {
+  FusedPlan f;     // G0 = SCAN_LEAF; only sep / lamhat / ent[t >= 1] / xsep / xlam of f.fb are allocated
+  ScanBufs sb;
+};
+
+inline bool scan_shape_ok(int n, int m) { return n == 12 && m == 4; }
+
+inline void scan_free(ScanPlan* p) {
+  cudaFree(p->sb.ent0); cudaFree(p->sb.sep_in);
+  p->f.fb.ent[0] = nullptr;  // alias of sb.ent0
+  fused_free(&p->f);
+  memset(p, 0, sizeof(*p));
+}
+
+inline int scan_plan(const Shape& s, int batch, ScanPlan* p, std::string& err) {
+  memset(p, 0, sizeof(*p));
+  if (!scan_shape_ok(s.n, s.m) || s.N < SCAN_LEAF) return 0;
+  FusedPlan& f = p->f;
+  f.ns = s.n; f.ni = s.m; f.G0 = SCAN_LEAF; f.M0 = s.N / SCAN_LEAF; f.use_dmma = 1;
+  int M = f.M0, span = f.G0;
+  while (M > 1) {
+    if (f.ntiers == 8) return 0;
+    const int e = M < 8 ? M : 8;
+    f.tiers[f.ntiers++] = FusedTier{M, e, span};
+    M /= e; span *= e;
+  }
+  const size_t n = s.n, ent = fused_ent_doubles(s.n, s.m), wsz = (2 * n + 1) * n;
+  auto alloc = [&](double** ptr, size_t cnt) {
+    f.bytes += cnt * sizeof(double);
+    return cudaMalloc((void**)ptr, cnt * sizeof(double)) == cudaSuccess;
+  };
+  bool ok = alloc(&f.fb.sep, (size_t)batch * f.M0 * wsz) && alloc(&f.fb.lamhat, (size_t)batch * (f.M0 + 1) * n) &&
+            alloc(&p->sb.sep_in, (size_t)batch * f.M0 * 3 * wsz) && alloc(&p->sb.ent0, (size_t)batch * f.M0 * ent) &&
+            alloc(&f.xsep, 8 * wsz) && alloc(&f.xlam, 9 * n);
+  f.fb.ent[0] = p->sb.ent0;
+  for (int t = 1; ok && t < f.ntiers; ++t) ok = alloc(&f.fb.ent[t], (size_t)batch * f.tiers[t].Min * ent);
+  if (!ok) {
+    cudaGetLastError();
+    scan_free(p);
+    err = "device allocation for the scan path failed";
+    return -4;
+  }
+  f.available = true;
+  return 0;
+}
+
+template <int NS, int NI>
+inline cudaError_t launch_scan_leaf(ScanPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st) {
+  constexpr int smem = scan_leaf_smem_doubles<NS, NI>() * (int)sizeof(double);
+  static bool attr_done = false;
+  if (!attr_done) {
+    cudaError_t e = cudaFuncSetAttribute(scan_leaf_kernel<NS, NI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    attr_done = true;
+  }
+  const long long nsub = (long long)batch * p.f.M0;
+  scan_leaf_kernel<NS, NI><<<(unsigned)((nsub + SCAN_WPC - 1) / SCAN_WPC), 32 * SCAN_WPC, smem, st>>>(s, b, p.sb, pack_rhs, p.f.M0, nsub);
+  return cudaGetLastError();
+}
+
+// top-down over the separators above the subtrees, then multipliers inside the subtrees + solution
+template <int NS, int NI>
+inline cudaError_t launch_scan_down(ScanPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st,
+                                    const double* left, const double* right) {
+  topdown_kernel<NS><<<batch, 128, 0, st>>>(p.f.fb.sep, p.f.fb.lamhat, p.f.M0, left, right);
+  ++p.f.launches;
+  const long long nsub = (long long)batch * p.f.M0;
+  scan_down_kernel<NS, NI><<<(unsigned)((nsub + 3) / 4), 128, 0, st>>>(s, b, p.sb, p.f.fb.lamhat, pack_rhs, p.f.M0, nsub);
+  ++p.f.launches;
+  return cudaGetLastError();
+}
+
+inline int scan_launch(ScanPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st, std::string& err,
+                       cudaEvent_t k0 = nullptr, cudaEvent_t k1 = nullptr) {
+  if (!p.f.available) { err = "shape not covered by the scan kernels"; return -5; }
+  p.f.launches = 1;
+  if (k0) cudaEventRecord(k0, st);  // k0..k1 bracket the dominant kernel (leaf) only
+  cudaError_t e = launch_scan_leaf<12, 4>(p, s, b, batch, pack_rhs, st);
+  if (k1) cudaEventRecord(k1, st);
+  if (e == cudaSuccess) e = launch_tiers<12, 4>(p.f, s, b, batch, st, nullptr, 0);
+  if (e == cudaSuccess) e = launch_scan_down<12, 4>(p, s, b, batch, pack_rhs, st, nullptr, nullptr);
+  if (e != cudaSuccess) { err = std::string("scan launch: ") + cudaGetErrorString(e); return -3; }
+  return 0;
+}
+
+// ---- shards of one long horizon ----
+inline int scan_shard_reduce(ScanPlan& p, const Shape& s, const Bufs& b, int pack_rhs, cudaStream_t st, double* payload,
+                             std::string& err) {
+  using D = Dim<12, 4>;
+  if (!p.f.available || p.f.ntiers < 1) { err = "shard needs the scan kernels and at least two subtrees"; return -5; }
+  p.f.launches = 1;
+  cudaError_t e = launch_scan_leaf<12, 4>(p, s, b, 1, pack_rhs, st);
+  if (e == cudaSuccess) e = launch_tiers<12, 4>(p.f, s, b, 1, st, payload, (long long)fused_payload_doubles(12, 4));
+  if (e == cudaSuccess)
+    e = cudaMemcpyAsync(payload + D::ENT, b.knots + (size_t)(s.N - 1) * s.stride + s.oA, sizeof(double) * 12 * 16,
+                        cudaMemcpyDeviceToDevice, st);
+  if (e != cudaSuccess) { err = std::string("shard reduce: ") + cudaGetErrorString(e); return -3; }
+  return 0;
+}
+
+inline int scan_shard_finish(ScanPlan& p, const Shape& s, const Bufs& b, int pack_rhs, cudaStream_t st, const double* gathered,
+                             int rank, int nranks, std::string& err) {
+  using D = Dim<12, 4>;
+  if (!p.f.available || p.f.ntiers < 1) { err = "shard needs the scan kernels"; return -5; }
+  const double *left = nullptr, *right = nullptr;
+  cudaError_t e = cudaSuccess;
+  if (nranks > 1) {
+    e = tier_attr<12, 4>();
+    if (e == cudaSuccess) {
+      TierArgs a;
+      const long long pay = (long long)fused_payload_doubles(12, 4);
+      a.in = gathered; a.in_stride = pay;
+      a.ab = gathered + D::ENT; a.ab_stride = pay; a.ab_pstride = 0;
+      a.sep = p.f.xsep; a.sep_pstride = 0; a.sep_mul = 1;
+      a.out = nullptr; a.out_stride = 0;
+      a.Min = nranks; a.ecount = nranks; a.span = 0;
+      launch_tier<12, 4>(s, b, a, 1, st);
+      topdown_kernel<12><<<1, 128, 0, st>>>(p.f.xsep, p.f.xlam, nranks, nullptr, nullptr);
+      p.f.launches += 2;
+      left = p.f.xlam + (size_t)rank * 12;
+      right = p.f.xlam + (size_t)(rank + 1) * 12;
+    }
+  }
+  if (e == cudaSuccess) e = launch_scan_down<12, 4>(p, s, b, 1, pack_rhs, st, left, right);
+  if (e != cudaSuccess) { err = std::string("shard finish: ") + cudaGetErrorString(e); return -3; }
+  return 0;
+}
+
+}  // namespace rslqr

@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "kernels_fused.cuh"
+#include "kernels_scan.cuh"
 #include "kernels_staged.cuh"
 #include "kernels_staged_mma.cuh"
 
@@ -48,6 +49,7 @@ struct rslqr_cuda_solver {
   // dominant-kernel timing
   bool ktime_on; std::vector<std::pair<cudaEvent_t, cudaEvent_t>> kspans; double k_ms; int k_n;
   FusedPlan fused; int force_dfma;
+  ScanPlan scan; int g0_pref;
   bool shard; bool own_stream;
   int r_first, r_count;            // problem range the next enqueue covers (whole batch by default)
   cudaStream_t s_h2d, s_d2h; bool pipe_made; std::vector<cudaEvent_t> ev_up, ev_done; cudaEvent_t ev_join;
@@ -117,7 +119,16 @@ extern "C" int rslqr_cuda_create(int n, int m, int N, int batch, int device, uns
     const char* g0 = getenv("RSLQR_G0");
     const char* fd = getenv("RSLQR_FORCE_DFMA");
     h->force_dfma = fd ? atoi(fd) : 0;
-    if (fused_plan(h->s, h->batch, g0 ? atoi(g0) : 8, &h->fused, g_err)) {
+    memset(&h->scan, 0, sizeof(h->scan));
+    memset(&h->fused, 0, sizeof(h->fused));
+    if (scan_plan(h->s, h->batch, &h->scan, g_err)) {
+      rslqr_cuda_destroy(h);
+      return RSLQR_E_NOMEM;
+    }
+    // the tiered buffers (dense state of every knot) are allocated up front only for shapes the scan kernels
+    // do not cover; otherwise on the first set_mode(RSLQR_MODE_FUSED)
+    h->g0_pref = g0 ? atoi(g0) : 8;
+    if (!h->scan.f.available && fused_plan(h->s, h->batch, h->g0_pref, &h->fused, g_err)) {
       rslqr_cuda_destroy(h);
       return RSLQR_E_NOMEM;
     }
@@ -135,6 +146,7 @@ extern "C" int rslqr_cuda_destroy(rslqr_cuda_solver* h) {
   cudaFree(h->d_knots); cudaFree(h->d_x0); cudaFree(h->b.soln); cudaFree(h->b.fact);
   cudaFree(h->b.status); cudaFree(h->b.flags); cudaFree(h->b.leafd);
   fused_free(&h->fused);
+  scan_free(&h->scan);
   for (auto ev : h->evpool) cudaEventDestroy(ev);
   for (auto& pr : h->kspans) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
   if (h->marks_made) for (auto ev : h->marks) cudaEventDestroy(ev);
@@ -186,9 +198,14 @@ extern "C" int rslqr_cuda_reset(rslqr_cuda_solver* h) {
 }
 
 extern "C" int rslqr_cuda_set_mode(rslqr_cuda_solver* h, int mode) {
-  if (!h || mode < RSLQR_MODE_AUTO || mode > RSLQR_MODE_FUSED) return fail(RSLQR_E_ARG, "set_mode: bad argument");
+  if (!h || mode < RSLQR_MODE_AUTO || mode > RSLQR_MODE_SCAN) return fail(RSLQR_E_ARG, "set_mode: bad argument");
   if (mode == RSLQR_MODE_STAGED && !h->b.fact) return fail(RSLQR_E_UNSUPPORTED, "staged mode needs RSLQR_KEEP_FACT");
-  if (mode == RSLQR_MODE_FUSED && !h->fused.available) return fail(RSLQR_E_UNSUPPORTED, "shape is not covered by the tiered (fused) kernels");
+  if (mode == RSLQR_MODE_FUSED && !h->fused.available) {
+    CU(cudaSetDevice(h->device));
+    if (fused_plan(h->s, h->batch, h->g0_pref, &h->fused, g_err)) return RSLQR_E_NOMEM;
+    if (!h->fused.available) return fail(RSLQR_E_UNSUPPORTED, "shape is not covered by the tiered (fused) kernels");
+  }
+  if (mode == RSLQR_MODE_SCAN && !h->scan.f.available) return fail(RSLQR_E_UNSUPPORTED, "shape is not covered by the scan kernels");
   h->mode = mode;
   return RSLQR_OK;
 }
@@ -196,6 +213,7 @@ extern "C" int rslqr_cuda_set_mode(rslqr_cuda_solver* h, int mode) {
 extern "C" int rslqr_cuda_get_mode(rslqr_cuda_solver* h) {
   if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
   if (h->mode != RSLQR_MODE_AUTO) return h->mode;
+  if (h->scan.f.available) return RSLQR_MODE_SCAN;
   if (h->fused.available) return RSLQR_MODE_FUSED;
   return RSLQR_MODE_STAGED;
 }
@@ -328,6 +346,29 @@ extern "C" int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs) {
   h->spans.clear();
   h->evused = 0;
   const int mode = rslqr_cuda_get_mode(h);
+  if (mode == RSLQR_MODE_SCAN) {
+    std::pair<cudaEvent_t, cudaEvent_t> kt;
+    if (h->ktime_on) { cudaEventCreate(&kt.first); cudaEventCreate(&kt.second); }
+    const Shape& s = h->s;
+    const size_t f = (size_t)h->r_first;
+    Bufs b = h->b;
+    b.knots += f * s.N * s.stride; b.x0 += f * s.n; b.soln += f * s.N * s.zs;
+    b.status += f * 3 * s.N; b.flags += f; b.leafd += f * s.N * (s.n + s.m);
+    ScanPlan q = h->scan;
+    {
+      const size_t ent = fused_ent_doubles(s.n, s.m), wsz = (2 * (size_t)s.n + 1) * s.n;
+      q.f.fb.sep += f * q.f.M0 * wsz; q.f.fb.lamhat += f * (q.f.M0 + 1) * s.n;
+      q.sb.sep_in += f * q.f.M0 * 3 * wsz; q.sb.ent0 += f * q.f.M0 * ent;
+      q.f.fb.ent[0] = q.sb.ent0;
+      for (int t = 1; t < q.f.ntiers; ++t) q.f.fb.ent[t] += f * q.f.tiers[t].Min * ent;
+    }
+    int rc = scan_launch(q, s, b, h->r_count, pack_rhs, h->stream, g_err, h->ktime_on ? kt.first : nullptr,
+                         h->ktime_on ? kt.second : nullptr);
+    if (h->ktime_on) h->kspans.push_back(kt);
+    if (rc) return rc;
+    h->launches = q.f.launches;
+    return RSLQR_OK;
+  }
   if (mode == RSLQR_MODE_FUSED) {
     std::pair<cudaEvent_t, cudaEvent_t> kt;
     if (h->ktime_on) { cudaEventCreate(&kt.first); cudaEventCreate(&kt.second); }
@@ -617,10 +658,10 @@ extern "C" int rslqr_cuda_create_shard(int n, int m, int nhorizon, int first_kno
   int rc = rslqr_cuda_create(n, m, shard_knots, 1, device, flags & ~RSLQR_KEEP_FACT, out);
   if (rc) return rc;
   rslqr_cuda_solver* h = *out;
-  if (!h->fused.available || h->fused.ntiers < 1) {
+  if (!(h->scan.f.available && h->scan.f.ntiers >= 1) && !(h->fused.available && h->fused.ntiers >= 1)) {
     rslqr_cuda_destroy(h);
     *out = nullptr;
-    return fail(RSLQR_E_UNSUPPORTED, "shards need a shape covered by the tiered kernels");
+    return fail(RSLQR_E_UNSUPPORTED, "shards need a shape covered by the scan or tiered kernels");
   }
   h->shard = true;
   h->s.kofs = first_knot;
@@ -635,6 +676,11 @@ extern "C" size_t rslqr_cuda_shard_payload_doubles(rslqr_cuda_solver* h) {
 extern "C" int rslqr_cuda_shard_reduce(rslqr_cuda_solver* h, double* d_payload) {
   if (!h || !d_payload || !h->shard) return fail(RSLQR_E_ARG, "shard_reduce: bad argument");
   CU(cudaSetDevice(h->device));
+  if (rslqr_cuda_get_mode(h) == RSLQR_MODE_SCAN) {
+    int rc = scan_shard_reduce(h->scan, h->s, h->b, 1, h->stream, d_payload, g_err);
+    h->launches = h->scan.f.launches;
+    return rc;
+  }
   int rc = fused_shard_reduce(h->fused, h->s, h->b, 1, h->force_dfma, h->stream, d_payload, g_err);
   h->launches = h->fused.launches;
   return rc;
@@ -645,6 +691,11 @@ extern "C" int rslqr_cuda_shard_finish(rslqr_cuda_solver* h, const double* d_gat
       (nranks > 1 && !d_gathered) || h->s.kofs != rank * h->s.N || h->s.Ng != nranks * h->s.N)
     return fail(RSLQR_E_ARG, "shard_finish: bad argument (rank / nranks must match the shard's position; nranks <= 8)");
   CU(cudaSetDevice(h->device));
+  if (rslqr_cuda_get_mode(h) == RSLQR_MODE_SCAN) {
+    int rc = scan_shard_finish(h->scan, h->s, h->b, 1, h->stream, d_gathered, rank, nranks, g_err);
+    h->launches = h->scan.f.launches;
+    return rc;
+  }
   int rc = fused_shard_finish(h->fused, h->s, h->b, h->stream, d_gathered, rank, nranks, g_err);
   h->launches = h->fused.launches;
   return rc;

@@ -16,7 +16,7 @@ if not os.path.exists(LIB_PATH):
         "(make -C rslqr_b200/csrc). There is no Python or CPU fallback for the solve path.")
 LIB = C.CDLL(LIB_PATH)
 
-MODE_AUTO, MODE_STAGED, MODE_FUSED = 0, 1, 2
+MODE_AUTO, MODE_STAGED, MODE_FUSED, MODE_SCAN = 0, 1, 2, 3
 KEEP_FACT, PROFILE = 1, 2
 STAGE = dict(PACK_RHS=0, LEAVES=1, PRODUCTS=2, CHOLESKY=3, SOLVES=4, SCHUR=5,
              RHS_PRODUCTS=6, RHS_SOLVES=7, RHS_SCHUR=8)

@@ -18,11 +18,12 @@ TOL = 1e-10
 
 def _modes(solver):
     out = [R.MODE_STAGED]
-    try:
-        solver.set_mode(R.MODE_FUSED)
-        out.append(R.MODE_FUSED)
-    except R.RslqrError:
-        pass
+    for mode in (R.MODE_FUSED, R.MODE_SCAN):
+        try:
+            solver.set_mode(mode)
+            out.append(mode)
+        except R.RslqrError:
+            pass
     return out
 
 
@@ -177,12 +178,32 @@ def test_tiered_path_variants(shape, g0, dfma, monkeypatch):
     s.close()
 
 
-def test_tiered_path_reports_cholesky_failure():
+@pytest.mark.parametrize("N", [4, 8, 16, 32, 64, 128, 256, 512, 4096])
+def test_scan_path_all_horizons(N):
+    # the scan path (one warp per 4-knot subtree, boundary entries at every level) from a single subtree (N = 4)
+    # to four tiers above the leaves, against the oracle; batch 7 also exercises partially filled CTAs
+    n, m, B = 12, 4, 7
+    kn, x0 = R.synth_problems(n, m, N, 78, 0, B)
+    s = R.CudaSolver(n, m, N, batch=B, flags=0)
+    assert s.mode == R.MODE_SCAN        # the default for the covered shape
+    s.upload(kn, x0)
+    s.solve()
+    z = s.solution()
+    assert not s.flags().any()
+    for p in range(B):
+        want, _ = O.port_solve(n, m, N, kn[p], x0[p], threads=2)
+        assert max(rel_err_classes(z[p], want, n, m, N)) < TOL, (N, p)
+        assert O.kkt_residual(n, m, N, kn[p], x0[p], z[p]) < 1e-10 * np.linalg.norm(z[p])
+    s.close()
+
+
+@pytest.mark.parametrize("mode", [R.MODE_FUSED, R.MODE_SCAN])
+def test_tiered_path_reports_cholesky_failure(mode):
     n, m, N = 12, 4, 64
     kn, x0 = R.synth_problems(n, m, N, 1, 0, 3)
     kn[1, 3, 2] = -1.0      # Q[2] of knot 3 of problem 1: leaf factorization fails
     s = R.CudaSolver(n, m, N, batch=3, flags=0)
-    s.set_mode(R.MODE_FUSED)
+    s.set_mode(mode)
     s.upload(kn, x0)
     s.solve()
     fl = s.flags()
@@ -357,7 +378,7 @@ def test_c_consumer_flow_runs(tmp_path):
         assert r.returncode == 0, (name, r.returncode, r.stdout, r.stderr)
 
 
-@pytest.mark.parametrize("mode", [R.MODE_FUSED, R.MODE_STAGED])
+@pytest.mark.parametrize("mode", [R.MODE_SCAN, R.MODE_FUSED, R.MODE_STAGED])
 def test_solve_host_pipeline_matches_resident_solve(mode):
     # the chunked host-to-host call (copies overlapped with kernels) returns bit-identical solutions
     n, m, N, B = 12, 4, 64, 37
