@@ -130,13 +130,16 @@ __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync
 //   Lsm   : NS*NS doubles of scratch for Lt (row-major); Wout: [f_L | f_R | zs] column-major ld NS
 // Returns non-zero (warp-uniform) when a pivot is <= 0 (reference: clap_CholeskyFactorize fails).
 // ---------------------------------------------------------------------------------------------------------
-template <int NS, int NI>
+template <int NS, int NI, bool LDG = true>
 __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const double* LXi, const double* RXi,
                                            const double* zxi, const double* LXn, const double* RXn,
                                            const double* zxn, const double* zln, double* Lsm, double* Wout) {
   static_assert(2 * NS + 1 <= 32, "one warp per separator needs 2n+1 <= 32");
   const int lane = threadIdx.x & 31;
   const int c = lane < NS ? lane : (lane < 2 * NS ? lane - NS : 0);
+  auto ldab = [](const double* p) -> double {  // [A|B] lives in global memory (read-only path) or in shared memory
+    if constexpr (LDG) return __ldg(p); else return *p;
+  };
   const double* src;
   int ss;
   if (lane < NS) { src = RXi + c; ss = NS; }
@@ -158,8 +161,8 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
 #pragma unroll
     for (int ks = 0; ks < KS; ++ks) {
       const int l = 4 * ks + q;
-      const double a0 = __ldg(AB + l * NS + rr);
-      const double a1 = (8 + rr < NS) ? __ldg(AB + l * NS + 8 + rr) : 0.0;
+      const double a0 = ldab(AB + l * NS + rr);
+      const double a1 = (8 + rr < NS) ? ldab(AB + l * NS + 8 + rr) : 0.0;
       double bf[4];
 #pragma unroll
       for (int nt = 0; nt < 4; ++nt) {
@@ -194,7 +197,7 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
       const double x = src[l * ss];
       const double* col = AB + l * NS;  // column l of [A | B] (B follows A, both have NS rows)
 #pragma unroll
-      for (int r = 0; r < NS; ++r) acc[r] = fma(__ldg(col + r), x, acc[r]);
+      for (int r = 0; r < NS; ++r) acc[r] = fma(ldab(col + r), x, acc[r]);
     }
   }
   const int mycol = lane <= 2 * NS ? lane : 2 * NS;

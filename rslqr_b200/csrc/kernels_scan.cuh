@@ -88,41 +88,77 @@ __device__ __forceinline__ double scan_rhs(const Shape& s, const Bufs& b, int pr
   return (s.kofs + k < s.Ng - 1) ? -kn[s.orr + rw - 2 * s.n] : 0.0;
 }
 
-// Per-lane leaf quantities of one knot (ndlqr_SolveLeaf on diagonal Q, R): lane l < NS+NI holds
-//   dinv = 1/Q[l] (l < NS) or 1/R[l-NS];  zi = entry l of the leaf-solved (z_x | z_u);  zl = z_lambda[l] (l < NS)
-struct LeafLane { double dinv, zi, zl; };
-
+// ---------------------------------------------------------------------------------------------------------
+// Shared-memory image of a warp's SCAN_LEAF flat knot blocks, brought in by ONE TMA bulk copy and rewritten in
+// place into what the leaf stage needs (ndlqr_SolveLeaf on diagonal Q, R, src/nested_dissection.c:10-105, with
+// the rhs packing of src/solver.c:138-190):
+//   region R = [ 12 doubles | block 0 | block 1 | ... ],  block j at R + NS + j*STRIDE  (STRIDE = flat knot block)
+//   block:  [0, NS+NI)        1/Q, 1/R            (was Q, R; 1/R = 0 on the last knot of the horizon)
+//           [NS+NI, 2(NS+NI)) leaf-solved z_x, z_u (was q, r)
+//           [OA, OD)          A, B column-major    (untouched)
+//           [OD, OD+NS)       z_lambda of the NEXT knot = -d   (was d)
+//   R[0..NS)                  z_lambda of block 0 (from the knot before the subtree, x0 or the knot-0 special)
+// Because OD + NS == STRIDE, z_lambda of block j is R + j*STRIDE for every j.
+// ---------------------------------------------------------------------------------------------------------
 template <int NS, int NI>
-__device__ __forceinline__ LeafLane leaf_lane(const Shape& s, const Bufs& b, int prob, int k, int pack_rhs, bool check) {
+struct RawDim {
+  static constexpr int VEC = 2 * NS + 2 * NI, AB = NS * (NS + NI);
+  static constexpr int STRIDE = VEC + 1 + AB + NS;
+  static constexpr int OZ = NS + NI, OA = VEC + 1, OD = OA + AB;
+  static_assert(OD + NS == STRIDE, "z_lambda of block j sits at R + j*STRIDE");
+};
+
+template <int NS, int NI, int NK>
+__device__ __forceinline__ void leaf_transform(const Shape& s, const Bufs& b, int prob, int k0, int pack_rhs, double* R) {
+  using RD = RawDim<NS, NI>;
+  constexpr int XU = NS + NI;
+  static_assert(XU == 16, "one half-warp per knot");
   const int lane = threadIdx.x & 31;
-  LeafLane o;
-  o.dinv = 0.0; o.zi = 0.0; o.zl = 0.0;
-  const int kg = s.kofs + k;
-  const bool last = kg == s.Ng - 1;
-  if (lane < NS + NI) {
-    const double* kn = knot_ptr(s, b, prob, k);
-    const double d = __ldg(kn + lane);  // Q then R are the first NS+NI doubles of the block
-    const bool isR = lane >= NS;
-    if (check && !(d > 0.0) && !(isR && last)) {
-      b.status[(size_t)prob * 3 * s.N + (isR ? rs_slot_R(k) : rs_slot_Q(k))] = -1;
+  const int N = s.N;
+  // z_lambda: -d in place, or the caller's rhs
+#pragma unroll 1
+  for (int it = lane; it < NK * NS; it += 32) {
+    const int j = it / NS, r = it - j * NS;
+    double v;
+    if (!pack_rhs) v = soln_ptr(s, b, prob, k0 + j)[r];
+    else if (j == 0) v = -(k0 == 0 ? b.x0[(size_t)prob * NS + r] : __ldg(knot_ptr(s, b, prob, k0) - RD::STRIDE + RD::OD + r));
+    else v = -R[j * RD::STRIDE + r];
+    R[j * RD::STRIDE + r] = v;
+  }
+  __syncwarp();
+#pragma unroll 1
+  for (int it = lane; it < NK * XU; it += 32) {
+    const int j = it >> 4, l = it & 15;
+    const int k = k0 + j, kg = s.kofs + k;
+    const bool last = kg == s.Ng - 1, isR = l >= NS;
+    double* B = R + NS + j * RD::STRIDE;
+    const double d = B[l];
+    if (!(d > 0.0) && !(isR && last)) {
+      b.status[(size_t)prob * 3 * N + (isR ? rs_slot_R(k) : rs_slot_Q(k))] = -1;
       b.flags[prob] = 1;
     }
-    o.dinv = (isR && last) ? 0.0 : 1.0 / d;
-    const double rx = scan_rhs(s, b, prob, k, NS + lane, pack_rhs);  // rhs of the x / u row
+    const double dinv = (isR && last) ? 0.0 : 1.0 / d;
+    double rx;
+    if (!pack_rhs) rx = soln_ptr(s, b, prob, k)[NS + l];
+    else rx = (isR && last) ? 0.0 : -B[RD::OZ + l];
+    double zi;
     if (kg == 0) {
-      const double rl = lane < NS ? scan_rhs(s, b, prob, k, lane, pack_rhs) : 0.0;
-      if (lane < NS) { o.zi = -rl; o.zl = -d * rl - rx; }
-      else o.zi = rx * o.dinv;
+      if (!isR) {
+        const double rl = R[l];  // rhs_lambda of knot 0 (-x0)
+        zi = -rl;
+        R[l] = -d * rl - rx;     // z_lambda(0) = Q x0 + q
+      } else zi = rx * dinv;
     } else {
-      if (lane < NS) { o.zi = rx * o.dinv; o.zl = scan_rhs(s, b, prob, k, lane, pack_rhs); }
-      else o.zi = last ? rx : rx * o.dinv;
+      zi = (isR && last) ? rx : rx * dinv;
     }
+    B[l] = dinv;
+    B[RD::OZ + l] = zi;
   }
-  return o;
+  __syncwarp();
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Level-0 merge of two single knots i (left) and i+1 (right), straight from their flat blocks:
+// Level-0 merge of two single knots i (left) and i+1 (right), straight from their transformed blocks Bl, Br:
 //   S   = A_i Q_i^-1 A_i^T + B_i R_i^-1 B_i^T + Q_{i+1}^-1      (ndlqr_FactorInnerProduct on the leaf factors)
 //   S_L = -A_i Q_i^-1,   S_R = -Q_{i+1}^-1 A_{i+1}^T,   s = A_i z_x(i) + B_i z_u(i) - z_x(i+1) - z_lambda(i+1)
 //   [f_L f_R zs] = S^-1 [S_L S_R s]                               (Cholesky + ndlqr_SolveCholeskyFactor)
@@ -130,26 +166,30 @@ __device__ __forceinline__ LeafLane leaf_lane(const Shape& s, const Bufs& b, int
 //         rows X(i+1) :  Q_{i+1}^-1 ([0|A_{i+1}^T] + [f_L f_R]),  z_x(i+1) + Q_{i+1}^-1 zs
 //         rows U(i+1) :  [0 | R_{i+1}^-1 B_{i+1}^T],  z_u(i+1)                              (unchanged)
 // Knot 0 has X_R = 0 and Lambda = -A_0^T (src/nested_dissection.c:24-59): its X rows stay (0, 0, x0).
-// The last knot of the horizon has R(k) = 0. ABl / ABr: [A|B] of the two knots (column-major, NS rows).
-// E: output entry (Dim::ENT layout), Wf: [f_L | f_R | zs] on return, Lsm: NS*NS scratch.
+// The last knot of the horizon has R(k) = 0. zlL / zlR: z_lambda of the two knots.
+// E: output entry (Dim::ENT layout; its head doubles as the factor scratch), Wf: [f_L | f_R | zs] on return.
 // ---------------------------------------------------------------------------------------------------------
 template <int NS, int NI>
-__device__ __forceinline__ int merge_raw(const double* __restrict__ ABl, const double* __restrict__ ABr, const LeafLane& ll,
-                                         const LeafLane& lr, bool first0, bool lastR, double* E, double* Lsm, double* Wf) {
+__device__ __forceinline__ int merge_raw(const double* Bl, const double* Br, const double* zlL, const double* zlR, bool first0,
+                                         bool lastR, double* E, double* Wf) {
   using D = Dim<NS, NI>;
+  using RD = RawDim<NS, NI>;
   constexpr int ZS = D::ZS, SLOT = D::SLOT;
   constexpr int KS = (NS + NI) / 4, KA = NS / 4;
-  static_assert(NS % 4 == 0 && (NS + NI) % 4 == 0 && NS > 8 && NS <= 16 && ((NS + NI) * 2 * NS) % 32 == 0, "tile shapes");
+  static_assert(NS % 4 == 0 && (NS + NI) % 4 == 0 && NS > 8 && NS <= 16 && 2 * NS == 24 && NS + NI == 16, "tile shapes");
   const int lane = threadIdx.x & 31, q = lane & 3, rr = lane >> 2;
   const bool r1 = 8 + rr < NS;  // second row tile is partial
+  const double* ABl = Bl + RD::OA;
+  const double* ABr = Br + RD::OA;
+  double* Lsm = E;
   double acc[NS];
   {
     double a0[KS], a1[KS];
 #pragma unroll
     for (int ks = 0; ks < KS; ++ks) {
       const int l = 4 * ks + q;
-      a0[ks] = __ldg(ABl + l * NS + rr);
-      a1[ks] = r1 ? __ldg(ABl + l * NS + 8 + rr) : 0.0;
+      a0[ks] = ABl[l * NS + rr];
+      a1[ks] = r1 ? ABl[l * NS + 8 + rr] : 0.0;
     }
     double d[2][2][2];
 #pragma unroll
@@ -159,9 +199,9 @@ __device__ __forceinline__ int merge_raw(const double* __restrict__ ABl, const d
     double p0 = 0.0, p1 = 0.0;
 #pragma unroll
     for (int ks = 0; ks < KS; ++ks) {
-      double dk = shfl_d(ll.dinv, 4 * ks + q);
+      double dk = Bl[4 * ks + q];
       if (first0 && ks < KA) dk = 0.0;  // X_R(0) = 0
-      const double zk = shfl_d(ll.zi, 4 * ks + q);
+      const double zk = Bl[RD::OZ + 4 * ks + q];
       const double b0 = a0[ks] * dk, b1 = a1[ks] * dk;
       dmma884(d[0][0][0], d[0][0][1], a0[ks], b0);
       dmma884(d[0][1][0], d[0][1][1], a0[ks], b1);
@@ -177,8 +217,8 @@ __device__ __forceinline__ int merge_raw(const double* __restrict__ ABl, const d
 #pragma unroll
     for (int mt = 0; mt < 2; ++mt) {
       const int row = 8 * mt + rr, rs = row < NS ? row : 0;
-      const double dr = shfl_d(lr.dinv, rs);
-      const double t = shfl_d(lr.zi, rs) + shfl_d(lr.zl, rs);
+      const double dr = Br[rs];
+      const double t = Br[RD::OZ + rs] + zlR[rs];
 #pragma unroll
       for (int nt = 0; nt < 2; ++nt)
 #pragma unroll
@@ -188,11 +228,11 @@ __device__ __forceinline__ int merge_raw(const double* __restrict__ ABl, const d
         }
       if (q == 0 && row < NS) Wf[2 * NS * NS + row] = (mt ? p1 : p0) - t;
     }
-    const int cl = (lane >= NS && lane < 2 * NS) ? lane - NS : 0;
-    const double dcs = shfl_d(ll.dinv, cl);
     if (lane >= NS && lane < 2 * NS) {
+      const int cl = lane - NS;
+      const double dcs = first0 ? 0.0 : -Bl[cl];
 #pragma unroll
-      for (int r = 0; r < NS; ++r) Wf[lane * NS + r] = first0 ? 0.0 : -__ldg(ABl + cl * NS + r) * dcs;
+      for (int r = 0; r < NS; ++r) Wf[lane * NS + r] = ABl[cl * NS + r] * dcs;
     }
     __syncwarp();
     const int mc = lane < NS ? lane : 0;
@@ -201,8 +241,7 @@ __device__ __forceinline__ int merge_raw(const double* __restrict__ ABl, const d
     __syncwarp();
   }
   const int bad = spine_factor_solve<NS>(acc, Lsm, Wf, [&](int r, int c) -> double {
-    const double dr = shfl_d(lr.dinv, r);
-    return lastR ? 0.0 : -__ldg(ABr + r * NS + c) * dr;
+    return lastR ? 0.0 : -ABr[r * NS + c] * Br[r];
   });
   // ---- entry rows X(i): A_i^T [f_L f_R] on DMMA ----
   {
@@ -213,13 +252,12 @@ __device__ __forceinline__ int merge_raw(const double* __restrict__ ABl, const d
       for (int nt = 0; nt < 3; ++nt) bf[ks][nt] = Wf[(8 * nt + rr) * NS + 4 * ks + q];
       zq[ks] = Wf[2 * NS * NS + 4 * ks + q];
     }
-    static_assert(2 * NS == 24, "three column tiles");
 #pragma unroll
     for (int mt = 0; mt < 2; ++mt) {
       const int row = 8 * mt + rr, rs = row < NS ? row : 0;
       double at[KA];
 #pragma unroll
-      for (int ks = 0; ks < KA; ++ks) at[ks] = row < NS ? __ldg(ABl + row * NS + 4 * ks + q) : 0.0;
+      for (int ks = 0; ks < KA; ++ks) at[ks] = row < NS ? ABl[rs * NS + 4 * ks + q] : 0.0;
       double c[3][2];
 #pragma unroll
       for (int nt = 0; nt < 3; ++nt) c[nt][0] = c[nt][1] = 0.0;
@@ -232,8 +270,8 @@ __device__ __forceinline__ int merge_raw(const double* __restrict__ ABl, const d
       }
       part += __shfl_xor_sync(0xffffffffu, part, 1);
       part += __shfl_xor_sync(0xffffffffu, part, 2);
-      const double dl = first0 ? 0.0 : shfl_d(ll.dinv, rs);
-      const double zrow = shfl_d(ll.zi, rs);
+      const double dl = first0 ? 0.0 : Bl[rs];
+      const double zrow = Bl[RD::OZ + rs];
       if (row < NS) {
 #pragma unroll
         for (int nt = 0; nt < 3; ++nt) {
@@ -247,25 +285,36 @@ __device__ __forceinline__ int merge_raw(const double* __restrict__ ABl, const d
       }
     }
   }
-  // ---- entry rows X(i+1), U(i+1): row scalings ----
-#pragma unroll 4
-  for (int e = lane; e < (NS + NI) * 2 * NS; e += 32) {
-    const int row = e / (2 * NS), col = e - row * 2 * NS;
-    const double dr = shfl_d(lr.dinv, row);
-    const double a = (col >= NS && !lastR) ? __ldg(ABr + row * NS + col - NS) : 0.0;  // A_{i+1}(c,r) / B_{i+1}(c,r-NS)
-    const double f = row < NS ? Wf[col * NS + row] : 0.0;
-    double* dst = col < NS ? E + (NS + row) * NS + col : E + SLOT + (NS + row) * NS + col - NS;
-    *dst = dr * (f + a);
-  }
+  // ---- entry rows X(i+1), U(i+1): row scalings. Element e = lane + 32 t of the 16 x 24 block [L | R]; since
+  //      96 = 4 * 24, the (row, col) pattern repeats every three steps with the row advanced by 4 ----
   {
+    int ro[3], co[3];
+#pragma unroll
+    for (int u = 0; u < 3; ++u) {
+      const int e = lane + 32 * u;
+      ro[u] = e / (2 * NS);
+      co[u] = e - ro[u] * 2 * NS;
+    }
+#pragma unroll
+    for (int tt = 0; tt < (NS + NI) / 4; ++tt)
+#pragma unroll
+      for (int u = 0; u < 3; ++u) {
+        const int row = 4 * tt + ro[u], col = co[u];
+        const double dr = Br[row];
+        const double a = (col >= NS && !lastR) ? ABr[row * NS + col - NS] : 0.0;  // A_{i+1}(c,r) / B_{i+1}(c,r-NS)
+        const double f = row < NS ? Wf[col * NS + row] : 0.0;
+        double* dst = col < NS ? E + (NS + row) * NS + col : E + SLOT + (NS + row) * NS + col - NS;
+        *dst = dr * (f + a);
+      }
     const int rs = lane < NS ? lane : 0;
     const double zs = Wf[2 * NS * NS + rs];
-    if (lane < NS + NI) E[2 * SLOT + NS + lane] = lane < NS ? fma(lr.dinv, zs, lr.zi) : lr.zi;
-    if (lane < NS) E[2 * SLOT + ZS + lane] = ll.zl;
+    if (lane < NS + NI) E[2 * SLOT + NS + lane] = lane < NS ? fma(Br[lane], zs, Br[RD::OZ + lane]) : Br[RD::OZ + lane];
+    if (lane < NS) E[2 * SLOT + ZS + lane] = zlL[lane];
   }
   __syncwarp();
   return bad;
 }
+
 
 // one row of the lean Schur update with separate source and destination (the right subtree's rows move into
 // the merged entry): dst <- keep - own * [f_L f_R zs]; side 0: own = R block (keep L), side 1: own = L block
@@ -304,68 +353,99 @@ struct ScanBufs {
 constexpr int SCAN_LEAF = 4;   // knots per warp in the leaf kernel
 constexpr int SCAN_WPC = 5;    // warps per CTA (independent of each other; sized for shared memory)
 
+// per warp: [NS | SCAN_LEAF flat knot blocks | entry 0 | entry 1 | W]
 template <int NS, int NI>
-constexpr int scan_leaf_smem_doubles() {
+__host__ __device__ constexpr int scan_leaf_warp_doubles() {
   using D = Dim<NS, NI>;
-  return SCAN_WPC * (2 * D::ENT + D::WSZ + NS * NS);
+  return NS + SCAN_LEAF * RawDim<NS, NI>::STRIDE + 2 * D::ENT + D::WSZ;
 }
+template <int NS, int NI>
+__host__ __device__ constexpr int scan_leaf_smem_doubles() { return SCAN_WPC * scan_leaf_warp_doubles<NS, NI>(); }
 
 template <int NS, int NI>
-__global__ void __launch_bounds__(32 * SCAN_WPC, 3) scan_leaf_kernel(Shape s, Bufs b, ScanBufs sb, int pack_rhs, int M0,
+__global__ void __launch_bounds__(32 * SCAN_WPC, 2) scan_leaf_kernel(Shape s, Bufs b, ScanBufs sb, int pack_rhs, int M0,
                                                                       long long nsub) {
   using D = Dim<NS, NI>;
+  using RD = RawDim<NS, NI>;
   constexpr int ZS = D::ZS, SLOT = D::SLOT, WSZ = D::WSZ, ENT = D::ENT;
+  constexpr int RAWB = SCAN_LEAF * RD::STRIDE * (int)sizeof(double);
+  static_assert(RAWB % 16 == 0 && (NS * 8) % 16 == 0 && scan_leaf_warp_doubles<NS, NI>() % 2 == 0 && (WSZ * 8) % 16 == 0, "TMA alignment");
   extern __shared__ __align__(16) double smf[];
+  __shared__ __align__(8) unsigned long long mbar[SCAN_WPC];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long sub = (long long)blockIdx.x * SCAN_WPC + warp;
   if (sub >= nsub) return;
-  double* E0 = smf + warp * (2 * ENT + WSZ + NS * NS);
+  double* R = smf + warp * scan_leaf_warp_doubles<NS, NI>();
+  double* E0 = R + NS + SCAN_LEAF * RD::STRIDE;
   double* E1 = E0 + ENT;
   double* Wf = E1 + ENT;
-  double* Lsm = Wf + WSZ;
   const int prob = (int)(sub / M0), grp = (int)(sub - (long long)prob * M0);
   const int k0 = grp * SCAN_LEAF;
   const int N = s.N;
+  // one TMA bulk copy brings the subtree's flat knot blocks (contiguous in HBM) into shared memory
+  if (lane == 0) {
+    mbar_init(&mbar[warp], 1);
+    fence_mbar_init();
+    mbar_expect_tx(&mbar[warp], RAWB);
+    bulk_g2s(R + NS, knot_ptr(s, b, prob, k0), RAWB, &mbar[warp]);
+  }
+  __syncwarp();
+  mbar_wait(&mbar[warp], 0);
+  leaf_transform<NS, NI, SCAN_LEAF>(s, b, prob, k0, pack_rhs, R);
   double* rec = sb.sep_in + ((size_t)prob * M0 + grp) * 3 * WSZ;
+  // record [f_L | f_R | zs] of a separator: TMA bulk store straight out of W; W may be rewritten once the copy
+  // engine has read it (wait_read), which happens before the next merge starts
+  auto store_rec = [&](int slot) {
+    fence_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      bulk_s2g(rec + slot * WSZ, Wf, WSZ * (int)sizeof(double));
+      bulk_commit();
+    }
+  };
+  auto rec_done = [&]() {
+    if (lane == 0) bulk_wait_read0();
+    __syncwarp();
+  };
   int bad;
   // ---- level 0: (k0, k0+1) -> E0, (k0+2, k0+3) -> E1 ----
 #pragma unroll 1
   for (int h = 0; h < 2; ++h) {
     const int k = k0 + 2 * h;
-    const LeafLane ll = leaf_lane<NS, NI>(s, b, prob, k, pack_rhs, true);
-    const LeafLane lr = leaf_lane<NS, NI>(s, b, prob, k + 1, pack_rhs, true);
-    const double* kl = knot_ptr(s, b, prob, k);
-    bad = merge_raw<NS, NI>(kl + s.oA, kl + s.stride + s.oA, ll, lr, s.kofs + k == 0, s.kofs + k + 1 == s.Ng - 1,
-                            h ? E1 : E0, Lsm, Wf);
-    for (int e = lane; e < WSZ; e += 32) rec[(2 * h) * WSZ + e] = Wf[e];
+    const double* Bl = R + NS + (2 * h) * RD::STRIDE;
+    bad = merge_raw<NS, NI>(Bl, Bl + RD::STRIDE, R + (2 * h) * RD::STRIDE, R + (2 * h + 1) * RD::STRIDE, s.kofs + k == 0,
+                            s.kofs + k + 1 == s.Ng - 1, h ? E1 : E0, Wf);
+    store_rec(2 * h);
     if (bad && lane == 0) {
       b.status[(size_t)prob * 3 * N + rs_slot_S(k >> 1, 0, N)] = -1;
       b.flags[prob] = 1;
     }
-    __syncwarp();
+    rec_done();
   }
-  // ---- level 1: E0 + E1 -> E0 (separator after knot k0+1) ----
-  bad = spine_merge<NS, NI>(knot_ptr(s, b, prob, k0 + 1) + s.oA, E0 + NS * NS, E0 + SLOT + NS * NS, E0 + 2 * SLOT + NS, E1,
-                            E1 + SLOT, E1 + 2 * SLOT, E1 + 2 * SLOT + ZS, Lsm, Wf);
-  for (int e = lane; e < WSZ; e += 32) rec[WSZ + e] = Wf[e];
+  // ---- level 1: E0 + E1 -> E0 (separator after knot k0+1); block 0 is dead and serves as the factor scratch ----
+  bad = spine_merge<NS, NI, false>(R + NS + RD::STRIDE + RD::OA, E0 + NS * NS, E0 + SLOT + NS * NS, E0 + 2 * SLOT + NS, E1,
+                                   E1 + SLOT, E1 + 2 * SLOT, E1 + 2 * SLOT + ZS, R + NS + RD::OA, Wf);
+  store_rec(1);
   if (bad && lane == 0) {
     b.status[(size_t)prob * 3 * N + rs_slot_S(k0 >> 2, 1, N)] = -1;
     b.flags[prob] = 1;
   }
-  if (M0 == 1) return;  // a single subtree is the whole problem: only the records are needed
-  if (lane < ZS) {
-    const double* S = lane < NS ? E0 : E1;
-    schur_row_io<NS>(S + lane * NS, S + SLOT + lane * NS, S + 2 * SLOT + lane, E0 + lane * NS, E0 + SLOT + lane * NS,
-                     E0 + 2 * SLOT + lane, Wf, lane < NS ? 0 : 1);
+  if (M0 > 1) {  // (a single subtree is the whole problem: only the records are needed)
+    if (lane < ZS) {
+      const double* S = lane < NS ? E0 : E1;
+      schur_row_io<NS>(S + lane * NS, S + SLOT + lane * NS, S + 2 * SLOT + lane, E0 + lane * NS, E0 + SLOT + lane * NS,
+                       E0 + 2 * SLOT + lane, Wf, lane < NS ? 0 : 1);
+    }
+    fence_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      bulk_s2g(sb.ent0 + ((size_t)prob * M0 + grp) * ENT, E0, ENT * (int)sizeof(double));
+      bulk_commit();
+    }
   }
-  fence_async_smem();
-  __syncwarp();
-  if (lane == 0) {
-    bulk_s2g(sb.ent0 + ((size_t)prob * M0 + grp) * ENT, E0, ENT * (int)sizeof(double));
-    bulk_commit();
-    bulk_wait_read0();
-  }
+  if (lane == 0) bulk_wait_read0();  // shared memory must stay valid until the copy engine has read it
 }
+
 
 // ---------------------------------------------------------------------------------------------------------
 // Down: one warp = one 4-knot subtree [4g, 4g+3]. lam[g], lam[g+1] are the multipliers of the separators
