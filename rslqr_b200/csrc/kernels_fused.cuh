@@ -114,6 +114,56 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
 
 __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 
+// ---- factor scratch with 128-bit broadcast loads: F = [Lr (NS*NS) | Lc (NS*NS) | Dv (NS)] -------------------
+// Lr row-major (row j = Lt(j, .), for the backward sweep), Lc column-major (column j = Lt(., j), for the forward
+// sweep), Dv = 1/D. Every sweep step then reads two factor entries per shared-memory wavefront instead of one.
+template <int NS>
+__host__ __device__ constexpr int factor_scratch_doubles() { return 2 * NS * NS + NS + (NS & 1); }
+
+template <int NS>
+__device__ __forceinline__ void store_factor2(const double (&acc)[NS], double* F) {
+  static_assert(NS % 2 == 0, "pairs");
+  const int lane = threadIdx.x & 31;
+  if (lane < NS) {
+#pragma unroll
+    for (int k = 0; k < NS; k += 2) *reinterpret_cast<double2*>(F + lane * NS + k) = make_double2(acc[k], acc[k + 1]);
+#pragma unroll
+    for (int k = 0; k < NS; ++k) F[NS * NS + k * NS + lane] = acc[k];
+  }
+}
+
+// acc (one right-hand-side column per lane) <- Lt^-T D^-1 Lt^-1 acc
+template <int NS>
+__device__ __forceinline__ void tri_solves2(double (&acc)[NS], const double* F) {
+  const double* Lr = F;
+  const double* Lc = F + NS * NS;
+  const double* Dv = F + 2 * NS * NS;
+#pragma unroll
+  for (int j = 0; j < NS - 1; ++j) {
+#pragma unroll
+    for (int p = (j + 1) & ~1; p < NS; p += 2) {
+      const double2 l = *reinterpret_cast<const double2*>(Lc + j * NS + p);
+      if (p > j) acc[p] = fma(-l.x, acc[j], acc[p]);
+      acc[p + 1] = fma(-l.y, acc[j], acc[p + 1]);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < NS; j += 2) {
+    const double2 d = *reinterpret_cast<const double2*>(Dv + j);
+    acc[j] *= d.x;
+    acc[j + 1] *= d.y;
+  }
+#pragma unroll
+  for (int j = NS - 1; j > 0; --j) {
+#pragma unroll
+    for (int p = 0; p < j; p += 2) {
+      const double2 l = *reinterpret_cast<const double2*>(Lr + j * NS + p);
+      acc[p] = fma(-l.x, acc[j], acc[p]);
+      if (p + 1 < j) acc[p + 1] = fma(-l.y, acc[j], acc[p + 1]);
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // One separator, one warp: inner products -> factorization -> solves. Lane roles:
 //   lanes [0,NS)      : column c of S  (then, for the solves, column c of S_R -> f_R)
@@ -130,7 +180,7 @@ __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync
 //   Lsm   : NS*NS doubles of scratch for Lt (row-major); Wout: [f_L | f_R | zs] column-major ld NS
 // Returns non-zero (warp-uniform) when a pivot is <= 0 (reference: clap_CholeskyFactorize fails).
 // ---------------------------------------------------------------------------------------------------------
-template <int NS, int NI, bool LDG = true>
+template <int NS, int NI, bool LDG = true, bool F2 = false>
 __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const double* LXi, const double* RXi,
                                            const double* zxi, const double* LXn, const double* RXn,
                                            const double* zxn, const double* zln, double* Lsm, double* Wout) {
@@ -228,7 +278,12 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
     }
     acc[j] = lane == j ? dinv : lij;  // the diagonal slot of Lt carries 1/D(j)
   }
-  if (lane < NS) {
+  if constexpr (F2) {  // Lsm has factor_scratch_doubles<NS>() doubles, 16-byte aligned
+    store_factor2<NS>(acc, Lsm);
+#pragma unroll
+    for (int k = 0; k < NS; ++k)
+      if (lane == k) Lsm[2 * NS * NS + k] = acc[k];
+  } else if (lane < NS) {
 #pragma unroll
     for (int k = 0; k < NS; ++k) Lsm[lane * NS + k] = acc[k];
   }
@@ -241,17 +296,21 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
 #pragma unroll
     for (int r = 0; r < NS; ++r) acc[r] = Wout[mycol * NS + r];
   }
+  if constexpr (F2) {
+    tri_solves2<NS>(acc, Lsm);
+  } else {
 #pragma unroll
-  for (int j = 0; j < NS; ++j) {
+    for (int j = 0; j < NS; ++j) {
 #pragma unroll
-    for (int i = j + 1; i < NS; ++i) acc[i] = fma(-Lsm[i * NS + j], acc[j], acc[i]);
-  }
+      for (int i = j + 1; i < NS; ++i) acc[i] = fma(-Lsm[i * NS + j], acc[j], acc[i]);
+    }
 #pragma unroll
-  for (int j = 0; j < NS; ++j) acc[j] *= Lsm[j * NS + j];
+    for (int j = 0; j < NS; ++j) acc[j] *= Lsm[j * NS + j];
 #pragma unroll
-  for (int j = NS - 1; j >= 0; --j) {
+    for (int j = NS - 1; j >= 0; --j) {
 #pragma unroll
-    for (int i = 0; i < j; ++i) acc[i] = fma(-Lsm[j * NS + i], acc[j], acc[i]);
+      for (int i = 0; i < j; ++i) acc[i] = fma(-Lsm[j * NS + i], acc[j], acc[i]);
+    }
   }
   __syncwarp();
   if (lane <= 2 * NS) {
@@ -393,6 +452,72 @@ __device__ __forceinline__ void schur_dfma(double* Ls, double* Rs, double* zv, c
     const int s = kn >> (j + 1);
     const bool special = (kn == ((2 * s + 1) << j)) && (row < NS);
     schur_row<NS>(Ls + R * NS, Rs + R * NS, zv + R, W + (s << j) * D::WSZ, side, special, row);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Lean Schur update of a merged boundary entry on the fp64 tensor cores (ndlqr_UpdateShurFactor restricted to the
+// rows that stay boundary rows). Entry rows 0..NS-1 = X(a) come from entry sA (own = its R block, keep L), rows
+// NS..ZS-1 = X(b), U(b) from entry sB (own = its L block, keep R):
+//     [L R z](row) <- keep - own(row) * [f_L f_R zs]
+// written to dA (rows < NS) / dB (rows >= NS), which may alias the sources. One warp; ZS rows = 4 tiles of 8
+// (the last one half empty), 2NS = 24 columns = 3 tiles, NS = 12 = 3 k-steps: 36 DMMA.
+// ---------------------------------------------------------------------------------------------------------
+template <int NS, int NI>
+__device__ __forceinline__ void lean_schur_dmma(const double* sA, const double* sB, double* dA, double* dB, const double* Wf) {
+  using D = Dim<NS, NI>;
+  constexpr int ZS = D::ZS, SLOT = D::SLOT, KS = NS / 4, NT = 2 * NS / 8, TILES = (ZS + 7) / 8;
+  static_assert(NS % 4 == 0 && (2 * NS) % 8 == 0, "tile shapes");
+  const int lane = threadIdx.x & 31, q = lane & 3, rr = lane >> 2;
+  double bneg[KS][NT], zq[KS];
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) bneg[ks][nt] = -Wf[(8 * nt + rr) * NS + 4 * ks + q];
+    zq[ks] = Wf[2 * NS * NS + 4 * ks + q];
+  }
+#pragma unroll
+  for (int t = 0; t < TILES; ++t) {
+    const int row = 8 * t + rr;
+    const bool valid = row < ZS;
+    const int side = row < NS ? 0 : 1;
+    const double* src = side ? sB : sA;
+    double* dst = side ? dB : dA;
+    const int rb = (valid ? row : 0) * NS;
+    const double* own = src + (side ? 0 : SLOT) + rb + q;
+    double a[KS];
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) a[ks] = valid ? own[4 * ks] : 0.0;
+    double c[NT][2];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      const int n = 8 * nt + 2 * q;
+      const bool inL = n < NS;
+      const bool keep = inL != (side == 1);  // side 0 keeps its L columns, side 1 its R columns
+      if (keep) {
+        const double2 v = *reinterpret_cast<const double2*>(src + (inL ? 0 : SLOT) + rb + (inL ? n : n - NS));
+        c[nt][0] = v.x; c[nt][1] = v.y;
+      } else { c[nt][0] = 0.0; c[nt][1] = 0.0; }
+    }
+    const double z0 = src[2 * SLOT + (valid ? row : 0)];
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks)
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) dmma884(c[nt][0], c[nt][1], a[ks], bneg[ks][nt]);
+    double part = 0.0;
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) part = fma(a[ks], zq[ks], part);
+    part += __shfl_xor_sync(0xffffffffu, part, 1);
+    part += __shfl_xor_sync(0xffffffffu, part, 2);
+    if (valid) {
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        const int n = 8 * nt + 2 * q;
+        const bool inL = n < NS;
+        *reinterpret_cast<double2*>(dst + (inL ? 0 : SLOT) + rb + (inL ? n : n - NS)) = make_double2(c[nt][0], c[nt][1]);
+      }
+      if (q == 0) dst[2 * SLOT + row] = z0 - part;
+    }
   }
 }
 
@@ -599,7 +724,7 @@ __global__ void __launch_bounds__(16 * G, 512 / (16 * G)) tier0_kernel(Shape s, 
 // boundary rows: X(a) of the left subtree's first entry (own = R) and X,U(b) of the right subtree's last entry
 // (own = L). The separator record [f_L | f_R | zs] goes to fb.sep for the top-down pass.
 // `span` = knots per input entry; warps = max(1, ecount/2).
-// dynamic smem: (ecount*ENT + warps*(WSZ + NS*NS)) doubles.
+// dynamic smem: (ecount*ENT + warps*(WSZ + factor_scratch_doubles<NS>())) doubles.
 // ---------------------------------------------------------------------------------------------------------
 // Where a tier reads and writes; lets the same kernel run the local tiers of a problem, the last local tier of
 // a shard (merged entry goes to the exchange payload) and the cross-GPU tier (entries, [A|B] blocks and records
@@ -660,8 +785,8 @@ __global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, TierArgs 
       double* El = ents + el * ENT;
       double* Er = ents + er * ENT;
       double* Wf = Wall + warp * WSZ;
-      const int bad = spine_merge<NS, NI>(AB, El + NS * NS, El + SLOT + NS * NS, El + 2 * SLOT + NS, Er, Er + SLOT,
-                                          Er + 2 * SLOT, Er + 2 * SLOT + ZS, Lall + warp * NS * NS, Wf);
+      const int bad = spine_merge<NS, NI, true, true>(AB, El + NS * NS, El + SLOT + NS * NS, El + 2 * SLOT + NS, Er, Er + SLOT,
+                                          Er + 2 * SLOT, Er + 2 * SLOT + ZS, Lall + warp * factor_scratch_doubles<NS>(), Wf);
       double* rec = a.sep + (size_t)prob * a.sep_pstride + (size_t)(ge + 1) * a.sep_mul * WSZ;
       for (int e = lane; e < WSZ; e += 32) rec[e] = Wf[e];
       if (bad && lane == 0) {
@@ -673,7 +798,9 @@ __global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, TierArgs 
         }
         b.flags[prob] = 1;
       }
-      if (lane < ZS) {
+      if constexpr (NS % 4 == 0) {
+        lean_schur_dmma<NS, NI>(ents + ea * ENT, ents + eb * ENT, ents + ea * ENT, ents + eb * ENT, Wf);
+      } else if (lane < ZS) {
         double* E = ents + (lane < NS ? ea : eb) * ENT;
         schur_row<NS>(E + lane * NS, E + SLOT + lane * NS, E + 2 * SLOT + lane, Wf, lane < NS ? 0 : 1, false, 0);
       }
@@ -843,7 +970,7 @@ inline cudaError_t tier_attr() {
   static bool attr_done = false;
   if (attr_done) return cudaSuccess;
   cudaError_t e = cudaFuncSetAttribute(tier_kernel<NS, NI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (8 * D::ENT + 4 * (D::WSZ + NS * NS)) * (int)sizeof(double));
+                                       (8 * D::ENT + 4 * (D::WSZ + factor_scratch_doubles<NS>())) * (int)sizeof(double));
   if (e == cudaSuccess) attr_done = true;
   return e;
 }
@@ -852,7 +979,7 @@ template <int NS, int NI>
 inline void launch_tier(const Shape& s, const Bufs& b, const TierArgs& a, int batch, cudaStream_t st) {
   using D = Dim<NS, NI>;
   const int warps = a.ecount / 2 > 0 ? a.ecount / 2 : 1;
-  const int smem = (a.ecount * D::ENT + warps * (D::WSZ + NS * NS)) * (int)sizeof(double);
+  const int smem = (a.ecount * D::ENT + warps * (D::WSZ + factor_scratch_doubles<NS>())) * (int)sizeof(double);
   tier_kernel<NS, NI><<<(unsigned)((size_t)batch * (a.Min / a.ecount)), 32 * warps, smem, st>>>(s, b, a);
 }
 

@@ -46,28 +46,17 @@ __device__ __forceinline__ int spine_factor_solve(double (&acc)[NS], double* Lsm
     }
     acc[j] = lane == j ? dinv : lij;
   }
-  if (lane < NS) {
+  store_factor2<NS>(acc, Lsm);  // Lsm: factor_scratch_doubles<NS>() doubles, 16-byte aligned
 #pragma unroll
-    for (int k = 0; k < NS; ++k) Lsm[lane * NS + k] = acc[k];
-  }
+  for (int k = 0; k < NS; ++k)
+    if (lane == k) Lsm[2 * NS * NS + k] = acc[k];
   __syncwarp();
 #pragma unroll
   for (int r = 0; r < NS; ++r) {
-    const double sr = load_sr(r, c);  // warp-uniform control flow inside (may shuffle)
+    const double sr = load_sr(r, c);  // warp-uniform control flow inside
     acc[r] = lane < NS ? sr : Wout[mycol * NS + r];
   }
-#pragma unroll
-  for (int j = 0; j < NS; ++j) {
-#pragma unroll
-    for (int i = j + 1; i < NS; ++i) acc[i] = fma(-Lsm[i * NS + j], acc[j], acc[i]);
-  }
-#pragma unroll
-  for (int j = 0; j < NS; ++j) acc[j] *= Lsm[j * NS + j];
-#pragma unroll
-  for (int j = NS - 1; j >= 0; --j) {
-#pragma unroll
-    for (int i = 0; i < j; ++i) acc[i] = fma(-Lsm[j * NS + i], acc[j], acc[i]);
-  }
+  tri_solves2<NS>(acc, Lsm);
   __syncwarp();
   if (lane <= 2 * NS) {
     const int wc = lane < NS ? NS + lane : (lane < 2 * NS ? lane - NS : 2 * NS);
@@ -422,20 +411,17 @@ __global__ void __launch_bounds__(32 * SCAN_WPC, 2) scan_leaf_kernel(Shape s, Bu
     }
     rec_done();
   }
-  // ---- level 1: E0 + E1 -> E0 (separator after knot k0+1); block 0 is dead and serves as the factor scratch ----
-  bad = spine_merge<NS, NI, false>(R + NS + RD::STRIDE + RD::OA, E0 + NS * NS, E0 + SLOT + NS * NS, E0 + 2 * SLOT + NS, E1,
-                                   E1 + SLOT, E1 + 2 * SLOT, E1 + 2 * SLOT + ZS, R + NS + RD::OA, Wf);
+  // ---- level 1: E0 + E1 -> E0 (separator after knot k0+1); blocks 2, 3 are dead and serve as the factor scratch ----
+  static_assert(factor_scratch_doubles<NS>() <= 2 * RD::STRIDE && (NS + 2 * RD::STRIDE) % 2 == 0, "factor scratch in blocks 2, 3");
+  bad = spine_merge<NS, NI, false, true>(R + NS + RD::STRIDE + RD::OA, E0 + NS * NS, E0 + SLOT + NS * NS, E0 + 2 * SLOT + NS, E1,
+                                         E1 + SLOT, E1 + 2 * SLOT, E1 + 2 * SLOT + ZS, R + NS + 2 * RD::STRIDE, Wf);
   store_rec(1);
   if (bad && lane == 0) {
     b.status[(size_t)prob * 3 * N + rs_slot_S(k0 >> 2, 1, N)] = -1;
     b.flags[prob] = 1;
   }
   if (M0 > 1) {  // (a single subtree is the whole problem: only the records are needed)
-    if (lane < ZS) {
-      const double* S = lane < NS ? E0 : E1;
-      schur_row_io<NS>(S + lane * NS, S + SLOT + lane * NS, S + 2 * SLOT + lane, E0 + lane * NS, E0 + SLOT + lane * NS,
-                       E0 + 2 * SLOT + lane, Wf, lane < NS ? 0 : 1);
-    }
+    lean_schur_dmma<NS, NI>(E0, E1, E0, E0, Wf);
     fence_async_smem();
     __syncwarp();
     if (lane == 0) {

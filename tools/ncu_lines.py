@@ -37,21 +37,24 @@ for blk in blocks[1:]:
     hh = rows[1]
     si, ie = hh.index("# Samples"), hh.index("Instructions Executed")
     ci = {k: hh.index(k) for k in hh if k.startswith("stall_") and "Not Issued" not in k}
-    agg, tot, totins = {}, 0, 0
+    wi, wid = hh.index("L1 Wavefronts Shared"), hh.index("L1 Wavefronts Shared Ideal")
+    agg, tot, totins, totw = {}, 0, 0, 0
     for i, r in enumerate(rows[2:]):
         try:
             n, ins = int(r[si]), int(r[ie])
         except Exception:
             continue
         key = lines.get(16 * i, (None, ""))[0]
-        a = agg.setdefault(key, [0, 0, {}])
+        a = agg.setdefault(key, [0, 0, {}, 0, 0])
         a[0] += n; a[1] += ins
+        a[3] += int(r[wi] or 0); a[4] += int(r[wid] or 0); totw += int(r[wi] or 0)
         for k, c in ci.items():
             v = int(r[c] or 0)
             if v:
                 a[2][k[6:]] = a[2].get(k[6:], 0) + v
         tot += n; totins += ins
-    print(f"## {rows[0][1][:80]}: {tot} samples, {totins/1e6:.1f}M warp instructions")
-    for key, (n, ins, st) in sorted(agg.items(), key=lambda x: -x[1][0])[:top]:
+    print(f"## {rows[0][1][:80]}: {tot} samples, {totins/1e6:.1f}M warp instructions, {totw/1e6:.1f}M shared wavefronts")
+    order = int(os.environ.get("NCU_LINES_SORT", "0"))  # 0 samples, 1 instructions, 3 shared wavefronts
+    for key, (n, ins, st, w, wideal) in sorted(agg.items(), key=lambda x: -x[1][order])[:top]:
         s = sorted(st.items(), key=lambda x: -x[1])[:3]
-        print(f"  {str(key):38s} {100*n/tot:5.1f}% samples {ins/1e6:8.2f}M inst  {[(k, round(100*v/tot,1)) for k, v in s]}")
+        print(f"  {str(key):34s} {100*n/tot:5.1f}% smp {ins/1e6:7.2f}M inst {w/1e6:7.2f}M smem-wf (ideal {wideal/1e6:6.2f})  {[(k, round(100*v/tot,1)) for k, v in s]}")
