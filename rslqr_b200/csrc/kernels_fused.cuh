@@ -828,24 +828,30 @@ __global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, TierArgs 
 // Slots 0 and M0 of fb.lamhat hold zeros (no separator outside the horizon). One CTA per problem.
 // ---------------------------------------------------------------------------------------------------------
 template <int NS>
-__global__ void topdown_kernel(const double* sep_all, double* lam_all, int M0, const double* left, const double* right) {
-  // left/right: multipliers of the separators bounding the range (a shard's neighbours), nullptr = none
+__global__ void topdown_kernel(const double* sep_all, double* lam_all, int M0, const double* left, const double* right,
+                               int span, int step) {
+  // left/right: multipliers of the separators bounding the range (a shard's neighbours), nullptr = none.
+  // A CTA covers the `span` slots after slot blk*span and resolves the separators at multiples of `step` inside it
+  // (coarsest first); the multipliers at both ends of its range are already final, or (span == M0) set here.
+  // Long horizons run two passes: (span = M0, step = H) with one CTA, then (span = H, step = 1) with M0/H CTAs.
   constexpr int WSZ = (2 * NS + 1) * NS;
-  const int prob = blockIdx.x;
+  const int nblk = M0 / span;
+  const int prob = blockIdx.x / nblk, base = (blockIdx.x % nblk) * span;
   double* lam = lam_all + (size_t)prob * (M0 + 1) * NS;
   const double* sep = sep_all + (size_t)prob * M0 * WSZ;
-  if (threadIdx.x < NS) {
+  if (span == M0 && threadIdx.x < NS) {
     lam[threadIdx.x] = left ? left[(size_t)prob * NS + threadIdx.x] : 0.0;
     lam[M0 * NS + threadIdx.x] = right ? right[(size_t)prob * NS + threadIdx.x] : 0.0;
   }
-  int T = 0;
-  while ((1 << T) < M0) ++T;
-  for (int t = T - 1; t >= 0; --t) {
+  int T = 0, T0 = 0;
+  while ((1 << T) < span) ++T;
+  while ((1 << T0) < step) ++T0;
+  for (int t = T - 1; t >= T0; --t) {
     __syncthreads();
-    const int cnt = M0 >> (t + 1), h = 1 << t;
+    const int cnt = span >> (t + 1), h = 1 << t;
     for (int idx = threadIdx.x; idx < cnt * NS; idx += blockDim.x) {
       const int u = idx / NS, r = idx - u * NS;
-      const int q = (2 * u + 1) << t;
+      const int q = base + ((2 * u + 1) << t);
       const double* rec = sep + (size_t)q * WSZ;
       const double* la = lam + (q - h) * NS;
       const double* lb = lam + (q + h) * NS;
@@ -855,6 +861,20 @@ __global__ void topdown_kernel(const double* sep_all, double* lam_all, int M0, c
       lam[q * NS + r] = v;
     }
   }
+}
+
+// host: one pass for short ranges, two for long ones (the serial chain of one CTA is log2(M0) global round trips)
+template <int NS>
+inline int launch_topdown(const double* sep, double* lam, int M0, int batch, const double* left, const double* right,
+                          cudaStream_t st) {
+  constexpr int H = 64;
+  if (M0 <= 2 * H) {
+    topdown_kernel<NS><<<batch, 128, 0, st>>>(sep, lam, M0, left, right, M0, 1);
+    return 1;
+  }
+  topdown_kernel<NS><<<batch, 128, 0, st>>>(sep, lam, M0, left, right, M0, H);
+  topdown_kernel<NS><<<batch * (M0 / H), 128, 0, st>>>(sep, lam, M0, left, right, H, 1);
+  return 2;
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -1012,8 +1032,7 @@ template <int NS, int NI>
 inline cudaError_t launch_down(FusedPlan& p, const Shape& s, const Bufs& b, int batch, cudaStream_t st,
                                const double* left, const double* right) {
   using D = Dim<NS, NI>;
-  topdown_kernel<NS><<<batch, 128, 0, st>>>(p.fb.sep, p.fb.lamhat, p.M0, left, right);
-  ++p.launches;
+  p.launches += launch_topdown<NS>(p.fb.sep, p.fb.lamhat, p.M0, batch, left, right, st);
   const long long rows = (long long)batch * s.N * D::ZS;
   finalize_kernel<NS, NI><<<(unsigned)((rows + 255) / 256), 256, 0, st>>>(s, b, p.fb, p.G0, p.M0, rows);
   ++p.launches;
@@ -1090,7 +1109,7 @@ inline cudaError_t shard_finish_t(FusedPlan& p, const Shape& s, const Bufs& b, c
     a.out = nullptr; a.out_stride = 0;
     a.Min = nranks; a.ecount = nranks; a.span = 0;
     launch_tier<NS, NI>(s, b, a, 1, st);  // every rank runs the top log2(nranks) levels redundantly, bit-identically
-    topdown_kernel<NS><<<1, 128, 0, st>>>(p.xsep, p.xlam, nranks, nullptr, nullptr);
+    topdown_kernel<NS><<<1, 128, 0, st>>>(p.xsep, p.xlam, nranks, nullptr, nullptr, nranks, 1);
     p.launches += 2;
     left = p.xlam + (size_t)rank * NS;
     right = p.xlam + (size_t)(rank + 1) * NS;

@@ -575,8 +575,7 @@ inline cudaError_t launch_scan_leaf(ScanPlan& p, const Shape& s, const Bufs& b, 
 template <int NS, int NI>
 inline cudaError_t launch_scan_down(ScanPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st,
                                     const double* left, const double* right) {
-  topdown_kernel<NS><<<batch, 128, 0, st>>>(p.f.fb.sep, p.f.fb.lamhat, p.f.M0, left, right);
-  ++p.f.launches;
+  p.f.launches += launch_topdown<NS>(p.f.fb.sep, p.f.fb.lamhat, p.f.M0, batch, left, right, st);
   const long long nsub = (long long)batch * p.f.M0;
   scan_down_kernel<NS, NI><<<(unsigned)((nsub + 3) / 4), 128, 0, st>>>(s, b, p.sb, p.f.fb.lamhat, pack_rhs, p.f.M0, nsub);
   ++p.f.launches;
@@ -628,7 +627,7 @@ inline int scan_shard_finish(ScanPlan& p, const Shape& s, const Bufs& b, int pac
       a.out = nullptr; a.out_stride = 0;
       a.Min = nranks; a.ecount = nranks; a.span = 0;
       launch_tier<12, 4>(s, b, a, 1, st);
-      topdown_kernel<12><<<1, 128, 0, st>>>(p.f.xsep, p.f.xlam, nranks, nullptr, nullptr);
+      topdown_kernel<12><<<1, 128, 0, st>>>(p.f.xsep, p.f.xlam, nranks, nullptr, nullptr, nranks, 1);
       p.f.launches += 2;
       left = p.f.xlam + (size_t)rank * 12;
       right = p.f.xlam + (size_t)(rank + 1) * 12;
