@@ -121,10 +121,11 @@ template <int NS>
 __host__ __device__ constexpr int factor_scratch_doubles() { return 2 * NS * NS + NS + (NS & 1); }
 
 template <int NS>
-__device__ __forceinline__ void store_factor2(const double (&acc)[NS], double* F) {
+__device__ __forceinline__ void store_factor2(const double (&acc)[NS], double mydinv, double* F) {
   static_assert(NS % 2 == 0, "pairs");
   const int lane = threadIdx.x & 31;
   if (lane < NS) {
+    F[2 * NS * NS + lane] = mydinv;
 #pragma unroll
     for (int k = 0; k < NS; k += 2) *reinterpret_cast<double2*>(F + lane * NS + k) = make_double2(acc[k], acc[k + 1]);
 #pragma unroll
@@ -265,6 +266,7 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
   }
   // ---- factorization, lane i < NS holds row i of S in acc[] (the other lanes run along on junk) ----
   int bad = 0;
+  double mydinv = 0.0;  // 1/D(lane)
 #pragma unroll
   for (int j = 0; j < NS; ++j) {
     const double d = shfl_d(acc[j], j);
@@ -277,12 +279,10 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
       acc[k] = fma(-lij, pk, acc[k]);
     }
     acc[j] = lane == j ? dinv : lij;  // the diagonal slot of Lt carries 1/D(j)
+    mydinv = lane == j ? dinv : mydinv;
   }
   if constexpr (F2) {  // Lsm has factor_scratch_doubles<NS>() doubles, 16-byte aligned
-    store_factor2<NS>(acc, Lsm);
-#pragma unroll
-    for (int k = 0; k < NS; ++k)
-      if (lane == k) Lsm[2 * NS * NS + k] = acc[k];
+    store_factor2<NS>(acc, mydinv, Lsm);
   } else if (lane < NS) {
 #pragma unroll
     for (int k = 0; k < NS; ++k) Lsm[lane * NS + k] = acc[k];

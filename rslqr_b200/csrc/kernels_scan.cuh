@@ -33,6 +33,7 @@ __device__ __forceinline__ int spine_factor_solve(double (&acc)[NS], double* Lsm
   const int c = lane < NS ? lane : 0;
   const int mycol = lane <= 2 * NS ? lane : 2 * NS;
   int bad = 0;
+  double mydinv = 0.0;
 #pragma unroll
   for (int j = 0; j < NS; ++j) {
     const double d = shfl_d(acc[j], j);
@@ -45,11 +46,9 @@ __device__ __forceinline__ int spine_factor_solve(double (&acc)[NS], double* Lsm
       acc[k] = fma(-lij, pk, acc[k]);
     }
     acc[j] = lane == j ? dinv : lij;
+    mydinv = lane == j ? dinv : mydinv;
   }
-  store_factor2<NS>(acc, Lsm);  // Lsm: factor_scratch_doubles<NS>() doubles, 16-byte aligned
-#pragma unroll
-  for (int k = 0; k < NS; ++k)
-    if (lane == k) Lsm[2 * NS * NS + k] = acc[k];
+  store_factor2<NS>(acc, mydinv, Lsm);  // Lsm: factor_scratch_doubles<NS>() doubles, 16-byte aligned
   __syncwarp();
 #pragma unroll
   for (int r = 0; r < NS; ++r) {
