@@ -78,8 +78,8 @@ def scan_leaf_bytes_per_subtree(n, m):
     return 8 * (4 * stride + ent + 3 * (2 * n + 1) * n)
 
 
-# dram bytes of scan_leaf_kernel per problem from the committed ncu --set full capture (None until captured)
-SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM = None
+# dram__bytes_read.sum + dram__bytes_write.sum of scan_leaf_kernel per problem from the committed ncu --set full capture
+SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM = (497.177344e6 + 788.987648e6) / 1024   # profiles/r01_ncu_scan_leaf_v2.md
 
 # dram__bytes_read.sum + dram__bytes_write.sum of tier0_kernel per problem, from the committed ncu --set full capture
 # (profiles/r01_ncu_tier0_v1.md: 0.995 GB + 4.060 GB at batch 2048)
@@ -228,6 +228,47 @@ def cpu_reference_rate(n, m, N, knots, x0, budget_s=12.0, cores=None):
                       f"num_threads=1 per solve (ndlqr_Solve only + reset/init)"}
 
 
+def cpu_riccati_baseline(n, m, N, knots, x0, budget_s=3.0):
+    """The reference's serial Riccati solver (src/riccati_solve.c:7-24, ndlqr_SolveRiccati) on ONE host core: a timing
+    baseline only -- its KKT residual is printed beside it because the recursion is unstable on this data."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import ctypes as C
+    import oracle_lib as O
+    zs = 2 * n + m
+    if O.REF is not None:
+        lib = O.REF
+        lib.ndlqr_NewRiccatiSolver.restype = C.c_void_p
+        lib.ndlqr_NewRiccatiSolver.argtypes = [C.c_void_p]
+        lib.ndlqr_SolveRiccati.restype = C.c_int
+        lib.ndlqr_SolveRiccati.argtypes = [C.c_void_p]
+        lib.ndlqr_CopyRiccatiSolution.restype = C.c_int
+        lib.ndlqr_CopyRiccatiSolution.argtypes = [C.c_void_p, C.c_void_p]
+        lib.ndlqr_FreeRiccatiSolver.argtypes = [C.c_void_p]
+        pp = O.ref_problem_from_flat(n, m, N, knots[0], x0[0])
+        rs = lib.ndlqr_NewRiccatiSolver(C.cast(pp, C.c_void_p))
+        lib.ndlqr_SolveRiccati(rs)
+        cnt, t0 = 0, time.perf_counter()
+        while time.perf_counter() - t0 < budget_s:
+            lib.ndlqr_SolveRiccati(rs)
+            cnt += 1
+        dt = time.perf_counter() - t0
+        z = np.zeros(N * zs)
+        lib.ndlqr_CopyRiccatiSolution(rs, z.ctypes.data_as(C.c_void_p))
+        lib.ndlqr_FreeRiccatiSolver(rs)
+        kind = "reference"
+    else:
+        O.riccati(n, m, N, knots[0], x0[0])
+        cnt, t0 = 0, time.perf_counter()
+        while time.perf_counter() - t0 < budget_s:
+            z = O.riccati(n, m, N, knots[0], x0[0])
+            cnt += 1
+        dt = time.perf_counter() - t0
+        kind = "port"
+    res = O.kkt_residual(n, m, N, knots[0], x0[0], z)
+    return {"value": cnt / dt, "unit": "solves/s", "cores": 1, "kind": kind, "kkt_residual": res,
+            "sample": f"{cnt} ndlqr_SolveRiccati calls on problem 0 in {dt:.1f}s, one core (timing baseline only)"}
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
@@ -242,6 +283,10 @@ def run_reference(args, rank, world):
     val = float(np.mean([r["value"] for r in rates]))
     base = rates[-1]
     base["value"] = val
+    try:
+        base["riccati"] = cpu_riccati_baseline(n, m, N, knots[:1], x0[:1])
+    except Exception as e:
+        base["riccati"] = {"unavailable": repr(e)}
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "solves/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -405,6 +450,10 @@ def run_ours(args, rank, world, local_rank):
         line["phase_ms"] = prof
     if rank == 0 and world == 1 and not args.no_cpu:
         line["cpu_baseline"] = cpu_reference_rate(n, m, N, h_knots[:64].copy(), h_x0[:64].copy(), budget_s=args.cpu_seconds)
+        try:
+            line["cpu_baseline"]["riccati"] = cpu_riccati_baseline(n, m, N, h_knots[:1].copy(), h_x0[:1].copy())
+        except Exception as e:  # the baseline must never take the bench line down
+            line["cpu_baseline"]["riccati"] = {"unavailable": repr(e)}
     if rank == 0:
         print(json.dumps(line), flush=True)
     s.close()
