@@ -531,6 +531,113 @@ def run_long(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def run_large(args, rank, world, local_rank):
+    """BASELINE configs[4]: larger-state LQR n=64 m=16 N=1024, batch 512 per run (split over ranks), staged path with the
+    DMMA block contractions. The dense factor array is 755 MB per problem, so a rank works through its share in chunks."""
+    import rslqr_b200 as R
+    n, m, N = 64, 16, 1024
+    total = args.batch if args.batch != 4096 else 512
+    share, chunk = total // world, min(args.chunk or 16, total // world)
+    dist = init_nccl(local_rank) if world > 1 else None
+    s = R.CudaSolver(n, m, N, batch=chunk, device=local_rank, flags=R.KEEP_FACT)
+    s.set_mode(R.MODE_STAGED)
+    kn, x0 = R.synth_problems(n, m, N, SEED, rank * share, chunk)
+    s.upload(kn, x0)
+
+    def one_chunk():
+        s.reset()
+        s.solve_async(True)
+    for _ in range(max(1, args.warmup // 3)):
+        one_chunk()
+    s.sync()
+    nchunks = share // chunk
+    steps = max(1, min(args.steps, 2))
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    if dist is not None:
+        dist.barrier()
+    s.mark(0)
+    for _ in range(steps * nchunks):   # every chunk re-solves resident problems of the same shape (inputs 44 MB each)
+        one_chunk()
+    s.mark(1)
+    ms = s.elapsed_ms(0, 1) / steps
+    s.sync()
+    if dist is not None:
+        import torch
+        tt = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms = float(tt.item())
+    assert not s.flags().any()
+    value = total / (ms * 1e-3)
+    fp64 = fp64_peak()
+    tf = flop_model(n, m, N) * value / 1e12
+    line = {"metric": "LQR solves/sec (n=64,m=16,N=1024 batched)", "value": value, "unit": "solves/s", "n_gpus": world,
+            "steps": steps, "warmup": max(1, args.warmup // 3), "ms_per_step": ms, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "larger-state LQR n=64 m=16 N=1024 batch %d (BASELINE configs[4])" % total, "chunk": chunk,
+                       "mode": "staged (DMMA products / Schur)", "l2": "factor array 755 MB per problem, larger than L2"},
+            "clocks": sampler.summary(), "gpu_launches": int(s.launches * nchunks * steps),
+            "roofline": {"kernel": "whole step (schur_mma_kernel dominates)", "bound": "tensor", "achieved": tf, "peak": fp64["tflops"],
+                         "unit": "TFLOP/s", "frac": tf / fp64["tflops"], "traffic": None, "peak_kind": fp64["kind"],
+                         "note": "structurally non-zero FLOPs of the reference algorithm (SURVEY 8d: 23.6 GFLOP per solve) / step time"}}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    s.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+def run_single(args, rank, world, local_rank):
+    """BASELINE configs[1]: the shipped lqr_prob_256.json (n=6, m=3, N=256), ONE solve through the reference-named C host
+    API (ndlqr_InitializeWithLQRProblem + ndlqr_Solve + solution copy), beside the reference on the host cores."""
+    if rank != 0:
+        return
+    import ctypes as C
+    import rslqr_b200 as R
+    path = os.path.join(ROOT, "tests", "golden", "lqr_prob_256.json")
+    LIB = R.LIB
+    pp = LIB.ndlqr_ReadLQRProblemJSONFile(path.encode())
+    n, m, N = 6, 3, 256
+    sv = R.NdLqrSolver(n, m, N)
+    z = np.zeros(N * (2 * n + m))
+    def once():
+        sv.reset(); sv.initialize(pp); sv.solve()
+        LIB.ndlqr_CopySolution(sv.p, z.ctypes.data_as(C.POINTER(C.c_double)))
+    for _ in range(max(3, args.warmup)):
+        once()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        once()
+    e2e_ms = (time.perf_counter() - t0) / args.steps * 1e3
+    dev_ms = float(sv.c.solve_time_ms)
+    want = np.array(json.load(open(path))["soln"]).reshape(-1)
+    err = float(np.linalg.norm(z[:want.size] - want))
+    line = {"metric": "single-solve latency (lqr_prob_256.json n=6,m=3,N=256)", "value": dev_ms, "unit": "ms", "n_gpus": 1,
+            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": dev_ms, "higher_is_better": False, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "shipped fixture",
+            "config": {"workload": "lqr_prob_256.json single solve via ndlqr_Solve (BASELINE configs[1])", "abs_err_vs_json_soln": err},
+            "e2e": {"value": e2e_ms, "unit": "ms", "h2d_bytes_per_step": int(N * R.knot_stride(n, m) * 8), "d2h_bytes_per_step": int(z.nbytes)},
+            "gpu_launches": 0}
+    if not args.no_cpu:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import oracle_lib as O
+        from rslqr_b200.lib import problem_to_flat
+        kn, x0 = problem_to_flat(pp, n, m)
+        cores = max(1, len(os.sched_getaffinity(0)))
+        base = {"unit": "ms", "kind": "reference" if O.REF is not None else "port", "cores": cores}
+        if O.REF is not None:
+            for th in sorted({1, max(1, cores // 2), cores}):
+                best = min(O.ref_solve(n, m, N, kn, x0, threads=th, want_fact=False)[2] for _ in range(6))
+                base["ndlqr_ms_threads_%d" % th] = best
+            base["value"] = min(v for k, v in base.items() if k.startswith("ndlqr_ms"))
+        r = cpu_riccati_baseline(n, m, N, kn[None], x0[None], budget_s=1.0)
+        base["riccati_ms"] = 1e3 / r["value"]; base["riccati_kkt_residual"] = r["kkt_residual"]
+        base["sample"] = "best of 6 ndlqr_Solve calls per thread count (solve_time_ms), Riccati averaged over 1 s"
+        line["cpu_baseline"] = base
+    print(json.dumps(line), flush=True)
+    sv.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -539,7 +646,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=4096)
     ap.add_argument("--mode", default="auto", choices=["auto", "staged", "fused", "scan"])
-    ap.add_argument("--workload", default="batch", choices=["batch", "long"],
+    ap.add_argument("--workload", default="batch", choices=["batch", "long", "large", "single"],
                     help="batch = BASELINE configs[2] (default, the headline metric); long = configs[3] single long horizon")
     ap.add_argument("--horizon", type=int, default=16384, help="horizon of the long workload")
     ap.add_argument("--cpu-long", action="store_true", help="long workload: also time one CPU solve (takes ~10-60 s)")
@@ -555,6 +662,10 @@ def main():
         run_reference(args, rank, world)
     elif args.workload == "long":
         run_long(args, rank, world, local_rank)
+    elif args.workload == "large":
+        run_large(args, rank, world, local_rank)
+    elif args.workload == "single":
+        run_single(args, rank, world, local_rank)
     else:
         run_ours(args, rank, world, local_rank)
 
