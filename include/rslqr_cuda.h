@@ -138,6 +138,8 @@ double rslqr_cuda_elapsed_ms(rslqr_cuda_solver* h, int slot_a, int slot_b);
 /* asynchronous copies on the handle's stream (host buffers should be pinned); pair with _sync */
 int rslqr_cuda_upload_async(rslqr_cuda_solver* h, const double* knots, const double* x0, int first, int count);
 int rslqr_cuda_download_solution_async(rslqr_cuda_solver* h, double* soln, int first, int count);
+int rslqr_cuda_upload_rhs_async(rslqr_cuda_solver* h, const double* soln, int first, int count);
+int rslqr_cuda_download_status_async(rslqr_cuda_solver* h, int* status, int problem);
 
 /* ---- one long horizon split over GPUs (BASELINE configs[3]): shard r owns knots [first_knot, first_knot+shard_knots)
  * of a horizon of `nhorizon` knots. Upload as usual (knots = the shard's knot blocks, x0 = x0 for the first shard, else

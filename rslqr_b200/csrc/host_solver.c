@@ -4,6 +4,7 @@
  * What stays on the host: allocation of the mirrors, copying the caller's LQRProblem into the
  * KKT mirror / rhs exactly where the reference puts it (reference src/solver.c:122-194), and moving
  * bytes to and from the device. All arithmetic of the solve happens in the kernels. */
+#include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -198,35 +199,38 @@ int ndlqr_InitializeWithLQRProblem(const LQRProblem* lqrprob, NdLqrSolver* solve
 
 /* ---- mirrors <-> device ---- */
 static int push_rhs(NdLqrSolver* s) {
-  return rslqr_cuda_upload_rhs((rslqr_cuda_solver*)s->device, s->soln->data, 0, 1);
+  return rslqr_cuda_upload_rhs_async((rslqr_cuda_solver*)s->device, s->soln->data, 0, 1);
 }
 
 static int pull_results(NdLqrSolver* s, int with_fact) {
   rslqr_cuda_solver* dev = (rslqr_cuda_solver*)s->device;
   const int n = s->nstates, m = s->ninputs, N = s->nhorizon;
-  int rc = rslqr_cuda_download_solution(dev, s->soln->data, 0, 1);
-  if (!rc && with_fact) rc = rslqr_cuda_download_fact(dev, s->fact->data, 0);
-  if (rc) return rc;
-  /* status words -> cholinfo[].success ; leaf factors sqrt(diag) -> diagonals */
+  /* the solution and the status words were queued behind the solve by ndlqr_Solve; one sync covers them */
   int* status = (int*)malloc(sizeof(int) * 3 * (size_t)N);
-  double* leaf = (double*)malloc(sizeof(double) * (size_t)N * (size_t)(n + m));
-  if (!status || !leaf) { free(status); free(leaf); return RSLQR_E_NOMEM; }
-  rc = rslqr_cuda_download_status(dev, status, 0);
-  if (!rc) rc = rslqr_cuda_download_leaf_factors(dev, leaf, 0);
-  if (!rc) {
+  if (!status) return RSLQR_E_NOMEM;
+  int rc = rslqr_cuda_download_solution_async(dev, s->soln->data, 0, 1);
+  if (!rc) rc = rslqr_cuda_download_status_async(dev, status, 0);
+  if (!rc) rc = rslqr_cuda_sync(dev);
+  if (!rc && with_fact) rc = rslqr_cuda_download_fact(dev, s->fact->data, 0);
+  if (rc) { free(status); return rc; }
+  /* status words -> cholinfo[].success. The leaf Cholesky factors the reference leaves in `diagonals`
+   * (sqrt of the diagonal Q_k, R_k, reference src/nested_dissection.c:61-73) are mirror bookkeeping: they are
+   * taken from the flat knot blocks here, since only the staged kernels materialise them on the device. */
+  {
+    const int blk = ndlqr_LQRDataBlockSize(n, m);
     for (int f = 0; f < s->cholfacts->numfacts; ++f) {
       s->cholfacts->cholinfo[f].success = status[f];
       s->cholfacts->cholinfo[f].uplo = 'L';
       s->cholfacts->cholinfo[f].lib = 'C';
     }
     for (int k = 0; k < N; ++k) {
-      for (int i = 0; i < n; ++i) s->diagonals[2 * k].data[i + n * i] = leaf[(size_t)k * (n + m) + i];
+      const double* kd = s->flat_knots + (size_t)k * blk; /* Q (n) then R (m) lead the block */
+      for (int i = 0; i < n; ++i) s->diagonals[2 * k].data[i + n * i] = kd[i] > 0 ? sqrt(kd[i]) : kd[i];
       if (k < N - 1)
-        for (int i = 0; i < m; ++i) s->diagonals[2 * k + 1].data[i + m * i] = leaf[(size_t)k * (n + m) + n + i];
+        for (int i = 0; i < m; ++i) s->diagonals[2 * k + 1].data[i + m * i] = kd[n + i] > 0 ? sqrt(kd[n + i]) : kd[n + i];
     }
   }
   free(status);
-  free(leaf);
   return rc;
 }
 
@@ -241,7 +245,7 @@ int ndlqr_Solve(NdLqrSolver* solver) {
   const double t0 = wall_ms();
   int rc = push_rhs(solver);
   if (!rc) rc = rslqr_cuda_set_mode(dev, solver->mirror_fact ? RSLQR_MODE_STAGED : RSLQR_MODE_AUTO);
-  if (!rc) rc = rslqr_cuda_solve(dev, 0);
+  if (!rc) rc = rslqr_cuda_solve_async(dev, 0);
   if (!rc) rc = pull_results(solver, solver->mirror_fact);
   if (rc) {
     fprintf(stderr, "ERROR: ndlqr_Solve failed on the GPU: %s\n", rslqr_cuda_last_error());

@@ -639,6 +639,22 @@ extern "C" int rslqr_cuda_upload_async(rslqr_cuda_solver* h, const double* knots
   return RSLQR_OK;
 }
 
+extern "C" int rslqr_cuda_upload_rhs_async(rslqr_cuda_solver* h, const double* soln, int first, int count) {
+  if (!h || !soln || !range_ok(h, first, count)) return fail(RSLQR_E_ARG, "upload_rhs_async: bad argument");
+  CU(cudaSetDevice(h->device));
+  const size_t per = (size_t)h->s.N * h->s.zs;
+  CU(cudaMemcpyAsync(h->b.soln + first * per, soln, sizeof(double) * per * count, cudaMemcpyHostToDevice, h->stream));
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_download_status_async(rslqr_cuda_solver* h, int* status, int problem) {
+  if (!h || !status || problem < 0 || problem >= h->batch) return fail(RSLQR_E_ARG, "download_status_async: bad argument");
+  CU(cudaSetDevice(h->device));
+  const size_t per = (size_t)3 * h->s.N;
+  CU(cudaMemcpyAsync(status, h->b.status + problem * per, sizeof(int) * (per - 1), cudaMemcpyDeviceToHost, h->stream));
+  return RSLQR_OK;
+}
+
 extern "C" int rslqr_cuda_download_solution_async(rslqr_cuda_solver* h, double* soln, int first, int count) {
   if (!h || !soln || !range_ok(h, first, count)) return fail(RSLQR_E_ARG, "download_solution_async: bad argument");
   CU(cudaSetDevice(h->device));
