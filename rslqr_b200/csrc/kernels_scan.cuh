@@ -27,8 +27,11 @@ namespace rslqr {
 // the spine after the inner products: lanes < NS hold column c of S in acc[]; the right-hand-side columns
 // S_L (lanes NS..2NS-1) and s (lane 2NS) are parked in Wout[lane*NS + r]; load_sr(r, c) yields S_R(r, c).
 // Same factorization / solves as spine_merge (kernels_fused.cuh).
-template <int NS, class LoadSR>
-__device__ __forceinline__ int spine_factor_solve(double (&acc)[NS], double* Lsm, double* Wout, LoadSR load_sr) {
+// Park: where the right-hand-side columns were parked, Park[lane*LDP + r]; an odd LDP makes the column-per-lane
+// accesses bank-conflict free (W itself keeps ld NS: it is the record format and the DMMA B operand).
+template <int NS, int LDP, class LoadSR>
+__device__ __forceinline__ int spine_factor_solve(double (&acc)[NS], double* Lsm, const double* Park, double* Wout,
+                                                   LoadSR load_sr) {
   const int lane = threadIdx.x & 31;
   const int c = lane < NS ? lane : 0;
   const int mycol = lane <= 2 * NS ? lane : 2 * NS;
@@ -53,7 +56,7 @@ __device__ __forceinline__ int spine_factor_solve(double (&acc)[NS], double* Lsm
 #pragma unroll
   for (int r = 0; r < NS; ++r) {
     const double sr = load_sr(r, c);  // warp-uniform control flow inside
-    acc[r] = lane < NS ? sr : Wout[mycol * NS + r];
+    acc[r] = lane < NS ? sr : Park[mycol * LDP + r];
   }
   tri_solves2<NS>(acc, Lsm);
   __syncwarp();
@@ -169,7 +172,10 @@ __device__ __forceinline__ int merge_raw(const double* Bl, const double* Br, con
   const bool r1 = 8 + rr < NS;  // second row tile is partial
   const double* ABl = Bl + RD::OA;
   const double* ABr = Br + RD::OA;
-  double* Lsm = E;
+  double* Lsm = E;                                   // factor scratch: head of the entry being produced
+  constexpr int LDP = NS + 1;                        // parking area for S / S_L / s, odd leading dimension
+  double* P = E + factor_scratch_doubles<NS>();
+  static_assert(factor_scratch_doubles<NS>() + (2 * NS + 1) * LDP <= D::ENT, "scratch fits in the entry");
   double acc[NS];
   {
     double a0[KS], a1[KS];
@@ -212,25 +218,56 @@ __device__ __forceinline__ int merge_raw(const double* Bl, const double* Br, con
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           const int col = 8 * nt + 2 * q + h;
-          if (row < NS && col < NS) Wf[col * NS + row] = d[mt][nt][h] + (col == row ? dr : 0.0);
+          if (row < NS && col < NS) P[col * LDP + row] = d[mt][nt][h] + (col == row ? dr : 0.0);
         }
-      if (q == 0 && row < NS) Wf[2 * NS * NS + row] = (mt ? p1 : p0) - t;
+      if (q == 0 && row < NS) P[2 * NS * LDP + row] = (mt ? p1 : p0) - t;
     }
     if (lane >= NS && lane < 2 * NS) {
       const int cl = lane - NS;
       const double dcs = first0 ? 0.0 : -Bl[cl];
 #pragma unroll
-      for (int r = 0; r < NS; ++r) Wf[lane * NS + r] = ABl[cl * NS + r] * dcs;
+      for (int r = 0; r < NS; ++r) P[lane * LDP + r] = ABl[cl * NS + r] * dcs;
     }
     __syncwarp();
     const int mc = lane < NS ? lane : 0;
 #pragma unroll
-    for (int r = 0; r < NS; ++r) acc[r] = Wf[mc * NS + r];
+    for (int r = 0; r < NS; ++r) acc[r] = P[mc * LDP + r];
     __syncwarp();
   }
-  const int bad = spine_factor_solve<NS>(acc, Lsm, Wf, [&](int r, int c) -> double {
+  const int bad = spine_factor_solve<NS, LDP>(acc, Lsm, P, Wf, [&](int r, int c) -> double {
     return lastR ? 0.0 : -ABr[r * NS + c] * Br[r];
   });
+  // ---- entry rows X(i+1), U(i+1) straight from the solved columns still in registers: lane c < NS holds
+  //      f_R(:,c), lane NS+c holds f_L(:,c), lane 2NS holds zs. Row r of the entry is a scaling by 1/Q_{i+1}(r):
+  //      L = f_L/Q, R = (A_{i+1}^T + f_R)/Q, z = z_x + zs/Q; the U rows are the leaf values. (The factor / parking
+  //      scratch in the head of E is dead by now.) ----
+  {
+    // branch-free: every lane loads unconditionally and selects; lanes > 2NS write to a private dump slot in the
+    // head of E (rows X(i) are written after this and overwrite it)
+    const bool isR = lane < NS, isL = lane >= NS && lane < 2 * NS, isz = lane == 2 * NS;
+    const int cc = isR ? lane : (isL ? lane - NS : 0);
+    double* dcol = isz ? E + 2 * SLOT + NS : (lane > 2 * NS ? E + lane : E + (isR ? SLOT : 0) + NS * NS + cc);
+    const int strd = isz ? 1 : (lane > 2 * NS ? 0 : NS);
+    const bool addA = isR && !lastR;
+#pragma unroll
+    for (int r = 0; r < NS; ++r) {
+      const double dr = Br[r];
+      const double al = ABr[r * NS + cc];
+      const double zx = Br[RD::OZ + r];
+      const double a = addA ? al : 0.0;
+      const double zadd = isz ? zx : 0.0;
+      dcol[r * strd] = fma(dr, acc[r] + a, zadd);
+    }
+#pragma unroll
+    for (int ru = 0; ru < NI; ++ru) {
+      const double du = Br[NS + ru];
+      const double bl = ABr[(NS + ru) * NS + cc];
+      const double zu = Br[RD::OZ + NS + ru];
+      const double v = addA ? du * bl : 0.0;
+      dcol[(NS + ru) * strd] = isz ? zu : v;
+    }
+    if (lane < NS) E[2 * SLOT + ZS + lane] = zlL[lane];
+  }
   // ---- entry rows X(i): A_i^T [f_L f_R] on DMMA ----
   {
     double bf[KA][3], zq[KA];
@@ -272,32 +309,6 @@ __device__ __forceinline__ int merge_raw(const double* Bl, const double* Br, con
         if (q == 0) E[2 * SLOT + row] = zrow - dl * part;
       }
     }
-  }
-  // ---- entry rows X(i+1), U(i+1): row scalings. Element e = lane + 32 t of the 16 x 24 block [L | R]; since
-  //      96 = 4 * 24, the (row, col) pattern repeats every three steps with the row advanced by 4 ----
-  {
-    int ro[3], co[3];
-#pragma unroll
-    for (int u = 0; u < 3; ++u) {
-      const int e = lane + 32 * u;
-      ro[u] = e / (2 * NS);
-      co[u] = e - ro[u] * 2 * NS;
-    }
-#pragma unroll
-    for (int tt = 0; tt < (NS + NI) / 4; ++tt)
-#pragma unroll
-      for (int u = 0; u < 3; ++u) {
-        const int row = 4 * tt + ro[u], col = co[u];
-        const double dr = Br[row];
-        const double a = (col >= NS && !lastR) ? ABr[row * NS + col - NS] : 0.0;  // A_{i+1}(c,r) / B_{i+1}(c,r-NS)
-        const double f = row < NS ? Wf[col * NS + row] : 0.0;
-        double* dst = col < NS ? E + (NS + row) * NS + col : E + SLOT + (NS + row) * NS + col - NS;
-        *dst = dr * (f + a);
-      }
-    const int rs = lane < NS ? lane : 0;
-    const double zs = Wf[2 * NS * NS + rs];
-    if (lane < NS + NI) E[2 * SLOT + NS + lane] = lane < NS ? fma(Br[lane], zs, Br[RD::OZ + lane]) : Br[RD::OZ + lane];
-    if (lane < NS) E[2 * SLOT + ZS + lane] = zlL[lane];
   }
   __syncwarp();
   return bad;
