@@ -410,6 +410,8 @@ def run_ours(args, rank, world, local_rank):
                 "traffic": SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM * B if SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM and (n, m, N) == (12, 4, 256) else None,
                 "peak_kind": pk_kind, "algorithmic_bytes_per_launch": nsub * by_sub, "bytes_per_subtree": by_sub,
                 "avg_launch_ms": k_avg_ms, "kernel_launches_timed": k_n, "kernel_share_of_step": k_avg_ms / ms_per_step,
+                "binding_unit": "LSU data pipe (shared-memory + shuffle wavefronts) at 70 % of peak, DRAM 20 % busy (ncu --set full, "
+                                "profiles/r01_ncu_scan_leaf_v2.md): ~770 wavefronts per merge = 2.08 ms per step at 100 % pipe utilisation",
                 "fp64_tflops_executed": nsub * fl_sub / (k_avg_ms * 1e-3) / 1e12, "fp64_frac_of_dmma_peak": nsub * fl_sub / (k_avg_ms * 1e-3) / 1e12 / fp64["tflops"],
                 "flops_per_subtree": fl_sub,
                 "reference_count_tflops_whole_step": flop_model(n, m, N) * B / (ms_per_step * 1e-3) / 1e12,

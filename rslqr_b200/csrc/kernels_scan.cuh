@@ -315,35 +315,6 @@ __device__ __forceinline__ int merge_raw(const double* Bl, const double* Br, con
 }
 
 
-// one row of the lean Schur update with separate source and destination (the right subtree's rows move into
-// the merged entry): dst <- keep - own * [f_L f_R zs]; side 0: own = R block (keep L), side 1: own = L block
-template <int NS>
-__device__ __forceinline__ void schur_row_io(const double* sL, const double* sR, const double* sz, double* dL, double* dR,
-                                             double* dz, const double* Wf, int side) {
-  double o[NS], kp[NS];
-  const double* own = side ? sL : sR;
-  const double* keep = side ? sR : sL;
-#pragma unroll
-  for (int k = 0; k < NS; ++k) { o[k] = own[k]; kp[k] = keep[k]; }
-  const double z0 = *sz;
-#pragma unroll 2
-  for (int c = 0; c < NS; ++c) {
-    double aL = side ? 0.0 : kp[c];
-    double aR = side ? kp[c] : 0.0;
-#pragma unroll
-    for (int k = 0; k < NS; ++k) {
-      aL = fma(-o[k], Wf[c * NS + k], aL);
-      aR = fma(-o[k], Wf[(NS + c) * NS + k], aR);
-    }
-    dL[c] = aL;
-    dR[c] = aR;
-  }
-  double az = z0;
-#pragma unroll
-  for (int k = 0; k < NS; ++k) az = fma(-o[k], Wf[2 * NS * NS + k], az);
-  *dz = az;
-}
-
 struct ScanBufs {
   double* ent0;    // [batch][M0][ENT]   entries of the 4-knot subtrees (input of the first tier)
   double* sep_in;  // [batch][M0][3][WSZ] records of the interior separators of a subtree: local knots 1, 2, 3
@@ -457,7 +428,7 @@ template <int NS, int NI>
 __global__ void __launch_bounds__(128) scan_down_kernel(Shape s, Bufs b, ScanBufs sb, const double* lam_all, int pack_rhs,
                                                          int M0, long long nsub) {
   using D = Dim<NS, NI>;
-  constexpr int ZS = D::ZS, WSZ = D::WSZ;
+  constexpr int WSZ = D::WSZ;
   static_assert(NS + NI <= 16 && NS <= 16, "two knots per warp pass");
   const int lane = threadIdx.x & 31;
   const long long sub = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
