@@ -197,6 +197,28 @@ def test_scan_path_all_horizons(N):
     s.close()
 
 
+def test_scan_path_is_bit_reproducible():
+    # warp-synchronous shared-memory code with TMA copies: a data race would show up as run-to-run differences.
+    # 40 repeated solves of the same resident batch (more warps than one wave of the GPU) must be bit-identical,
+    # and so must the same problems solved alone (different CTA / warp placement).
+    n, m, N, B = 12, 4, 64, 1500
+    kn, x0 = R.synth_problems(n, m, N, 11, 0, B)
+    s = R.CudaSolver(n, m, N, batch=B, flags=0)
+    s.upload(kn, x0)
+    s.solve()
+    first = s.solution().copy()
+    for _ in range(40):
+        s.solve()
+        assert np.array_equal(s.solution(), first)
+    s.close()
+    one = R.CudaSolver(n, m, N, batch=1, flags=0)
+    for p in (0, 777, 1499):
+        one.upload(kn[p:p + 1], x0[p:p + 1])
+        one.solve()
+        assert np.array_equal(one.solution()[0], first[p])
+    one.close()
+
+
 @pytest.mark.parametrize("mode", [R.MODE_FUSED, R.MODE_SCAN])
 def test_tiered_path_reports_cholesky_failure(mode):
     n, m, N = 12, 4, 64
