@@ -511,17 +511,25 @@ inline int scan_plan(const Shape& s, int batch, ScanPlan* p, std::string& err) {
   if (!scan_shape_ok(s.n, s.m) || s.N < SCAN_LEAF) return 0;
   FusedPlan& f = p->f;
   f.ns = s.n; f.ni = s.m; f.G0 = SCAN_LEAF; f.M0 = s.N / SCAN_LEAF; f.use_dmma = 1;
-  int M = f.M0, span = f.G0;
-  while (M > 1) {
-    if (f.ntiers == 8) return 0;
-    // entries per tier CTA: 4 for batches (2 then 1 of 2 warps active over a CTA's two levels, measured +1.7 % over 8),
-    // 8 for a single long horizon (fewer dependent launches); RSLQR_TIER_E = 2, 4 or 8 overrides
-    const char* tv = getenv("RSLQR_TIER_E");
-    int tier_e = tv ? atoi(tv) : (batch >= 64 ? 4 : 8);
-    if (tier_e != 2 && tier_e != 4 && tier_e != 8) tier_e = 8;
-    const int e = M < tier_e ? M : tier_e;
-    f.tiers[f.ntiers++] = FusedTier{M, e, span};
-    M /= e; span *= e;
+  // entries per tier CTA: 4 for batches (2 then 1 of 2 warps active over a CTA's two levels, measured +1.7 % over 8),
+  // 8 for a single long horizon (fewer dependent launches); RSLQR_TIER_E = 2, 4 or 8 overrides. Falls back to 8 when a
+  // smaller arity would need more than the 8 tier slots.
+  const char* tv = getenv("RSLQR_TIER_E");
+  int tier_e = tv ? atoi(tv) : (batch >= 64 ? 4 : 8);
+  if (tier_e != 2 && tier_e != 4 && tier_e != 8) tier_e = 8;
+  for (;;) {
+    int M = f.M0, span = f.G0;
+    f.ntiers = 0;
+    bool fits = true;
+    while (M > 1) {
+      if (f.ntiers == 8) { fits = false; break; }
+      const int e = M < tier_e ? M : tier_e;
+      f.tiers[f.ntiers++] = FusedTier{M, e, span};
+      M /= e; span *= e;
+    }
+    if (fits) break;
+    if (tier_e == 8) { memset(p, 0, sizeof(*p)); return 0; }
+    tier_e = 8;
   }
   const size_t n = s.n, ent = fused_ent_doubles(s.n, s.m), wsz = (2 * n + 1) * n;
   auto alloc = [&](double** ptr, size_t cnt) {
