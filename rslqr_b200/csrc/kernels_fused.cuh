@@ -166,6 +166,70 @@ __device__ __forceinline__ void tri_solves2(double (&acc)[NS], const double* F) 
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// LDL^T sweep with the right-hand sides riding along as extra ROWS, then the backward sweep.
+//   lanes [0,NS)    : acc = row i of S                                   (acc2 unused)
+//   lanes [NS,2NS)  : acc = S_L(:,c), acc2 = S_R(:,c), c = lane - NS     (two right-hand sides per lane)
+//   lane  2NS       : acc = s
+// Eliminating an appended row y with the pivot rows of S leaves the multipliers y_j <- (D^-1 Lt^-1 y)_j behind: the
+// forward substitution and the diagonal scaling of EVERY right-hand side come out of the same pivot-row shuffles the
+// factorization needs anyway (no factor loads, no parking of the right-hand sides in shared memory). Only the
+// backward sweep Lt^-T reads the factor (row-major Lr, 128-bit broadcast loads shared by both columns of a lane).
+// On return Wout = [f_L | f_R | zs] (column-major, ld NS) and acc / acc2 still hold the lane's solved columns.
+// Same S = Lt D Lt^T as clap_CholeskyFactorize (src/linalg_custom.c:88) up to the diagonal scaling.
+// ---------------------------------------------------------------------------------------------------------
+template <int NS>
+__device__ __forceinline__ int spine_core2(double (&acc)[NS], double (&acc2)[NS], double* Lr, double* Wout) {
+  static_assert(NS % 2 == 0 && 2 * NS + 1 <= 32, "pairs; one warp per separator");
+  const int lane = threadIdx.x & 31;
+  int bad = 0;
+#pragma unroll
+  for (int j = 0; j < NS; ++j) {
+    const double d = shfl_d(acc[j], j);
+    if (!(d > 0.0)) bad = 1;
+    const double dinv = fast_rcp(d);
+    const double lij = acc[j] * dinv, lij2 = acc2[j] * dinv;
+#pragma unroll
+    for (int k = j + 1; k < NS; ++k) {
+      const double pk = shfl_d(acc[k], j);  // pivot row element S'(j,k)
+      acc[k] = fma(-lij, pk, acc[k]);
+      acc2[k] = fma(-lij2, pk, acc2[k]);
+    }
+    acc[j] = lane == j ? dinv : lij;
+    acc2[j] = lij2;
+  }
+  if (lane < NS) {
+#pragma unroll
+    for (int k = 0; k < NS; k += 2) *reinterpret_cast<double2*>(Lr + lane * NS + k) = make_double2(acc[k], acc[k + 1]);
+  }
+  __syncwarp();
+#pragma unroll
+  for (int j = NS - 1; j > 0; --j) {
+#pragma unroll
+    for (int p = 0; p < j; p += 2) {
+      const double2 l = *reinterpret_cast<const double2*>(Lr + j * NS + p);
+      acc[p] = fma(-l.x, acc[j], acc[p]);
+      acc2[p] = fma(-l.x, acc2[j], acc2[p]);
+      if (p + 1 < j) {
+        acc[p + 1] = fma(-l.y, acc[j], acc[p + 1]);
+        acc2[p + 1] = fma(-l.y, acc2[j], acc2[p + 1]);
+      }
+    }
+  }
+  if (lane >= NS && lane <= 2 * NS) {
+    const int c = lane - NS;  // lane 2NS: c = NS -> column 2NS of W is written through the f_L expression below
+    double* w1 = lane < 2 * NS ? Wout + c * NS : Wout + 2 * NS * NS;
+#pragma unroll
+    for (int r = 0; r < NS; ++r) w1[r] = acc[r];
+    if (lane < 2 * NS) {
+#pragma unroll
+      for (int r = 0; r < NS; ++r) Wout[(NS + c) * NS + r] = acc2[r];
+    }
+  }
+  __syncwarp();
+  return bad;
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // One separator, one warp: inner products -> factorization -> solves. Lane roles:
 //   lanes [0,NS)      : column c of S  (then, for the solves, column c of S_R -> f_R)
 //   lanes [NS,2NS)    : column c of S_L -> f_L
@@ -250,6 +314,17 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
 #pragma unroll
       for (int r = 0; r < NS; ++r) acc[r] = fma(ldab(col + r), x, acc[r]);
     }
+  }
+  if constexpr (F2) {
+    // right-hand sides stay in registers: lanes [NS,2NS) carry S_L (acc) and S_R = -X_R(i+1) (acc2), lane 2NS carries s
+    double acc2[NS];
+#pragma unroll
+    for (int r = 0; r < NS; ++r) {
+      const double ln = LXn[r * NS + c], rn = RXn[r * NS + c], zz = zxn[r] + zln[r];
+      acc[r] = lane < NS ? acc[r] - ln : (lane >= 2 * NS ? acc[r] - zz : acc[r]);
+      acc2[r] = (lane >= NS && lane < 2 * NS) ? -rn : 0.0;
+    }
+    return spine_core2<NS>(acc, acc2, Lsm, Wout);
   }
   const int mycol = lane <= 2 * NS ? lane : 2 * NS;
   if (lane < NS) {
