@@ -114,56 +114,9 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
 
 __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 
-// ---- factor scratch with 128-bit broadcast loads: F = [Lr (NS*NS) | Lc (NS*NS) | Dv (NS)] -------------------
-// Lr row-major (row j = Lt(j, .), for the backward sweep), Lc column-major (column j = Lt(., j), for the forward
-// sweep), Dv = 1/D. Every sweep step then reads two factor entries per shared-memory wavefront instead of one.
+// factor scratch of spine_core2: Lt row-major (row j = Lt(j, .)), 16-byte aligned for the 128-bit broadcast loads
 template <int NS>
-__host__ __device__ constexpr int factor_scratch_doubles() { return 2 * NS * NS + NS + (NS & 1); }
-
-template <int NS>
-__device__ __forceinline__ void store_factor2(const double (&acc)[NS], double mydinv, double* F) {
-  static_assert(NS % 2 == 0, "pairs");
-  const int lane = threadIdx.x & 31;
-  if (lane < NS) {
-    F[2 * NS * NS + lane] = mydinv;
-#pragma unroll
-    for (int k = 0; k < NS; k += 2) *reinterpret_cast<double2*>(F + lane * NS + k) = make_double2(acc[k], acc[k + 1]);
-#pragma unroll
-    for (int k = 0; k < NS; ++k) F[NS * NS + k * NS + lane] = acc[k];
-  }
-}
-
-// acc (one right-hand-side column per lane) <- Lt^-T D^-1 Lt^-1 acc
-template <int NS>
-__device__ __forceinline__ void tri_solves2(double (&acc)[NS], const double* F) {
-  const double* Lr = F;
-  const double* Lc = F + NS * NS;
-  const double* Dv = F + 2 * NS * NS;
-#pragma unroll
-  for (int j = 0; j < NS - 1; ++j) {
-#pragma unroll
-    for (int p = (j + 1) & ~1; p < NS; p += 2) {
-      const double2 l = *reinterpret_cast<const double2*>(Lc + j * NS + p);
-      if (p > j) acc[p] = fma(-l.x, acc[j], acc[p]);
-      acc[p + 1] = fma(-l.y, acc[j], acc[p + 1]);
-    }
-  }
-#pragma unroll
-  for (int j = 0; j < NS; j += 2) {
-    const double2 d = *reinterpret_cast<const double2*>(Dv + j);
-    acc[j] *= d.x;
-    acc[j + 1] *= d.y;
-  }
-#pragma unroll
-  for (int j = NS - 1; j > 0; --j) {
-#pragma unroll
-    for (int p = 0; p < j; p += 2) {
-      const double2 l = *reinterpret_cast<const double2*>(Lr + j * NS + p);
-      acc[p] = fma(-l.x, acc[j], acc[p]);
-      if (p + 1 < j) acc[p + 1] = fma(-l.y, acc[j], acc[p + 1]);
-    }
-  }
-}
+__host__ __device__ constexpr int factor_scratch_doubles() { return NS * NS + (NS & 1); }
 
 // ---------------------------------------------------------------------------------------------------------
 // LDL^T sweep with the right-hand sides riding along as extra ROWS, then the backward sweep.
@@ -242,7 +195,8 @@ __device__ __forceinline__ int spine_core2(double (&acc)[NS], double (&acc2)[NS]
 //   LXi/RXi : X rows of knot i in its L / R block (row-major, ld NS), the U rows follow directly
 //   zxi   : z_x(i) followed by z_u(i)
 //   LXn/RXn : X rows of knot i+1; zxn = z_x(i+1); zln = z_lambda(i+1)
-//   Lsm   : NS*NS doubles of scratch for Lt (row-major); Wout: [f_L | f_R | zs] column-major ld NS
+//   Lsm   : NS*NS doubles of scratch for Lt (row-major, 16-byte aligned when F2); Wout: [f_L | f_R | zs] column-major ld NS
+//   F2    : the right-hand sides ride through the factorization (spine_core2) instead of being parked and solved after it
 // Returns non-zero (warp-uniform) when a pivot is <= 0 (reference: clap_CholeskyFactorize fails).
 // ---------------------------------------------------------------------------------------------------------
 template <int NS, int NI, bool LDG = true, bool F2 = false>
@@ -341,7 +295,6 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
   }
   // ---- factorization, lane i < NS holds row i of S in acc[] (the other lanes run along on junk) ----
   int bad = 0;
-  double mydinv = 0.0;  // 1/D(lane)
 #pragma unroll
   for (int j = 0; j < NS; ++j) {
     const double d = shfl_d(acc[j], j);
@@ -354,11 +307,8 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
       acc[k] = fma(-lij, pk, acc[k]);
     }
     acc[j] = lane == j ? dinv : lij;  // the diagonal slot of Lt carries 1/D(j)
-    mydinv = lane == j ? dinv : mydinv;
   }
-  if constexpr (F2) {  // Lsm has factor_scratch_doubles<NS>() doubles, 16-byte aligned
-    store_factor2<NS>(acc, mydinv, Lsm);
-  } else if (lane < NS) {
+  if (lane < NS) {
 #pragma unroll
     for (int k = 0; k < NS; ++k) Lsm[lane * NS + k] = acc[k];
   }
@@ -371,21 +321,17 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
 #pragma unroll
     for (int r = 0; r < NS; ++r) acc[r] = Wout[mycol * NS + r];
   }
-  if constexpr (F2) {
-    tri_solves2<NS>(acc, Lsm);
-  } else {
 #pragma unroll
-    for (int j = 0; j < NS; ++j) {
+  for (int j = 0; j < NS; ++j) {
 #pragma unroll
-      for (int i = j + 1; i < NS; ++i) acc[i] = fma(-Lsm[i * NS + j], acc[j], acc[i]);
-    }
+    for (int i = j + 1; i < NS; ++i) acc[i] = fma(-Lsm[i * NS + j], acc[j], acc[i]);
+  }
 #pragma unroll
-    for (int j = 0; j < NS; ++j) acc[j] *= Lsm[j * NS + j];
+  for (int j = 0; j < NS; ++j) acc[j] *= Lsm[j * NS + j];
 #pragma unroll
-    for (int j = NS - 1; j >= 0; --j) {
+  for (int j = NS - 1; j >= 0; --j) {
 #pragma unroll
-      for (int i = 0; i < j; ++i) acc[i] = fma(-Lsm[j * NS + i], acc[j], acc[i]);
-    }
+    for (int i = 0; i < j; ++i) acc[i] = fma(-Lsm[j * NS + i], acc[j], acc[i]);
   }
   __syncwarp();
   if (lane <= 2 * NS) {

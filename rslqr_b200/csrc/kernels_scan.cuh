@@ -24,51 +24,6 @@
 
 namespace rslqr {
 
-// the spine after the inner products: lanes < NS hold column c of S in acc[]; the right-hand-side columns
-// S_L (lanes NS..2NS-1) and s (lane 2NS) are parked in Wout[lane*NS + r]; load_sr(r, c) yields S_R(r, c).
-// Same factorization / solves as spine_merge (kernels_fused.cuh).
-// Park: where the right-hand-side columns were parked, Park[lane*LDP + r]; an odd LDP makes the column-per-lane
-// accesses bank-conflict free (W itself keeps ld NS: it is the record format and the DMMA B operand).
-template <int NS, int LDP, class LoadSR>
-__device__ __forceinline__ int spine_factor_solve(double (&acc)[NS], double* Lsm, const double* Park, double* Wout,
-                                                   LoadSR load_sr) {
-  const int lane = threadIdx.x & 31;
-  const int c = lane < NS ? lane : 0;
-  const int mycol = lane <= 2 * NS ? lane : 2 * NS;
-  int bad = 0;
-  double mydinv = 0.0;
-#pragma unroll
-  for (int j = 0; j < NS; ++j) {
-    const double d = shfl_d(acc[j], j);
-    if (!(d > 0.0)) bad = 1;
-    const double dinv = fast_rcp(d);
-    const double lij = acc[j] * dinv;
-#pragma unroll
-    for (int k = j + 1; k < NS; ++k) {
-      const double pk = shfl_d(acc[k], j);
-      acc[k] = fma(-lij, pk, acc[k]);
-    }
-    acc[j] = lane == j ? dinv : lij;
-    mydinv = lane == j ? dinv : mydinv;
-  }
-  store_factor2<NS>(acc, mydinv, Lsm);  // Lsm: factor_scratch_doubles<NS>() doubles, 16-byte aligned
-  __syncwarp();
-#pragma unroll
-  for (int r = 0; r < NS; ++r) {
-    const double sr = load_sr(r, c);  // warp-uniform control flow inside
-    acc[r] = lane < NS ? sr : Park[mycol * LDP + r];
-  }
-  tri_solves2<NS>(acc, Lsm);
-  __syncwarp();
-  if (lane <= 2 * NS) {
-    const int wc = lane < NS ? NS + lane : (lane < 2 * NS ? lane - NS : 2 * NS);
-#pragma unroll
-    for (int r = 0; r < NS; ++r) Wout[wc * NS + r] = acc[r];
-  }
-  __syncwarp();
-  return bad;
-}
-
 // entry `rw` of the negated right-hand side of local knot k (reference src/solver.c:138-190), either packed on the
 // fly from the flat knot blocks or read from the soln buffer (pack_rhs == 0: the caller uploaded its own rhs)
 __device__ __forceinline__ double scan_rhs(const Shape& s, const Bufs& b, int prob, int k, int rw, int pack_rhs) {
@@ -222,52 +177,61 @@ __device__ __forceinline__ int merge_raw(const double* Bl, const double* Br, con
         }
       if (q == 0 && row < NS) P[2 * NS * LDP + row] = (mt ? p1 : p0) - t;
     }
-    if (lane >= NS && lane < 2 * NS) {
-      const int cl = lane - NS;
-      const double dcs = first0 ? 0.0 : -Bl[cl];
+    __syncwarp();
+    // lanes < NS: column (= row) of S; lanes [NS,2NS): S_L(:,c) = -A_i(:,c)/Q_i(c) and S_R(:,c) = -A_{i+1}(c,:)^T/Q_{i+1}
+    // straight into registers; lane 2NS: s
+    const bool isL = lane >= NS && lane < 2 * NS;
+    const int cl = isL ? lane - NS : 0;
+    const int mc = lane < NS ? lane : 2 * NS;
+    const double dcs = (first0 || !isL) ? 0.0 : -Bl[cl];
 #pragma unroll
-      for (int r = 0; r < NS; ++r) P[lane * LDP + r] = ABl[cl * NS + r] * dcs;
+    for (int r = 0; r < NS; ++r) {
+      const double pv = P[mc * LDP + r], al = ABl[cl * NS + r];
+      acc[r] = isL ? al * dcs : pv;
     }
-    __syncwarp();
-    const int mc = lane < NS ? lane : 0;
-#pragma unroll
-    for (int r = 0; r < NS; ++r) acc[r] = P[mc * LDP + r];
-    __syncwarp();
   }
-  const int bad = spine_factor_solve<NS, LDP>(acc, Lsm, P, Wf, [&](int r, int c) -> double {
-    return lastR ? 0.0 : -ABr[r * NS + c] * Br[r];
-  });
-  // ---- entry rows X(i+1), U(i+1) straight from the solved columns still in registers: lane c < NS holds
-  //      f_R(:,c), lane NS+c holds f_L(:,c), lane 2NS holds zs. Row r of the entry is a scaling by 1/Q_{i+1}(r):
-  //      L = f_L/Q, R = (A_{i+1}^T + f_R)/Q, z = z_x + zs/Q; the U rows are the leaf values. (The factor / parking
-  //      scratch in the head of E is dead by now.) ----
+  double acc2[NS];
   {
-    // branch-free: every lane loads unconditionally and selects; lanes > 2NS write to a private dump slot in the
-    // head of E (rows X(i) are written after this and overwrite it)
-    const bool isR = lane < NS, isL = lane >= NS && lane < 2 * NS, isz = lane == 2 * NS;
-    const int cc = isR ? lane : (isL ? lane - NS : 0);
-    double* dcol = isz ? E + 2 * SLOT + NS : (lane > 2 * NS ? E + lane : E + (isR ? SLOT : 0) + NS * NS + cc);
-    const int strd = isz ? 1 : (lane > 2 * NS ? 0 : NS);
-    const bool addA = isR && !lastR;
+    const bool isL = lane >= NS && lane < 2 * NS;
+    const int cl = isL ? lane - NS : 0;
+#pragma unroll
+    for (int r = 0; r < NS; ++r) {
+      const double ar = ABr[r * NS + cl], dr = Br[r];
+      acc2[r] = (isL && !lastR) ? -ar * dr : 0.0;
+    }
+  }
+  const int bad = spine_core2<NS>(acc, acc2, Lsm, Wf);
+  // ---- entry rows X(i+1), U(i+1) straight from the solved columns still in registers: lane NS+c holds f_L(:,c)
+  //      (acc) and f_R(:,c) (acc2), lane 2NS holds zs. Row r of the entry is a scaling by 1/Q_{i+1}(r):
+  //      L = f_L/Q, R = (A_{i+1}^T + f_R)/Q, z = z_x + zs/Q; the U rows are the leaf values. Branch-free: every lane
+  //      loads unconditionally and selects; lanes without a column write to private dump slots in the head of E
+  //      (dead scratch now; rows X(i) are written after this and overwrite it). ----
+  {
+    const bool isL = lane >= NS && lane < 2 * NS, isz = lane == 2 * NS;
+    const int cc = isL ? lane - NS : 0;
+    double* d1 = isL ? E + NS * NS + cc : (isz ? E + 2 * SLOT + NS : E + lane);          // L part / z
+    double* d2 = isL ? E + SLOT + NS * NS + cc : E + 32 + lane;                           // R part
+    const int s1 = isL ? NS : (isz ? 1 : 0), s2 = isL ? NS : 0;
+    const bool addA = isL && !lastR;
 #pragma unroll
     for (int r = 0; r < NS; ++r) {
       const double dr = Br[r];
       const double al = ABr[r * NS + cc];
       const double zx = Br[RD::OZ + r];
-      const double a = addA ? al : 0.0;
-      const double zadd = isz ? zx : 0.0;
-      dcol[r * strd] = fma(dr, acc[r] + a, zadd);
+      d1[r * s1] = fma(dr, acc[r], isz ? zx : 0.0);
+      d2[r * s2] = dr * (acc2[r] + (addA ? al : 0.0));
     }
 #pragma unroll
     for (int ru = 0; ru < NI; ++ru) {
       const double du = Br[NS + ru];
       const double bl = ABr[(NS + ru) * NS + cc];
       const double zu = Br[RD::OZ + NS + ru];
-      const double v = addA ? du * bl : 0.0;
-      dcol[(NS + ru) * strd] = isz ? zu : v;
+      d1[(NS + ru) * s1] = isz ? zu : 0.0;
+      d2[(NS + ru) * s2] = addA ? du * bl : 0.0;
     }
     if (lane < NS) E[2 * SLOT + ZS + lane] = zlL[lane];
   }
+  __syncwarp();
   // ---- entry rows X(i): A_i^T [f_L f_R] on DMMA ----
   {
     double bf[KA][3], zq[KA];
@@ -553,7 +517,9 @@ inline int scan_plan(const Shape& s, int batch, ScanPlan* p, std::string& err) {
 
 template <int NS, int NI>
 inline cudaError_t launch_scan_leaf(ScanPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st) {
-  constexpr int smem = scan_leaf_smem_doubles<NS, NI>() * (int)sizeof(double);
+  // RSLQR_LEAF_PAD_KB: extra (unused) shared memory per CTA, an occupancy knob for experiments
+  static const int pad = [] { const char* v = getenv("RSLQR_LEAF_PAD_KB"); return v ? atoi(v) * 1024 : 0; }();
+  const int smem = scan_leaf_smem_doubles<NS, NI>() * (int)sizeof(double) + pad;
   static bool attr_done = false;
   if (!attr_done) {
     cudaError_t e = cudaFuncSetAttribute(scan_leaf_kernel<NS, NI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
