@@ -475,7 +475,7 @@ def run_long(args, rank, world, local_rank):
     if world > 1:
         dist = init_nccl(local_rank)
     knots, x0 = R.synth_problems(n, m, N, SEED, 0, 1)
-    lh = LongHorizon(n, m, N, rank, world, local_rank)
+    lh = LongHorizon(n, m, N, rank, world, local_rank, exchange=args.exchange)
     lh.upload(knots[0], x0[0])
     for _ in range(max(args.warmup, 3)):
         lh.solve_async()
@@ -513,7 +513,9 @@ def run_long(args, rank, world, local_rank):
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": False, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"single long-horizon LQR n={n} m={m} N={N} (BASELINE configs[3])", "seed": SEED,
-                       "parallelism": f"{world} subtrees of {N // world} knots, one all-gather of {lh.shard.payload_doubles * 8} B per rank",
+                       "parallelism": f"{world} subtrees of {N // world} knots, one exchange of {lh.shard.payload_doubles * 8} B per rank",
+                       "exchange": ("peer stores over NVLink into symmetric memory + arrival flags (own kernels)" if lh.exchange == "p2p"
+                                    else "NCCL all-gather") if world > 1 else "none",
                        "l2": "working set (state 92 MB + inputs 31 MB over all ranks) vs 126 MB L2 per GPU; no explicit flush"},
             "clocks": clocks,
             "e2e": {"value": e2e_ms, "unit": "ms", "h2d_bytes_per_step": int(knots.nbytes // world), "d2h_bytes_per_step": int(z.nbytes)},
@@ -664,6 +666,8 @@ def main():
     ap.add_argument("--workload", default="batch", choices=["batch", "long", "large", "single"],
                     help="batch = BASELINE configs[2] (default, the headline metric); long = configs[3] single long horizon")
     ap.add_argument("--horizon", type=int, default=16384, help="horizon of the long workload")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "p2p", "nccl"],
+                    help="long workload: transport of the shard payloads (auto = p2p when symmetric memory works)")
     ap.add_argument("--cpu-long", action="store_true", help="long workload: also time one CPU solve (takes ~10-60 s)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--chunk", type=int, default=0, help="problems per pipeline chunk of the e2e call (0 = automatic)")

@@ -154,6 +154,15 @@ size_t rslqr_cuda_shard_payload_doubles(rslqr_cuda_solver* h);
 int rslqr_cuda_shard_reduce(rslqr_cuda_solver* h, double* d_payload);
 int rslqr_cuda_shard_finish(rslqr_cuda_solver* h, const double* d_gathered, int rank, int nranks);
 int rslqr_cuda_shard_exchange(rslqr_cuda_solver** hs, int nranks, double** d_payload, double** d_gathered);
+/* Exchange without a collective: shard_push stores the payload into every rank's gathered buffer over NVLink peer
+ * mappings (peer_gathered[r], peer_flags[r]: rank r's buffers as mapped into this process) and raises flag `rank` there
+ * to `epoch`; shard_finish_wait = shard_finish whose cross-GPU tier kernel first waits (bounded) until the local flags of
+ * all ranks have reached `epoch`. Epochs must increase by one per solve and the gathered buffer alternate between two
+ * halves, so that a rank one solve ahead never overwrites data still being read. Scan kernels only. */
+int rslqr_cuda_shard_push(rslqr_cuda_solver* h, const double* d_payload, double* const* peer_gathered,
+                          unsigned long long* const* peer_flags, int rank, int nranks, unsigned long long epoch);
+int rslqr_cuda_shard_finish_wait(rslqr_cuda_solver* h, const double* d_gathered, const unsigned long long* d_flags,
+                                 unsigned long long epoch, int rank, int nranks);
 /* enqueue on a caller-owned cudaStream_t (e.g. the stream NCCL collectives are ordered on) */
 int rslqr_cuda_set_stream(rslqr_cuda_solver* h, void* stream);
 

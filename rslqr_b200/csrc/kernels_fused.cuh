@@ -762,7 +762,45 @@ struct TierArgs {
   long long out_stride;
   int Min, ecount;
   int span;                // knots per input entry (status words only; 0 = cross-GPU tier, flags only)
+  // cross-GPU tier fed by peer stores over NVLink (shard_push_kernel): entry e is complete once wait_flags[e] >= wait_epoch
+  const unsigned long long* wait_flags;  // nullptr = inputs are already complete (stream order / NCCL)
+  unsigned long long wait_epoch;
 };
+
+// ---- peer-to-peer exchange of the shard payloads (one long horizon split over GPUs) ----
+struct PeerPtrs {
+  double* gathered[8];             // rank r's gathered buffer (payload slots of all ranks), mapped into this process
+  unsigned long long* flags[8];    // rank r's arrival flags, one per source rank
+};
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// CTA r stores this rank's payload into rank r's gathered buffer (slot `rank`) with plain peer stores over NVLink,
+// then publishes it: system-scope fence, release store of the epoch into rank r's flag word for this source.
+__global__ void shard_push_kernel(const double* src, PeerPtrs peers, int rank, int pay, unsigned long long epoch) {
+  const int r = blockIdx.x;
+  double* dst = peers.gathered[r] + (size_t)rank * pay;
+  if (dst != src) {
+    const double2* s2 = reinterpret_cast<const double2*>(src);
+    double2* d2 = reinterpret_cast<double2*>(dst);
+    for (int i = threadIdx.x; i < pay / 2; i += blockDim.x) d2[i] = s2[i];
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) st_release_sys(peers.flags[r] + rank, epoch);
+}
 
 template <int NS, int NI>
 __global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, TierArgs a) {
@@ -786,6 +824,17 @@ __global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, TierArgs 
     fence_mbar_init();
   }
   __syncthreads();
+  if (a.wait_flags) {  // entries arrive by peer stores: wait for their flags (bounded: a lost peer must not hang the GPU)
+    if (tid < a.Min) {
+      const unsigned long long t0 = global_ns();
+      while (ld_acquire_sys(a.wait_flags + tid) < a.wait_epoch) {
+        if (global_ns() - t0 > 4000000000ull) { b.flags[prob] = 2; break; }
+        __nanosleep(64);
+      }
+    }
+    __syncthreads();
+    asm volatile("fence.proxy.async;" ::: "memory");  // the TMA (async proxy) reads what the acquire made visible
+  }
   if (tid == 0) {  // TMA bulk copies (one when the CTA's entries are contiguous in HBM)
     mbar_expect_tx(&mbar, ecount * ENT * (int)sizeof(double));
     if (a.in_stride == ENT) bulk_g2s(ents, in, ecount * ENT * (int)sizeof(double), &mbar);
@@ -1033,7 +1082,7 @@ inline cudaError_t launch_tiers(FusedPlan& p, const Shape& s, const Bufs& b, int
   if (e != cudaSuccess) return e;
   for (int t = 0; t < p.ntiers; ++t) {
     const FusedTier& T = p.tiers[t];
-    TierArgs a;
+    TierArgs a{};
     a.in = p.fb.ent[t]; a.in_stride = D::ENT;
     a.ab = b.knots + (size_t)(T.span - 1) * s.stride + s.oA; a.ab_stride = (long long)T.span * s.stride;
     a.ab_pstride = (long long)s.N * s.stride;
@@ -1122,7 +1171,7 @@ inline cudaError_t shard_finish_t(FusedPlan& p, const Shape& s, const Bufs& b, c
   if (nranks > 1) {
     cudaError_t e = tier_attr<NS, NI>();
     if (e != cudaSuccess) return e;
-    TierArgs a;
+    TierArgs a{};
     const long long pay = (long long)fused_payload_doubles(NS, NI);
     a.in = gathered; a.in_stride = pay;
     a.ab = gathered + D::ENT; a.ab_stride = pay; a.ab_pstride = 0;

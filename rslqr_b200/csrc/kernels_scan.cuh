@@ -571,7 +571,8 @@ inline int scan_shard_reduce(ScanPlan& p, const Shape& s, const Bufs& b, int pac
 }
 
 inline int scan_shard_finish(ScanPlan& p, const Shape& s, const Bufs& b, int pack_rhs, cudaStream_t st, const double* gathered,
-                             int rank, int nranks, std::string& err) {
+                             int rank, int nranks, std::string& err, const unsigned long long* wait_flags = nullptr,
+                             unsigned long long wait_epoch = 0) {
   using D = Dim<12, 4>;
   if (!p.f.available || p.f.ntiers < 1) { err = "shard needs the scan kernels"; return -5; }
   const double *left = nullptr, *right = nullptr;
@@ -579,8 +580,9 @@ inline int scan_shard_finish(ScanPlan& p, const Shape& s, const Bufs& b, int pac
   if (nranks > 1) {
     e = tier_attr<12, 4>();
     if (e == cudaSuccess) {
-      TierArgs a;
+      TierArgs a{};
       const long long pay = (long long)fused_payload_doubles(12, 4);
+      a.wait_flags = wait_flags; a.wait_epoch = wait_epoch;
       a.in = gathered; a.in_stride = pay;
       a.ab = gathered + D::ENT; a.ab_stride = pay; a.ab_pstride = 0;
       a.sep = p.f.xsep; a.sep_pstride = 0; a.sep_mul = 1;

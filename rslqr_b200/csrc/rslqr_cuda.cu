@@ -717,6 +717,37 @@ extern "C" int rslqr_cuda_shard_finish(rslqr_cuda_solver* h, const double* d_gat
   return rc;
 }
 
+// Peer-to-peer exchange (NVLink): instead of an all-gather collective, shard_push stores this rank's payload straight
+// into every rank's gathered buffer and raises a flag there; shard_finish_wait lets the cross-GPU tier kernel wait for
+// the flags of all ranks. `peer_gathered[r]` / `peer_flags[r]` are rank r's buffers as mapped into THIS process
+// (torch symmetric memory / cudaIpc; plain device pointers when the ranks are handles of one process).
+extern "C" int rslqr_cuda_shard_push(rslqr_cuda_solver* h, const double* d_payload, double* const* peer_gathered,
+                                     unsigned long long* const* peer_flags, int rank, int nranks, unsigned long long epoch) {
+  if (!h || !h->shard || !d_payload || !peer_gathered || !peer_flags || nranks < 1 || nranks > 8 || rank < 0 || rank >= nranks)
+    return fail(RSLQR_E_ARG, "shard_push: bad argument");
+  CU(cudaSetDevice(h->device));
+  PeerPtrs pp;
+  memset(&pp, 0, sizeof(pp));
+  for (int r = 0; r < nranks; ++r) { pp.gathered[r] = peer_gathered[r]; pp.flags[r] = peer_flags[r]; }
+  const int pay = (int)fused_payload_doubles(h->s.n, h->s.m);
+  shard_push_kernel<<<nranks, 256, 0, h->stream>>>(d_payload, pp, rank, pay, epoch);
+  CU(cudaGetLastError());
+  ++h->launches;
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_shard_finish_wait(rslqr_cuda_solver* h, const double* d_gathered, const unsigned long long* d_flags,
+                                            unsigned long long epoch, int rank, int nranks) {
+  if (!h || !h->shard || nranks < 1 || nranks > 8 || (nranks & (nranks - 1)) || rank < 0 || rank >= nranks ||
+      (nranks > 1 && (!d_gathered || !d_flags)) || h->s.kofs != rank * h->s.N || h->s.Ng != nranks * h->s.N)
+    return fail(RSLQR_E_ARG, "shard_finish_wait: bad argument");
+  if (rslqr_cuda_get_mode(h) != RSLQR_MODE_SCAN) return fail(RSLQR_E_UNSUPPORTED, "the peer-to-peer exchange needs the scan kernels");
+  CU(cudaSetDevice(h->device));
+  int rc = scan_shard_finish(h->scan, h->s, h->b, 1, h->stream, d_gathered, rank, nranks, g_err, d_flags, epoch);
+  h->launches = h->scan.f.launches;
+  return rc;
+}
+
 // Enqueue on a caller-owned stream (e.g. the one NCCL collectives are ordered on) instead of the handle's own.
 extern "C" int rslqr_cuda_set_stream(rslqr_cuda_solver* h, void* stream) {
   if (!h) return fail(RSLQR_E_ARG, "handle is NULL");

@@ -4,7 +4,9 @@
   (SURVEY.md 8e, first row);
 * one long horizon: shard r owns knots [r*N/G, (r+1)*N/G); the only exchange is one all-gather of the per-shard
   payload (boundary entry + [A|B] of the shard's last knot, 7.2 KB at n=12) -- the top log2(G) separator levels are
-  then computed redundantly on every rank (second row).
+  then computed redundantly on every rank (second row). Two transports: peer stores over NVLink into
+  symmetric memory with arrival flags, issued by our own kernels (`exchange="p2p"`, no collective launch on the
+  critical path), or an NCCL all-gather (`exchange="nccl"`, also the fallback when symmetric memory is unavailable).
 """
 import numpy as np
 
@@ -26,22 +28,60 @@ def allgather_payload(send, gathered, group=None):
 class LongHorizon:
     """One rank's part of a single long-horizon solve (BASELINE configs[3])."""
 
-    def __init__(self, n, m, N, rank, world, device):
+    def __init__(self, n, m, N, rank, world, device, exchange="auto"):
         import torch
         from .lib import ShardSolver
         self.torch = torch
         self.shard = ShardSolver(n, m, N, rank, world, device=device)
-        self.world = world
-        pay = self.shard.payload_doubles
+        self.world, self.rank = world, rank
+        pay = self.pay = self.shard.payload_doubles
         self.d_pay = torch.zeros(pay, dtype=torch.float64, device=f"cuda:{device}")
         self.d_gat = torch.zeros(pay * world, dtype=torch.float64, device=f"cuda:{device}")
         # kernels and the collective are ordered on torch's current stream: no host synchronisation in between
         self.shard.set_stream(torch.cuda.current_stream(device).cuda_stream)
+        self.exchange, self.epoch, self.symm = "nccl", 0, None
+        if world > 1 and exchange in ("auto", "p2p"):
+            try:
+                self._setup_p2p(device)
+                self.exchange = "p2p"
+            except Exception as e:   # no symmetric memory on this box / build: keep the NCCL all-gather
+                if exchange == "p2p":
+                    raise
+                self.p2p_error = repr(e)
+
+    def _setup_p2p(self, device):
+        """One symmetric allocation per rank: [2][world][pay] gathered payload slots (double-buffered by epoch parity)
+        followed by `world` 64-bit arrival flags; every rank maps every other rank's allocation (NVLink peer access)."""
+        torch = self.torch
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        from .lib import MODE_SCAN
+        if self.shard.mode != MODE_SCAN:
+            raise RuntimeError("the peer-to-peer exchange needs the scan kernels")
+        words = 2 * self.world * self.pay + self.world
+        buf = symm.empty(words, dtype=torch.float64, device=torch.device("cuda", device))
+        buf.zero_()
+        hdl = symm.rendezvous(buf, dist.group.WORLD.group_name)
+        ptrs = [int(p) for p in hdl.buffer_ptrs]
+        self.symm, self.symm_hdl = buf, hdl
+        self.peer_base = ptrs
+        self.flag_off = 2 * self.world * self.pay * 8
+        torch.cuda.synchronize()
+        dist.barrier()
 
     def upload(self, knots_full, x0):
         self.shard.upload_shard(knots_full, x0)
 
     def solve_async(self):
+        if self.exchange == "p2p":
+            self.epoch += 1
+            half = (self.epoch & 1) * self.world * self.pay * 8
+            mine = self.peer_base[self.rank] + half
+            self.shard.reduce(mine + self.rank * self.pay * 8)       # payload lands in the own slot of the own buffer
+            self.shard.push(mine + self.rank * self.pay * 8, [b + half for b in self.peer_base],
+                            [b + self.flag_off for b in self.peer_base], self.epoch)
+            self.shard.finish_wait(mine, self.peer_base[self.rank] + self.flag_off, self.epoch)
+            return
         self.shard.reduce(self.d_pay.data_ptr())
         if self.world > 1:
             allgather_payload(self.d_pay, self.d_gat)

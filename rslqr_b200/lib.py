@@ -73,6 +73,8 @@ _sig("rslqr_cuda_create_shard", C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c
 _sig("rslqr_cuda_shard_payload_doubles", C.c_size_t, C.c_void_p)
 _sig("rslqr_cuda_shard_reduce", C.c_int, C.c_void_p, C.c_void_p)
 _sig("rslqr_cuda_shard_finish", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int)
+_sig("rslqr_cuda_shard_push", C.c_int, C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_uint64)
+_sig("rslqr_cuda_shard_finish_wait", C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int)
 _sig("rslqr_cuda_shard_exchange", C.c_int, C.POINTER(C.c_void_p), C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p))
 _sig("rslqr_cuda_set_stream", C.c_int, C.c_void_p, C.c_void_p)
 _sig("rslqr_synth_fill", C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.c_void_p)
@@ -499,6 +501,17 @@ class ShardSolver(CudaSolver):
 
     def set_stream(self, stream_ptr):
         _check(LIB.rslqr_cuda_set_stream(self.h, C.c_void_p(stream_ptr)), "set_stream")
+
+    def push(self, d_payload_ptr, peer_gathered_ptrs, peer_flag_ptrs, epoch):
+        """peer stores of this shard's payload into every rank's gathered buffer + flag (NVLink peer mappings)"""
+        n = self.nranks
+        pg = (C.c_void_p * n)(*peer_gathered_ptrs)
+        pf = (C.c_void_p * n)(*peer_flag_ptrs)
+        _check(LIB.rslqr_cuda_shard_push(self.h, C.c_void_p(d_payload_ptr), pg, pf, self.rank, n, epoch), "shard_push")
+
+    def finish_wait(self, d_gathered_ptr, d_flags_ptr, epoch):
+        _check(LIB.rslqr_cuda_shard_finish_wait(self.h, C.c_void_p(d_gathered_ptr), C.c_void_p(d_flags_ptr), epoch,
+                                                self.rank, self.nranks), "shard_finish_wait")
 
 
 def shard_exchange(shards, payload_ptrs, gathered_ptrs):

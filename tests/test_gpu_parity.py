@@ -462,6 +462,43 @@ def test_long_horizon_shards_emulated_on_one_gpu(shape, nranks):
         s.close()
 
 
+@pytest.mark.parametrize("N,nranks", [(256, 2), (1024, 8)])
+def test_long_horizon_peer_store_exchange_emulated(N, nranks):
+    # the exchange without a collective: every shard stores its payload into every rank's gathered buffer and raises a
+    # flag; the cross-GPU tier kernel waits on the flags. Ranks are handles on ONE device here, their "peer mappings"
+    # plain device pointers; two epochs exercise the double buffering.
+    import torch
+    n, m = 12, 4
+    kn, x0 = R.synth_problems(n, m, N, 21, 0, 1)
+    want, _ = O.port_solve(n, m, N, kn[0], x0[0], threads=2)
+    shards = [R.ShardSolver(n, m, N, r, nranks, device=0) for r in range(nranks)]
+    pay = shards[0].payload_doubles
+    bufs = [torch.zeros(2 * nranks * pay + nranks, dtype=torch.float64, device="cuda:0") for _ in range(nranks)]
+    base = [b.data_ptr() for b in bufs]
+    flag_off = 2 * nranks * pay * 8
+    for s in shards:
+        s.upload_shard(kn[0], x0[0])
+    for epoch in (1, 2):
+        half = (epoch & 1) * nranks * pay * 8
+        for r, s in enumerate(shards):      # all pushes are queued before any finish: nothing can spin forever here
+            own = base[r] + half + r * pay * 8
+            s.reduce(own)
+            s.push(own, [b + half for b in base], [b + flag_off for b in base], epoch)
+        for r, s in enumerate(shards):
+            s.finish_wait(base[r] + half, base[r] + flag_off, epoch)
+        z = []
+        for s in shards:
+            s.sync()
+            assert not s.flags().any()
+            z.append(s.solution()[0])
+        z = np.concatenate(z)
+        assert max(rel_err_classes(z, want, n, m, N)) < TOL, (N, nranks, epoch)
+    for b in bufs:   # every flag word carries the last epoch
+        assert (b[-nranks:].view(torch.int64) == 2).all()
+    for s in shards:
+        s.close()
+
+
 def test_long_horizon_16384_eight_shards_kkt():
     # BASELINE configs[3] at full size: n=12, m=4, N=16384 as 8 subtrees of 2048 knots (ranks emulated on one device).
     # Size-independent checks: KKT residual and agreement with the single-handle tiered solve.
