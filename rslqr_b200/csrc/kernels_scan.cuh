@@ -285,13 +285,14 @@ struct ScanBufs {
 };
 
 constexpr int SCAN_LEAF = 4;   // knots per warp in the leaf kernel
-constexpr int SCAN_WPC = 5;    // warps per CTA (independent of each other; sized for shared memory)
+constexpr int SCAN_WPC = 6;    // warps per CTA (independent of each other; sized for shared memory: 2 CTAs = 12 warps / SM)
 
-// per warp: [NS | SCAN_LEAF flat knot blocks | entry 0 | entry 1 | W]
+// per warp: [NS | SCAN_LEAF flat knot blocks | entry 0 | entry 1]. The record W = [f_L | f_R | zs] of a merge has no
+// region of its own: it is written where something is dead at that moment (see scan_leaf_kernel).
 template <int NS, int NI>
 __host__ __device__ constexpr int scan_leaf_warp_doubles() {
   using D = Dim<NS, NI>;
-  return NS + SCAN_LEAF * RawDim<NS, NI>::STRIDE + 2 * D::ENT + D::WSZ;
+  return NS + SCAN_LEAF * RawDim<NS, NI>::STRIDE + 2 * D::ENT;
 }
 template <int NS, int NI>
 __host__ __device__ constexpr int scan_leaf_smem_doubles() { return SCAN_WPC * scan_leaf_warp_doubles<NS, NI>(); }
@@ -312,7 +313,10 @@ __global__ void __launch_bounds__(32 * SCAN_WPC, 2) scan_leaf_kernel(Shape s, Bu
   double* R = smf + warp * scan_leaf_warp_doubles<NS, NI>();
   double* E0 = R + NS + SCAN_LEAF * RD::STRIDE;
   double* E1 = E0 + ENT;
-  double* Wf = E1 + ENT;
+  double* B23 = R + NS + 2 * RD::STRIDE;  // knot blocks 2, 3: dead once the merge (k0+2, k0+3) is done
+  static_assert(WSZ + factor_scratch_doubles<NS>() <= 2 * RD::STRIDE && WSZ <= ENT && WSZ % 2 == 0 &&
+                    (NS + 2 * RD::STRIDE) % 2 == 0 && (NS + SCAN_LEAF * RD::STRIDE) % 2 == 0,
+                "W and the level-1 factor scratch fit in blocks 2, 3, 16-byte aligned");
   const int prob = (int)(sub / M0), grp = (int)(sub - (long long)prob * M0);
   const int k0 = grp * SCAN_LEAF;
   const int N = s.N;
@@ -327,9 +331,9 @@ __global__ void __launch_bounds__(32 * SCAN_WPC, 2) scan_leaf_kernel(Shape s, Bu
   mbar_wait(&mbar[warp], 0);
   leaf_transform<NS, NI, SCAN_LEAF>(s, b, prob, k0, pack_rhs, R);
   double* rec = sb.sep_in + ((size_t)prob * M0 + grp) * 3 * WSZ;
-  // record [f_L | f_R | zs] of a separator: TMA bulk store straight out of W; W may be rewritten once the copy
-  // engine has read it (wait_read), which happens before the next merge starts
-  auto store_rec = [&](int slot) {
+  // record [f_L | f_R | zs] of a separator: TMA bulk store straight out of W; the region holding W may be rewritten
+  // once the copy engine has read it (rec_done)
+  auto store_rec = [&](int slot, const double* Wf) {
     fence_async_smem();
     __syncwarp();
     if (lane == 0) {
@@ -342,25 +346,27 @@ __global__ void __launch_bounds__(32 * SCAN_WPC, 2) scan_leaf_kernel(Shape s, Bu
     __syncwarp();
   };
   int bad;
-  // ---- level 0: (k0, k0+1) -> E0, (k0+2, k0+3) -> E1 ----
+  // ---- level 0: first (k0+2, k0+3) -> E1 with its W in the still unused E0, then (k0, k0+1) -> E0 with its W in the
+  //      now dead blocks 2, 3 ----
 #pragma unroll 1
-  for (int h = 0; h < 2; ++h) {
+  for (int h = 1; h >= 0; --h) {
     const int k = k0 + 2 * h;
     const double* Bl = R + NS + (2 * h) * RD::STRIDE;
+    double* Wf = h ? E0 : B23;
     bad = merge_raw<NS, NI>(Bl, Bl + RD::STRIDE, R + (2 * h) * RD::STRIDE, R + (2 * h + 1) * RD::STRIDE, s.kofs + k == 0,
                             s.kofs + k + 1 == s.Ng - 1, h ? E1 : E0, Wf);
-    store_rec(2 * h);
+    store_rec(2 * h, Wf);
     if (bad && lane == 0) {
       b.status[(size_t)prob * 3 * N + rs_slot_S(k >> 1, 0, N)] = -1;
       b.flags[prob] = 1;
     }
     rec_done();
   }
-  // ---- level 1: E0 + E1 -> E0 (separator after knot k0+1); blocks 2, 3 are dead and serve as the factor scratch ----
-  static_assert(factor_scratch_doubles<NS>() <= 2 * RD::STRIDE && (NS + 2 * RD::STRIDE) % 2 == 0, "factor scratch in blocks 2, 3");
+  // ---- level 1: E0 + E1 -> E0 (separator after knot k0+1); W and the factor scratch in the dead blocks 2, 3 ----
+  double* Wf = B23;
   bad = spine_merge<NS, NI, false, true>(R + NS + RD::STRIDE + RD::OA, E0 + NS * NS, E0 + SLOT + NS * NS, E0 + 2 * SLOT + NS, E1,
-                                         E1 + SLOT, E1 + 2 * SLOT, E1 + 2 * SLOT + ZS, R + NS + 2 * RD::STRIDE, Wf);
-  store_rec(1);
+                                         E1 + SLOT, E1 + 2 * SLOT, E1 + 2 * SLOT + ZS, B23 + WSZ, Wf);
+  store_rec(1, Wf);
   if (bad && lane == 0) {
     b.status[(size_t)prob * 3 * N + rs_slot_S(k0 >> 2, 1, N)] = -1;
     b.flags[prob] = 1;
