@@ -112,11 +112,19 @@ __device__ __forceinline__ void dmma884(double& d0, double& d1, double a, double
                : "d"(a), "d"(b));
 }
 
+// st.shared.f64 predicated on `on` (a per-lane predicate the compiler must not turn into a branch)
+__device__ __forceinline__ void sts_pred(unsigned saddr, double v, int on) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %2, 0;\n\t@p st.shared.f64 [%0], %1;\n\t}" ::"r"(saddr), "d"(v), "r"(on) : "memory");
+}
 __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
 
-// factor scratch of spine_core2: Lt row-major (row j = Lt(j, .)), 16-byte aligned for the 128-bit broadcast loads
+// factor scratch of spine_core2: Lt row-major (row j = Lt(j, .)) with leading dimension NS + 2: rows stay 16-byte
+// aligned for the 128-bit broadcast loads, and the 128-bit row stores of 8 neighbouring lanes (28 words apart for
+// NS = 12) fall into distinct banks
 template <int NS>
-__host__ __device__ constexpr int factor_scratch_doubles() { return NS * NS + (NS & 1); }
+__host__ __device__ constexpr int factor_ld() { return NS + 2; }
+template <int NS>
+__host__ __device__ constexpr int factor_scratch_doubles() { return NS * factor_ld<NS>(); }
 
 // ---------------------------------------------------------------------------------------------------------
 // LDL^T sweep with the right-hand sides riding along as extra ROWS, then the backward sweep.
@@ -133,6 +141,7 @@ __host__ __device__ constexpr int factor_scratch_doubles() { return NS * NS + (N
 template <int NS>
 __device__ __forceinline__ int spine_core2(double (&acc)[NS], double (&acc2)[NS], double* Lr, double* Wout) {
   static_assert(NS % 2 == 0 && 2 * NS + 1 <= 32, "pairs; one warp per separator");
+  constexpr int LDF = factor_ld<NS>();
   const int lane = threadIdx.x & 31;
   int bad = 0;
 #pragma unroll
@@ -152,14 +161,14 @@ __device__ __forceinline__ int spine_core2(double (&acc)[NS], double (&acc2)[NS]
   }
   if (lane < NS) {
 #pragma unroll
-    for (int k = 0; k < NS; k += 2) *reinterpret_cast<double2*>(Lr + lane * NS + k) = make_double2(acc[k], acc[k + 1]);
+    for (int k = 0; k < NS; k += 2) *reinterpret_cast<double2*>(Lr + lane * LDF + k) = make_double2(acc[k], acc[k + 1]);
   }
   __syncwarp();
 #pragma unroll
   for (int j = NS - 1; j > 0; --j) {
 #pragma unroll
     for (int p = 0; p < j; p += 2) {
-      const double2 l = *reinterpret_cast<const double2*>(Lr + j * NS + p);
+      const double2 l = *reinterpret_cast<const double2*>(Lr + j * LDF + p);
       acc[p] = fma(-l.x, acc[j], acc[p]);
       acc2[p] = fma(-l.x, acc2[j], acc2[p]);
       if (p + 1 < j) {
@@ -168,14 +177,15 @@ __device__ __forceinline__ int spine_core2(double (&acc)[NS], double (&acc2)[NS]
       }
     }
   }
+  // a lane's solved column is contiguous in W (column-major, ld NS): 128-bit stores (Wout is 16-byte aligned)
   if (lane >= NS && lane <= 2 * NS) {
-    const int c = lane - NS;  // lane 2NS: c = NS -> column 2NS of W is written through the f_L expression below
+    const int c = lane - NS;  // lane 2NS: c = NS -> column 2NS of W (zs)
     double* w1 = lane < 2 * NS ? Wout + c * NS : Wout + 2 * NS * NS;
 #pragma unroll
-    for (int r = 0; r < NS; ++r) w1[r] = acc[r];
+    for (int r = 0; r < NS; r += 2) *reinterpret_cast<double2*>(w1 + r) = make_double2(acc[r], acc[r + 1]);
     if (lane < 2 * NS) {
 #pragma unroll
-      for (int r = 0; r < NS; ++r) Wout[(NS + c) * NS + r] = acc2[r];
+      for (int r = 0; r < NS; r += 2) *reinterpret_cast<double2*>(Wout + (NS + c) * NS + r) = make_double2(acc2[r], acc2[r + 1]);
     }
   }
   __syncwarp();

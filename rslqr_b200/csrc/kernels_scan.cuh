@@ -158,6 +158,10 @@ __device__ __forceinline__ int merge_raw(const double* Bl, const double* Br, con
       dmma884(d[1][1][0], d[1][1][1], a1[ks], b1);
       p0 = fma(a0[ks], zk, p0);
       p1 = fma(a1[ks], zk, p1);
+      if (ks < KA) {  // the scaled operand IS -S_L: S_L(r, l) = -A_i(r, l) / Q_i(l), parked as column NS + l
+        P[(NS + 4 * ks + q) * LDP + rr] = -b0;
+        if (r1) P[(NS + 4 * ks + q) * LDP + 8 + rr] = -b1;
+      }
     }
     p0 += __shfl_xor_sync(0xffffffffu, p0, 1);
     p0 += __shfl_xor_sync(0xffffffffu, p0, 2);
@@ -178,18 +182,12 @@ __device__ __forceinline__ int merge_raw(const double* Bl, const double* Br, con
       if (q == 0 && row < NS) P[2 * NS * LDP + row] = (mt ? p1 : p0) - t;
     }
     __syncwarp();
-    // lanes < NS: column (= row) of S; lanes [NS,2NS): S_L(:,c) = -A_i(:,c)/Q_i(c) and S_R(:,c) = -A_{i+1}(c,:)^T/Q_{i+1}
-    // straight into registers; lane 2NS: s
-    const bool isL = lane >= NS && lane < 2 * NS;
-    const int cl = isL ? lane - NS : 0;
-    const int mc = lane < NS ? lane : 2 * NS;
-    const double dcs = (first0 || !isL) ? 0.0 : -Bl[cl];
+    // lane c <= 2NS takes column c of the parking area [S | S_L | s] (odd leading dimension: conflict-free)
+    const int mc = lane <= 2 * NS ? lane : 2 * NS;
 #pragma unroll
-    for (int r = 0; r < NS; ++r) {
-      const double pv = P[mc * LDP + r], al = ABl[cl * NS + r];
-      acc[r] = isL ? al * dcs : pv;
-    }
+    for (int r = 0; r < NS; ++r) acc[r] = P[mc * LDP + r];
   }
+  // S_R(:,c) = -A_{i+1}(c,:)^T / Q_{i+1} straight into the second register column of lanes [NS,2NS)
   double acc2[NS];
   {
     const bool isL = lane >= NS && lane < 2 * NS;
@@ -203,31 +201,31 @@ __device__ __forceinline__ int merge_raw(const double* Bl, const double* Br, con
   const int bad = spine_core2<NS>(acc, acc2, Lsm, Wf);
   // ---- entry rows X(i+1), U(i+1) straight from the solved columns still in registers: lane NS+c holds f_L(:,c)
   //      (acc) and f_R(:,c) (acc2), lane 2NS holds zs. Row r of the entry is a scaling by 1/Q_{i+1}(r):
-  //      L = f_L/Q, R = (A_{i+1}^T + f_R)/Q, z = z_x + zs/Q; the U rows are the leaf values. Branch-free: every lane
-  //      loads unconditionally and selects; lanes without a column write to private dump slots in the head of E
-  //      (dead scratch now; rows X(i) are written after this and overwrite it). ----
+  //      L = f_L/Q, R = (A_{i+1}^T + f_R)/Q, z = z_x + zs/Q; the U rows are the leaf values. Every lane loads
+  //      unconditionally; the stores are predicated per lane (no branches, no traffic from idle lanes). ----
   {
     const bool isL = lane >= NS && lane < 2 * NS, isz = lane == 2 * NS;
     const int cc = isL ? lane - NS : 0;
-    double* d1 = isL ? E + NS * NS + cc : (isz ? E + 2 * SLOT + NS : E + lane);          // L part / z
-    double* d2 = isL ? E + SLOT + NS * NS + cc : E + 32 + lane;                           // R part
-    const int s1 = isL ? NS : (isz ? 1 : 0), s2 = isL ? NS : 0;
+    const int act1 = isL || isz, act2 = isL;
+    const unsigned d1 = smem_u32(isz ? E + 2 * SLOT + NS : E + NS * NS + cc);  // L part / z
+    const unsigned d2 = smem_u32(E + SLOT + NS * NS + cc);                      // R part
+    const unsigned s1 = (isz ? 1 : NS) * (unsigned)sizeof(double), s2 = NS * (unsigned)sizeof(double);
     const bool addA = isL && !lastR;
 #pragma unroll
     for (int r = 0; r < NS; ++r) {
       const double dr = Br[r];
       const double al = ABr[r * NS + cc];
       const double zx = Br[RD::OZ + r];
-      d1[r * s1] = fma(dr, acc[r], isz ? zx : 0.0);
-      d2[r * s2] = dr * (acc2[r] + (addA ? al : 0.0));
+      sts_pred(d1 + r * s1, fma(dr, acc[r], isz ? zx : 0.0), act1);
+      sts_pred(d2 + r * s2, dr * (acc2[r] + (addA ? al : 0.0)), act2);
     }
 #pragma unroll
     for (int ru = 0; ru < NI; ++ru) {
       const double du = Br[NS + ru];
       const double bl = ABr[(NS + ru) * NS + cc];
       const double zu = Br[RD::OZ + NS + ru];
-      d1[(NS + ru) * s1] = isz ? zu : 0.0;
-      d2[(NS + ru) * s2] = addA ? du * bl : 0.0;
+      sts_pred(d1 + (NS + ru) * s1, isz ? zu : 0.0, act1);
+      sts_pred(d2 + (NS + ru) * s2, addA ? du * bl : 0.0, act2);
     }
     if (lane < NS) E[2 * SLOT + ZS + lane] = zlL[lane];
   }
