@@ -205,7 +205,7 @@ __device__ __forceinline__ int spine_core2(double (&acc)[NS], double (&acc2)[NS]
 //   LXi/RXi : X rows of knot i in its L / R block (row-major, ld NS), the U rows follow directly
 //   zxi   : z_x(i) followed by z_u(i)
 //   LXn/RXn : X rows of knot i+1; zxn = z_x(i+1); zln = z_lambda(i+1)
-//   Lsm   : NS*NS doubles of scratch for Lt (row-major, 16-byte aligned when F2); Wout: [f_L | f_R | zs] column-major ld NS
+//   Lsm   : scratch for Lt (F2: factor_scratch_doubles, 16-byte aligned, directly behind Wout; else NS*NS); Wout: [f_L | f_R | zs] column-major ld NS
 //   F2    : the right-hand sides ride through the factorization (spine_core2) instead of being parked and solved after it
 // Returns non-zero (warp-uniform) when a pivot is <= 0 (reference: clap_CholeskyFactorize fails).
 // ---------------------------------------------------------------------------------------------------------
@@ -230,7 +230,11 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
     // [A_i | B_i] (NS x (NS+NI), padded to 16 rows) times [X_R;U_R | X_L;U_L | z_x;z_u](i) ((NS+NI) x (2NS+1),
     // padded to 32 columns) on the fp64 tensor cores: 2 x 4 tiles, (NS+NI)/4 k-steps; the 8x8 result fragments
     // are dropped into Wout (column-major, ld NS) and picked up again one column per lane.
+    // F2: the transpose buffer has an odd leading dimension (column reads of 16 lanes hit 16 distinct bank pairs)
+    // and runs over the end of Wout into the Lt scratch, which must follow it directly (Lsm == Wout + WSZ).
     constexpr int KS = (NS + NI) / 4;
+    constexpr int TLD = F2 ? NS + 1 : NS;
+    static_assert(!F2 || (2 * NS + 1) * (NS + 1) <= (2 * NS + 1) * NS + factor_scratch_doubles<NS>(), "transpose buffer fits");
     const int q = lane & 3, rr = lane >> 2;
     double d[2][4][2];
 #pragma unroll
@@ -261,12 +265,12 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
           const int row = 8 * mt + rr, col = 8 * nt + 2 * q + h;
-          if (row < NS && col <= 2 * NS) Wout[col * NS + row] = d[mt][nt][h];
+          if (row < NS && col <= 2 * NS) Wout[col * TLD + row] = d[mt][nt][h];
         }
     __syncwarp();
     const int mc = lane <= 2 * NS ? lane : 2 * NS;
 #pragma unroll
-    for (int r = 0; r < NS; ++r) acc[r] = Wout[mc * NS + r];
+    for (int r = 0; r < NS; ++r) acc[r] = Wout[mc * TLD + r];
     __syncwarp();
   } else {
 #pragma unroll
@@ -820,13 +824,13 @@ __global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, TierArgs 
   extern __shared__ __align__(16) double smf[];
   double* sm = smf;
   const int tid = threadIdx.x, nthr = blockDim.x;
-  const int warp = tid >> 5, lane = tid & 31, nwarp = nthr >> 5;
+  const int warp = tid >> 5, lane = tid & 31;
   const int ecount = a.ecount;
   const int ncta = a.Min / ecount;
   const int prob = blockIdx.x / ncta, sg = blockIdx.x % ncta;
   double* ents = sm;
+  constexpr int WSCR = WSZ + factor_scratch_doubles<NS>();  // per warp: [W | Lt scratch], contiguous (spine_merge F2)
   double* Wall = ents + ecount * ENT;
-  double* Lall = Wall + nwarp * WSZ;
   const double* in = a.in + ((size_t)prob * a.Min + (size_t)sg * ecount) * a.in_stride;
   __shared__ __align__(8) unsigned long long mbar;
   if (tid == 0) {
@@ -864,9 +868,9 @@ __global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, TierArgs 
       const double* AB = a.ab + (size_t)prob * a.ab_pstride + (size_t)ge * a.ab_stride;
       double* El = ents + el * ENT;
       double* Er = ents + er * ENT;
-      double* Wf = Wall + warp * WSZ;
+      double* Wf = Wall + warp * WSCR;
       const int bad = spine_merge<NS, NI, true, true>(AB, El + NS * NS, El + SLOT + NS * NS, El + 2 * SLOT + NS, Er, Er + SLOT,
-                                          Er + 2 * SLOT, Er + 2 * SLOT + ZS, Lall + warp * factor_scratch_doubles<NS>(), Wf);
+                                          Er + 2 * SLOT, Er + 2 * SLOT + ZS, Wf + WSZ, Wf);
       double* rec = a.sep + (size_t)prob * a.sep_pstride + (size_t)(ge + 1) * a.sep_mul * WSZ;
       for (int e = lane; e < WSZ; e += 32) rec[e] = Wf[e];
       if (bad && lane == 0) {
