@@ -231,10 +231,10 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
     // padded to 32 columns) on the fp64 tensor cores: 2 x 4 tiles, (NS+NI)/4 k-steps; the 8x8 result fragments
     // are dropped into Wout (column-major, ld NS) and picked up again one column per lane.
     // F2: the transpose buffer has an odd leading dimension (column reads of 16 lanes hit 16 distinct bank pairs)
-    // and runs over the end of Wout into the Lt scratch, which must follow it directly (Lsm == Wout + WSZ).
+    // and runs (2NS+1) doubles over the end of W: Wout must have (2NS+1)(NS+1) doubles (the overflow may be the head
+    // of the Lt scratch, which is written only after the buffer has been read back).
     constexpr int KS = (NS + NI) / 4;
     constexpr int TLD = F2 ? NS + 1 : NS;
-    static_assert(!F2 || (2 * NS + 1) * (NS + 1) <= (2 * NS + 1) * NS + factor_scratch_doubles<NS>(), "transpose buffer fits");
     const int q = lane & 3, rr = lane >> 2;
     double d[2][4][2];
 #pragma unroll
@@ -816,8 +816,11 @@ __global__ void shard_push_kernel(const double* src, PeerPtrs peers, int rank, i
   if (threadIdx.x == 0) st_release_sys(peers.flags[r] + rank, epoch);
 }
 
+template <int NS>
+__host__ __device__ constexpr int tier_warp_scratch() { return ((2 * NS + 1) * (NS + 1) + 1) & ~1; }
+
 template <int NS, int NI>
-__global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, TierArgs a) {
+__global__ void __launch_bounds__(128, 4) tier_kernel(Shape s, Bufs b, TierArgs a) {
   using D = Dim<NS, NI>;
   constexpr int ZS = D::ZS, SLOT = D::SLOT, WSZ = D::WSZ, ENT = D::ENT;
   static_assert(ZS <= 32, "lean Schur update maps one row per lane");
@@ -829,7 +832,10 @@ __global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, TierArgs 
   const int ncta = a.Min / ecount;
   const int prob = blockIdx.x / ncta, sg = blockIdx.x % ncta;
   double* ents = sm;
-  constexpr int WSCR = WSZ + factor_scratch_doubles<NS>();  // per warp: [W | Lt scratch], contiguous (spine_merge F2)
+  // per warp: W plus the overflow of the transpose buffer of spine_merge (F2). The Lt scratch needs no room of its
+  // own: rows X(b), U(b) of the LEFT entry of a merge are dead once the inner products are formed.
+  constexpr int WSCR = tier_warp_scratch<NS>();
+  static_assert(factor_scratch_doubles<NS>() <= (ZS - NS) * NS, "Lt scratch fits in the dead rows of the left entry");
   double* Wall = ents + ecount * ENT;
   const double* in = a.in + ((size_t)prob * a.Min + (size_t)sg * ecount) * a.in_stride;
   __shared__ __align__(8) unsigned long long mbar;
@@ -870,7 +876,7 @@ __global__ void __launch_bounds__(128, 3) tier_kernel(Shape s, Bufs b, TierArgs 
       double* Er = ents + er * ENT;
       double* Wf = Wall + warp * WSCR;
       const int bad = spine_merge<NS, NI, true, true>(AB, El + NS * NS, El + SLOT + NS * NS, El + 2 * SLOT + NS, Er, Er + SLOT,
-                                          Er + 2 * SLOT, Er + 2 * SLOT + ZS, Wf + WSZ, Wf);
+                                          Er + 2 * SLOT, Er + 2 * SLOT + ZS, El + NS * NS, Wf);
       double* rec = a.sep + (size_t)prob * a.sep_pstride + (size_t)(ge + 1) * a.sep_mul * WSZ;
       for (int e = lane; e < WSZ; e += 32) rec[e] = Wf[e];
       if (bad && lane == 0) {
@@ -1074,7 +1080,7 @@ inline cudaError_t tier_attr() {
   static bool attr_done = false;
   if (attr_done) return cudaSuccess;
   cudaError_t e = cudaFuncSetAttribute(tier_kernel<NS, NI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (8 * D::ENT + 4 * (D::WSZ + factor_scratch_doubles<NS>())) * (int)sizeof(double));
+                                       (8 * D::ENT + 4 * tier_warp_scratch<NS>()) * (int)sizeof(double));
   if (e == cudaSuccess) attr_done = true;
   return e;
 }
@@ -1083,7 +1089,7 @@ template <int NS, int NI>
 inline void launch_tier(const Shape& s, const Bufs& b, const TierArgs& a, int batch, cudaStream_t st) {
   using D = Dim<NS, NI>;
   const int warps = a.ecount / 2 > 0 ? a.ecount / 2 : 1;
-  const int smem = (a.ecount * D::ENT + warps * (D::WSZ + factor_scratch_doubles<NS>())) * (int)sizeof(double);
+  const int smem = (a.ecount * D::ENT + warps * tier_warp_scratch<NS>()) * (int)sizeof(double);
   tier_kernel<NS, NI><<<(unsigned)((size_t)batch * (a.Min / a.ecount)), 32 * warps, smem, st>>>(s, b, a);
 }
 
