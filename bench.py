@@ -79,7 +79,7 @@ def scan_leaf_bytes_per_subtree(n, m):
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum of scan_leaf_kernel per problem from the committed ncu --set full capture
-SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM = (497.191936e6 + 788.914944e6) / 1024   # profiles/r01_ncu_scan_v4.md
+SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM = (497.240576e6 + 788.572672e6) / 1024   # profiles/r01_ncu_scan_v9.md
 
 # dram__bytes_read.sum + dram__bytes_write.sum of tier0_kernel per problem, from the committed ncu --set full capture
 # (profiles/r01_ncu_tier0_v1.md: 0.995 GB + 4.060 GB at batch 2048)
@@ -410,8 +410,8 @@ def run_ours(args, rank, world, local_rank):
                 "traffic": SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM * B if SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM and (n, m, N) == (12, 4, 256) else None,
                 "peak_kind": pk_kind, "algorithmic_bytes_per_launch": nsub * by_sub, "bytes_per_subtree": by_sub,
                 "avg_launch_ms": k_avg_ms, "kernel_launches_timed": k_n, "kernel_share_of_step": k_avg_ms / ms_per_step,
-                "binding_unit": "LSU data pipe (shared-memory + shuffle wavefronts) at 69 % of peak and dependent-chain latency at 10 warps/SM; "
-                                "DRAM 22 % busy (ncu --set full, profiles/r01_ncu_scan_v4.md, r01_ncu_scan_leaf_v2.md)",
+                "binding_unit": "LSU data pipe (shared-memory + shuffle wavefronts) at 75 % of peak and dependent-chain latency at 12 warps/SM; "
+                                "DRAM 25 % busy (ncu --set full, profiles/r01_ncu_scan_v9.md)",
                 "fp64_tflops_executed": nsub * fl_sub / (k_avg_ms * 1e-3) / 1e12, "fp64_frac_of_dmma_peak": nsub * fl_sub / (k_avg_ms * 1e-3) / 1e12 / fp64["tflops"],
                 "flops_per_subtree": fl_sub,
                 "reference_count_tflops_whole_step": flop_model(n, m, N) * B / (ms_per_step * 1e-3) / 1e12,
