@@ -68,7 +68,8 @@ enum {
   RSLQR_STAGE_SCHUR = 5,       /* ndlqr_UpdateShurFactor, item = knot, col = upper level         */
   RSLQR_STAGE_RHS_PRODUCTS = 6,
   RSLQR_STAGE_RHS_SOLVES = 7,
-  RSLQR_STAGE_RHS_SCHUR = 8
+  RSLQR_STAGE_RHS_SCHUR = 8,
+  RSLQR_STAGE_LEAF_RHS = 9     /* the rhs half of ndlqr_SolveLeaf alone (stored factorization, new rhs) */
 };
 
 int rslqr_cuda_device_count(void);
@@ -94,6 +95,19 @@ int rslqr_cuda_get_mode(rslqr_cuda_solver* h);         /* the mode solve() will 
 int rslqr_cuda_solve(rslqr_cuda_solver* h, int pack_rhs);
 /* Same, but only enqueues on the handle's stream (for overlap with copies); pair with _sync. */
 int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs);
+
+/* Factor once, solve many (the reference cannot separate the two halves of ndlqr_Solve,
+ * docs/rslqr_usage.dox:53-54). Staged mode only (it is the mode that keeps the reference's `fact` array):
+ *   rslqr_cuda_factor_async    zeroes `fact`, then leaves + the K factor levels (src/solve.c:57-133).
+ *   rslqr_cuda_solve_rhs_async applies the stored factorization to a new right-hand side: pack it from the
+ *                              flat problems (`pack_rhs`, e.g. after re-uploading q, r, d, x0) or take the one
+ *                              uploaded with rslqr_cuda_upload_rhs; then the rhs half of the leaf stage and the
+ *                              K rhs levels (src/solve.c:141-181).
+ * A staged rslqr_cuda_solve also leaves a valid factorization behind. As with getrf / getrs the caller keeps the
+ * two consistent: re-uploaded knot blocks may change q, r, d, x0 but not Q, R, A, B. rslqr_cuda_reset drops the
+ * factorization; solve_rhs then fails with RSLQR_E_UNSUPPORTED. Both calls only enqueue. */
+int rslqr_cuda_factor_async(rslqr_cuda_solver* h);
+int rslqr_cuda_solve_rhs_async(rslqr_cuda_solver* h, int pack_rhs);
 int rslqr_cuda_sync(rslqr_cuda_solver* h);
 /* End to end from HOST buffers (pinned for full PCIe rate): upload `count` problems, solve them (rhs packed from
  * the problem data, as ndlqr_InitializeWithLQRProblem + ndlqr_Solve do, reference src/solver.c:122, src/solve.c:38)

@@ -18,6 +18,14 @@ int ndlqr_CopySolution(NdLqrSolver* solver, double* soln);  /* returns nvars, -1
 /* Convenience named by the task statement (no reference counterpart): initialize + solve. */
 int ndlqr_SolveLQRProblem(const LQRProblem* lqrprob, NdLqrSolver* solver);
 
+/* Factor once, solve many (no reference counterpart: docs/rslqr_usage.dox:53-54 notes that the reference cannot
+ * separate the two halves). After an ndlqr_Solve, write a NEW right-hand side into solver->soln->data (same layout
+ * and sign convention as ndlqr_InitializeWithLQRProblem leaves there, src/solver.c:138-190) and call this: only the
+ * rhs phase (src/solve.c:141-181) runs, on the factorization the device still holds. solver->fact is not
+ * touched. Returns 0, or -1 when there is no factorization (no previous solve, or a solver created with
+ * mirror_fact == 0) or no device. */
+int ndlqr_SolveRhsOnly(NdLqrSolver* solver);
+
 #ifdef __cplusplus
 }
 #endif

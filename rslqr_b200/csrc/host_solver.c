@@ -265,6 +265,28 @@ int ndlqr_Solve(NdLqrSolver* solver) {
   return 0;
 }
 
+int ndlqr_SolveRhsOnly(NdLqrSolver* solver) {
+  if (!solver) return -1;
+  if (!solver->device) {
+    fprintf(stderr, "ERROR: ndlqr_SolveRhsOnly: no CUDA device is attached to this solver (no CPU fallback).\n");
+    return -1;
+  }
+  rslqr_cuda_solver* dev = (rslqr_cuda_solver*)solver->device;
+  const double t0 = wall_ms();
+  int rc = push_rhs(solver);
+  if (!rc) rc = rslqr_cuda_solve_rhs_async(dev, 0);
+  if (!rc) rc = pull_results(solver, 0);
+  if (rc) {
+    fprintf(stderr, "ERROR: ndlqr_SolveRhsOnly failed: %s\n", rslqr_cuda_last_error());
+    return -1;
+  }
+  double ms[7] = {0};
+  rslqr_cuda_get_profile(dev, ms);
+  solver->solve_time_ms = wall_ms() - t0;
+  solver->linalg_time_ms = ms[0];
+  return 0;
+}
+
 int ndlqr_SolveLQRProblem(const LQRProblem* lqrprob, NdLqrSolver* solver) {
   if (!lqrprob || !solver) return -1;
   ndlqr_ResetSolver(solver);

@@ -145,6 +145,35 @@ __global__ void leaf_kernel(Shape s, Bufs b, Sel sel) {
   for (int e = t; e < m * n; e += nt) Fp[2 * nn + e] = 0.0;
 }
 
+// ---------------------------------------------------------------------------------------------
+// The rhs half of ndlqr_SolveLeaf alone (reference src/nested_dissection.c:41-59, 84-90): used when a stored
+// factorization is applied to a new right-hand side (factor once, solve many). Q, R are read from the knot blocks.
+// ---------------------------------------------------------------------------------------------
+__global__ void leaf_rhs_kernel(Shape s, Bufs b, Sel sel) {
+  const long long gid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int per = s.n + s.m;
+  if (gid >= (long long)sel.np * sel.nitems * per) return;
+  const int i = (int)(gid % per);
+  const long long task = gid / per;
+  const int prob = sel.p0 + (int)(task / sel.nitems);
+  const int k = sel.item0 + (int)(task % sel.nitems);
+  const int n = s.n;
+  const double* kn = knot_ptr(s, b, prob, k);
+  double* z = soln_ptr(s, b, prob, k);
+  if (i >= n) {  // z_u <- R \ z_u (no input at the last knot)
+    if (k != s.N - 1) z[2 * n + (i - n)] = z[2 * n + (i - n)] / kn[s.oR + (i - n)];
+    return;
+  }
+  const double Qd = kn[s.oQ + i];
+  if (k == 0) {  // zy <- -Q zy - zx ; zx <- -zy(old)
+    const double zy = z[i], zx = z[n + i];
+    z[i] = -Qd * zy - zx;
+    z[n + i] = -zy;
+  } else {
+    z[n + i] = z[n + i] / Qd;
+  }
+}
+
 // decode (leaf, column-slot) for the product / solve kernels. Slot 0 = own column (products only),
 // 1 = left boundary column, 2 = right boundary column. Returns -1 when the slot is absent.
 __device__ __forceinline__ int active_col(const Shape& s, int leaf, int level, int slot) {

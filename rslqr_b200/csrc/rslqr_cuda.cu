@@ -50,6 +50,7 @@ struct rslqr_cuda_solver {
   bool ktime_on; std::vector<std::pair<cudaEvent_t, cudaEvent_t>> kspans; double k_ms; int k_n;
   FusedPlan fused; int force_dfma;
   ScanPlan scan; int g0_pref;
+  int factored = 0;  // `fact` holds a finished staged factorization of the uploaded problems
   bool shard; bool own_stream;
   int r_first, r_count;            // problem range the next enqueue covers (whole batch by default)
   cudaStream_t s_h2d, s_d2h; bool pipe_made; std::vector<cudaEvent_t> ev_up, ev_done; cudaEvent_t ev_join;
@@ -194,6 +195,7 @@ extern "C" int rslqr_cuda_reset(rslqr_cuda_solver* h) {
   CU(cudaMemsetAsync(h->b.status, 0, sizeof(int) * (size_t)h->batch * 3 * s.N, h->stream));
   CU(cudaMemsetAsync(h->b.flags, 0, sizeof(int) * (size_t)h->batch, h->stream));
   CU(cudaStreamSynchronize(h->stream));
+  h->factored = 0;
   return RSLQR_OK;
 }
 
@@ -278,6 +280,9 @@ static int launch_stage(rslqr_cuda_solver* h, int stage, int level, Sel sel) {
     case RSLQR_STAGE_RHS_SCHUR:
       rhs_schur_kernel<<<(unsigned)((tasks * s.zs + 127) / 128), 128, 0, st>>>(s, h->b, sel, level);
       break;
+    case RSLQR_STAGE_LEAF_RHS:
+      leaf_rhs_kernel<<<(unsigned)((tasks * (n + s.m) + 127) / 128), 128, 0, st>>>(s, h->b, sel);
+      break;
     default:
       return fail(RSLQR_E_ARG, "unknown stage");
   }
@@ -311,15 +316,13 @@ static Sel all_items(const rslqr_cuda_solver* h, int nitems) {
   return sel;
 }
 
-static int solve_staged(rslqr_cuda_solver* h, int pack_rhs) {
+// the two halves of the staged solve: factorization (reference src/solve.c:57-133) and rhs phase (:141-181)
+static int staged_factor_levels(rslqr_cuda_solver* h) {
   const Shape& s = h->s;
-  if (!h->b.fact) return fail(RSLQR_E_UNSUPPORTED, "staged mode needs RSLQR_KEEP_FACT");
   int rc = 0;
   if (s.n * s.n * 2 * sizeof(double) > 48 * 1024) {
     CU(cudaFuncSetAttribute(solves_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(s.n * s.n * 2 * sizeof(double))));
   }
-  if (pack_rhs) rc |= timed_stage(h, 6, RSLQR_STAGE_PACK_RHS, 0, all_items(h, s.N));
-  rc |= timed_stage(h, 1, RSLQR_STAGE_LEAVES, 0, all_items(h, s.N));
   for (int level = 0; level < s.K && !rc; ++level) {
     const int leaves = 1 << (s.K - level - 1);
     rc |= timed_stage(h, 2, RSLQR_STAGE_PRODUCTS, level, all_items(h, leaves));
@@ -329,12 +332,65 @@ static int solve_staged(rslqr_cuda_solver* h, int pack_rhs) {
       rc |= timed_stage(h, 5, RSLQR_STAGE_SCHUR, level, all_items(h, s.N));
     }
   }
+  return rc;
+}
+
+static int staged_rhs_levels(rslqr_cuda_solver* h) {
+  const Shape& s = h->s;
+  int rc = 0;
   for (int level = 0; level < s.K && !rc; ++level) {
     const int leaves = 1 << (s.K - level - 1);
     rc |= timed_stage(h, 6, RSLQR_STAGE_RHS_PRODUCTS, level, all_items(h, leaves));
     rc |= timed_stage(h, 6, RSLQR_STAGE_RHS_SOLVES, level, all_items(h, leaves));
     rc |= timed_stage(h, 6, RSLQR_STAGE_RHS_SCHUR, level, all_items(h, s.N));
   }
+  return rc;
+}
+
+static int solve_staged(rslqr_cuda_solver* h, int pack_rhs) {
+  const Shape& s = h->s;
+  if (!h->b.fact) return fail(RSLQR_E_UNSUPPORTED, "staged mode needs RSLQR_KEEP_FACT");
+  int rc = 0;
+  if (pack_rhs) rc |= timed_stage(h, 6, RSLQR_STAGE_PACK_RHS, 0, all_items(h, s.N));
+  rc |= timed_stage(h, 1, RSLQR_STAGE_LEAVES, 0, all_items(h, s.N));
+  if (!rc) rc = staged_factor_levels(h);
+  if (!rc) rc = staged_rhs_levels(h);
+  if (!rc && h->r_first == 0 && h->r_count == h->batch) h->factored = 1;
+  return rc;
+}
+
+static int staged_entry(rslqr_cuda_solver* h, const char* what) {
+  if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
+  if (h->shard) return fail(RSLQR_E_UNSUPPORTED, "a shard has no stored factorization");
+  if (rslqr_cuda_get_mode(h) != RSLQR_MODE_STAGED || !h->b.fact) return fail(RSLQR_E_UNSUPPORTED, what);
+  CU(cudaSetDevice(h->device));
+  h->launches = 0;
+  h->spans.clear();
+  h->evused = 0;
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_factor_async(rslqr_cuda_solver* h) {
+  int rc = staged_entry(h, "factor: only the staged mode keeps a factorization (rslqr_cuda_set_mode(RSLQR_MODE_STAGED))");
+  if (rc) return rc;
+  const Shape& s = h->s;
+  h->factored = 0;
+  CU(cudaMemsetAsync(h->b.fact + (size_t)h->r_first * s.K * s.N * s.fs, 0, sizeof(double) * (size_t)h->r_count * s.K * s.N * s.fs,
+                     h->stream));
+  rc = timed_stage(h, 1, RSLQR_STAGE_LEAVES, 0, all_items(h, s.N));  // (also scales whatever rhs is in soln: harmless)
+  if (!rc) rc = staged_factor_levels(h);
+  if (!rc && h->r_first == 0 && h->r_count == h->batch) h->factored = 1;
+  return rc;
+}
+
+extern "C" int rslqr_cuda_solve_rhs_async(rslqr_cuda_solver* h, int pack_rhs) {
+  int rc = staged_entry(h, "solve_rhs: only the staged mode keeps a factorization (rslqr_cuda_set_mode(RSLQR_MODE_STAGED))");
+  if (rc) return rc;
+  if (!h->factored) return fail(RSLQR_E_UNSUPPORTED, "solve_rhs: no factorization (call rslqr_cuda_factor_async or a staged solve first)");
+  const Shape& s = h->s;
+  if (pack_rhs) rc |= timed_stage(h, 6, RSLQR_STAGE_PACK_RHS, 0, all_items(h, s.N));
+  rc |= timed_stage(h, 6, RSLQR_STAGE_LEAF_RHS, 0, all_items(h, s.N));
+  if (!rc) rc = staged_rhs_levels(h);
   return rc;
 }
 

@@ -49,6 +49,8 @@ _sig("rslqr_cuda_get_mode", C.c_int, C.c_void_p)
 _sig("rslqr_cuda_solve", C.c_int, C.c_void_p, C.c_int)
 _sig("rslqr_cuda_solve_async", C.c_int, C.c_void_p, C.c_int)
 _sig("rslqr_cuda_sync", C.c_int, C.c_void_p)
+_sig("rslqr_cuda_factor_async", C.c_int, C.c_void_p)
+_sig("rslqr_cuda_solve_rhs_async", C.c_int, C.c_void_p, C.c_int)
 _sig("rslqr_cuda_solve_host", C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int)
 _sig("rslqr_cuda_stage", C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int)
 _sig("rslqr_cuda_schur_task", C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int)
@@ -161,6 +163,15 @@ class CudaSolver:
 
     def sync(self):
         _check(LIB.rslqr_cuda_sync(self.h), "sync")
+
+    # factor once, solve many (staged mode): include/rslqr_cuda.h
+    def factor(self):
+        _check(LIB.rslqr_cuda_factor_async(self.h), "factor")
+        self.sync()
+
+    def solve_rhs(self, pack_rhs=False):
+        _check(LIB.rslqr_cuda_solve_rhs_async(self.h, int(pack_rhs)), "solve_rhs")
+        self.sync()
 
     def solve_host(self, knots, x0, soln, count=None, chunk=0):
         """host buffers in, host solutions out, copies and kernels pipelined; asynchronous (call sync())"""
@@ -364,6 +375,7 @@ def bind_host_api(lib, solver_struct):
     sig("ndlqr_ResetSolver", None, SP)
     sig("ndlqr_Solve", C.c_int, SP)
     sig("ndlqr_SolveLQRProblem", C.c_int, PP, SP)
+    sig("ndlqr_SolveRhsOnly", C.c_int, SP)
     sig("ndlqr_GetSolution", Matrix, SP)
     sig("ndlqr_CopySolution", C.c_int, SP, c_dp)
     sig("ndlqr_GetNumVars", C.c_int, SP)

@@ -275,6 +275,84 @@ def test_linearity_in_rhs():
     s.close()
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [(12, 4, 256), (6, 3, 8), (64, 16, 32)])
+def test_factor_once_solve_many(shape):
+    # the stored staged factorization applied to new right-hand sides must give exactly what a full
+    # solve of the same right-hand side gives (same rhs-phase kernels, same leaf scaling arithmetic)
+    n, m, N = shape
+    kn, x0 = R.synth_problems(n, m, N, 11, 0, 2)
+    rng = np.random.default_rng(5)
+    s = R.CudaSolver(n, m, N, batch=2, flags=R.KEEP_FACT)
+    s.set_mode(R.MODE_STAGED)
+    s.upload(kn, x0)
+    with pytest.raises(R.RslqrError):
+        s.solve_rhs()                      # nothing factored yet
+    # (1) factor, then the packed rhs of the problems themselves == the full solve
+    s.factor()
+    s.solve_rhs(pack_rhs=True)
+    z_split = s.solution().copy()
+    s.reset()
+    s.solve(pack_rhs=True)
+    z_full = s.solution().copy()
+    assert np.array_equal(z_split, z_full)
+    want, _ = O.port_solve(n, m, N, kn[0], x0[0], threads=2)
+    assert max(rel_err_classes(z_full[0], want, n, m, N)) < TOL
+    # (2) the factorization left behind by a full solve serves any number of new right-hand sides
+    fact_before = s.fact(0).copy()
+    for _ in range(3):
+        b = rng.standard_normal((2, N * s.zs))
+        b[:, -m:] = 0
+        s.upload_rhs(b)
+        s.solve_rhs()
+        z_many = s.solution().copy()
+        t = R.CudaSolver(n, m, N, batch=2, flags=R.KEEP_FACT)
+        t.set_mode(R.MODE_STAGED)
+        t.upload(kn, x0)
+        t.upload_rhs(b)
+        t.solve(pack_rhs=False)
+        assert np.array_equal(z_many, t.solution())
+        t.close()
+    assert np.array_equal(fact_before, s.fact(0))   # the rhs phase does not touch `fact`
+    # (3) reset drops the factorization; the scan / tiered kernels keep none
+    s.reset()
+    with pytest.raises(R.RslqrError):
+        s.solve_rhs()
+    if (n, m) == (12, 4):
+        s.set_mode(R.MODE_SCAN)
+        with pytest.raises(R.RslqrError):
+            s.factor()
+    s.close()
+
+
+@pytest.mark.gpu
+def test_host_api_solve_rhs_only():
+    # ndlqr_Solve, then new right-hand sides through ndlqr_SolveRhsOnly (include/solve.h) vs fresh full solves
+    LIB = R.LIB
+    pp = LIB.ndlqr_ReadLQRProblemJSONFile(os.path.join(GOLDEN, "lqr_prob_256.json").encode())
+    s = R.NdLqrSolver(6, 3, 256)
+    t = R.NdLqrSolver(6, 3, 256)
+    assert LIB.ndlqr_SolveRhsOnly(s.p) == -1            # no factorization yet
+    assert s.initialize(pp) == 0
+    rhs0 = s.soln_array().copy()
+    assert s.solve() == 0
+    z0 = s.solution().copy()
+    rng = np.random.default_rng(9)
+    for scale in (1.0, -0.5, 3.0):
+        rhs = rhs0 * scale + 0.01 * rng.standard_normal(rhs0.shape)
+        rhs[-3:] = 0
+        s.soln_array()[:] = rhs
+        assert LIB.ndlqr_SolveRhsOnly(s.p) == 0
+        t.reset()
+        assert t.initialize(pp) == 0
+        t.soln_array()[:] = rhs
+        assert t.solve() == 0
+        assert np.array_equal(s.solution(), t.solution())
+    s.soln_array()[:] = rhs0
+    assert LIB.ndlqr_SolveRhsOnly(s.p) == 0 and np.array_equal(s.solution(), z0)
+    LIB.ndlqr_FreeLQRProblem(pp)
+
+
 def test_cholesky_failure_is_reported():
     # a non-positive Q entry must raise the status word (reference stores cholinfo->success, src/linalg.c:84)
     n, m, N = 6, 3, 8
