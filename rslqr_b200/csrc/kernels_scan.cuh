@@ -54,8 +54,18 @@ struct RawDim {
   static_assert(OD + NS == STRIDE, "z_lambda of block j sits at R + j*STRIDE");
 };
 
+// zl0 (lanes < NS): -z_lambda of block 0 when the rhs is packed here, loaded by the caller BEFORE it waits for the
+// knot blocks so that this second DRAM round trip overlaps the first (leaf_zl0).
+template <int NS, int NI>
+__device__ __forceinline__ double leaf_zl0(const Shape& s, const Bufs& b, int prob, int k0, int pack_rhs) {
+  using RD = RawDim<NS, NI>;
+  const int lane = threadIdx.x & 31;
+  if (!pack_rhs || lane >= NS) return 0.0;
+  return k0 == 0 ? b.x0[(size_t)prob * NS + lane] : __ldg(knot_ptr(s, b, prob, k0) - RD::STRIDE + RD::OD + lane);
+}
+
 template <int NS, int NI, int NK>
-__device__ __forceinline__ void leaf_transform(const Shape& s, const Bufs& b, int prob, int k0, int pack_rhs, double* R) {
+__device__ __forceinline__ void leaf_transform(const Shape& s, const Bufs& b, int prob, int k0, int pack_rhs, double* R, double zl0) {
   using RD = RawDim<NS, NI>;
   constexpr int XU = NS + NI;
   static_assert(XU == 16, "one half-warp per knot");
@@ -67,7 +77,7 @@ __device__ __forceinline__ void leaf_transform(const Shape& s, const Bufs& b, in
     const int j = it / NS, r = it - j * NS;
     double v;
     if (!pack_rhs) v = soln_ptr(s, b, prob, k0 + j)[r];
-    else if (j == 0) v = -(k0 == 0 ? b.x0[(size_t)prob * NS + r] : __ldg(knot_ptr(s, b, prob, k0) - RD::STRIDE + RD::OD + r));
+    else if (j == 0) v = -zl0;  // (it < NS here: r == lane)
     else v = -R[j * RD::STRIDE + r];
     R[j * RD::STRIDE + r] = v;
   }
@@ -326,8 +336,9 @@ __global__ void __launch_bounds__(32 * SCAN_WPC, 2) scan_leaf_kernel(Shape s, Bu
     bulk_g2s(R + NS, knot_ptr(s, b, prob, k0), RAWB, &mbar[warp]);
   }
   __syncwarp();
+  const double zl0 = leaf_zl0<NS, NI>(s, b, prob, k0, pack_rhs);
   mbar_wait(&mbar[warp], 0);
-  leaf_transform<NS, NI, SCAN_LEAF>(s, b, prob, k0, pack_rhs, R);
+  leaf_transform<NS, NI, SCAN_LEAF>(s, b, prob, k0, pack_rhs, R, zl0);
   double* rec = sb.sep_in + ((size_t)prob * M0 + grp) * 3 * WSZ;
   // record [f_L | f_R | zs] of a separator: TMA bulk store straight out of W; the region holding W may be rewritten
   // once the copy engine has read it (rec_done)
