@@ -209,10 +209,14 @@ __device__ __forceinline__ int spine_core2(double (&acc)[NS], double (&acc2)[NS]
 //   F2    : the right-hand sides ride through the factorization (spine_core2) instead of being parked and solved after it
 // Returns non-zero (warp-uniform) when a pivot is <= 0 (reference: clap_CholeskyFactorize fails).
 // ---------------------------------------------------------------------------------------------------------
-template <int NS, int NI, bool LDG = true, bool F2 = false>
+//   before_write : hook called after the tensor-core products and before the first store into Wout / Lsm (a caller
+//           whose copy engine may still be reading those regions waits there instead of before the merge)
+struct NoHook { __device__ __forceinline__ void operator()() const {} };
+template <int NS, int NI, bool LDG = true, bool F2 = false, class Hook = NoHook>
 __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const double* LXi, const double* RXi,
                                            const double* zxi, const double* LXn, const double* RXn,
-                                           const double* zxn, const double* zln, double* Lsm, double* Wout) {
+                                           const double* zxn, const double* zln, double* Lsm, double* Wout,
+                                           Hook before_write = Hook()) {
   static_assert(2 * NS + 1 <= 32, "one warp per separator needs 2n+1 <= 32");
   const int lane = threadIdx.x & 31;
   const int c = lane < NS ? lane : (lane < 2 * NS ? lane - NS : 0);
@@ -258,6 +262,7 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
         dmma884(d[1][nt][0], d[1][nt][1], a1, bf[nt]);
       }
     }
+    before_write();
 #pragma unroll
     for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
@@ -273,6 +278,7 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
     for (int r = 0; r < NS; ++r) acc[r] = Wout[mc * TLD + r];
     __syncwarp();
   } else {
+    before_write();
 #pragma unroll
     for (int r = 0; r < NS; ++r) acc[r] = 0.0;
 #pragma unroll 4

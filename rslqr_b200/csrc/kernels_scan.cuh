@@ -125,9 +125,11 @@ __device__ __forceinline__ void leaf_transform(const Shape& s, const Bufs& b, in
 // The last knot of the horizon has R(k) = 0. zlL / zlR: z_lambda of the two knots.
 // E: output entry (Dim::ENT layout; its head doubles as the factor scratch), Wf: [f_L | f_R | zs] on return.
 // ---------------------------------------------------------------------------------------------------------
-template <int NS, int NI>
+// before_write(): called once, after the operand loads and tensor-core products and before the first store into E --
+// the caller's hook for "the copy engine must have finished reading what used to be there".
+template <int NS, int NI, class Hook>
 __device__ __forceinline__ int merge_raw(const double* Bl, const double* Br, const double* zlL, const double* zlR, bool first0,
-                                         bool lastR, double* E, double* Wf) {
+                                         bool lastR, double* E, double* Wf, Hook&& before_write) {
   using D = Dim<NS, NI>;
   using RD = RawDim<NS, NI>;
   constexpr int ZS = D::ZS, SLOT = D::SLOT;
@@ -156,6 +158,7 @@ __device__ __forceinline__ int merge_raw(const double* Bl, const double* Br, con
 #pragma unroll
       for (int nt = 0; nt < 2; ++nt) d[mt][nt][0] = d[mt][nt][1] = 0.0;
     double p0 = 0.0, p1 = 0.0;
+    double sl0[KA], sl1[KA];
 #pragma unroll
     for (int ks = 0; ks < KS; ++ks) {
       double dk = Bl[4 * ks + q];
@@ -168,15 +171,18 @@ __device__ __forceinline__ int merge_raw(const double* Bl, const double* Br, con
       dmma884(d[1][1][0], d[1][1][1], a1[ks], b1);
       p0 = fma(a0[ks], zk, p0);
       p1 = fma(a1[ks], zk, p1);
-      if (ks < KA) {  // the scaled operand IS -S_L: S_L(r, l) = -A_i(r, l) / Q_i(l), parked as column NS + l
-        P[(NS + 4 * ks + q) * LDP + rr] = -b0;
-        if (r1) P[(NS + 4 * ks + q) * LDP + 8 + rr] = -b1;
-      }
+      if (ks < KA) { sl0[ks] = -b0; sl1[ks] = -b1; }
     }
     p0 += __shfl_xor_sync(0xffffffffu, p0, 1);
     p0 += __shfl_xor_sync(0xffffffffu, p0, 2);
     p1 += __shfl_xor_sync(0xffffffffu, p1, 1);
     p1 += __shfl_xor_sync(0xffffffffu, p1, 2);
+    before_write();
+#pragma unroll
+    for (int ks = 0; ks < KA; ++ks) {  // the scaled operand IS -S_L: S_L(r, l) = -A_i(r, l) / Q_i(l), parked as column NS + l
+      P[(NS + 4 * ks + q) * LDP + rr] = sl0[ks];
+      if (r1) P[(NS + 4 * ks + q) * LDP + 8 + rr] = sl1[ks];
+    }
 #pragma unroll
     for (int mt = 0; mt < 2; ++mt) {
       const int row = 8 * mt + rr, rs = row < NS ? row : 0;
@@ -362,19 +368,20 @@ __global__ void __launch_bounds__(32 * SCAN_WPC, 2) scan_leaf_kernel(Shape s, Bu
     const int k = k0 + 2 * h;
     const double* Bl = R + NS + (2 * h) * RD::STRIDE;
     double* Wf = h ? E0 : B23;
+    // (h == 0 writes into E0, which the copy engine may still be reading as the record of merge h == 1: the wait
+    //  sits behind this merge's operand loads and products instead of right after the store)
     bad = merge_raw<NS, NI>(Bl, Bl + RD::STRIDE, R + (2 * h) * RD::STRIDE, R + (2 * h + 1) * RD::STRIDE, s.kofs + k == 0,
-                            s.kofs + k + 1 == s.Ng - 1, h ? E1 : E0, Wf);
+                            s.kofs + k + 1 == s.Ng - 1, h ? E1 : E0, Wf, rec_done);
     store_rec(2 * h, Wf);
     if (bad && lane == 0) {
       b.status[(size_t)prob * 3 * N + rs_slot_S(k >> 1, 0, N)] = -1;
       b.flags[prob] = 1;
     }
-    rec_done();
   }
   // ---- level 1: E0 + E1 -> E0 (separator after knot k0+1); W and the factor scratch in the dead blocks 2, 3 ----
   double* Wf = B23;
   bad = spine_merge<NS, NI, false, true>(R + NS + RD::STRIDE + RD::OA, E0 + NS * NS, E0 + SLOT + NS * NS, E0 + 2 * SLOT + NS, E1,
-                                         E1 + SLOT, E1 + 2 * SLOT, E1 + 2 * SLOT + ZS, B23 + WSZ, Wf);
+                                         E1 + SLOT, E1 + 2 * SLOT, E1 + 2 * SLOT + ZS, B23 + WSZ, Wf, rec_done);
   store_rec(1, Wf);
   if (bad && lane == 0) {
     b.status[(size_t)prob * 3 * N + rs_slot_S(k0 >> 2, 1, N)] = -1;
