@@ -35,6 +35,19 @@ int rslqr_synth_fill(int nstates, int ninputs, int nhorizon, uint64_t seed, int 
                      double* knots, double* x0);
 LQRProblem* rslqr_synth_problem(int nstates, int ninputs, int nhorizon, uint64_t seed, int id);
 
+/* Flat binary container for batches of problems (the reference only has JSON, src/json_utils.h:24-61,
+ * which is impractical for 4096 x 256 knots). A 64-byte header (magic "RSLQRB01", n, m, N, count, byte-order tag),
+ * then per problem x0[n] followed by N flat knot blocks in the LQRData order Q,R,q,r,c,A,B,d
+ * (src/lqr_data.c:25-36) -- the layout rslqr_cuda_upload / ndlqr_BatchInitializeFlat take, so a range of problems
+ * is read straight into the upload buffers. All return 0 / -1 (+stderr); the reader returns NULL on failure. */
+int rslqr_WriteProblemsBinary(const char* path, int nstates, int ninputs, int nhorizon, int count, const double* knots,
+                              const double* x0);
+int rslqr_ReadProblemsBinaryHeader(const char* path, int* nstates, int* ninputs, int* nhorizon, int* count);
+/* problems [first, first+count) -> knots[count][N][block], x0[count][n] */
+int rslqr_ReadProblemsBinary(const char* path, int first, int count, double* knots, double* x0);
+int rslqr_WriteLQRProblemsBinary(const char* path, const LQRProblem* const* probs, int count);
+LQRProblem* rslqr_ReadLQRProblemBinary(const char* path, int index);  /* free with ndlqr_FreeLQRProblem */
+
 #ifdef __cplusplus
 }
 #endif

@@ -407,6 +407,12 @@ def bind_host_api(lib, solver_struct):
         C.POINTER(C.POINTER(CholeskyInfo)))
     sig("rslqr_synth_problem", PP, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_int)
     sig("ndlqr_LQRDataBlockSize", C.c_int, C.c_int, C.c_int)
+    ip = C.POINTER(C.c_int)
+    sig("rslqr_WriteProblemsBinary", C.c_int, C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p)
+    sig("rslqr_ReadProblemsBinaryHeader", C.c_int, C.c_char_p, ip, ip, ip, ip)
+    sig("rslqr_ReadProblemsBinary", C.c_int, C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p)
+    sig("rslqr_WriteLQRProblemsBinary", C.c_int, C.c_char_p, C.POINTER(PP), C.c_int)
+    sig("rslqr_ReadLQRProblemBinary", PP, C.c_char_p, C.c_int)
     return lib
 
 
@@ -422,6 +428,32 @@ def problem_to_flat(prob_ptr, n, m):
         knots[k] = np.ctypeslib.as_array(pr.lqrdata[k].contents.Q, shape=(st,))
     x0 = np.ctypeslib.as_array(pr.x0, shape=(n,)).copy()
     return knots, x0
+
+
+def write_problems_binary(path, n, m, N, knots, x0):
+    """Write flat problems (knots[count,N,stride], x0[count,n]) to the binary container of include/rslqr_batch.h."""
+    knots = np.ascontiguousarray(knots, dtype=np.float64)
+    x0 = np.ascontiguousarray(x0, dtype=np.float64)
+    count = x0.size // n
+    if LIB.rslqr_WriteProblemsBinary(os.fsencode(path), n, m, N, count, _ptr(knots), _ptr(x0)) != 0:
+        raise RslqrError(f"could not write {path}")
+
+
+def read_problems_binary(path, first=0, count=None, knots=None, x0=None):
+    """Read problems [first, first+count) of a binary container. Returns (n, m, N, knots[count,N,stride], x0[count,n]);
+    `knots` / `x0` may be preallocated (e.g. pinned) arrays."""
+    n, m, N, total = (C.c_int() for _ in range(4))
+    if LIB.rslqr_ReadProblemsBinaryHeader(os.fsencode(path), C.byref(n), C.byref(m), C.byref(N), C.byref(total)) != 0:
+        raise RslqrError(f"could not read {path}")
+    n, m, N, total = n.value, m.value, N.value, total.value
+    count = total - first if count is None else count
+    if knots is None:
+        knots = np.empty((count, N, knot_stride(n, m)))
+    if x0 is None:
+        x0 = np.empty((count, n))
+    if LIB.rslqr_ReadProblemsBinary(os.fsencode(path), first, count, _ptr(knots), _ptr(x0)) != 0:
+        raise RslqrError(f"could not read problems [{first}, {first + count}) from {path}")
+    return n, m, N, knots, x0
 
 
 def load_problem_json(path):

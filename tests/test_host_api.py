@@ -100,6 +100,53 @@ def test_json_loader_errors(tmp_path):
     assert not LIB.ndlqr_ReadLQRDataJSONFile(str(short).encode())   # Q too short
 
 
+def test_binary_problem_container(tmp_path):
+    # flat binary container; round trips, range reads, LQRProblem <-> file, error paths
+    n, m, N = 12, 4, 16
+    kn, x0 = R.synth_problems(n, m, N, 5, 0, 6)
+    path = str(tmp_path / "batch.rslqr")
+    L.write_problems_binary(path, n, m, N, kn, x0)
+    assert os.path.getsize(path) == 64 + 8 * 6 * (n + N * R.knot_stride(n, m))
+    rn, rm, rN, rk, rx = L.read_problems_binary(path)
+    assert (rn, rm, rN) == (n, m, N) and np.array_equal(rk, kn) and np.array_equal(rx, x0)
+    _, _, _, rk, rx = L.read_problems_binary(path, first=2, count=3)
+    assert np.array_equal(rk, kn[2:5]) and np.array_equal(rx, x0[2:5])
+    with pytest.raises(R.RslqrError):
+        L.read_problems_binary(path, first=4, count=3)            # past the end
+    # one record as an LQRProblem of the reference's struct layout, and back through the LQRProblem writer
+    pp = LIB.rslqr_ReadLQRProblemBinary(path.encode(), 3)
+    k3, x3 = L.problem_to_flat(pp, n, m)
+    assert pp.contents.nhorizon == N and np.array_equal(k3, kn[3]) and np.array_equal(x3, x0[3])
+    arr = (C.POINTER(L.LQRProblem) * 2)(pp, pp)
+    path2 = str(tmp_path / "two.rslqr")
+    assert LIB.rslqr_WriteLQRProblemsBinary(path2.encode(), arr, 2) == 0
+    _, _, _, rk, rx = L.read_problems_binary(path2)
+    assert np.array_equal(rk[0], kn[3]) and np.array_equal(rk[1], kn[3]) and np.array_equal(rx[1], x0[3])
+    LIB.ndlqr_FreeLQRProblem(pp)
+    # the JSON problem of the reference survives JSON -> binary -> LQRProblem
+    jp = LIB.ndlqr_ReadLQRProblemJSONFile(os.path.join(GOLDEN, "lqr_prob.json").encode())
+    arr1 = (C.POINTER(L.LQRProblem) * 1)(jp)
+    path3 = str(tmp_path / "json.rslqr")
+    assert LIB.rslqr_WriteLQRProblemsBinary(path3.encode(), arr1, 1) == 0
+    bp = LIB.rslqr_ReadLQRProblemBinary(path3.encode(), 0)
+    ka, xa = L.problem_to_flat(jp, 6, 3)
+    kb, xb = L.problem_to_flat(bp, 6, 3)
+    assert np.array_equal(ka, kb) and np.array_equal(xa, xb)
+    LIB.ndlqr_FreeLQRProblem(jp)
+    LIB.ndlqr_FreeLQRProblem(bp)
+    # error paths: missing file, wrong magic, truncated payload, bad arguments
+    assert not LIB.rslqr_ReadLQRProblemBinary(b"/nonexistent/file.rslqr", 0)
+    bad = tmp_path / "bad.rslqr"
+    bad.write_bytes(b"NOTRSLQR" + bytes(56))
+    assert LIB.rslqr_ReadProblemsBinaryHeader(str(bad).encode(), None, None, None, None) == -1
+    trunc = tmp_path / "trunc.rslqr"
+    trunc.write_bytes(open(path, "rb").read()[:-100])
+    with pytest.raises(R.RslqrError):
+        L.read_problems_binary(str(trunc))
+    assert not LIB.rslqr_ReadLQRProblemBinary(path.encode(), 6)     # index == count
+    assert LIB.rslqr_WriteProblemsBinary(None, n, m, N, 1, None, None) == -1
+
+
 def test_nddata_layout():
     # test/nddata_test.c:15-28,61-126
     assert not LIB.ndlqr_NewNdData(6, 3, 7, 6)
