@@ -13,6 +13,7 @@
 
 #include "kernels_fused.cuh"
 #include "kernels_scan.cuh"
+#include "kernels_riccati.cuh"
 #include "kernels_staged.cuh"
 #include "kernels_staged_mma.cuh"
 
@@ -51,6 +52,7 @@ struct rslqr_cuda_solver {
   FusedPlan fused; int force_dfma;
   ScanPlan scan; int g0_pref;
   int factored = 0;  // `fact` holds a finished staged factorization of the uploaded problems
+  double* ric_gain = nullptr;  // [batch][N][K | dv | P | p] of the Riccati comparison solver (allocated on first use)
   bool shard; bool own_stream;
   int r_first, r_count;            // problem range the next enqueue covers (whole batch by default)
   cudaStream_t s_h2d, s_d2h; bool pipe_made; std::vector<cudaEvent_t> ev_up, ev_done; cudaEvent_t ev_join;
@@ -145,7 +147,7 @@ extern "C" int rslqr_cuda_destroy(rslqr_cuda_solver* h) {
   cudaSetDevice(h->device);
   cudaStreamSynchronize(h->stream);
   cudaFree(h->d_knots); cudaFree(h->d_x0); cudaFree(h->b.soln); cudaFree(h->b.fact);
-  cudaFree(h->b.status); cudaFree(h->b.flags); cudaFree(h->b.leafd);
+  cudaFree(h->b.status); cudaFree(h->b.flags); cudaFree(h->b.leafd); cudaFree(h->ric_gain);
   fused_free(&h->fused);
   scan_free(&h->scan);
   for (auto ev : h->evpool) cudaEventDestroy(ev);
@@ -392,6 +394,25 @@ extern "C" int rslqr_cuda_solve_rhs_async(rslqr_cuda_solver* h, int pack_rhs) {
   rc |= timed_stage(h, 6, RSLQR_STAGE_LEAF_RHS, 0, all_items(h, s.N));
   if (!rc) rc = staged_rhs_levels(h);
   return rc;
+}
+
+// The Riccati recursion of the reference's own baseline solver (src/riccati_solve.c:27-150) on the device: one warp
+// per problem, result in the same [lambda, x, u] layout as the nested-dissection solve. Comparison solver only.
+extern "C" int rslqr_cuda_riccati_solve_async(rslqr_cuda_solver* h) {
+  if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
+  if (h->shard) return fail(RSLQR_E_UNSUPPORTED, "riccati: not for shards");
+  const Shape& s = h->s;
+  if (!(s.n == 12 && s.m == 4 && s.N >= 2)) return fail(RSLQR_E_UNSUPPORTED, "riccati: the device kernel covers n=12, m=4");
+  CU(cudaSetDevice(h->device));
+  if (!h->ric_gain)
+    CU(cudaMalloc(&h->ric_gain, sizeof(double) * (size_t)h->batch * s.N * RicDim<12, 4>::GSZ));
+  h->launches = 0;
+  const size_t f = (size_t)h->r_first;
+  Bufs b = h->b;
+  b.knots += f * s.N * s.stride; b.x0 += f * s.n; b.soln += f * s.N * s.zs; b.flags += f;
+  if (launch_riccati<12, 4>(s, b, h->ric_gain + f * s.N * RicDim<12, 4>::GSZ, h->r_count, h->stream, g_err)) return RSLQR_E_CUDA;
+  h->launches = 1;
+  return RSLQR_OK;
 }
 
 extern "C" int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs) {

@@ -50,6 +50,7 @@ _sig("rslqr_cuda_solve", C.c_int, C.c_void_p, C.c_int)
 _sig("rslqr_cuda_solve_async", C.c_int, C.c_void_p, C.c_int)
 _sig("rslqr_cuda_sync", C.c_int, C.c_void_p)
 _sig("rslqr_cuda_factor_async", C.c_int, C.c_void_p)
+_sig("rslqr_cuda_riccati_solve_async", C.c_int, C.c_void_p)
 _sig("rslqr_cuda_solve_rhs_async", C.c_int, C.c_void_p, C.c_int)
 _sig("rslqr_cuda_solve_host", C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int)
 _sig("rslqr_cuda_stage", C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int)
@@ -167,6 +168,11 @@ class CudaSolver:
     # factor once, solve many (staged mode): include/rslqr_cuda.h
     def factor(self):
         _check(LIB.rslqr_cuda_factor_async(self.h), "factor")
+        self.sync()
+
+    def riccati(self):
+        """Comparison solver: Riccati recursion on the device (n=12, m=4), same output layout as solve()."""
+        _check(LIB.rslqr_cuda_riccati_solve_async(self.h), "riccati")
         self.sync()
 
     def solve_rhs(self, pack_rhs=False):

@@ -353,6 +353,26 @@ def test_host_api_solve_rhs_only():
     LIB.ndlqr_FreeLQRProblem(pp)
 
 
+@pytest.mark.parametrize("N", [2, 4, 16, 256, 1024])
+def test_riccati_comparison_solver_matches_nested_dissection(N):
+    # the reference's own baseline recursion (src/riccati_solve.c) on the device solves the same KKT
+    # system; its [lambda, x, u] vector must agree with the oracle's nested-dissection solve
+    n, m = 12, 4
+    kn, x0 = R.synth_problems(n, m, N, 21, 0, 5)
+    s = R.CudaSolver(n, m, N, batch=5, flags=R.KEEP_FACT)
+    s.upload(kn, x0)
+    s.riccati()
+    z = s.solution().copy()
+    assert not s.flags().any()
+    for p in range(5):
+        want, _ = O.port_solve(n, m, N, kn[p], x0[p], threads=2)
+        assert max(rel_err_classes(z[p], want, n, m, N)) < 1e-9, (N, p)
+        assert O.kkt_residual(n, m, N, kn[p], x0[p], z[p]) < 1e-9 * max(1.0, np.linalg.norm(z[p]))
+    s.solve()
+    assert max(rel_err_classes(z[0], s.solution()[0], n, m, N)) < 1e-9
+    s.close()
+
+
 def test_cholesky_failure_is_reported():
     # a non-positive Q entry must raise the status word (reference stores cholinfo->success, src/linalg.c:84)
     n, m, N = 6, 3, 8
