@@ -38,7 +38,7 @@ struct RicDim {
 };
 
 template <int NS, int NI>
-__global__ void __launch_bounds__(32 * RIC_WPC) riccati_kernel(Shape s, Bufs b, double* gain, int nprob) {
+__global__ void __launch_bounds__(32 * RIC_WPC, 4) riccati_kernel(Shape s, Bufs b, double* gain, int nprob) {
   using RD = RawDim<NS, NI>;
   using D = RicDim<NS, NI>;
   constexpr int XU = D::XU, LDM = D::LDM, LDH = D::LDH, GSZ = D::GSZ, PAIR = D::PAIR;
@@ -261,60 +261,62 @@ __global__ void __launch_bounds__(32 * RIC_WPC) riccati_kernel(Shape s, Bufs b, 
     }
   }
   if (bad && lane == 0) b.flags[prob] = 1;
-  // ------------------------------------------------------------------ forward pass
-  // lane r < NS owns state row r (x_r, lambda_r), lanes NS .. NS+NI-1 own the input rows. The operands of the NEXT
-  // knot are fetched into registers while the current one is computed.
-  {
-    const bool isx = lane < NS, isu = lane >= NS && lane < XU;
-    const int r = isx ? lane : (isu ? lane - NS : 0);
-    double xr = isx ? b.x0[(size_t)prob * NS + r] : 0.0;
-    double* out = soln_ptr(s, b, prob, 0);
-    const int ZS = 2 * NS + NI;
-    struct Ops { double A[NS], B[NI], P[NS], tail, dk; };  // lane < NS: A(r,:), B(r,:), P(r,:), p_r, d_r; u lanes: K(l,:) in P, dv_l in tail
-    auto load_step = [&](int k, Ops& o) {
-      const double* g = G + (size_t)k * GSZ;
-      const double* kb = kn0 + (size_t)k * RD::STRIDE;
-      const double* prow = isu ? g + r * NS : g + NI * NS + NI + r * NS;
+}
+
+// ------------------------------------------------------------------ forward pass (its own kernel: no shared memory and
+// a small register footprint, so most problems of a batch of 4096 are resident at once and the per-knot DRAM latency
+// of the serial rollout is hidden by the other warps).
+// Lane roles: lanes [0,NS) lambda rows (P(r,:), p_r), lanes [NS,NS+NI) input rows (K(l,:), dv_l), lanes [16,16+NS)
+// next-state rows (A(r,:), B(r,:), d_r) -- x_k lives in lanes 16.. . The operands of the NEXT knot are fetched into
+// registers while the current one is computed.
+template <int NS, int NI>
+__global__ void __launch_bounds__(32 * RIC_WPC, 5) riccati_forward_kernel(Shape s, Bufs b, const double* gain, int nprob) {
+  using RD = RawDim<NS, NI>;
+  constexpr int XU = NS + NI, GSZ = RicDim<NS, NI>::GSZ, ZS = 2 * NS + NI;
+  static_assert(XU == 16 && NS <= 16, "lane roles");
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int prob = blockIdx.x * RIC_WPC + warp;
+  if (prob >= nprob) return;
+  const int N = s.N;
+  const double* kn0 = knot_ptr(s, b, prob, 0);
+  const double* G = gain + (size_t)prob * N * GSZ;
+  double* out = soln_ptr(s, b, prob, 0);
+  const bool isl = lane < NS, isu = lane >= NS && lane < XU, isx = lane >= XU && lane < XU + NS;
+  const int r = isl ? lane : (isu ? lane - NS : (isx ? lane - XU : 0));
+  // a lane's row: 12 doubles `row` (P / K / A), 4 doubles `rb` (B, x lanes only), one scalar `tail` (p_r / dv_l / d_r)
+  struct Ops { double row[NS], rb[NI], tail; };
+  auto load_step = [&](int k, Ops& o) {
+    const double* g = G + (size_t)k * GSZ;
+    const double* kb = kn0 + (size_t)k * RD::STRIDE;
+    // row-major P and K rows are contiguous; A(r,:) is strided by NS in the column-major block
+    const double* base = isl ? g + NI * NS + NI + r * NS : (isu ? g + r * NS : kb + RD::OA + r);
+    const int st = isx ? NS : 1;
 #pragma unroll
-      for (int c = 0; c < NS; ++c) o.P[c] = (isx || isu) ? prow[c] : 0.0;
-      o.tail = isu ? g[NI * NS + r] : (isx ? g[NI * NS + NI + NS * NS + r] : 0.0);
+    for (int c = 0; c < NS; ++c) o.row[c] = base[c * st];
 #pragma unroll
-      for (int c = 0; c < NS; ++c) o.A[c] = isx ? kb[RD::OA + c * NS + r] : 0.0;
+    for (int c = 0; c < NI; ++c) o.rb[c] = isx ? kb[RD::OA + (NS + c) * NS + r] : 0.0;
+    o.tail = isl ? g[NI * NS + NI + NS * NS + r] : (isu ? g[NI * NS + r] : kb[RD::OD + r]);
+  };
+  double xr = isx ? b.x0[(size_t)prob * NS + r] : 0.0;
+  Ops cur, nxt;
+  load_step(0, cur);
+  for (int k = 0; k < N; ++k) {
+    if (k + 1 < N) load_step(k + 1, nxt);  // in flight while this knot is computed
+    double acc0 = cur.tail, acc1 = 0.0;    // P_r . x + p_r  |  K_l . x + dv_l  |  A_r . x + d_r
 #pragma unroll
-      for (int c = 0; c < NI; ++c) o.B[c] = isx ? kb[RD::OA + (NS + c) * NS + r] : 0.0;
-      o.dk = isx ? kb[RD::OD + r] : 0.0;
-    };
-    Ops cur, nxt;
-    load_step(0, cur);
-    for (int k = 0; k < N; ++k) {
-      if (k + 1 < N) load_step(k + 1, nxt);  // in flight while this knot is computed
-      double xs[NS];
-#pragma unroll
-      for (int c = 0; c < NS; ++c) xs[c] = shfl_d(xr, c);
-      double acc0 = cur.tail, acc1 = 0.0;  // P_r . x + p_r   |   K_l . x + dv_l
-#pragma unroll
-      for (int c = 0; c < NS; c += 2) {
-        acc0 = fma(cur.P[c], xs[c], acc0);
-        acc1 = fma(cur.P[c + 1], xs[c + 1], acc1);
-      }
-      const double val = acc0 + acc1;      // lambda_r (x lanes) or -(u_l) (u lanes)
-      double us[NI];
-#pragma unroll
-      for (int c = 0; c < NI; ++c) us[c] = -shfl_d(val, NS + c);
-      double nx0 = cur.dk, nx1 = 0.0;
-#pragma unroll
-      for (int c = 0; c < NS; c += 2) {
-        nx0 = fma(cur.A[c], xs[c], nx0);
-        nx1 = fma(cur.A[c + 1], xs[c + 1], nx1);
-      }
-#pragma unroll
-      for (int c = 0; c < NI; ++c) nx0 = fma(cur.B[c], us[c], nx0);
-      double* o = out + (size_t)k * ZS;
-      if (isx) { o[r] = val; o[NS + r] = xr; }
-      else if (isu) o[2 * NS + r] = (k == N - 1) ? 0.0 : -val;
-      xr = nx0 + nx1;
-      cur = nxt;
+    for (int c = 0; c < NS; c += 2) {
+      acc0 = fma(cur.row[c], shfl_d(xr, XU + c), acc0);
+      acc1 = fma(cur.row[c + 1], shfl_d(xr, XU + c + 1), acc1);
     }
+    double val = acc0 + acc1;              // lambda_r | -(u_l) | partial x_{k+1}
+#pragma unroll
+    for (int c = 0; c < NI; ++c) val = fma(cur.rb[c], -shfl_d(val, NS + c), val);  // (rb = 0 outside the x lanes)
+    double* o = out + (size_t)k * ZS;
+    if (isl) o[r] = val;
+    else if (isu) o[2 * NS + r] = (k == N - 1) ? 0.0 : -val;
+    else if (isx) o[NS + r] = xr;
+    xr = val;
+    cur = nxt;
   }
 }
 
@@ -329,6 +331,7 @@ inline int launch_riccati(const Shape& s, const Bufs& b, double* gain, int nprob
     attr_done = true;
   }
   riccati_kernel<NS, NI><<<(unsigned)((nprob + RIC_WPC - 1) / RIC_WPC), 32 * RIC_WPC, smem, st>>>(s, b, gain, nprob);
+  riccati_forward_kernel<NS, NI><<<(unsigned)((nprob + RIC_WPC - 1) / RIC_WPC), 32 * RIC_WPC, 0, st>>>(s, b, gain, nprob);
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) { err = std::string("riccati: ") + cudaGetErrorString(e); return 1; }
   return 0;
