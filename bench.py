@@ -456,11 +456,37 @@ def run_ours(args, rank, world, local_rank):
             line["cpu_baseline"]["riccati"] = cpu_riccati_baseline(n, m, N, h_knots[:1].copy(), h_x0[:1].copy())
         except Exception as e:  # the baseline must never take the bench line down
             line["cpu_baseline"]["riccati"] = {"unavailable": repr(e)}
+    if rank == 0 and world == 1 and (n, m) == (12, 4):
+        try:
+            line["riccati_gpu"] = gpu_riccati_comparison(R, s, B)
+        except Exception as e:  # a comparison figure must never take the bench line down
+            line["riccati_gpu"] = {"unavailable": repr(e)}
     if rank == 0:
         print(json.dumps(line), flush=True)
     s.close()
     if dist is not None:
         dist.destroy_process_group()
+
+
+def gpu_riccati_comparison(R, s, B, reps=5):
+    """the reference's own baseline algorithm (Riccati recursion, src/riccati_solve.c) on the same GPU and
+    the same resident batch, one warp per problem -- NOT the path this repo accelerates; reported so that the
+    nested-dissection number can be read against the best serial-in-time competitor. Outside every timed region above."""
+    s.solve_async(True)
+    s.sync()
+    z_nd = s.solution(0, min(B, 64)).copy()
+    for _ in range(2):
+        s.riccati()
+    s.mark(4)
+    for _ in range(reps):
+        R.LIB.rslqr_cuda_riccati_solve_async(s.h)
+    s.mark(5)
+    s.sync()
+    ms = s.elapsed_ms(4, 5) / reps
+    z_r = s.solution(0, min(B, 64))
+    return {"value": B / (ms * 1e-3), "unit": "solves/s", "ms_per_step": ms, "kernels": "riccati_kernel + riccati_forward_kernel",
+            "rel_diff_vs_nested_dissection": float(np.linalg.norm(z_r - z_nd) / np.linalg.norm(z_nd)),
+            "note": "comparison only: Riccati recursion (serial in the horizon, parallel over the batch), same inputs resident in HBM"}
 
 
 def run_long(args, rank, world, local_rank):
