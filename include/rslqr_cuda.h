@@ -109,7 +109,7 @@ int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs);
 int rslqr_cuda_factor_async(rslqr_cuda_solver* h);
 /* Comparison solver: the Riccati recursion of the reference's own baseline, ndlqr_BackwardPass /
  * ndlqr_ForwardPass (src/riccati_solve.c:27-150), one warp per problem; writes the same [lambda_k, x_k, u_k] vector
- * the nested-dissection solve produces (rhs taken from the uploaded problems). n=12, m=4 only; needs batch*N*1664
+ * the nested-dissection solve produces (rhs taken from the uploaded problems). n=12, m=4 only; needs batch*N*1136
  * bytes of extra device memory, allocated on the first call. Enqueues only. */
 int rslqr_cuda_riccati_solve_async(rslqr_cuda_solver* h);
 int rslqr_cuda_solve_rhs_async(rslqr_cuda_solver* h, int pack_rhs);

@@ -13,7 +13,7 @@
 //   K = Quu^-1 Qux, dv = Quu^-1 Qu         (4 x 4 LDL^T, every lane redundantly; lane c solves column c)
 //   P_k = Qxx - Qux^T K,  p_k = Qx - Qux^T dv                                                       6 DMMA
 // (the reference's Joseph-form update src/riccati_solve.c:104-117 equals this in exact arithmetic; P is symmetrised
-// when it is read back as an operand). Per knot [K | dv | P_k | p_k] (208 doubles) goes to HBM for the forward pass.
+// when it is read back as an operand). Per knot [K | dv | P_k (lower triangle) | p_k] (142 doubles) goes to HBM for the forward pass.
 // Forward pass (src/riccati_solve.c:121-150): lambda_k = P_k x_k + p_k, u_k = -K_k x_k - dv_k, x_{k+1} = A x + B u + d.
 // The knot blocks stream through shared memory in PAIRS (one flat block is 1896 bytes, a pair is 16-byte aligned)
 // by double-buffered TMA bulk copies.
@@ -29,10 +29,11 @@ struct RicDim {
   static constexpr int XU = NS + NI, NC = XU + 1;
   static constexpr int LDM = NS + 1;                       // M column-major, odd leading dimension
   static constexpr int LDH = NC;                           // H row-major [XU][NC]
-  static constexpr int GSZ = NI * NS + NI + NS * NS + NS;  // [K (NI x NS row-major) | dv | P (row-major) | p]
+  static constexpr int PK = NS * (NS + 1) / 2;             // P is symmetric: its lower triangle, row by row
+  static constexpr int GSZ = NI * NS + NI + PK + NS;       // [K (NI x NS row-major) | dv | P (packed) | p]
   static constexpr int PAIR = 2 * RawDim<NS, NI>::STRIDE;
-  // per warp: [knot pair x2 | K dv P p (GSZ, contiguous: copied to HBM as one run) | M | H]
-  static constexpr int OG = 2 * PAIR, OM = OG + GSZ, OH = OM + ((NC * LDM + 1) & ~1);
+  // per warp: [knot pair x2 | K dv Ppacked p (GSZ, contiguous: copied to HBM as one run) | P (full, operand) | M | H]
+  static constexpr int OG = 2 * PAIR, OP = OG + GSZ, OM = OP + NS * NS, OH = OM + ((NC * LDM + 1) & ~1);
   static constexpr int WARP = OH + XU * LDH;
   static_assert(PAIR % 2 == 0 && GSZ % 2 == 0 && WARP % 2 == 0, "16-byte alignment of the regions");
 };
@@ -41,7 +42,7 @@ template <int NS, int NI>
 __global__ void __launch_bounds__(32 * RIC_WPC, 4) riccati_kernel(Shape s, Bufs b, double* gain, int nprob) {
   using RD = RawDim<NS, NI>;
   using D = RicDim<NS, NI>;
-  constexpr int XU = D::XU, LDM = D::LDM, LDH = D::LDH, GSZ = D::GSZ, PAIR = D::PAIR;
+  constexpr int XU = D::XU, LDM = D::LDM, LDH = D::LDH, GSZ = D::GSZ, PAIR = D::PAIR, PK = D::PK;
   constexpr int KA = NS / 4;
   static_assert(NS == 12 && NI == 4, "tile shapes below are written for n = 12, m = 4");
   extern __shared__ __align__(16) double smf[];
@@ -52,10 +53,11 @@ __global__ void __launch_bounds__(32 * RIC_WPC, 4) riccati_kernel(Shape s, Bufs 
   const int N = s.N, NP = N / 2;
   double* W = smf + warp * D::WARP;
   double* KB = W;                 // two pair buffers
-  double* Kk = W + D::OG;         // K (NI x NS), then dv, P, p contiguous
+  double* Kk = W + D::OG;         // K (NI x NS), then dv, packed P, p contiguous
   double* dv = Kk + NI * NS;
-  double* Ps = dv + NI;
-  double* pv = Ps + NS * NS;
+  double* Pk = dv + NI;
+  double* pv = Pk + PK;
+  double* Ps = W + D::OP;         // full P: the operand of the next step
   double* Ms = W + D::OM;
   double* Hs = W + D::OH;
   const double* kn0 = knot_ptr(s, b, prob, 0);
@@ -72,7 +74,7 @@ __global__ void __launch_bounds__(32 * RIC_WPC, 4) riccati_kernel(Shape s, Bufs 
       bulk_g2s(KB + buf * PAIR, kn0 + (size_t)j * PAIR, PAIR * (int)sizeof(double), &mbar[warp][buf]);
     }
   };
-  auto store_gain = [&](int k) {  // [K | dv | P | p] of knot k -> HBM (one contiguous run)
+  auto store_gain = [&](int k) {  // [K | dv | P (packed) | p] of knot k -> HBM (one contiguous run); call after a __syncwarp
     double2* dst = reinterpret_cast<double2*>(G + (size_t)k * GSZ);
     const double2* src = reinterpret_cast<const double2*>(Kk);
     for (int e = lane; e < GSZ / 2; e += 32) dst[e] = src[e];
@@ -95,6 +97,9 @@ __global__ void __launch_bounds__(32 * RIC_WPC, 4) riccati_kernel(Shape s, Bufs 
       const double* kb = KB + buf * PAIR + h2 * RD::STRIDE;
       if (k == N - 1) {  // terminal knot: P = diag(Q), p = q, no input (src/riccati_solve.c:31-38)
         for (int e = lane; e < NS * NS; e += 32) Ps[e] = (e / NS == e % NS) ? kb[e / NS] : 0.0;
+        for (int e = lane; e < PK; e += 32) Pk[e] = 0.0;
+        __syncwarp();
+        if (lane < NS) Pk[lane * (lane + 1) / 2 + lane] = kb[lane];
         for (int e = lane; e < NI * NS + NI; e += 32) Kk[e] = 0.0;
         if (lane < NS) pv[lane] = kb[XU + lane];
         __syncwarp();
@@ -250,6 +255,7 @@ __global__ void __launch_bounds__(32 * RIC_WPC, 4) riccati_kernel(Shape s, Bufs 
               for (int h = 0; h < 2; ++h) {
                 const int col = 8 * nt + 2 * q + h;
                 if (col < NS) Ps[i * NS + col] = hc[mt][nt][h];
+                if (col <= i) Pk[i * (i + 1) / 2 + col] = hc[mt][nt][h];  // the lower triangle is what the forward pass reads
               }
             if (q == 0) pv[i] = hc[mt][2][0];
           }
@@ -289,13 +295,14 @@ __global__ void __launch_bounds__(32 * RIC_WPC, 5) riccati_forward_kernel(Shape 
     const double* g = G + (size_t)k * GSZ;
     const double* kb = kn0 + (size_t)k * RD::STRIDE;
     // row-major P and K rows are contiguous; A(r,:) is strided by NS in the column-major block
-    const double* base = isl ? g + NI * NS + NI + r * NS : (isu ? g + r * NS : kb + RD::OA + r);
+    // (P is packed: element (r, c) of the symmetric matrix sits at max(r,c)(max(r,c)+1)/2 + min(r,c))
+    const double* base = isl ? g + NI * NS + NI : (isu ? g + r * NS : kb + RD::OA + r);
     const int st = isx ? NS : 1;
 #pragma unroll
-    for (int c = 0; c < NS; ++c) o.row[c] = base[c * st];
+    for (int c = 0; c < NS; ++c) o.row[c] = base[isl ? (c <= r ? r * (r + 1) / 2 + c : c * (c + 1) / 2 + r) : c * st];
 #pragma unroll
     for (int c = 0; c < NI; ++c) o.rb[c] = isx ? kb[RD::OA + (NS + c) * NS + r] : 0.0;
-    o.tail = isl ? g[NI * NS + NI + NS * NS + r] : (isu ? g[NI * NS + r] : kb[RD::OD + r]);
+    o.tail = isl ? g[NI * NS + NI + RicDim<NS, NI>::PK + r] : (isu ? g[NI * NS + r] : kb[RD::OD + r]);
   };
   double xr = isx ? b.x0[(size_t)prob * NS + r] : 0.0;
   Ops cur, nxt;
