@@ -10,7 +10,7 @@
 //                      flat knot blocks (the leaf factors of ndlqr_SolveLeaf, src/nested_dissection.c:10-105,
 //                      are diagonal scalings, so S = A Q^-1 A^T + B R^-1 B^T + Q^-1 and the Schur update of a
 //                      leaf pair is one 12x12x24 product), the level-1 merge is the general one. No CTA barrier.
-//   tier_kernel      : (kernels_fused.cuh) the remaining levels, 8 entries per CTA.
+//   tier_kernel      : (kernels_fused.cuh) the remaining levels, 4 (batches) or 8 (one long horizon) entries per CTA.
 //   topdown_kernel   : (kernels_fused.cuh) multipliers of the separators above the 4-knot subtrees.
 //   scan_down_kernel : one warp = 4 knots: multipliers of its three interior separators from the stored records
 //                      [f_L | f_R | zs], then x_k, u_k from the leaf equations (the reference's rhs propagation
