@@ -125,6 +125,26 @@ class stdout_to_stderr:
         os.close(self.saved)
 
 
+def bind_to_gpu_cpus(dev):
+    """Pin this rank to the CPU cores local to its GPU (NVML affinity) BEFORE the pinned host buffers are allocated,
+    so that with several ranks on one box every rank's host copies stay on its GPU's NUMA node. Returns a short note
+    for the JSON line; never fails the run."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(dev)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * i + bit for i, w in enumerate(mask) for bit in range(64) if (w >> bit) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return "gpu-local cpus not in this process's cpuset"
+        os.sched_setaffinity(0, cpus)
+        return "%d gpu-local cpus" % len(cpus)
+    except Exception as e:  # NVML absent, CUDA_VISIBLE_DEVICES remapping, ...
+        return "unbound (%s)" % type(e).__name__
+
+
 def init_nccl(local_rank):
     import torch
     import torch.distributed as dist
@@ -306,6 +326,7 @@ def run_ours(args, rank, world, local_rank):
     from rslqr_b200.lib import pinned_array
     n, m, N, B = N_STATES, N_INPUTS, HORIZON, args.batch
     dist = None
+    cpu_binding = bind_to_gpu_cpus(local_rank) if world > 1 and not os.environ.get("RSLQR_BENCH_NO_BIND") else "not bound (one rank)"
     if world > 1:
         dist = init_nccl(local_rank)
 
@@ -442,7 +463,8 @@ def run_ours(args, rank, world, local_rank):
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": WORKLOAD, "batch_per_gpu": B, "global_batch": B * world, "seed": SEED,
                        "mode": {R.MODE_STAGED: "staged", R.MODE_FUSED: "fused (tiered)", R.MODE_SCAN: "scan"}[s.mode], "parallelism": f"batch-shard x{world}, no collective",
-                       "l2": "inputs (%.2f GB/GPU) larger than L2; no explicit flush" % (B * N * st * 8 / 1e9)},
+                       "l2": "inputs (%.2f GB/GPU) larger than L2; no explicit flush" % (B * N * st * 8 / 1e9),
+                       "host_cpu_binding": cpu_binding},
             "clocks": clocks,
             "e2e": {"value": world * B * args.steps / e2e_s, "unit": "solves/s",
                     "h2d_bytes_per_step": int(h_knots.nbytes + h_x0.nbytes), "d2h_bytes_per_step": int(h_soln.nbytes)},
