@@ -341,6 +341,64 @@ __global__ void rhs_solves_kernel(Shape s, Bufs b, Sel sel, int level) {
   for (int e = threadIdx.x; e < n; e += blockDim.x) z[e] = sz[e];
 }
 
+// rhs variant for n <= 64 without CTA barriers: ONE WARP per separator. L is staged into the warp's shared memory with
+// an odd leading dimension (column reads of the forward sweep and row reads of the backward sweep are both
+// conflict-free), the right-hand side lives in registers (rows lane and lane + 32), the pivot element travels by
+// shuffle. Same operation order per row as clap_LowerTriBackSub / clap_CholeskySolve (src/linalg_custom.c:113-150):
+// subtract the products in increasing (forward) / decreasing (backward) column order, then scale by the pivot
+// (multiplication by its reciprocal instead of the reference's division: at most one ulp apart per step).
+// dynamic smem: warps * n * (n + 1) doubles.
+__global__ void rhs_solves_warp_kernel(Shape s, Bufs b, Sel sel, int level) {
+  extern __shared__ double sm[];
+  const int wpc = blockDim.x >> 5, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long task = (long long)blockIdx.x * wpc + warp;
+  if (task >= (long long)sel.np * sel.nitems) return;
+  const int prob = sel.p0 + (int)(task / sel.nitems);
+  const int leaf = sel.item0 + (int)(task % sel.nitems);
+  const int n = s.n, ld = n + 1;
+  const int i1 = rs_sep_index(leaf, level) + 1;
+  const double* L = fact_ptr(s, b, prob, i1, level);
+  double* z = soln_ptr(s, b, prob, i1);
+  double* sL = sm + (size_t)warp * n * ld;
+  const int r0 = lane, r1 = lane + 32;
+  // column by column (coalesced global reads, no integer division), 8 columns of loads in flight
+  for (int c0 = 0; c0 < n; c0 += 8) {
+    double v0[8], v1[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int c = c0 + u;
+      v0[u] = (c < n && r0 < n) ? __ldg(L + r0 + n * c) : 0.0;
+      v1[u] = (c < n && r1 < n) ? __ldg(L + r1 + n * c) : 0.0;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int c = c0 + u;
+      if (c < n && r0 < n) sL[r0 + ld * c] = v0[u];
+      if (c < n && r1 < n) sL[r1 + ld * c] = v1[u];
+    }
+  }
+  double y0 = r0 < n ? z[r0] : 0.0, y1 = r1 < n ? z[r1] : 0.0;
+  __syncwarp();
+  // reciprocal pivots once per row (the division would otherwise sit on the dependent chain of every step)
+  const double inv0 = r0 < n ? 1.0 / sL[r0 + ld * r0] : 0.0, inv1 = r1 < n ? 1.0 / sL[r1 + ld * r1] : 0.0;
+  for (int j = 0; j < n; ++j) {  // L y = z
+    const double yj = __shfl_sync(0xffffffffu, j < 32 ? y0 : y1, j & 31) * __shfl_sync(0xffffffffu, j < 32 ? inv0 : inv1, j & 31);
+    if (r0 == j) y0 = yj;
+    if (r1 == j) y1 = yj;
+    if (r0 > j && r0 < n) y0 -= sL[r0 + ld * j] * yj;
+    if (r1 > j && r1 < n) y1 -= sL[r1 + ld * j] * yj;
+  }
+  for (int j = n - 1; j >= 0; --j) {  // L^T x = y
+    const double xj = __shfl_sync(0xffffffffu, j < 32 ? y0 : y1, j & 31) * __shfl_sync(0xffffffffu, j < 32 ? inv0 : inv1, j & 31);
+    if (r0 == j) y0 = xj;
+    if (r1 == j) y1 = xj;
+    if (r0 < j) y0 -= sL[j + ld * r0] * xj;
+    if (r1 < j) y1 -= sL[j + ld * r1] * xj;
+  }
+  if (r0 < n) z[r0] = y0;
+  if (r1 < n) z[r1] = y1;
+}
+
 // ---------------------------------------------------------------------------------------------
 // Schur update: ndlqr_UpdateShurFactor (reference src/nested_dissection.c:154-171):
 //   F(k,p) -= F(k,level) * f,  f = F(index+1,p).Lambda, Lambda rows only if calc_lambda.

@@ -277,6 +277,16 @@ static int launch_stage(rslqr_cuda_solver* h, int stage, int level, Sel sel) {
       rhs_products_kernel<<<(unsigned)((tasks * n + 127) / 128), 128, 0, st>>>(s, h->b, sel, level);
       break;
     case RSLQR_STAGE_RHS_SOLVES:
+      if (n <= 64 && !getenv("RSLQR_NO_WARP_RHS_SOLVE")) {  // one warp per separator, no CTA barrier
+        const int wpc = n > 32 ? 2 : 4;
+        const size_t smem = sizeof(double) * (size_t)wpc * n * (n + 1);
+        static size_t attr_smem = 0;
+        if (smem > 48 * 1024 && smem > attr_smem) {
+          CU(cudaFuncSetAttribute(rhs_solves_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+          attr_smem = smem;
+        }
+        rhs_solves_warp_kernel<<<(unsigned)((tasks + wpc - 1) / wpc), 32 * wpc, smem, st>>>(s, h->b, sel, level);
+      } else
       rhs_solves_kernel<<<(unsigned)tasks, clampi(round32(n), 32, 256), sizeof(double) * (nn + n), st>>>(s, h->b, sel, level);
       break;
     case RSLQR_STAGE_RHS_SCHUR:
