@@ -109,6 +109,7 @@ __global__ void __launch_bounds__(32 * RIC_WPC, 4) riccati_kernel(Shape s, Bufs 
       }
       const double* AB = kb + RD::OA;
       // ---- M = P [A | B | d]  (+ p on the last column) ----
+      double ab[KA][2];  // fragments of [A | B]: B operand here, A operand of the next product (same elements)
       {
         double c[2][3][2];
 #pragma unroll
@@ -125,8 +126,8 @@ __global__ void __launch_bounds__(32 * RIC_WPC, 4) riccati_kernel(Shape s, Bufs 
             const double v = 0.5 * (Ps[rs * NS + kk] + Ps[kk * NS + rs]);
             a[mt] = row < NS ? v : 0.0;
           }
-          bb[0] = AB[rr * NS + kk];
-          bb[1] = AB[(8 + rr) * NS + kk];
+          bb[0] = ab[ks][0] = AB[rr * NS + kk];
+          bb[1] = ab[ks][1] = AB[(8 + rr) * NS + kk];
           bb[2] = rr == 0 ? kb[RD::OD + kk] : 0.0;
 #pragma unroll
           for (int mt = 0; mt < 2; ++mt)
@@ -157,8 +158,8 @@ __global__ void __launch_bounds__(32 * RIC_WPC, 4) riccati_kernel(Shape s, Bufs 
         for (int ks = 0; ks < KA; ++ks) {
           const int kk = 4 * ks + q;
           double a[2], bb[3];
-          a[0] = AB[rr * NS + kk];
-          a[1] = AB[(8 + rr) * NS + kk];
+          a[0] = ab[ks][0];
+          a[1] = ab[ks][1];
           bb[0] = Ms[rr * LDM + kk];
           bb[1] = Ms[(8 + rr) * LDM + kk];
           bb[2] = rr == 0 ? Ms[XU * LDM + kk] : 0.0;
@@ -178,11 +179,11 @@ __global__ void __launch_bounds__(32 * RIC_WPC, 4) riccati_kernel(Shape s, Bufs 
             for (int h = 0; h < 2; ++h) {
               const int col = 8 * nt + 2 * q + h;
               if (col == i) hc[mt][nt][h] += dg;
-              Hs[i * LDH + col] = hc[mt][nt][h];
+              if (i >= NS) Hs[i * LDH + col] = hc[mt][nt][h];  // only the input rows [Qux | Quu] are read back
             }
           if (q == 0) {
             hc[mt][2][0] += gr;
-            Hs[i * LDH + XU] = hc[mt][2][0];
+            if (i >= NS) Hs[i * LDH + XU] = hc[mt][2][0];
           }
         }
       }
