@@ -959,17 +959,105 @@ __global__ void topdown_kernel(const double* sep_all, double* lam_all, int M0, c
   }
 }
 
-// host: one pass for short ranges, two for long ones (the serial chain of one CTA is log2(M0) global round trips)
+// Latency variant of topdown_kernel for few CTAs (one long horizon): the records of the CTA's range (at most 63) come
+// into shared memory by TMA bulk copies up front and the multipliers of the range live in shared memory too, so the
+// log2(span/step) dependent levels cost shared-memory round trips instead of L2 / HBM ones. Same arithmetic, same
+// order. dynamic smem: ((span/step - 1) * WSZ + (span/step + 1) * NS) doubles.
+template <int NS>
+__global__ void __launch_bounds__(128) topdown_smem_kernel(const double* sep_all, double* lam_all, int M0, const double* left,
+                                                            const double* right, int span, int step) {
+  constexpr int WSZ = (2 * NS + 1) * NS;
+  extern __shared__ __align__(16) double tsm[];
+  __shared__ __align__(8) unsigned long long mbar;
+  const int nblk = M0 / span, nloc = span / step;
+  const int prob = blockIdx.x / nblk, base = (blockIdx.x % nblk) * span;
+  double* lam = lam_all + (size_t)prob * (M0 + 1) * NS;
+  const double* sep = sep_all + (size_t)prob * M0 * WSZ;
+  double* recs = tsm;                               // record of local separator i (1 .. nloc-1) at recs + (i-1)*WSZ
+  double* lams = tsm + (size_t)(nloc - 1) * WSZ;    // multipliers of local slots 0 .. nloc
+  if (threadIdx.x == 0) {
+    mbar_init(&mbar, 1);
+    fence_mbar_init();
+    mbar_expect_tx(&mbar, (nloc - 1) * WSZ * (int)sizeof(double));
+    if (step == 1) bulk_g2s(recs, sep + (size_t)(base + 1) * WSZ, (nloc - 1) * WSZ * (int)sizeof(double), &mbar);
+    else
+      for (int i = 1; i < nloc; ++i)
+        bulk_g2s(recs + (size_t)(i - 1) * WSZ, sep + (size_t)(base + i * step) * WSZ, WSZ * (int)sizeof(double), &mbar);
+  }
+  if (threadIdx.x < NS) {
+    const int r = threadIdx.x;
+    double la, lb;
+    if (span == M0) {
+      la = left ? left[(size_t)prob * NS + r] : 0.0;
+      lb = right ? right[(size_t)prob * NS + r] : 0.0;
+      lam[r] = la;
+      lam[M0 * NS + r] = lb;
+    } else {
+      la = lam[base * NS + r];
+      lb = lam[(base + span) * NS + r];
+    }
+    lams[r] = la;
+    lams[nloc * NS + r] = lb;
+  }
+  __syncthreads();
+  mbar_wait(&mbar, 0);
+  int T = 0;
+  while ((1 << T) < nloc) ++T;
+  for (int t = T - 1; t >= 0; --t) {
+    const int cnt = nloc >> (t + 1), h = 1 << t;
+    for (int idx = threadIdx.x; idx < cnt * NS; idx += blockDim.x) {
+      const int u = idx / NS, r = idx - u * NS;
+      const int i = (2 * u + 1) << t;
+      const double* rec = recs + (size_t)(i - 1) * WSZ;
+      const double* la = lams + (i - h) * NS;
+      const double* lb = lams + (i + h) * NS;
+      double v = rec[2 * NS * NS + r];
+#pragma unroll
+      for (int c = 0; c < NS; ++c) v = fma(-rec[c * NS + r], la[c], fma(-rec[(NS + c) * NS + r], lb[c], v));
+      lams[i * NS + r] = v;
+    }
+    __syncthreads();
+  }
+  for (int idx = threadIdx.x; idx < (nloc - 1) * NS; idx += blockDim.x) {
+    const int i = 1 + idx / NS, r = idx % NS;
+    lam[(size_t)(base + i * step) * NS + r] = lams[i * NS + r];
+  }
+}
+
+// host: one pass for short ranges, two for long ones (the serial chain of one CTA is log2(M0) dependent levels). With
+// few CTAs (a single long horizon) the levels run out of shared memory (topdown_smem_kernel); a full batch keeps the
+// streaming kernel, which has many CTAs per SM in flight.
 template <int NS>
 inline int launch_topdown(const double* sep, double* lam, int M0, int batch, const double* left, const double* right,
                           cudaStream_t st) {
-  constexpr int H = 64;
-  if (M0 <= 2 * H) {
-    topdown_kernel<NS><<<batch, 128, 0, st>>>(sep, lam, M0, left, right, M0, 1);
+  constexpr int H = 64, WSZ = (2 * NS + 1) * NS;
+  static const int force = [] { const char* v = getenv("RSLQR_TOPDOWN_SMEM"); return v ? atoi(v) : -1; }();
+  auto pass = [&](int span, int step) {
+    const int nloc = span / step, ctas = batch * (M0 / span);
+    const bool smem_ok = nloc >= 2 && nloc <= H;
+    const bool use_smem = smem_ok && (force >= 0 ? force != 0 : ctas <= 1024);
+    if (use_smem) {
+      const int bytes = ((nloc - 1) * WSZ + (nloc + 1) * NS) * (int)sizeof(double);
+      static int attr_bytes = 0;
+      if (bytes > 48 * 1024 && bytes > attr_bytes) {
+        cudaFuncSetAttribute(topdown_smem_kernel<NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+        attr_bytes = bytes;
+      }
+      topdown_smem_kernel<NS><<<ctas, 128, bytes, st>>>(sep, lam, M0, left, right, span, step);
+    } else {
+      topdown_kernel<NS><<<ctas, 128, 0, st>>>(sep, lam, M0, left, right, span, step);
+    }
+  };
+  if (M0 <= H) {
+    pass(M0, 1);
     return 1;
   }
-  topdown_kernel<NS><<<batch, 128, 0, st>>>(sep, lam, M0, left, right, M0, H);
-  topdown_kernel<NS><<<batch * (M0 / H), 128, 0, st>>>(sep, lam, M0, left, right, H, 1);
+  if (M0 <= 2 * H && batch * 1 > 1024) {  // (throughput regime: one streaming pass, as before)
+    pass(M0, 1);
+    return 1;
+  }
+  pass(M0, H);
+  pass(H, 1);
   return 2;
 }
 
