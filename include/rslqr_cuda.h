@@ -188,6 +188,11 @@ int rslqr_cuda_set_stream(rslqr_cuda_solver* h, void* stream);
 /* pinned host memory helpers so that callers can stage uploads at full PCIe rate */
 void* rslqr_cuda_host_alloc(size_t bytes);
 void rslqr_cuda_host_free(void* p);
+/* page-lock (and later release) memory the caller already owns, e.g. the malloc'ed mirrors behind solver->fact /
+ * solver->soln of the host API, so that their copies run at the pinned rate and truly asynchronously. 0, or
+ * RSLQR_E_CUDA when the range cannot be locked (the copies then simply stay pageable). */
+int rslqr_cuda_host_register(void* p, size_t bytes);
+int rslqr_cuda_host_unregister(void* p);
 
 #ifdef __cplusplus
 }

@@ -56,6 +56,7 @@ typedef struct {
   double* flat_knots; /* staging copy of the problem in flat knot-block form */
   double* flat_x0;
   int mirror_fact;    /* 1 (default): copy `fact` back after Solve; 0: solution only */
+  int pinned_fact, pinned_soln, pinned_knots; /* the mirrors are page-locked (rslqr_cuda_host_register) */
 } NdLqrSolver;
 
 NdLqrSolver* ndlqr_NewNdLqrSolver(int nstates, int ninputs, int nhorizon);

@@ -119,6 +119,13 @@ NdLqrSolver* ndlqr_NewNdLqrSolver(int nstates, int ninputs, int nhorizon) {
     dev = NULL;
   }
   s->device = dev;
+  if (dev) {
+    /* page-lock the mirrors the solve copies to and from (best effort: a refused range just stays pageable) */
+    const size_t fs = (size_t)(2 * n + m) * n;
+    s->pinned_fact = rslqr_cuda_host_register(s->fact->data, sizeof(double) * fs * (size_t)N * (size_t)s->depth) == RSLQR_OK;
+    s->pinned_soln = rslqr_cuda_host_register(s->soln->data, sizeof(double) * (size_t)(2 * n + m) * (size_t)N) == RSLQR_OK;
+    s->pinned_knots = rslqr_cuda_host_register(s->flat_knots, sizeof(double) * (size_t)N * ndlqr_LQRDataBlockSize(n, m)) == RSLQR_OK;
+  }
   registry_add(s);
   return s;
 }
@@ -126,6 +133,9 @@ NdLqrSolver* ndlqr_NewNdLqrSolver(int nstates, int ninputs, int nhorizon) {
 int ndlqr_FreeNdLqrSolver(NdLqrSolver* solver) {
   if (!solver) return -1;
   registry_remove(solver);
+  if (solver->pinned_fact) rslqr_cuda_host_unregister(solver->fact->data);
+  if (solver->pinned_soln) rslqr_cuda_host_unregister(solver->soln->data);
+  if (solver->pinned_knots) rslqr_cuda_host_unregister(solver->flat_knots);
   if (solver->device) rslqr_cuda_destroy((rslqr_cuda_solver*)solver->device);
   ndlqr_FreeTree(&solver->tree);
   ndlqr_FreeNdData(solver->data);

@@ -315,7 +315,13 @@ static cudaEvent_t take_event(rslqr_cuda_solver* h) {
 static int timed_stage(rslqr_cuda_solver* h, int phase, int stage, int level, const Sel& sel) {
   const bool prof = (h->flags & RSLQR_PROFILE) != 0;
   PhaseSpan sp;
-  if (prof) { sp.phase = phase; sp.t0 = take_event(h); sp.t1 = take_event(h); cudaEventRecord(sp.t0, h->stream); }
+  if (prof) {
+    // a stage starts where the previous one of the same enqueue ended: one event record per stage, not two
+    sp.phase = phase;
+    if (h->spans.empty()) { sp.t0 = take_event(h); cudaEventRecord(sp.t0, h->stream); }
+    else sp.t0 = h->spans.back().t1;
+    sp.t1 = take_event(h);
+  }
   int rc = launch_stage(h, stage, level, sel);
   if (prof) { cudaEventRecord(sp.t1, h->stream); h->spans.push_back(sp); }
   return rc;
@@ -694,6 +700,22 @@ extern "C" void* rslqr_cuda_host_alloc(size_t bytes) {
 }
 extern "C" void rslqr_cuda_host_free(void* p) {
   if (p) cudaFreeHost(p);
+}
+extern "C" int rslqr_cuda_host_register(void* p, size_t bytes) {
+  if (!p || !bytes) return fail(RSLQR_E_ARG, "host_register: bad argument");
+  if (cudaHostRegister(p, bytes, cudaHostRegisterDefault) != cudaSuccess) {
+    cudaGetLastError();
+    return fail(RSLQR_E_CUDA, "cudaHostRegister failed");
+  }
+  return RSLQR_OK;
+}
+extern "C" int rslqr_cuda_host_unregister(void* p) {
+  if (!p) return fail(RSLQR_E_ARG, "host_unregister: bad argument");
+  if (cudaHostUnregister(p) != cudaSuccess) {
+    cudaGetLastError();
+    return fail(RSLQR_E_CUDA, "cudaHostUnregister failed");
+  }
+  return RSLQR_OK;
 }
 
 extern "C" int rslqr_cuda_mark(rslqr_cuda_solver* h, int slot) {

@@ -72,6 +72,8 @@ _sig("rslqr_cuda_upload_async", C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c
 _sig("rslqr_cuda_download_solution_async", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int)
 _sig("rslqr_cuda_host_alloc", C.c_void_p, C.c_size_t)
 _sig("rslqr_cuda_host_free", None, C.c_void_p)
+_sig("rslqr_cuda_host_register", C.c_int, C.c_void_p, C.c_size_t)
+_sig("rslqr_cuda_host_unregister", C.c_int, C.c_void_p)
 _sig("rslqr_cuda_create_shard", C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint, C.POINTER(C.c_void_p))
 _sig("rslqr_cuda_shard_payload_doubles", C.c_size_t, C.c_void_p)
 _sig("rslqr_cuda_shard_reduce", C.c_int, C.c_void_p, C.c_void_p)
@@ -347,7 +349,8 @@ class RefSolverStruct(C.Structure):  # layout of the reference's NdLqrSolver (sr
 
 class SolverStruct(C.Structure):  # this build: same prefix + appended fields (include/solver.h)
     _fields_ = _REF_SOLVER_FIELDS + [("device", C.c_void_p), ("flat_knots", c_dp), ("flat_x0", c_dp),
-                                     ("mirror_fact", C.c_int)]
+                                     ("mirror_fact", C.c_int), ("pinned_fact", C.c_int), ("pinned_soln", C.c_int),
+                                     ("pinned_knots", C.c_int)]
 
 
 def bind_host_api(lib, solver_struct):
