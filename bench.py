@@ -177,6 +177,18 @@ class ClockSampler(threading.Thread):
                 pass
             time.sleep(0.1)
 
+    def keep_loaded(self, step, sync, iters):
+        """For timed regions of a few ms (one nvidia-smi query takes longer): issue the SAME step `iters` more times,
+        untimed, so that samples are taken under that load. `iters` must be the same on every rank (the long-horizon step
+        exchanges data between ranks). Returns how the clocks were obtained (goes into `clocks`)."""
+        if len(self.rows) >= 3:
+            return "during the timed region"
+        for _ in range(iters):
+            step()
+        sync()
+        return (f"untimed continuation of the same step loop ({iters} steps) right after the timed region "
+                "(the timed region is shorter than one nvidia-smi query)")
+
     def summary(self):
         self.stop_flag = True
         if not self.rows:
@@ -566,7 +578,9 @@ def run_long(args, rank, world, local_rank):
         t = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
+    how = sampler.keep_loaded(lh.solve_async, torch.cuda.synchronize, int(min(20000, max(100, 600.0 / ms))))
     clocks = sampler.summary()
+    clocks["sampled"] = how
     assert not lh.shard.flags().any() and np.isfinite(z).all()
     line = {"metric": f"single long-horizon LQR solve latency (n={n},m={m},N={N})", "value": ms, "unit": "ms", "n_gpus": world,
             "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms, "higher_is_better": False, "scaling": "strong",
@@ -684,11 +698,14 @@ def run_single(args, rank, world, local_rank):
         LIB.ndlqr_CopySolution(sv.p, z.ctypes.data_as(C.POINTER(C.c_double)))
     for _ in range(max(3, args.warmup)):
         once()
+    sampler = ClockSampler(0)
+    sampler.start()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         once()
     e2e_ms = (time.perf_counter() - t0) / args.steps * 1e3
     dev_ms = float(sv.c.solve_time_ms)
+    launches_default = int(LIB.rslqr_cuda_kernel_launches(sv.c.device))
     # the default call mirrors the reference's dense `fact` array back to solver->fact (staged kernels + 1.5 MB
     # download, what the reference's stage tests inspect); solver->mirror_fact = 0 returns the solution only
     sv.c.mirror_fact = 0
@@ -699,6 +716,11 @@ def run_single(args, rank, world, local_rank):
         once()
     fast_e2e_ms = (time.perf_counter() - t0) / args.steps * 1e3
     fast_ms = float(sv.c.solve_time_ms)
+    launches_fast = int(LIB.rslqr_cuda_kernel_launches(sv.c.device))
+    sv.c.mirror_fact = 1
+    how = sampler.keep_loaded(once, lambda: None, int(min(5000, max(100, 600.0 / max(e2e_ms, 1e-3)))))
+    clocks = sampler.summary()
+    clocks["sampled"] = how
     want = np.array(json.load(open(path))["soln"]).reshape(-1)
     err = float(np.linalg.norm(z[:want.size] - want))
     line = {"metric": "single-solve latency (lqr_prob_256.json n=6,m=3,N=256)", "value": dev_ms, "unit": "ms", "n_gpus": 1,
@@ -708,8 +730,9 @@ def run_single(args, rank, world, local_rank):
                        "ndlqr_Solve_ms_solution_only (solver->mirror_fact = 0)": fast_ms,
                        "reset+init+solve+copy_ms_solution_only": fast_e2e_ms,
                        "note": "value = default ndlqr_Solve, which also mirrors the dense fact array into solver->fact"},
+            "clocks": clocks,
             "e2e": {"value": e2e_ms, "unit": "ms", "h2d_bytes_per_step": int(N * R.knot_stride(n, m) * 8), "d2h_bytes_per_step": int(z.nbytes)},
-            "gpu_launches": 0}
+            "gpu_launches": launches_default * args.steps, "gpu_launches_per_solve_solution_only": launches_fast}
     if not args.no_cpu:
         sys.path.insert(0, os.path.join(ROOT, "tests"))
         import oracle_lib as O
