@@ -26,6 +26,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 N_STATES, N_INPUTS, HORIZON, SEED = 12, 4, 256, 2024
 METRIC = "LQR solves/sec (n=12,m=4,N=256 batched)"
+VALUE_KIND = ("resident: problems already in HBM when the timed region starts, solutions left in HBM; "
+              "the host-to-host figure through the C-ABI is `e2e` (the one to hold against the reference arm)")
 WORKLOAD = "batched quadrotor LQR n=12 m=4 N=256 (BASELINE configs[2])"
 
 
@@ -301,13 +303,26 @@ def cpu_riccati_baseline(n, m, N, knots, x0, budget_s=3.0):
             "sample": f"{cnt} ndlqr_SolveRiccati calls on problem 0 in {dt:.1f}s, one core (timing baseline only)"}
 
 
+def synth_only(n, m, N, seed, first, count):
+    """Synthetic problems from rslqr_b200/libsynth.so (the generator alone, plain host C): the CPU reference arm uses
+    this so that it never maps the product library (same generator, same bits as rslqr_b200.synth_problems)."""
+    import ctypes as C
+    lib = C.CDLL(os.path.join(ROOT, "rslqr_b200", "libsynth.so"))
+    lib.rslqr_synth_fill.restype = C.c_int
+    lib.rslqr_synth_fill.argtypes = [C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+    st = 2 * n + 2 * m + 1 + n * n + n * m + n
+    knots, x0 = np.empty((count, N, st)), np.empty((count, n))
+    if lib.rslqr_synth_fill(n, m, N, seed, first, count, knots.ctypes.data_as(C.c_void_p), x0.ctypes.data_as(C.c_void_p)) != 0:
+        raise RuntimeError("rslqr_synth_fill failed")
+    return knots, x0
+
+
 def run_reference(args, rank, world):
     if rank != 0:
         return
     n, m, N = N_STATES, N_INPUTS, HORIZON
-    import rslqr_b200 as R  # generator only (host C); the solve below is the reference's CPU code
     cores = max(1, len(os.sched_getaffinity(0)))
-    knots, x0 = R.synth_problems(n, m, N, SEED, 0, min(args.batch, 4 * cores))
+    knots, x0 = synth_only(n, m, N, SEED, 0, min(args.batch, 4 * cores))
     per_step = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
     for _ in range(args.warmup):
         cpu_reference_rate(n, m, N, knots, x0, budget_s=min(2.0, per_step), cores=cores)
@@ -322,8 +337,11 @@ def run_reference(args, rank, world):
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": "solves/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "batch_per_gpu": args.batch, "seed": SEED,
-                       "note": "reference ndlqr_Solve (OpenMP/C, unmodified sources compiled by oracle/Makefile) on host cores"},
+            "config": {"workload": WORKLOAD, "batch_per_gpu": args.batch, "global_batch": args.batch * world, "seed": SEED,
+                       "mode": "reference ndlqr_Solve on host cores", "parallelism": "one problem per host core, num_threads=1",
+                       "note": "reference ndlqr_Solve (OpenMP/C, unmodified sources compiled by oracle/Makefile) on host cores; "
+                               "bounded sample of the same generator and seed, extrapolated to the batch"},
+            "native_libraries": ["oracle/_ref/libref_rslqr.so (or oracle/liboracle_port.so)", "rslqr_b200/libsynth.so (problem generator only)"],
             "cpu_baseline": base,
             "e2e": {"value": val, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -381,9 +399,7 @@ def run_ours(args, rank, world, local_rank):
     s.upload(h_knots, h_x0)
 
     def step_resident():
-        if staged:
-            s.reset()          # the staged kernels accumulate into a zeroed factor array (reference contract)
-        s.solve_async(True)
+        s.solve_async(True)    # (a staged solve clears its factor array itself, stream-ordered: no host sync in here)
 
     def step_e2e():
         # the user-facing call: host problems in, host solutions out (chunked, copies overlap the kernels)
@@ -393,7 +409,7 @@ def run_ours(args, rank, world, local_rank):
     for _ in range(args.warmup):
         step_resident()
         s.sync()
-    launches_per_step = s.launches + (4 if staged else 0)
+    launches_per_step = s.launches
     s.kernel_timing(enable=True, reset=True)
     sampler = ClockSampler(local_rank)
     sampler.start()
@@ -472,7 +488,7 @@ def run_ours(args, rank, world, local_rank):
                         "reference_count = SURVEY 8d figure (32.2 MFLOP/solve as the reference executes it) over the whole step"}
     line = {"metric": METRIC, "value": value, "unit": "solves/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "value_kind": VALUE_KIND,
             "config": {"workload": WORKLOAD, "batch_per_gpu": B, "global_batch": B * world, "seed": SEED,
                        "mode": {R.MODE_STAGED: "staged", R.MODE_FUSED: "fused (tiered)", R.MODE_SCAN: "scan"}[s.mode], "parallelism": f"batch-shard x{world}, no collective",
                        "l2": "inputs (%.2f GB/GPU) larger than L2; no explicit flush" % (B * N * st * 8 / 1e9),
@@ -500,6 +516,81 @@ def run_ours(args, rank, world, local_rank):
     s.close()
     if dist is not None:
         dist.destroy_process_group()
+
+
+def kkt_residual_numpy(n, m, N, knots, x0, z):
+    """2-norm of K z - b for the LQR KKT system, straight from the flat knot blocks; terminal-knot
+    R, r, A, B, d are ignored like the reference does. A self-check of what bench.py reports, in numpy on the host."""
+    Z = np.asarray(z).reshape(N, 2 * n + m)
+    lam, x, u = Z[:, :n], Z[:, n:2 * n], Z[:, 2 * n:]
+    oA = 2 * n + 2 * m + 1
+    Q, Rr, q, r = knots[:, :n], knots[:, n:n + m], knots[:, n + m:2 * n + m], knots[:, 2 * n + m:2 * n + 2 * m]
+    A = knots[:, oA:oA + n * n].reshape(N, n, n).transpose(0, 2, 1)            # column-major blocks
+    B = knots[:, oA + n * n:oA + n * n + n * m].reshape(N, m, n).transpose(0, 2, 1)
+    d = knots[:, oA + n * n + n * m:]
+    res = [x[0] - x0]
+    rx = Q * x - lam + q
+    rx[:-1] += np.einsum("kij,ki->kj", A[:-1], lam[1:])
+    res.append(rx)
+    res.append(Rr[:-1] * u[:-1] + np.einsum("kij,ki->kj", B[:-1], lam[1:]) + r[:-1])
+    res.append(np.einsum("kij,kj->ki", A[:-1], x[:-1]) + np.einsum("kij,kj->ki", B[:-1], u[:-1]) - x[1:] + d[:-1])
+    return float(np.sqrt(sum(float(np.sum(np.square(t))) for t in res)))
+
+
+def long_horizon_record(R, dist, rank, world, local_rank, steps=20, N=16384):
+    """BASELINE configs[3] on the SAME ranks, after the timed batch region: one n=12, m=4, N=16384 problem split into
+    `world` subtrees. Latency with CUDA events (max over ranks), the KKT residual of the gathered
+    solution, whether it is bit-identical to the one-GPU solve of the same problem, and what the exchange moved."""
+    import torch
+    from rslqr_b200.dist import LongHorizon
+    n, m = N_STATES, N_INPUTS
+    knots, x0 = R.synth_problems(n, m, N, SEED, 0, 1)
+    lh = LongHorizon(n, m, N, rank, world, local_rank, exchange="auto")
+    lh.upload(knots[0], x0[0])
+    for _ in range(5):
+        lh.solve_async()
+    lh.check()
+    dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(steps):
+        lh.solve_async()
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1) / steps], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    z = torch.from_numpy(lh.solution()).cuda()
+    parts = [torch.empty_like(z) for _ in range(world)]
+    dist.all_gather(parts, z)
+    rec = None
+    if rank == 0:
+        zz = torch.cat(parts).cpu().numpy()
+        one = R.CudaSolver(n, m, N, batch=1, device=local_rank, flags=0)
+        one.upload(knots, x0)
+        for _ in range(5):
+            one.solve_async(True)
+        one.sync()
+        one.mark(6)
+        for _ in range(steps):
+            one.solve_async(True)
+        one.mark(7)
+        ms1 = one.elapsed_ms(6, 7) / steps
+        z1 = one.solution()[0]
+        launches1 = one.launches
+        one.close()
+        pay = lh.shard.payload_doubles * 8
+        rec = {"workload": f"single long-horizon LQR n={n} m={m} N={N} (BASELINE configs[3])", "n_gpus": world,
+               "latency_ms": ms, "latency_ms_one_gpu_same_box": ms1, "speedup_vs_one_gpu": ms1 / ms,
+               "kkt_residual": kkt_residual_numpy(n, m, N, knots[0], x0[0], zz), "z_norm": float(np.linalg.norm(zz)),
+               "bit_identical_to_1gpu": bool(np.array_equal(zz, z1)),
+               "rel_diff_vs_1gpu": float(np.linalg.norm(zz - z1) / np.linalg.norm(z1)),
+               "exchange": lh.exchange, "exchanges_per_solve": 1, "exchange_bytes_per_rank_per_solve": int(pay * (world - 1)),
+               "kernel_launches_per_solve_per_rank": int(lh.shard.launches), "kernel_launches_per_solve_one_gpu": int(launches1),
+               "timing": f"CUDA events on the launching stream around {steps} back-to-back solves, max over ranks"}
+    lh.close()
+    return rec
 
 
 def gpu_riccati_comparison(R, s, B, reps=5):
@@ -706,18 +797,18 @@ def run_single(args, rank, world, local_rank):
     e2e_ms = (time.perf_counter() - t0) / args.steps * 1e3
     dev_ms = float(sv.c.solve_time_ms)
     launches_default = int(LIB.rslqr_cuda_kernel_launches(sv.c.device))
-    # the default call mirrors the reference's dense `fact` array back to solver->fact (staged kernels + 1.5 MB
-    # download, what the reference's stage tests inspect); solver->mirror_fact = 0 returns the solution only
-    sv.c.mirror_fact = 0
+    # solver->mirror_fact = 1 (or RSLQR_MIRROR_FACT=1): every solve runs the reference's phases one launch each and
+    # copies the dense `fact` array (1.5 MB here) back into solver->fact, which is what the reference leaves there
+    sv.c.mirror_fact = 1
     for _ in range(5):
         once()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         once()
-    fast_e2e_ms = (time.perf_counter() - t0) / args.steps * 1e3
-    fast_ms = float(sv.c.solve_time_ms)
-    launches_fast = int(LIB.rslqr_cuda_kernel_launches(sv.c.device))
-    sv.c.mirror_fact = 1
+    mirror_e2e_ms = (time.perf_counter() - t0) / args.steps * 1e3
+    mirror_ms = float(sv.c.solve_time_ms)
+    launches_mirror = int(LIB.rslqr_cuda_kernel_launches(sv.c.device))
+    sv.c.mirror_fact = 0
     how = sampler.keep_loaded(once, lambda: None, int(min(5000, max(100, 600.0 / max(e2e_ms, 1e-3)))))
     clocks = sampler.summary()
     clocks["sampled"] = how
@@ -727,12 +818,14 @@ def run_single(args, rank, world, local_rank):
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": dev_ms, "higher_is_better": False, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "shipped fixture",
             "config": {"workload": "lqr_prob_256.json single solve via ndlqr_Solve (BASELINE configs[1])", "abs_err_vs_json_soln": err,
-                       "ndlqr_Solve_ms_solution_only (solver->mirror_fact = 0)": fast_ms,
-                       "reset+init+solve+copy_ms_solution_only": fast_e2e_ms,
-                       "note": "value = default ndlqr_Solve, which also mirrors the dense fact array into solver->fact"},
+                       "ndlqr_Solve_ms_with_fact_mirror (solver->mirror_fact = 1)": mirror_ms,
+                       "reset+init+solve+copy_ms_with_fact_mirror": mirror_e2e_ms,
+                       "note": "value = ndlqr_Solve as a consumer calls it (solve_time_ms: rhs upload + on-chip kernels + solution "
+                               "download); solver->fact is refreshed on request (ndlqr_SyncFactMirror) or by every solve with mirror_fact = 1"},
             "clocks": clocks,
             "e2e": {"value": e2e_ms, "unit": "ms", "h2d_bytes_per_step": int(N * R.knot_stride(n, m) * 8), "d2h_bytes_per_step": int(z.nbytes)},
-            "gpu_launches": launches_default * args.steps, "gpu_launches_per_solve_solution_only": launches_fast}
+            "gpu_launches": launches_default * args.steps, "gpu_launches_per_solve": launches_default,
+            "gpu_launches_per_solve_with_fact_mirror": launches_mirror}
     if not args.no_cpu:
         sys.path.insert(0, os.path.join(ROOT, "tests"))
         import oracle_lib as O

@@ -45,8 +45,9 @@ enum {
 
 /* create() flags */
 enum {
-  RSLQR_KEEP_FACT = 1u << 0, /* allocate the dense `fact` array (needed by staged mode, stage
-                                calls and download_fact); without it only the fused kernel runs */
+  RSLQR_KEEP_FACT = 1u << 0, /* allocate the dense `fact` array at creation; without it the array is
+                                allocated (and zeroed) on first need: staged mode, a stage call,
+                                factor-once, or rslqr_cuda_ensure_fact */
   RSLQR_PROFILE = 1u << 1    /* record CUDA events around each phase in staged mode */
 };
 
@@ -87,11 +88,22 @@ int rslqr_cuda_upload(rslqr_cuda_solver* h, const double* knots, const double* x
 int rslqr_cuda_upload_rhs(rslqr_cuda_solver* h, const double* soln, int first, int count);
 
 int rslqr_cuda_reset(rslqr_cuda_solver* h);            /* zero fact, soln and status           */
+/* The dense factor array [batch][K][N][fs] in the reference's NdData order (src/nddata.c:93):
+ *   ensure_fact        allocates + zeroes it if it does not exist yet (no-op otherwise);
+ *   zero_fact          zeroes it (ndlqr_ResetNdData(solver->fact), reference src/nddata.c:71) and drops the factorization;
+ *   has_factorization  1 when it holds a finished staged factorization of the uploaded problems. */
+int rslqr_cuda_ensure_fact(rslqr_cuda_solver* h);
+int rslqr_cuda_zero_fact(rslqr_cuda_solver* h);
+int rslqr_cuda_has_factorization(rslqr_cuda_solver* h);
+/* forget the stored factorization without touching memory (the uploaded Q, R, A, B changed) */
+int rslqr_cuda_invalidate_factorization(rslqr_cuda_solver* h);
+/* RSLQR_MODE_STAGED allocates the dense factor array on first use (rslqr_cuda_ensure_fact). */
 int rslqr_cuda_set_mode(rslqr_cuda_solver* h, int mode);
 int rslqr_cuda_get_mode(rslqr_cuda_solver* h);         /* the mode solve() will actually use   */
 
 /* Whole solve for all problems of the handle: pack rhs (if `pack_rhs`), leaves, K factor levels,
- * K rhs levels. Blocks until the result is on the device. */
+ * K rhs levels. Blocks until the result is on the device. Every solve starts from cleared status words and
+ * flags, and (staged mode) from a zeroed factor array, so a handle can be re-solved without rslqr_cuda_reset. */
 int rslqr_cuda_solve(rslqr_cuda_solver* h, int pack_rhs);
 /* Same, but only enqueues on the handle's stream (for overlap with copies); pair with _sync. */
 int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs);
@@ -121,7 +133,7 @@ int rslqr_cuda_sync(rslqr_cuda_solver* h);
 int rslqr_cuda_solve_host(rslqr_cuda_solver* h, const double* knots, const double* x0, double* soln, int count,
                           int chunk);
 
-/* One phase (or one task of it) in staged mode; needs RSLQR_KEEP_FACT. `problem` -1 = all. */
+/* One phase (or one task of it) of the staged path, on the dense factor array (created on first use). `problem` -1 = all. */
 int rslqr_cuda_stage(rslqr_cuda_solver* h, int stage, int level, int item, int col, int problem);
 /* ndlqr_UpdateShurFactor with an explicit calc_lambda (the reference lets the caller choose). */
 int rslqr_cuda_schur_task(rslqr_cuda_solver* h, int index, int knot, int level, int upper_level,
@@ -130,6 +142,9 @@ int rslqr_cuda_schur_task(rslqr_cuda_solver* h, int index, int knot, int level, 
 /* device -> host */
 int rslqr_cuda_download_solution(rslqr_cuda_solver* h, double* soln, int first, int count);
 int rslqr_cuda_download_fact(rslqr_cuda_solver* h, double* fact, int problem);
+/* host -> device: overwrite one problem's factor array (enqueues; the stage calls of the host API push the host mirror
+ * first, so that helper calls made on views of solver->fact between two stage calls are seen by the next one) */
+int rslqr_cuda_upload_fact(rslqr_cuda_solver* h, const double* fact, int problem);
 /* per problem: 3N-1 status words in NdLqrCholeskyFactors slot order, 0 = ok, -1 = pivot <= 0 */
 int rslqr_cuda_download_status(rslqr_cuda_solver* h, int* status, int problem);
 /* per problem summary: 0 = every factorization succeeded */
@@ -141,7 +156,7 @@ int rslqr_cuda_download_leaf_factors(rslqr_cuda_solver* h, double* out, int prob
 int rslqr_cuda_get_profile(rslqr_cuda_solver* h, double ms[7]);
 
 /* raw device pointers for callers that keep data resident (benchmarks, other CUDA code).
- * Layouts as for upload / download. `fact` is NULL without RSLQR_KEEP_FACT. */
+ * Layouts as for upload / download. `fact` is NULL until the factor array exists. */
 int rslqr_cuda_device_pointers(rslqr_cuda_solver* h, double** knots, double** x0, double** soln,
                                double** fact);
 void* rslqr_cuda_stream(rslqr_cuda_solver* h);          /* cudaStream_t the handle launches on */
@@ -184,6 +199,19 @@ int rslqr_cuda_shard_finish_wait(rslqr_cuda_solver* h, const double* d_gathered,
                                  unsigned long long epoch, int rank, int nranks);
 /* enqueue on a caller-owned cudaStream_t (e.g. the stream NCCL collectives are ordered on) */
 int rslqr_cuda_set_stream(rslqr_cuda_solver* h, void* stream);
+
+/* ---- dense helper primitives on the device (kernels_linalg.cuh): what the reference-named helper API of
+ * include/linalg.h / include/linalg_custom.h (MatrixMultiply, MatrixCholeskyFactorize, clap_* ...; reference
+ * src/linalg.h:103-191, src/linalg_custom.h:44-159) binds to. HOST pointers in and out, column-major, leading dimension =
+ * rows, synchronous, on the current CUDA device; not on the solve path. rslqr_cuda_la_last_error() has the message. */
+const char* rslqr_cuda_la_last_error(void);
+/* C = beta C + alpha op(A) op(B); symmetric != 0: A symmetric, lower triangle read (tA, tB ignored) */
+int rslqr_cuda_la_gemm(const double* A, int arows, int acols, const double* B, int brows, int bcols, double* C, int crows,
+                       int ccols, int tA, int tB, double alpha, double beta, int symmetric);
+int rslqr_cuda_la_axpy(const double* A, double* B, long long count, double alpha); /* B += alpha A; A == NULL: B *= alpha */
+int rslqr_cuda_la_add_diagonal(double* A, int n, double alpha);
+int rslqr_cuda_la_cholesky(double* A, int n, int* info);          /* in-place lower Cholesky; *info = 0 ok, -1 pivot <= 0 */
+int rslqr_cuda_la_trisolve(const double* L, int n, double* b, int m, int which); /* 0: L^-1 b, 1: L^-T b, 2: both */
 
 /* pinned host memory helpers so that callers can stage uploads at full PCIe rate */
 void* rslqr_cuda_host_alloc(size_t bytes);

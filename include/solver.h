@@ -55,8 +55,13 @@ typedef struct {
   void* device;       /* rslqr_cuda_solver* (NULL when no CUDA device could be opened) */
   double* flat_knots; /* staging copy of the problem in flat knot-block form */
   double* flat_x0;
-  int mirror_fact;    /* 1 (default): copy `fact` back after Solve; 0: solution only */
+  int mirror_fact;    /* 0 (default): ndlqr_Solve returns the solution (on-chip kernels), solver->fact is refreshed by
+                         ndlqr_SyncFactMirror / the stage calls; 1 (or RSLQR_MIRROR_FACT=1 in the environment):
+                         every ndlqr_Solve runs the staged kernels and copies the dense `fact` array back */
   int pinned_fact, pinned_soln, pinned_knots; /* the mirrors are page-locked (rslqr_cuda_host_register) */
+  int initialized;    /* a problem has been uploaded (ndlqr_InitializeWithLQRProblem) */
+  int fact_dirty;     /* the factor mirror has been written since the last reset */
+  int* status_host;   /* pinned staging buffer for the 3N-1 status words (cholinfo[].success) */
 } NdLqrSolver;
 
 NdLqrSolver* ndlqr_NewNdLqrSolver(int nstates, int ninputs, int nhorizon);

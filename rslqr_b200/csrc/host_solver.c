@@ -5,6 +5,7 @@
  * KKT mirror / rhs exactly where the reference puts it (reference src/solver.c:122-194), and moving
  * bytes to and from the device. All arithmetic of the solve happens in the kernels. */
 #include <math.h>
+#include <pthread.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -17,27 +18,49 @@
 #include "solve.h"
 #include "tree_math.h"
 
-/* ---- registry of live solvers (lets the reference-signature stage calls find their solver) ---- */
-#define RSLQR_MAX_LIVE 256
-static NdLqrSolver* g_live[RSLQR_MAX_LIVE];
+/* ---- registry of live solvers (lets the reference-signature stage calls find their solver) ----
+ * A growing array behind a mutex: any number of solvers, created and freed from any thread. */
+static NdLqrSolver** g_live = NULL;
+static int g_live_cap = 0;
+static pthread_mutex_t g_live_mu = PTHREAD_MUTEX_INITIALIZER;
 
-static void registry_add(NdLqrSolver* s) {
-  for (int i = 0; i < RSLQR_MAX_LIVE; ++i)
-    if (!g_live[i]) { g_live[i] = s; return; }
+static int registry_add(NdLqrSolver* s) {
+  int ok = 0;
+  pthread_mutex_lock(&g_live_mu);
+  for (int i = 0; i < g_live_cap && !ok; ++i)
+    if (!g_live[i]) { g_live[i] = s; ok = 1; }
+  if (!ok) {
+    const int cap = g_live_cap ? 2 * g_live_cap : 64;
+    NdLqrSolver** grown = (NdLqrSolver**)realloc(g_live, sizeof(NdLqrSolver*) * (size_t)cap);
+    if (grown) {
+      memset(grown + g_live_cap, 0, sizeof(NdLqrSolver*) * (size_t)(cap - g_live_cap));
+      grown[g_live_cap] = s;
+      g_live = grown;
+      g_live_cap = cap;
+      ok = 1;
+    }
+  }
+  pthread_mutex_unlock(&g_live_mu);
+  return ok ? 0 : -1;
 }
 static void registry_remove(NdLqrSolver* s) {
-  for (int i = 0; i < RSLQR_MAX_LIVE; ++i)
+  pthread_mutex_lock(&g_live_mu);
+  for (int i = 0; i < g_live_cap; ++i)
     if (g_live[i] == s) g_live[i] = NULL;
+  pthread_mutex_unlock(&g_live_mu);
 }
 NdLqrSolver* rslqr_owner_of(const NdData* nd, int* which) {
-  for (int i = 0; i < RSLQR_MAX_LIVE; ++i) {
+  NdLqrSolver* found = NULL;
+  pthread_mutex_lock(&g_live_mu);
+  for (int i = 0; i < g_live_cap && !found; ++i) {
     NdLqrSolver* s = g_live[i];
     if (!s) continue;
-    if (s->data == nd) { if (which) *which = 0; return s; }
-    if (s->fact == nd) { if (which) *which = 1; return s; }
-    if (s->soln == nd) { if (which) *which = 2; return s; }
+    if (s->data == nd) { if (which) *which = 0; found = s; }
+    else if (s->fact == nd) { if (which) *which = 1; found = s; }
+    else if (s->soln == nd) { if (which) *which = 2; found = s; }
   }
-  return NULL;
+  pthread_mutex_unlock(&g_live_mu);
+  return found;
 }
 
 static double wall_ms(void) {
@@ -111,23 +134,34 @@ NdLqrSolver* ndlqr_NewNdLqrSolver(int nstates, int ninputs, int nhorizon) {
   s->num_threads = (int)(procs > 1 ? procs / 2 : 1);
   s->flat_knots = (double*)calloc((size_t)N * ndlqr_LQRDataBlockSize(n, m), sizeof(double));
   s->flat_x0 = (double*)calloc((size_t)n, sizeof(double));
-  s->mirror_fact = 1;
+  /* The dense factor mirror solver->fact is refreshed on request (ndlqr_SyncFactMirror, the stage calls), not by every
+   * ndlqr_Solve: the solve then runs the on-chip kernels and moves only the solution. RSLQR_MIRROR_FACT=1 (or
+   * solver->mirror_fact = 1) restores "every solve leaves the reference's fact array in solver->fact". */
+  const char* mf = getenv("RSLQR_MIRROR_FACT");
+  s->mirror_fact = mf ? (atoi(mf) != 0) : 0;
   rslqr_cuda_solver* dev = NULL;
-  if (rslqr_cuda_create(n, m, N, 1, 0, RSLQR_KEEP_FACT | RSLQR_PROFILE, &dev) != RSLQR_OK) {
+  if (rslqr_cuda_create(n, m, N, 1, 0, RSLQR_PROFILE, &dev) != RSLQR_OK) {
     fprintf(stderr, "ERROR: rsLQR could not open a CUDA device (%s). ndlqr_Solve will fail; there is no CPU path.\n",
             rslqr_cuda_last_error());
     dev = NULL;
   }
   s->device = dev;
   if (dev) {
-    /* page-lock the mirrors the solve copies to and from (best effort: a refused range just stays pageable) */
-    const size_t fs = (size_t)(2 * n + m) * n;
-    s->pinned_fact = rslqr_cuda_host_register(s->fact->data, sizeof(double) * fs * (size_t)N * (size_t)s->depth) == RSLQR_OK;
+    /* page-lock the mirrors the solve copies to and from (best effort: a refused range just stays pageable); the
+     * factor mirror (N log2(N) blocks: 617 MB at n=12, N=16384) stays untouched calloc memory until it is first
+     * downloaded into (pin_fact_mirror) */
     s->pinned_soln = rslqr_cuda_host_register(s->soln->data, sizeof(double) * (size_t)(2 * n + m) * (size_t)N) == RSLQR_OK;
     s->pinned_knots = rslqr_cuda_host_register(s->flat_knots, sizeof(double) * (size_t)N * ndlqr_LQRDataBlockSize(n, m)) == RSLQR_OK;
+    s->status_host = (int*)rslqr_cuda_host_alloc(sizeof(int) * 3 * (size_t)N);
   }
-  registry_add(s);
+  if (registry_add(s) != 0) fprintf(stderr, "WARNING: rsLQR solver registry is out of memory; stage calls on this solver will fail.\n");
   return s;
+}
+
+static void pin_fact_mirror(NdLqrSolver* s) {
+  if (s->pinned_fact || !s->device) return;
+  const size_t fs = (size_t)(2 * s->nstates + s->ninputs) * (size_t)s->nstates;
+  s->pinned_fact = rslqr_cuda_host_register(s->fact->data, sizeof(double) * fs * (size_t)s->nhorizon * (size_t)s->depth) == RSLQR_OK;
 }
 
 int ndlqr_FreeNdLqrSolver(NdLqrSolver* solver) {
@@ -136,6 +170,7 @@ int ndlqr_FreeNdLqrSolver(NdLqrSolver* solver) {
   if (solver->pinned_fact) rslqr_cuda_host_unregister(solver->fact->data);
   if (solver->pinned_soln) rslqr_cuda_host_unregister(solver->soln->data);
   if (solver->pinned_knots) rslqr_cuda_host_unregister(solver->flat_knots);
+  if (solver->status_host) rslqr_cuda_host_free(solver->status_host);
   if (solver->device) rslqr_cuda_destroy((rslqr_cuda_solver*)solver->device);
   ndlqr_FreeTree(&solver->tree);
   ndlqr_FreeNdData(solver->data);
@@ -152,7 +187,9 @@ int ndlqr_FreeNdLqrSolver(NdLqrSolver* solver) {
 
 void ndlqr_ResetSolver(NdLqrSolver* solver) {
   ndlqr_ResetNdData(solver->data);
-  ndlqr_ResetNdData(solver->fact);
+  /* the factor mirror is only ever written by a download (fact_dirty): an untouched one is still all zeros */
+  if (solver->fact_dirty) ndlqr_ResetNdData(solver->fact);
+  solver->fact_dirty = 0;
   ndlqr_ResetNdData(solver->soln);
   ndlqr_ResetProfile(&solver->profile);
   for (int i = 0; i < 2 * solver->nhorizon; ++i) MatrixSetConst(&solver->diagonals[i], 0.0);
@@ -204,6 +241,8 @@ int ndlqr_InitializeWithLQRProblem(const LQRProblem* lqrprob, NdLqrSolver* solve
     fprintf(stderr, "ERROR: upload to the GPU failed: %s\n", rslqr_cuda_last_error());
     return -1;
   }
+  if (solver->device) rslqr_cuda_invalidate_factorization((rslqr_cuda_solver*)solver->device); /* new Q, R, A, B */
+  solver->initialized = 1;
   return 0;
 }
 
@@ -212,35 +251,44 @@ static int push_rhs(NdLqrSolver* s) {
   return rslqr_cuda_upload_rhs_async((rslqr_cuda_solver*)s->device, s->soln->data, 0, 1);
 }
 
+/* The leaf Cholesky factors the reference leaves in `diagonals` (sqrt of the diagonal Q_k, R_k, reference
+ * src/nested_dissection.c:61-73) are mirror bookkeeping like `fact`: refreshed together with it (mirror_fact,
+ * ndlqr_SyncFactMirror, stage calls), from the flat knot blocks, since only the staged kernels materialise them on
+ * the device. */
+static void refresh_leaf_factors(NdLqrSolver* s) {
+  const int n = s->nstates, m = s->ninputs, N = s->nhorizon;
+  const int blk = ndlqr_LQRDataBlockSize(n, m);
+  for (int k = 0; k < N; ++k) {
+    const double* kd = s->flat_knots + (size_t)k * blk; /* Q (n) then R (m) lead the block */
+    for (int i = 0; i < n; ++i) s->diagonals[2 * k].data[i + n * i] = kd[i] > 0 ? sqrt(kd[i]) : kd[i];
+    if (k < N - 1)
+      for (int i = 0; i < m; ++i) s->diagonals[2 * k + 1].data[i + m * i] = kd[n + i] > 0 ? sqrt(kd[n + i]) : kd[n + i];
+  }
+}
+
 static int pull_results(NdLqrSolver* s, int with_fact) {
   rslqr_cuda_solver* dev = (rslqr_cuda_solver*)s->device;
-  const int n = s->nstates, m = s->ninputs, N = s->nhorizon;
+  const int N = s->nhorizon;
   /* the solution and the status words were queued behind the solve by ndlqr_Solve; one sync covers them */
-  int* status = (int*)malloc(sizeof(int) * 3 * (size_t)N);
+  int* status = s->status_host; /* pinned, allocated with the solver */
   if (!status) return RSLQR_E_NOMEM;
   int rc = rslqr_cuda_download_solution_async(dev, s->soln->data, 0, 1);
   if (!rc) rc = rslqr_cuda_download_status_async(dev, status, 0);
   if (!rc) rc = rslqr_cuda_sync(dev);
-  if (!rc && with_fact) rc = rslqr_cuda_download_fact(dev, s->fact->data, 0);
-  if (rc) { free(status); return rc; }
-  /* status words -> cholinfo[].success. The leaf Cholesky factors the reference leaves in `diagonals`
-   * (sqrt of the diagonal Q_k, R_k, reference src/nested_dissection.c:61-73) are mirror bookkeeping: they are
-   * taken from the flat knot blocks here, since only the staged kernels materialise them on the device. */
-  {
-    const int blk = ndlqr_LQRDataBlockSize(n, m);
-    for (int f = 0; f < s->cholfacts->numfacts; ++f) {
-      s->cholfacts->cholinfo[f].success = status[f];
-      s->cholfacts->cholinfo[f].uplo = 'L';
-      s->cholfacts->cholinfo[f].lib = 'C';
-    }
-    for (int k = 0; k < N; ++k) {
-      const double* kd = s->flat_knots + (size_t)k * blk; /* Q (n) then R (m) lead the block */
-      for (int i = 0; i < n; ++i) s->diagonals[2 * k].data[i + n * i] = kd[i] > 0 ? sqrt(kd[i]) : kd[i];
-      if (k < N - 1)
-        for (int i = 0; i < m; ++i) s->diagonals[2 * k + 1].data[i + m * i] = kd[n + i] > 0 ? sqrt(kd[n + i]) : kd[n + i];
-    }
+  if (!rc && with_fact) {
+    pin_fact_mirror(s);
+    rc = rslqr_cuda_download_fact(dev, s->fact->data, 0);
+    s->fact_dirty = 1;
   }
-  free(status);
+  if (rc) return rc;
+  /* status words -> cholinfo[].success */
+  for (int f = 0; f < s->cholfacts->numfacts; ++f) {
+    s->cholfacts->cholinfo[f].success = status[f];
+    s->cholfacts->cholinfo[f].uplo = 'L';
+    s->cholfacts->cholinfo[f].lib = 'C';
+  }
+  if (with_fact) refresh_leaf_factors(s);
+  (void)N;
   return rc;
 }
 
@@ -281,9 +329,14 @@ int ndlqr_SolveRhsOnly(NdLqrSolver* solver) {
     fprintf(stderr, "ERROR: ndlqr_SolveRhsOnly: no CUDA device is attached to this solver (no CPU fallback).\n");
     return -1;
   }
+  if (!solver->initialized) return -1; /* nothing to factor yet */
   rslqr_cuda_solver* dev = (rslqr_cuda_solver*)solver->device;
   const double t0 = wall_ms();
-  int rc = push_rhs(solver);
+  /* the rhs phase runs on the staged factorization; a solver whose last solve took the on-chip path (which keeps
+   * none) factors here, once */
+  int rc = rslqr_cuda_set_mode(dev, RSLQR_MODE_STAGED);
+  if (!rc && !rslqr_cuda_has_factorization(dev)) rc = rslqr_cuda_factor_async(dev);
+  if (!rc) rc = push_rhs(solver);
   if (!rc) rc = rslqr_cuda_solve_rhs_async(dev, 0);
   if (!rc) rc = pull_results(solver, 0);
   if (rc) {
@@ -295,6 +348,24 @@ int ndlqr_SolveRhsOnly(NdLqrSolver* solver) {
   solver->solve_time_ms = wall_ms() - t0;
   solver->linalg_time_ms = ms[0];
   return 0;
+}
+
+/* solver->fact <- the reference's factor array for the problem the solver was initialized with (what ndlqr_Solve of
+ * the reference leaves there, src/solve.c:57-133): downloaded if the device holds a staged factorization, else
+ * factored first by the staged kernels. */
+int ndlqr_SyncFactMirror(NdLqrSolver* solver) {
+  if (!solver || !solver->device || !solver->initialized) return -1;
+  rslqr_cuda_solver* dev = (rslqr_cuda_solver*)solver->device;
+  int rc = rslqr_cuda_set_mode(dev, RSLQR_MODE_STAGED);
+  if (!rc && !rslqr_cuda_has_factorization(dev)) rc = rslqr_cuda_factor_async(dev);
+  if (!rc) {
+    pin_fact_mirror(solver);
+    rc = rslqr_cuda_download_fact(dev, solver->fact->data, 0);
+    solver->fact_dirty = 1;
+    refresh_leaf_factors(solver);
+  }
+  if (rc) fprintf(stderr, "ERROR: ndlqr_SyncFactMirror failed: %s\n", rslqr_cuda_last_error());
+  return rc ? -1 : 0;
 }
 
 int ndlqr_SolveLQRProblem(const LQRProblem* lqrprob, NdLqrSolver* solver) {
@@ -341,8 +412,16 @@ int ndlqr_PrintSolveProfile(NdLqrSolver* solver) {
 NdLqrProfile ndlqr_GetProfile(NdLqrSolver* solver) { return solver->profile; }
 
 /* ---- stage calls (reference src/nested_dissection.c) ---------------------------------------
- * Device `fact` is authoritative between calls; the rhs mirror is pushed before and both mirrors
- * are pulled after each call, so a test can interleave calls with reads of solver->fact / soln. */
+ * The HOST mirrors are authoritative between calls: solver->soln and solver->fact are pushed before and pulled after
+ * each call, so a caller can interleave stage calls with reads of, and helper calls on, views of solver->fact / soln
+ * (the reference's own test does: MatrixCholeskyFactorize / MatrixCholeskySolve on F->lambda between
+ * ndlqr_FactorInnerProduct and ndlqr_ComputeShurCompliment, test/nested_dissection_test.c:138-190). */
+static int push_fact(NdLqrSolver* s) {
+  pin_fact_mirror(s);
+  s->fact_dirty = 1;
+  return rslqr_cuda_upload_fact((rslqr_cuda_solver*)s->device, s->fact->data, 0);
+}
+
 static int run_stage(NdLqrSolver* s, int stage, int level, int item, int col) {
   if (!s) return -1;
   if (!s->device) {
@@ -351,6 +430,7 @@ static int run_stage(NdLqrSolver* s, int stage, int level, int item, int col) {
   }
   rslqr_cuda_solver* dev = (rslqr_cuda_solver*)s->device;
   int rc = push_rhs(s);
+  if (!rc) rc = push_fact(s);
   if (!rc) rc = rslqr_cuda_stage(dev, stage, level, item, col, 0);
   if (!rc) rc = pull_results(s, 1);
   if (rc) fprintf(stderr, "ERROR: GPU stage %d failed: %s\n", stage, rslqr_cuda_last_error());
@@ -401,6 +481,7 @@ int ndlqr_SolverUpdateShurFactor(NdLqrSolver* solver, int index, int i, int leve
   }
   rslqr_cuda_solver* dev = (rslqr_cuda_solver*)solver->device;
   int rc = push_rhs(solver);
+  if (!rc) rc = push_fact(solver);
   if (!rc) rc = rslqr_cuda_schur_task(dev, index, i, level, upper_level, calc_lambda ? 1 : 0, use_rhs, 0);
   if (!rc) rc = pull_results(solver, 1);
   if (rc) fprintf(stderr, "ERROR: GPU Schur update failed: %s\n", rslqr_cuda_last_error());

@@ -7,6 +7,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include "rslqr_cuda.h"
 #include "rslqr_host_internal.h"
 #include "tree_math.h"
 
@@ -151,6 +152,11 @@ void ndlqr_ResetNdData(NdData* nddata) {
   const size_t count = (size_t)(nddata->nsegments + 1) * (size_t)nddata->depth;
   const size_t each = (size_t)(2 * nddata->nstates + nddata->ninputs) * (size_t)nddata->width;
   memset(nddata->data, 0, count * each * sizeof(double));
+  /* ndlqr_ResetNdData(solver->fact) is the reference's way to prepare a re-solve (src/solve.h:28-32,
+   * test/nested_dissection_test.c:301): the device copy of that array is the one the stage calls work on */
+  int which = -1;
+  NdLqrSolver* owner = rslqr_owner_of(nddata, &which);
+  if (owner && which == 1 && owner->device) rslqr_cuda_zero_fact((rslqr_cuda_solver*)owner->device);
 }
 
 int ndlqr_FreeNdData(NdData* nddata) {

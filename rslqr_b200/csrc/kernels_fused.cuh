@@ -193,6 +193,90 @@ __device__ __forceinline__ int spine_core2(double (&acc)[NS], double (&acc2)[NS]
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// Same sweep as spine_core2 with the pivot rows broadcast through shared memory instead of by shuffles: at step j
+// lane j scales its row, U(j, k) = S'(j, k) / d_j = Lt(k, j), and stores [1/d_j | U(j, j+1..)] as row j of Ur (one
+// lane, 128-bit stores: one wavefront each); every lane reads the row back with 128-bit broadcast loads (one
+// wavefront per pair of elements, against two per element for a 64-bit shuffle) and eliminates with its own
+// unscaled element: acc[k] -= acc[j] * U(j, k). Row j of Ur is exactly what the backward sweep x_j = y_j -
+// sum_{k>j} Lt(k, j) x_k needs, so the factor is never stored a second time. LSU wavefronts per merge: 42 stores
+// + 42 + 36 broadcast loads = 120 (spine_core2: 178 shuffle + 12 store + 36 load = 226). Same arithmetic, same
+// rounding as spine_core2 (lij * pk = (acc[j] / d) * pk there, acc[j] * (pk / d) here: one rounding apart).
+// ---------------------------------------------------------------------------------------------------------
+template <int NS>
+__device__ __forceinline__ int spine_core3(double (&acc)[NS], double (&acc2)[NS], double* Ur, double* Wout) {
+  static_assert(NS % 2 == 0 && 2 * NS + 1 <= 32, "pairs; one warp per separator");
+  constexpr int LDF = factor_ld<NS>();
+  const int lane = threadIdx.x & 31;
+  int bad = 0;
+#pragma unroll
+  for (int j = 0; j < NS; ++j) {
+    const int j0 = j & ~1;  // first element of the 128-bit pair that holds 1/d_j
+    if (lane == j) {
+      const double d = acc[j];
+      if (!(d > 0.0)) bad = 1;
+      const double dinv = fast_rcp(d);
+      double row[NS];
+#pragma unroll
+      for (int k = j0; k < NS; ++k) row[k] = k < j ? 0.0 : (k == j ? dinv : acc[k] * dinv);
+#pragma unroll
+      for (int k = j0; k < NS; k += 2) *reinterpret_cast<double2*>(Ur + j * LDF + k) = make_double2(row[k], row[k + 1]);
+    }
+    __syncwarp();
+    const double m1 = acc[j], m2 = acc2[j];
+    double dinv = 0.0;
+#pragma unroll
+    for (int k = j0; k < NS; k += 2) {
+      const double2 u = *reinterpret_cast<const double2*>(Ur + j * LDF + k);
+      if (k == j) dinv = u.x;
+      else if (k > j) { acc[k] = fma(-m1, u.x, acc[k]); acc2[k] = fma(-m2, u.x, acc2[k]); }
+      if (k + 1 == j) dinv = u.y;
+      else if (k + 1 > j) { acc[k + 1] = fma(-m1, u.y, acc[k + 1]); acc2[k + 1] = fma(-m2, u.y, acc2[k + 1]); }
+    }
+    acc[j] = m1 * dinv;
+    acc2[j] = m2 * dinv;
+  }
+  bad = __any_sync(0xffffffffu, bad);
+  // backward sweep: x_j = y_j - sum_{k > j} U(j, k) x_k, the latest x last so that the dependent chain is one FMA per j
+#pragma unroll
+  for (int j = NS - 2; j >= 0; --j) {
+    const int k0 = (j + 1) & ~1;
+    double2 u[NS / 2];
+#pragma unroll
+    for (int k = k0; k < NS; k += 2) u[k / 2] = *reinterpret_cast<const double2*>(Ur + j * LDF + k);
+#pragma unroll
+    for (int k = NS - 1; k > j; --k) {
+      const double uk = (k & 1) ? u[k / 2].y : u[k / 2].x;
+      acc[j] = fma(-uk, acc[k], acc[j]);
+      acc2[j] = fma(-uk, acc2[k], acc2[j]);
+    }
+  }
+  if (lane >= NS && lane <= 2 * NS) {
+    const int c = lane - NS;  // lane 2NS: c = NS -> column 2NS of W (zs)
+    double* w1 = lane < 2 * NS ? Wout + c * NS : Wout + 2 * NS * NS;
+#pragma unroll
+    for (int r = 0; r < NS; r += 2) *reinterpret_cast<double2*>(w1 + r) = make_double2(acc[r], acc[r + 1]);
+    if (lane < 2 * NS) {
+#pragma unroll
+      for (int r = 0; r < NS; r += 2) *reinterpret_cast<double2*>(Wout + (NS + c) * NS + r) = make_double2(acc2[r], acc2[r + 1]);
+    }
+  }
+  __syncwarp();
+  return bad;
+}
+
+#ifndef RSLQR_SPINE_SMEM
+#define RSLQR_SPINE_SMEM 0
+#endif
+template <int NS>
+__device__ __forceinline__ int spine_core(double (&acc)[NS], double (&acc2)[NS], double* Lr, double* Wout) {
+#if RSLQR_SPINE_SMEM
+  return spine_core3<NS>(acc, acc2, Lr, Wout);
+#else
+  return spine_core2<NS>(acc, acc2, Lr, Wout);
+#endif
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // One separator, one warp: inner products -> factorization -> solves. Lane roles:
 //   lanes [0,NS)      : column c of S  (then, for the solves, column c of S_R -> f_R)
 //   lanes [NS,2NS)    : column c of S_L -> f_L
@@ -298,7 +382,7 @@ __device__ __forceinline__ int spine_merge(const double* __restrict__ AB, const 
       acc[r] = lane < NS ? acc[r] - ln : (lane >= 2 * NS ? acc[r] - zz : acc[r]);
       acc2[r] = (lane >= NS && lane < 2 * NS) ? -rn : 0.0;
     }
-    return spine_core2<NS>(acc, acc2, Lsm, Wout);
+    return spine_core<NS>(acc, acc2, Lsm, Wout);
   }
   const int mycol = lane <= 2 * NS ? lane : 2 * NS;
   if (lane < NS) {
@@ -1038,11 +1122,7 @@ inline int launch_topdown(const double* sep, double* lam, int M0, int batch, con
     const bool use_smem = smem_ok && (force >= 0 ? force != 0 : ctas <= 1024);
     if (use_smem) {
       const int bytes = ((nloc - 1) * WSZ + (nloc + 1) * NS) * (int)sizeof(double);
-      static int attr_bytes = 0;
-      if (bytes > 48 * 1024 && bytes > attr_bytes) {
-        cudaFuncSetAttribute(topdown_smem_kernel<NS>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-        attr_bytes = bytes;
-      }
+      smem_optin(topdown_smem_kernel<NS>, bytes);
       topdown_smem_kernel<NS><<<ctas, 128, bytes, st>>>(sep, lam, M0, left, right, span, step);
     } else {
       topdown_kernel<NS><<<ctas, 128, 0, st>>>(sep, lam, M0, left, right, span, step);
@@ -1158,12 +1238,8 @@ inline void fused_free(FusedPlan* p) {
 template <int NS, int NI, int G, bool DMMA>
 inline cudaError_t launch_tier0(const FusedPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st) {
   constexpr int smem = tier0_smem_doubles<NS, NI, G>() * (int)sizeof(double);
-  static bool attr_done = false;
-  if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(tier0_kernel<NS, NI, G, DMMA>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return e;
-    attr_done = true;
-  }
+  cudaError_t e = smem_optin(tier0_kernel<NS, NI, G, DMMA>, smem);
+  if (e != cudaSuccess) return e;
   tier0_kernel<NS, NI, G, DMMA><<<(unsigned)((size_t)batch * p.M0), 16 * G, smem, st>>>(s, b, p.fb, pack_rhs, p.M0);
   return cudaGetLastError();
 }
@@ -1171,12 +1247,7 @@ inline cudaError_t launch_tier0(const FusedPlan& p, const Shape& s, const Bufs& 
 template <int NS, int NI>
 inline cudaError_t tier_attr() {
   using D = Dim<NS, NI>;
-  static bool attr_done = false;
-  if (attr_done) return cudaSuccess;
-  cudaError_t e = cudaFuncSetAttribute(tier_kernel<NS, NI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (8 * D::ENT + 4 * tier_warp_scratch<NS>()) * (int)sizeof(double));
-  if (e == cudaSuccess) attr_done = true;
-  return e;
+  return smem_optin(tier_kernel<NS, NI>, (8 * D::ENT + 4 * tier_warp_scratch<NS>()) * (int)sizeof(double));
 }
 
 template <int NS, int NI>

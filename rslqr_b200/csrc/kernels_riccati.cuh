@@ -332,11 +332,9 @@ template <int NS, int NI>
 inline int launch_riccati(const Shape& s, const Bufs& b, double* gain, int nprob, cudaStream_t st, std::string& err) {
   using D = RicDim<NS, NI>;
   const int smem = RIC_WPC * D::WARP * (int)sizeof(double);
-  static bool attr_done = false;
-  if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(riccati_kernel<NS, NI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  {
+    cudaError_t e = smem_optin(riccati_kernel<NS, NI>, smem);
     if (e != cudaSuccess) { err = std::string("riccati: ") + cudaGetErrorString(e); return 1; }
-    attr_done = true;
   }
   riccati_kernel<NS, NI><<<(unsigned)((nprob + RIC_WPC - 1) / RIC_WPC), 32 * RIC_WPC, smem, st>>>(s, b, gain, nprob);
   riccati_forward_kernel<NS, NI><<<(unsigned)((nprob + RIC_WPC - 1) / RIC_WPC), 32 * RIC_WPC, 0, st>>>(s, b, gain, nprob);

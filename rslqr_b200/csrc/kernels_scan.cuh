@@ -214,7 +214,7 @@ __device__ __forceinline__ int merge_raw(const double* Bl, const double* Br, con
       acc2[r] = (isL && !lastR) ? -ar * dr : 0.0;
     }
   }
-  const int bad = spine_core2<NS>(acc, acc2, Lsm, Wf);
+  const int bad = spine_core<NS>(acc, acc2, Lsm, Wf);
   // ---- entry rows X(i+1), U(i+1) straight from the solved columns still in registers: lane NS+c holds f_L(:,c)
   //      (acc) and f_R(:,c) (acc2), lane 2NS holds zs. Row r of the entry is a scaling by 1/Q_{i+1}(r):
   //      L = f_L/Q, R = (A_{i+1}^T + f_R)/Q, z = z_x + zs/Q; the U rows are the leaf values. Every lane loads
@@ -542,12 +542,8 @@ inline cudaError_t launch_scan_leaf(ScanPlan& p, const Shape& s, const Bufs& b, 
   // RSLQR_LEAF_PAD_KB: extra (unused) shared memory per CTA, an occupancy knob for experiments
   static const int pad = [] { const char* v = getenv("RSLQR_LEAF_PAD_KB"); return v ? atoi(v) * 1024 : 0; }();
   const int smem = scan_leaf_smem_doubles<NS, NI>() * (int)sizeof(double) + pad;
-  static bool attr_done = false;
-  if (!attr_done) {
-    cudaError_t e = cudaFuncSetAttribute(scan_leaf_kernel<NS, NI>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return e;
-    attr_done = true;
-  }
+  cudaError_t e = smem_optin(scan_leaf_kernel<NS, NI>, smem);
+  if (e != cudaSuccess) return e;
   const long long nsub = (long long)batch * p.f.M0;
   scan_leaf_kernel<NS, NI><<<(unsigned)((nsub + SCAN_WPC - 1) / SCAN_WPC), 32 * SCAN_WPC, smem, st>>>(s, b, p.sb, pack_rhs, p.f.M0, nsub);
   return cudaGetLastError();

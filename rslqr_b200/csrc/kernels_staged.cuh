@@ -11,9 +11,31 @@
 // C(i+1,j) = (-I, 0) are read straight from the flat knot blocks.
 #pragma once
 #include <cuda_runtime.h>
+#include <map>
+#include <mutex>
+#include <utility>
 #include "tree_math.h"
 
 namespace rslqr {
+
+// Opt-in to more than 48 KB of dynamic shared memory. cudaFuncSetAttribute applies to the CURRENT device only, so
+// what has been granted is remembered per (kernel, device): a process that opens handles on several GPUs gets the
+// attribute on each of them (a process-wide flag would leave every device but the first without it).
+template <class Kernel>
+inline cudaError_t smem_optin(Kernel kernel, int bytes) {
+  if (bytes <= 48 * 1024) return cudaSuccess;
+  static std::mutex mu;
+  static std::map<std::pair<const void*, int>, int> granted;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  std::lock_guard<std::mutex> lock(mu);
+  int& have = granted[std::make_pair(reinterpret_cast<const void*>(kernel), dev)];
+  if (bytes <= have) return cudaSuccess;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) have = bytes;
+  return e;
+}
 
 struct Shape {
   int n, m, N, K;

@@ -52,6 +52,7 @@ struct rslqr_cuda_solver {
   FusedPlan fused; int force_dfma;
   ScanPlan scan; int g0_pref;
   int factored = 0;  // `fact` holds a finished staged factorization of the uploaded problems
+  bool prof_keep = false;  // keep the profile spans across enqueues (the chunks of solve_host)
   double* ric_gain = nullptr;  // [batch][N][K | dv | P | p] of the Riccati comparison solver (allocated on first use)
   bool shard; bool own_stream;
   int r_first, r_count;            // problem range the next enqueue covers (whole batch by default)
@@ -107,9 +108,13 @@ extern "C" int rslqr_cuda_create(int n, int m, int N, int batch, int device, uns
   ok &= alloc((void**)&h->d_knots, sizeof(double) * (size_t)batch * N * s.stride) == cudaSuccess;
   ok &= alloc((void**)&h->d_x0, sizeof(double) * (size_t)batch * n) == cudaSuccess;
   ok &= alloc((void**)&h->b.soln, sizeof(double) * (size_t)batch * N * s.zs) == cudaSuccess;
-  ok &= alloc((void**)&h->b.status, sizeof(int) * (size_t)batch * 3 * N) == cudaSuccess;
-  ok &= alloc((void**)&h->b.flags, sizeof(int) * (size_t)batch) == cudaSuccess;
+  // status words and per-problem flags share one allocation ([batch][3N] then [batch]): a full-batch solve clears
+  // both with one memset node
+  ok &= alloc((void**)&h->b.status, sizeof(int) * ((size_t)batch * 3 * N + (size_t)batch)) == cudaSuccess;
+  if (ok) h->b.flags = h->b.status + (size_t)batch * 3 * N;
   ok &= alloc((void**)&h->b.leafd, sizeof(double) * (size_t)batch * N * (n + m)) == cudaSuccess;
+  // RSLQR_KEEP_FACT allocates the dense factor array up front; without it the array appears on first need
+  // (staged mode, stage calls, factor-once: ensure_fact)
   if (ok && (flags & RSLQR_KEEP_FACT))
     ok &= alloc((void**)&h->b.fact, sizeof(double) * (size_t)batch * s.K * N * s.fs) == cudaSuccess;
   if (!ok) {
@@ -147,7 +152,7 @@ extern "C" int rslqr_cuda_destroy(rslqr_cuda_solver* h) {
   cudaSetDevice(h->device);
   cudaStreamSynchronize(h->stream);
   cudaFree(h->d_knots); cudaFree(h->d_x0); cudaFree(h->b.soln); cudaFree(h->b.fact);
-  cudaFree(h->b.status); cudaFree(h->b.flags); cudaFree(h->b.leafd); cudaFree(h->ric_gain);
+  cudaFree(h->b.status); cudaFree(h->b.leafd); cudaFree(h->ric_gain);
   fused_free(&h->fused);
   scan_free(&h->scan);
   for (auto ev : h->evpool) cudaEventDestroy(ev);
@@ -194,16 +199,73 @@ extern "C" int rslqr_cuda_reset(rslqr_cuda_solver* h) {
   const Shape& s = h->s;
   if (h->b.fact) CU(cudaMemsetAsync(h->b.fact, 0, sizeof(double) * (size_t)h->batch * s.K * s.N * s.fs, h->stream));
   CU(cudaMemsetAsync(h->b.soln, 0, sizeof(double) * (size_t)h->batch * s.N * s.zs, h->stream));
-  CU(cudaMemsetAsync(h->b.status, 0, sizeof(int) * (size_t)h->batch * 3 * s.N, h->stream));
-  CU(cudaMemsetAsync(h->b.flags, 0, sizeof(int) * (size_t)h->batch, h->stream));
+  CU(cudaMemsetAsync(h->b.status, 0, sizeof(int) * ((size_t)h->batch * 3 * s.N + (size_t)h->batch), h->stream));
   CU(cudaStreamSynchronize(h->stream));
   h->factored = 0;
   return RSLQR_OK;
 }
 
+// The dense factor array [batch][K][N][fs] of the staged path (reference NdData order, src/nddata.c:93): allocated and
+// zeroed on first need unless RSLQR_KEEP_FACT asked for it at creation.
+static int ensure_fact(rslqr_cuda_solver* h) {
+  if (h->b.fact) return RSLQR_OK;
+  const Shape& s = h->s;
+  const size_t bytes = sizeof(double) * (size_t)h->batch * s.K * s.N * s.fs;
+  if (cudaMalloc((void**)&h->b.fact, bytes) != cudaSuccess) {
+    cudaGetLastError();
+    h->b.fact = nullptr;
+    return fail(RSLQR_E_NOMEM, "device allocation of the dense factor array failed");
+  }
+  CU(cudaMemsetAsync(h->b.fact, 0, bytes, h->stream));
+  h->factored = 0;
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_ensure_fact(rslqr_cuda_solver* h) {
+  if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
+  if (h->shard) return fail(RSLQR_E_UNSUPPORTED, "a shard keeps no factor array");
+  CU(cudaSetDevice(h->device));
+  return ensure_fact(h);
+}
+
+extern "C" int rslqr_cuda_zero_fact(rslqr_cuda_solver* h) {
+  if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
+  CU(cudaSetDevice(h->device));
+  h->factored = 0;
+  if (!h->b.fact) return RSLQR_OK;
+  const Shape& s = h->s;
+  CU(cudaMemsetAsync(h->b.fact, 0, sizeof(double) * (size_t)h->batch * s.K * s.N * s.fs, h->stream));
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_has_factorization(rslqr_cuda_solver* h) { return h ? h->factored : 0; }
+extern "C" int rslqr_cuda_invalidate_factorization(rslqr_cuda_solver* h) {
+  if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
+  h->factored = 0;
+  return RSLQR_OK;
+}
+
+// status words and flags of the problem range the next enqueue covers: cleared at the start of EVERY solve, so a
+// failure (or an exchange time-out) of one solve is not reported for the next one
+static int clear_status(rslqr_cuda_solver* h) {
+  const Shape& s = h->s;
+  if (h->r_first == 0 && h->r_count == h->batch) {
+    CU(cudaMemsetAsync(h->b.status, 0, sizeof(int) * ((size_t)h->batch * 3 * s.N + (size_t)h->batch), h->stream));
+  } else {
+    CU(cudaMemsetAsync(h->b.status + (size_t)h->r_first * 3 * s.N, 0, sizeof(int) * (size_t)h->r_count * 3 * s.N, h->stream));
+    CU(cudaMemsetAsync(h->b.flags + h->r_first, 0, sizeof(int) * (size_t)h->r_count, h->stream));
+  }
+  return RSLQR_OK;
+}
+
 extern "C" int rslqr_cuda_set_mode(rslqr_cuda_solver* h, int mode) {
   if (!h || mode < RSLQR_MODE_AUTO || mode > RSLQR_MODE_SCAN) return fail(RSLQR_E_ARG, "set_mode: bad argument");
-  if (mode == RSLQR_MODE_STAGED && !h->b.fact) return fail(RSLQR_E_UNSUPPORTED, "staged mode needs RSLQR_KEEP_FACT");
+  if (mode == RSLQR_MODE_STAGED) {
+    if (h->shard) return fail(RSLQR_E_UNSUPPORTED, "a shard has no staged mode");
+    CU(cudaSetDevice(h->device));
+    int rc = ensure_fact(h);
+    if (rc) return rc;
+  }
   if (mode == RSLQR_MODE_FUSED && !h->fused.available) {
     CU(cudaSetDevice(h->device));
     if (fused_plan(h->s, h->batch, h->g0_pref, &h->fused, g_err)) return RSLQR_E_NOMEM;
@@ -231,6 +293,9 @@ static int launch_stage(rslqr_cuda_solver* h, int stage, int level, Sel sel) {
   const int n = s.n, nn = n * n;
   if (sel.np <= 0 || sel.nitems <= 0) return RSLQR_OK;
   const long long tasks = (long long)sel.np * sel.nitems;
+  // grid.x of every stage kernel is a small multiple of `tasks` (times at most zs / 128 * 3): keep it inside 2^31 - 1
+  if (tasks * 3 > 0x7fffffffLL || tasks * (long long)s.zs * s.N / 128 > 0x7fffffffLL * 64)
+    return fail(RSLQR_E_ARG, "stage launch too large for one grid: split the batch");
   cudaStream_t st = h->stream;
   switch (stage) {
     case RSLQR_STAGE_PACK_RHS: {
@@ -257,8 +322,7 @@ static int launch_stage(rslqr_cuda_solver* h, int stage, int level, Sel sel) {
     case RSLQR_STAGE_SOLVES:
       if (n == 64 && s.m == 16 && !getenv("RSLQR_NO_MMA_STAGED")) {
         constexpr int smem = (64 * 66 + 64 * 65 + 64) * (int)sizeof(double);
-        static bool attr = false;
-        if (!attr) { CU(cudaFuncSetAttribute(solves_cols_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem)); attr = true; }
+        CU(smem_optin(solves_cols_kernel<64>, smem));
         solves_cols_kernel<64><<<(unsigned)(tasks * (sel.col < 0 ? 2 : 1)), 64, smem, st>>>(s, h->b, sel, level);
       } else if (n == 16 && s.m == 16 && !getenv("RSLQR_NO_MMA_STAGED")) {
         solves_cols_kernel<16><<<(unsigned)(tasks * (sel.col < 0 ? 2 : 1)), 16, (16 * 18 + 16 * 17 + 16) * sizeof(double), st>>>(s, h->b, sel, level);
@@ -280,11 +344,7 @@ static int launch_stage(rslqr_cuda_solver* h, int stage, int level, Sel sel) {
       if (n <= 64 && !getenv("RSLQR_NO_WARP_RHS_SOLVE")) {  // one warp per separator, no CTA barrier
         const int wpc = n > 32 ? 2 : 4;
         const size_t smem = sizeof(double) * (size_t)wpc * n * (n + 1);
-        static size_t attr_smem = 0;
-        if (smem > 48 * 1024 && smem > attr_smem) {
-          CU(cudaFuncSetAttribute(rhs_solves_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-          attr_smem = smem;
-        }
+        CU(smem_optin(rhs_solves_warp_kernel, (int)smem));
         rhs_solves_warp_kernel<<<(unsigned)((tasks + wpc - 1) / wpc), 32 * wpc, smem, st>>>(s, h->b, sel, level);
       } else
       rhs_solves_kernel<<<(unsigned)tasks, clampi(round32(n), 32, 256), sizeof(double) * (nn + n), st>>>(s, h->b, sel, level);
@@ -338,9 +398,7 @@ static Sel all_items(const rslqr_cuda_solver* h, int nitems) {
 static int staged_factor_levels(rslqr_cuda_solver* h) {
   const Shape& s = h->s;
   int rc = 0;
-  if (s.n * s.n * 2 * sizeof(double) > 48 * 1024) {
-    CU(cudaFuncSetAttribute(solves_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(s.n * s.n * 2 * sizeof(double))));
-  }
+  CU(smem_optin(solves_kernel, (int)(s.n * s.n * 2 * sizeof(double))));
   for (int level = 0; level < s.K && !rc; ++level) {
     const int leaves = 1 << (s.K - level - 1);
     rc |= timed_stage(h, 2, RSLQR_STAGE_PRODUCTS, level, all_items(h, leaves));
@@ -367,8 +425,14 @@ static int staged_rhs_levels(rslqr_cuda_solver* h) {
 
 static int solve_staged(rslqr_cuda_solver* h, int pack_rhs) {
   const Shape& s = h->s;
-  if (!h->b.fact) return fail(RSLQR_E_UNSUPPORTED, "staged mode needs RSLQR_KEEP_FACT");
-  int rc = 0;
+  int rc = ensure_fact(h);
+  if (rc) return rc;
+  // the staged kernels ACCUMULATE into the factor array (products: -F + ..., Schur: F - ...), exactly like the
+  // reference, whose contract is a zeroed `fact` before every solve (src/solve.h:28-32); the array is cleared here
+  // so that a second Initialize + Solve on the same handle cannot factorize on top of the previous factors
+  h->factored = 0;
+  CU(cudaMemsetAsync(h->b.fact + (size_t)h->r_first * s.K * s.N * s.fs, 0, sizeof(double) * (size_t)h->r_count * s.K * s.N * s.fs,
+                     h->stream));
   if (pack_rhs) rc |= timed_stage(h, 6, RSLQR_STAGE_PACK_RHS, 0, all_items(h, s.N));
   rc |= timed_stage(h, 1, RSLQR_STAGE_LEAVES, 0, all_items(h, s.N));
   if (!rc) rc = staged_factor_levels(h);
@@ -380,11 +444,12 @@ static int solve_staged(rslqr_cuda_solver* h, int pack_rhs) {
 static int staged_entry(rslqr_cuda_solver* h, const char* what) {
   if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
   if (h->shard) return fail(RSLQR_E_UNSUPPORTED, "a shard has no stored factorization");
-  if (rslqr_cuda_get_mode(h) != RSLQR_MODE_STAGED || !h->b.fact) return fail(RSLQR_E_UNSUPPORTED, what);
+  if (rslqr_cuda_get_mode(h) != RSLQR_MODE_STAGED) return fail(RSLQR_E_UNSUPPORTED, what);
   CU(cudaSetDevice(h->device));
+  int rc = ensure_fact(h);
+  if (rc) return rc;
   h->launches = 0;
-  h->spans.clear();
-  h->evused = 0;
+  if (!h->prof_keep) { h->spans.clear(); h->evused = 0; }
   return RSLQR_OK;
 }
 
@@ -393,6 +458,8 @@ extern "C" int rslqr_cuda_factor_async(rslqr_cuda_solver* h) {
   if (rc) return rc;
   const Shape& s = h->s;
   h->factored = 0;
+  rc = clear_status(h);
+  if (rc) return rc;
   CU(cudaMemsetAsync(h->b.fact + (size_t)h->r_first * s.K * s.N * s.fs, 0, sizeof(double) * (size_t)h->r_count * s.K * s.N * s.fs,
                      h->stream));
   rc = timed_stage(h, 1, RSLQR_STAGE_LEAVES, 0, all_items(h, s.N));  // (also scales whatever rhs is in soln: harmless)
@@ -423,6 +490,10 @@ extern "C" int rslqr_cuda_riccati_solve_async(rslqr_cuda_solver* h) {
   if (!h->ric_gain)
     CU(cudaMalloc(&h->ric_gain, sizeof(double) * (size_t)h->batch * s.N * RicDim<12, 4>::GSZ));
   h->launches = 0;
+  {
+    int rc = clear_status(h);
+    if (rc) return rc;
+  }
   const size_t f = (size_t)h->r_first;
   Bufs b = h->b;
   b.knots += f * s.N * s.stride; b.x0 += f * s.n; b.soln += f * s.N * s.zs; b.flags += f;
@@ -436,8 +507,15 @@ extern "C" int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs) {
   if (h->shard) return fail(RSLQR_E_UNSUPPORTED, "a shard is solved with shard_reduce / exchange / shard_finish");
   CU(cudaSetDevice(h->device));
   h->launches = 0;
-  h->spans.clear();
-  h->evused = 0;
+  if (!h->prof_keep) {  // (solve_host accumulates the spans of all its chunks)
+    h->spans.clear();
+    h->evused = 0;
+    memset(h->prof, 0, sizeof(h->prof));
+  }
+  {
+    int rc = clear_status(h);
+    if (rc) return rc;
+  }
   const int mode = rslqr_cuda_get_mode(h);
   if (mode == RSLQR_MODE_SCAN) {
     std::pair<cudaEvent_t, cudaEvent_t> kt;
@@ -520,7 +598,6 @@ extern "C" int rslqr_cuda_solve_host(rslqr_cuda_solver* h, const double* knots, 
   CU(cudaStreamWaitEvent(h->s_h2d, h->ev_join, 0));
   CU(cudaStreamWaitEvent(h->s_d2h, h->ev_join, 0));
   const size_t kper = (size_t)s.N * s.stride, zper = (size_t)s.N * s.zs;
-  const int staged = rslqr_cuda_get_mode(h) == RSLQR_MODE_STAGED;
   int launches = 0, rc = 0;
   for (int c = 0; c < nch && !rc; ++c) {
     const int first = c * chunk, cnt = (first + chunk <= count) ? chunk : count - first;
@@ -528,11 +605,10 @@ extern "C" int rslqr_cuda_solve_host(rslqr_cuda_solver* h, const double* knots, 
     CU(cudaMemcpyAsync(h->d_x0 + (size_t)first * s.n, x0 + (size_t)first * s.n, sizeof(double) * (size_t)s.n * cnt, cudaMemcpyHostToDevice, h->s_h2d));
     CU(cudaEventRecord(h->ev_up[c], h->s_h2d));
     CU(cudaStreamWaitEvent(h->stream, h->ev_up[c], 0));
-    if (staged) {  // the staged kernels accumulate into a zeroed factor array (reference contract, src/solve.h:28-32)
-      CU(cudaMemsetAsync(h->b.fact + (size_t)first * s.K * s.N * s.fs, 0, sizeof(double) * (size_t)cnt * s.K * s.N * s.fs, h->stream));
-    }
     h->r_first = first; h->r_count = cnt;
+    h->prof_keep = c > 0;  // RSLQR_PROFILE: the phase times cover all chunks, not only the last one
     rc = rslqr_cuda_solve_async(h, 1);
+    h->prof_keep = false;
     launches += h->launches;
     h->r_first = 0; h->r_count = h->batch;
     if (rc) break;
@@ -578,10 +654,14 @@ extern "C" int rslqr_cuda_solve(rslqr_cuda_solver* h, int pack_rhs) {
 
 extern "C" int rslqr_cuda_stage(rslqr_cuda_solver* h, int stage, int level, int item, int col, int problem) {
   if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
-  if (!h->b.fact) return fail(RSLQR_E_UNSUPPORTED, "stage calls need RSLQR_KEEP_FACT");
+  if (h->shard) return fail(RSLQR_E_UNSUPPORTED, "stage calls are not available on a shard");
   const Shape& s = h->s;
   if (level < 0 || level >= s.K || problem >= h->batch) return fail(RSLQR_E_ARG, "stage: level/problem out of range");
   CU(cudaSetDevice(h->device));
+  {
+    int rc = ensure_fact(h);
+    if (rc) return rc;
+  }
   const bool per_knot = stage == RSLQR_STAGE_LEAVES || stage == RSLQR_STAGE_SCHUR ||
                         stage == RSLQR_STAGE_RHS_SCHUR || stage == RSLQR_STAGE_PACK_RHS;
   const int nall = per_knot ? s.N : (1 << (s.K - level - 1));
@@ -590,8 +670,7 @@ extern "C" int rslqr_cuda_stage(rslqr_cuda_solver* h, int stage, int level, int 
   if (problem >= 0) { sel.p0 = problem; sel.np = 1; }
   if (item >= 0) { sel.item0 = item; sel.nitems = 1; }
   sel.col = col;
-  if (s.n * s.n * 2 * sizeof(double) > 48 * 1024)
-    CU(cudaFuncSetAttribute(solves_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(s.n * s.n * 2 * sizeof(double))));
+  CU(smem_optin(solves_kernel, (int)(s.n * s.n * 2 * sizeof(double))));
   int rc = launch_stage(h, stage, level, sel);
   if (rc) return rc;
   CU(cudaStreamSynchronize(h->stream));
@@ -601,7 +680,12 @@ extern "C" int rslqr_cuda_stage(rslqr_cuda_solver* h, int stage, int level, int 
 extern "C" int rslqr_cuda_schur_task(rslqr_cuda_solver* h, int index, int knot, int level, int upper_level,
                                      int calc_lambda, int use_rhs, int problem) {
   if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
-  if (!h->b.fact) return fail(RSLQR_E_UNSUPPORTED, "stage calls need RSLQR_KEEP_FACT");
+  if (h->shard) return fail(RSLQR_E_UNSUPPORTED, "stage calls are not available on a shard");
+  {
+    CU(cudaSetDevice(h->device));
+    int rc = ensure_fact(h);
+    if (rc) return rc;
+  }
   const Shape& s = h->s;
   if (level < 0 || level >= s.K || upper_level < 0 || upper_level >= s.K || knot < 0 || knot >= s.N ||
       index < 0 || index >= s.N - 1 || problem >= h->batch)
@@ -628,11 +712,25 @@ extern "C" int rslqr_cuda_download_solution(rslqr_cuda_solver* h, double* soln, 
 
 extern "C" int rslqr_cuda_download_fact(rslqr_cuda_solver* h, double* fact, int problem) {
   if (!h || !fact || problem < 0 || problem >= h->batch) return fail(RSLQR_E_ARG, "download_fact: bad argument");
-  if (!h->b.fact) return fail(RSLQR_E_UNSUPPORTED, "download_fact needs RSLQR_KEEP_FACT");
+  if (!h->b.fact) return fail(RSLQR_E_UNSUPPORTED, "download_fact: no factor array yet (staged mode, a stage call or rslqr_cuda_ensure_fact creates it)");
   CU(cudaSetDevice(h->device));
   const size_t per = (size_t)h->s.K * h->s.N * h->s.fs;
   CU(cudaMemcpyAsync(fact, h->b.fact + problem * per, sizeof(double) * per, cudaMemcpyDeviceToHost, h->stream));
   CU(cudaStreamSynchronize(h->stream));
+  return RSLQR_OK;
+}
+
+// host -> device copy of one problem's dense factor array (the stage calls of the host API treat the host mirror as
+// authoritative between calls: the reference's tests run helper routines on views of solver->fact in between)
+extern "C" int rslqr_cuda_upload_fact(rslqr_cuda_solver* h, const double* fact, int problem) {
+  if (!h || !fact || problem < 0 || problem >= h->batch) return fail(RSLQR_E_ARG, "upload_fact: bad argument");
+  if (h->shard) return fail(RSLQR_E_UNSUPPORTED, "a shard keeps no factor array");
+  CU(cudaSetDevice(h->device));
+  int rc = ensure_fact(h);
+  if (rc) return rc;
+  const size_t per = (size_t)h->s.K * h->s.N * h->s.fs;
+  h->factored = 0;
+  CU(cudaMemcpyAsync(h->b.fact + problem * per, fact, sizeof(double) * per, cudaMemcpyHostToDevice, h->stream));
   return RSLQR_OK;
 }
 
@@ -801,6 +899,10 @@ extern "C" size_t rslqr_cuda_shard_payload_doubles(rslqr_cuda_solver* h) {
 extern "C" int rslqr_cuda_shard_reduce(rslqr_cuda_solver* h, double* d_payload) {
   if (!h || !d_payload || !h->shard) return fail(RSLQR_E_ARG, "shard_reduce: bad argument");
   CU(cudaSetDevice(h->device));
+  {
+    int rc = clear_status(h);  // (a time-out or failure of the previous solve must not stick)
+    if (rc) return rc;
+  }
   if (rslqr_cuda_get_mode(h) == RSLQR_MODE_SCAN) {
     int rc = scan_shard_reduce(h->scan, h->s, h->b, 1, h->stream, d_payload, g_err);
     h->launches = h->scan.f.launches;

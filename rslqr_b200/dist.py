@@ -25,6 +25,18 @@ def allgather_payload(send, gathered, group=None):
     return gathered
 
 
+def agree_all(ok, device=None):
+    """1 only if `ok` is true on every rank (MIN all-reduce; CPU tensor over gloo, device tensor over NCCL)"""
+    import torch
+    import torch.distributed as dist
+    if not dist.is_initialized() or dist.get_world_size() == 1:
+        return int(bool(ok))
+    dev = "cpu" if dist.get_backend() == "gloo" else torch.device("cuda", device)
+    t = torch.tensor([int(bool(ok))], dtype=torch.int32, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return int(t.item())
+
+
 class LongHorizon:
     """One rank's part of a single long-horizon solve (BASELINE configs[3])."""
 
@@ -39,15 +51,20 @@ class LongHorizon:
         self.d_gat = torch.zeros(pay * world, dtype=torch.float64, device=f"cuda:{device}")
         # kernels and the collective are ordered on torch's current stream: no host synchronisation in between
         self.shard.set_stream(torch.cuda.current_stream(device).cuda_stream)
-        self.exchange, self.epoch, self.symm = "nccl", 0, None
+        self.exchange, self.epoch, self.symm, self.p2p_error = "nccl", 0, None, None
         if world > 1 and exchange in ("auto", "p2p"):
             try:
                 self._setup_p2p(device)
-                self.exchange = "p2p"
+                ok = 1
             except Exception as e:   # no symmetric memory on this box / build: keep the NCCL all-gather
-                if exchange == "p2p":
-                    raise
-                self.p2p_error = repr(e)
+                ok, self.p2p_error = 0, repr(e)
+            # the transport is a property of the JOB, not of a rank: a rank that fell back to NCCL alone would block in
+            # all_gather while the others spin on arrival flags. All ranks take p2p only if every rank could set it up.
+            ok = agree_all(ok, device)
+            if ok:
+                self.exchange = "p2p"
+            elif exchange == "p2p":
+                raise RuntimeError("peer-to-peer exchange requested but not available on every rank: %s" % self.p2p_error)
 
     def _setup_p2p(self, device):
         """One symmetric allocation per rank: [2][world][pay] gathered payload slots (double-buffered by epoch parity)
@@ -89,8 +106,19 @@ class LongHorizon:
             self.d_gat.copy_(self.d_pay)
         self.shard.finish(self.d_gat.data_ptr())
 
-    def solution(self):
+    def check(self):
+        """Fail-stop: raise if the last solve on this rank saw a failed factorization (flag 1) or an exchange whose
+        arrival flags timed out (flag 2: the cross-GPU tier then merged incomplete data and the solution is garbage)."""
         self.torch.cuda.synchronize()
+        flag = int(self.shard.flags()[0])
+        if flag:
+            from .lib import RslqrError
+            why = {1: "a separator or leaf factorization failed (pivot <= 0)",
+                   2: "the peer-to-peer exchange timed out waiting for a rank's payload"}.get(flag, "flag %d" % flag)
+            raise RslqrError("long-horizon solve failed on rank %d: %s" % (self.rank, why))
+
+    def solution(self):
+        self.check()
         return self.shard.solution()[0]
 
     def close(self):

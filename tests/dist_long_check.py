@@ -1,4 +1,5 @@
-"""Manual multi-GPU check (run under torchrun on a box with >= 2 GPUs; the round-end GPU tests have one GPU):
+"""Multi-GPU check, run under torchrun by tests/test_gpu_parity.py::test_long_horizon_split_over_real_gpus on a box with
+>= 2 GPUs (skipped on the one-GPU round-end box), or by hand:
 one long-horizon problem split over the ranks, both exchange transports, solution gathered on rank 0 and checked
 against the oracle's KKT residual and against the single-GPU solve.
 
@@ -23,7 +24,7 @@ torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 n, m, N = 12, 4, 4096
 kn, x0 = R.synth_problems(n, m, N, 2024, 0, 1)
-for ex in ("p2p", "nccl"):
+for ex in ("auto", "nccl"):      # auto = peer stores + flags when every rank could map symmetric memory, else NCCL
     lh = LongHorizon(n, m, N, rank, world, local, exchange=ex)
     lh.upload(kn[0], x0[0])
     for _ in range(5):            # several epochs: exercises the double-buffered gathered halves

@@ -149,7 +149,7 @@ REF = None
 if os.path.exists(_REF_PATH):
     import sys
     sys.path.insert(0, ROOT)
-    from rslqr_b200 import lib as _pl  # struct definitions + prototype table only
+    from rslqr_b200 import ctypes_api as _pl  # struct definitions + prototype table only (loads no library)
     REF = _pl.bind_host_api(C.CDLL(_REF_PATH), _pl.RefSolverStruct)
     REF.ndlqr_SolveRiccati = getattr(REF, "ndlqr_SolveRiccati")
 

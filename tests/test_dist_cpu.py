@@ -22,7 +22,7 @@ def test_shard_range_partitions():
 def _worker(rank, world, port, q):
     import torch
     import torch.distributed as dist
-    from rslqr_b200.dist import allgather_payload, shard_range
+    from rslqr_b200.dist import agree_all, allgather_payload, shard_range
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -35,7 +35,9 @@ def _worker(rank, world, port, q):
     # batch sharding: ranks agree on a disjoint cover
     spans = [None] * world
     dist.all_gather_object(spans, (lo, hi))
-    q.put((rank, gathered.numpy().copy(), spans))
+    # transport agreement: one rank without peer access sends every rank to the fallback
+    votes = (agree_all(True), agree_all(rank != 1), agree_all(False))
+    q.put((rank, gathered.numpy().copy(), spans, votes))
     dist.destroy_process_group()
 
 
@@ -49,7 +51,8 @@ def test_payload_allgather_gloo_world2():
     out = [q.get(timeout=120) for _ in range(2)]
     [p.join(timeout=60) for p in procs]
     assert all(p.exitcode == 0 for p in procs)
-    for rank, g, spans in out:
+    for rank, g, spans, votes in out:
+        assert votes == (1, 0, 0)
         g = g.reshape(2, 904)
         assert g[0, 0] == 100.0 and g[1, 0] == 101.0           # rank order = shard order along the horizon
         assert (g[0, 1:] == 1.0).all() and (g[1, 1:] == 2.0).all()

@@ -332,7 +332,8 @@ def test_host_api_solve_rhs_only():
     pp = LIB.ndlqr_ReadLQRProblemJSONFile(os.path.join(GOLDEN, "lqr_prob_256.json").encode())
     s = R.NdLqrSolver(6, 3, 256)
     t = R.NdLqrSolver(6, 3, 256)
-    assert LIB.ndlqr_SolveRhsOnly(s.p) == -1            # no factorization yet
+    t.c.mirror_fact = 1                                 # fresh full solves on the staged kernels (bitwise comparison)
+    assert LIB.ndlqr_SolveRhsOnly(s.p) == -1            # nothing initialized yet
     assert s.initialize(pp) == 0
     rhs0 = s.soln_array().copy()
     assert s.solve() == 0
@@ -348,8 +349,11 @@ def test_host_api_solve_rhs_only():
         t.soln_array()[:] = rhs
         assert t.solve() == 0
         assert np.array_equal(s.solution(), t.solution())
+    # the original rhs again: agrees with the first solve, which took the default (on-chip) path -- different kernels,
+    # same answer to rounding
     s.soln_array()[:] = rhs0
-    assert LIB.ndlqr_SolveRhsOnly(s.p) == 0 and np.array_equal(s.solution(), z0)
+    assert LIB.ndlqr_SolveRhsOnly(s.p) == 0
+    assert np.linalg.norm(s.solution() - z0) <= TOL * np.linalg.norm(z0)
     LIB.ndlqr_FreeLQRProblem(pp)
 
 
@@ -406,27 +410,100 @@ def test_host_api_solve_flow_and_solve_twice():
     out = np.zeros(117)
     assert LIB.ndlqr_CopySolution(s.p, out.ctypes.data_as(C.POINTER(C.c_double))) == 117
     assert np.array_equal(out, z)
+    # the default solve moves the solution only: the factor mirror is untouched until it is asked for
+    assert not s.c.fact_dirty and not s.nddata_array("fact").any()
+    assert s.sync_fact() == 0
     # fact mirror holds the reference's F{k}2* blocks
     sp = golden_json("sample_problem.json")
     f = s.nddata_array("fact")
     for k in range(8):
         L_, X, U = blocks(f[2, k], 6, 3)
         assert np.linalg.norm(X - jmat(sp[f"F{k}2x"])) < 1e-9
-    # diagonals hold the Cholesky factors sqrt(Q)
+    # diagonals hold the Cholesky factors sqrt(Q) (mirrored together with fact)
     Q0 = np.ctypeslib.as_array(s.c.diagonals[0].data, shape=(36,)).reshape(6, 6)
     assert np.allclose(np.diag(Q0), np.sqrt(golden_json("lqr_prob.json")["lqrdata"][0]["Q"]))
     assert s.c.cholfacts.contents.cholinfo[0].success == 0
     assert s.c.solve_time_ms > 0
-    prof = LIB.ndlqr_GetProfile(s.p)
-    assert prof.t_shur_ms > 0 and prof.t_leaves_ms > 0
     # solve twice: reset + initialize + solve reproduces the answer bit for bit
     s.reset()
     assert s.initialize(pp) == 0 and s.solve() == 0
     assert np.array_equal(s.solution(), z)
+    # solver->mirror_fact = 1: every solve runs the reference's phases one launch each and leaves `fact` and the
+    # per-phase profile behind (reference src/solve.c:15-25)
+    s.c.mirror_fact = 1
+    s.reset()
+    assert s.initialize(pp) == 0 and s.solve() == 0
+    assert np.linalg.norm(s.solution() - want) < 1e-6 and np.linalg.norm(s.solution() - z) / np.linalg.norm(z) < TOL
+    prof = LIB.ndlqr_GetProfile(s.p)
+    assert prof.t_shur_ms > 0 and prof.t_leaves_ms > 0
+    f2 = s.nddata_array("fact").copy()
+    assert np.array_equal(f2, f)
+    s.c.mirror_fact = 0
     # the convenience entry named by the task statement
     assert LIB.ndlqr_SolveLQRProblem(pp, s.p) == 0
     assert np.array_equal(s.solution(), z)
     LIB.ndlqr_FreeLQRProblem(pp)
+
+
+@pytest.mark.parametrize("mirror", [0, 1])
+def test_host_api_reference_solve_twice_sequences(mirror):
+    # the reference's documented re-solve flow (src/solve.h:28-32, test/nested_dissection_test.c:289-313 SolveTwice,
+    # test/sample_problem_test.c:144): ndlqr_ResetNdData(solver->fact); Initialize; Solve -- and a plain
+    # Initialize + Solve repeated without any reset. Both on the default path and on the staged path (mirror_fact = 1),
+    # whose kernels accumulate into the device factor array and therefore need it cleared between solves.
+    LIB = R.LIB
+    pp = LIB.ndlqr_ReadLQRProblemJSONFile(os.path.join(GOLDEN, "lqr_prob.json").encode())
+    want = np.array(golden_json("lqr_prob.json")["soln"]).reshape(-1)
+    s = R.NdLqrSolver(6, 3, 8)
+    s.c.mirror_fact = mirror
+    assert s.initialize(pp) == 0 and s.solve() == 0
+    z = s.solution()
+    assert np.linalg.norm(z - want) < 1e-6
+    f = s.nddata_array("fact").copy()
+    LIB.ndlqr_ResetNdData(s.c.fact)                     # reference SolveTwice
+    assert not s.nddata_array("fact").any()
+    assert s.initialize(pp) == 0 and s.solve() == 0
+    assert np.array_equal(s.solution(), z)
+    assert np.array_equal(s.nddata_array("fact"), f)
+    for _ in range(2):                                  # no reset at all
+        assert s.initialize(pp) == 0 and s.solve() == 0
+        assert np.array_equal(s.solution(), z)
+    if mirror:
+        assert f.any() and np.array_equal(s.nddata_array("fact"), f)
+    # a failing solve must not stick: break Q, solve (status raised), restore, solve again (status clear)
+    q00 = pp.contents.lqrdata[2].contents.Q[1]
+    pp.contents.lqrdata[2].contents.Q[1] = -1.0
+    assert s.initialize(pp) == 0 and s.solve() == 0
+    assert s.c.cholfacts.contents.cholinfo[2 * 2].success != 0
+    pp.contents.lqrdata[2].contents.Q[1] = q00
+    assert s.initialize(pp) == 0 and s.solve() == 0
+    assert s.c.cholfacts.contents.cholinfo[2 * 2].success == 0
+    assert np.array_equal(s.solution(), z)
+    LIB.ndlqr_FreeLQRProblem(pp)
+
+
+def test_cuda_abi_resolve_without_reset_and_sticky_status():
+    # C-ABI: every solve starts from cleared status words / flags and (staged) a zeroed factor array
+    n, m, N = 6, 3, 16
+    kn, x0 = R.synth_problems(n, m, N, 5, 0, 3)
+    bad = kn.copy()
+    bad[1, 4, 0] = -2.0
+    for mode in (R.MODE_STAGED, R.MODE_AUTO):
+        s = R.CudaSolver(n, m, N, batch=3, flags=0)          # no KEEP_FACT: the factor array appears on first need
+        s.set_mode(mode)
+        s.upload(kn, x0)
+        s.solve()
+        z = s.solution().copy()
+        s.solve()
+        assert np.array_equal(s.solution(), z), mode
+        s.upload(bad, x0)
+        s.solve()
+        assert list(s.flags()) == [0, 1, 0]
+        s.upload(kn, x0)
+        s.solve()
+        assert not s.flags().any() and not s.status(1).any()
+        assert np.array_equal(s.solution(), z), mode
+        s.close()
 
 
 def test_host_api_stage_calls():
@@ -624,3 +701,166 @@ def test_long_horizon_16384_eight_shards_kkt():
     one.close()
     for s in shards:
         s.close()
+
+
+# ---------------------------------------------------------------------------------------------
+# reference parity AT SIZE for BASELINE configs[3] and configs[4]: outputs of the unmodified reference stored by
+# tests/golden/make_golden_large.py (same spirit as test/sample_problem_test.c:150-157: solve vs stored solution)
+# ---------------------------------------------------------------------------------------------
+def _large_golden():
+    return np.load(os.path.join(GOLDEN, "ref_synth_large.npz"))
+
+
+def test_long_horizon_16384_vs_reference():
+    # configs[3]: n=12, m=4, N=16384. (a) one handle, (b) the 8-shard split (ranks emulated on one device), both against
+    # the reference's own ndlqr_Solve output: <= 1e-10 relative per variable class, KKT residual no worse than 2x its.
+    import torch
+    n, m, N, G = 12, 4, 16384, 8
+    g = _large_golden()
+    ref, ref_kkt = g["quad_n12_m4_N16384_id0_soln"], float(g["quad_n12_m4_N16384_id0_kkt"])
+    kn, x0 = R.synth_problems(n, m, N, 2024, 0, 1)
+    one = R.CudaSolver(n, m, N, batch=1, flags=0)
+    assert one.mode == R.MODE_SCAN
+    one.upload(kn, x0)
+    one.solve()
+    z1 = one.solution()[0].copy()
+    assert not one.flags().any()
+    one.close()
+    shards = [R.ShardSolver(n, m, N, r, G, device=0) for r in range(G)]
+    pay = shards[0].payload_doubles
+    d_pay = [torch.zeros(pay, dtype=torch.float64, device="cuda:0") for _ in range(G)]
+    d_gat = [torch.zeros(pay * G, dtype=torch.float64, device="cuda:0") for _ in range(G)]
+    for s in shards:
+        s.upload_shard(kn[0], x0[0])
+    for s, p in zip(shards, d_pay):
+        s.reduce(p.data_ptr())
+    R.shard_exchange(shards, [p.data_ptr() for p in d_pay], [gg.data_ptr() for gg in d_gat])
+    for s, gg in zip(shards, d_gat):
+        s.finish(gg.data_ptr())
+    z8 = np.concatenate([(s.sync(), s.solution()[0])[1] for s in shards])
+    for s in shards:
+        assert not s.flags().any()
+        s.close()
+    for what, z in (("single handle", z1), ("8 shards", z8)):
+        errs = rel_err_classes(z, ref, n, m, N)
+        assert max(errs) < TOL, (what, errs)
+        kkt = O.kkt_residual(n, m, N, kn[0], x0[0], z)
+        assert kkt <= 2 * ref_kkt + 1e-13 * np.linalg.norm(z), (what, kkt, ref_kkt)
+
+
+def test_large_state_n64_N1024_vs_reference():
+    # configs[4]: n=64, m=16, N=1024 (755 MB dense factor array per problem) against the reference's stored solution
+    n, m, N = 64, 16, 1024
+    g = _large_golden()
+    ref, ref_kkt = g["gen_n64_m16_N1024_id0_soln"], float(g["gen_n64_m16_N1024_id0_kkt"])
+    kn, x0 = R.synth_problems(n, m, N, 2024, 0, 1)
+    s = R.CudaSolver(n, m, N, batch=1, flags=0)
+    s.upload(kn, x0)
+    s.solve()
+    z = s.solution()[0].copy()
+    assert not s.flags().any()
+    s.close()
+    errs = rel_err_classes(z, ref, n, m, N)
+    assert max(errs) < TOL, errs
+    kkt = O.kkt_residual(n, m, N, kn[0], x0[0], z)
+    assert kkt <= 2 * ref_kkt + 1e-13 * np.linalg.norm(z), (kkt, ref_kkt)
+
+
+def test_default_drop_in_solve_takes_the_fast_path_at_16384():
+    # ndlqr_NewNdLqrSolver(12, 4, 16384) + Initialize + Solve: the on-chip (scan) kernels, no 617 MB factor array on
+    # either side of the bus
+    LIB = R.LIB
+    n, m, N = 12, 4, 16384
+    pp = LIB.rslqr_synth_problem(n, m, N, 2024, 0)
+    g = _large_golden()
+    ref = g["quad_n12_m4_N16384_id0_soln"]
+    s = R.NdLqrSolver(n, m, N)
+    assert s.initialize(pp) == 0 and s.solve() == 0
+    assert LIB.rslqr_cuda_get_mode(s.c.device) == R.MODE_SCAN
+    assert not s.c.pinned_fact and not s.c.fact_dirty
+    ptrs = [C.c_void_p() for _ in range(4)]
+    LIB.rslqr_cuda_device_pointers(s.c.device, *[C.byref(p) for p in ptrs])
+    assert not ptrs[3].value                                  # no device factor array was ever allocated
+    z = np.zeros(N * 28)
+    z[:s.c.nvars] = s.solution()
+    assert max(rel_err_classes(z, ref, n, m, N)) < TOL
+    for _ in range(3):
+        assert s.initialize(pp) == 0 and s.solve() == 0
+    assert s.c.solve_time_ms < 5.0                            # (0.2-0.3 ms on a B200; the staged path takes ~40 ms)
+    s.close()
+    LIB.ndlqr_FreeLQRProblem(pp)
+
+
+# ---------------------------------------------------------------------------------------------
+# more than one device (skipped on a one-GPU box; run with `gpurun --gpus 2`)
+# ---------------------------------------------------------------------------------------------
+def _ndev():
+    return R.LIB.rslqr_cuda_device_count()
+
+
+@pytest.mark.skipif(_ndev() < 2, reason="needs two GPUs")
+def test_two_devices_in_one_process():
+    # the > 48 KB shared-memory opt-in is per device (cudaFuncSetAttribute): handles on devices 0 and 1 of ONE process
+    # must both launch the scan / staged kernels
+    LIB = R.LIB
+    n, m, N, B = 12, 4, 64, 7
+    kn, x0 = R.synth_problems(n, m, N, 33, 0, B)
+    want = [O.port_solve(n, m, N, kn[p], x0[p])[0] for p in range(B)]
+    hs = [R.CudaSolver(n, m, N, batch=B, device=d, flags=0) for d in (0, 1)]
+    for mode in (R.MODE_SCAN, R.MODE_FUSED, R.MODE_STAGED):
+        for h in hs:
+            h.set_mode(mode)
+            h.upload(kn, x0)
+            h.solve_async(True)
+        for d, h in enumerate(hs):
+            h.sync()
+            assert not h.flags().any()
+            z = h.solution()
+            for p in range(B):
+                assert max(rel_err_classes(z[p], want[p], n, m, N)) < TOL, (mode, d, p)
+    for h in hs:
+        h.riccati()
+        h.close()
+    # n=64 staged kernels with > 48 KB of dynamic shared memory on the second device
+    kn2, x2 = R.synth_problems(64, 16, 16, 3, 0, 1)
+    w2, _ = O.port_solve(64, 16, 16, kn2[0], x2[0])
+    for d in (1, 0):
+        h = R.CudaSolver(64, 16, 16, batch=1, device=d, flags=0)
+        h.upload(kn2, x2)
+        h.solve()
+        assert max(rel_err_classes(h.solution()[0], w2, 64, 16, 16)) < TOL
+        h.close()
+    # the batch host API on device 1
+    LIB.ndlqr_NewBatchSolver.restype = C.c_void_p
+    LIB.ndlqr_NewBatchSolver.argtypes = [C.c_int] * 5
+    for fn in ("ndlqr_FreeBatchSolver", "ndlqr_BatchSolve", "ndlqr_BatchGetNumVars"):
+        getattr(LIB, fn).argtypes = [C.c_void_p]
+    LIB.ndlqr_BatchInitialize.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+    LIB.ndlqr_BatchCopySolution.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+    probs = [LIB.rslqr_synth_problem(n, m, N, 33, i) for i in range(B)]
+    arr = (C.c_void_p * B)(*[C.cast(p, C.c_void_p) for p in probs])
+    bs = LIB.ndlqr_NewBatchSolver(n, m, N, B, 1)
+    assert bs and LIB.ndlqr_BatchInitialize(bs, arr, B) == 0 and LIB.ndlqr_BatchSolve(bs) == 0
+    nv = LIB.ndlqr_BatchGetNumVars(bs)
+    for p in range(B):
+        z = np.zeros(nv)
+        assert LIB.ndlqr_BatchCopySolution(bs, p, z.ctypes.data_as(C.c_void_p)) == nv
+        assert np.linalg.norm(z - want[p][:nv]) / np.linalg.norm(want[p]) < TOL
+    LIB.ndlqr_FreeBatchSolver(bs)
+    for p in probs:
+        LIB.ndlqr_FreeLQRProblem(p)
+
+
+@pytest.mark.skipif(_ndev() < 2, reason="needs two GPUs")
+def test_long_horizon_split_over_real_gpus():
+    # SURVEY 8e row 2 on real devices: one rank per GPU under torchrun, both transports (peer stores + flags, NCCL),
+    # KKT residual and agreement with the one-GPU solve (tests/dist_long_check.py asserts them on rank 0)
+    import subprocess
+    import sys
+    world = 2 if _ndev() < 4 else (4 if _ndev() < 8 else 8)
+    here = os.path.dirname(os.path.abspath(__file__))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+           "--master-port", "29731", os.path.join(here, "dist_long_check.py")]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-2000:])
+    assert "exchange=p2p" in r.stdout or "exchange=nccl" in r.stdout
