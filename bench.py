@@ -72,11 +72,13 @@ def scan_leaf_flops_per_subtree(n, m):
     return 2.0 * (2 * raw + gen)
 
 
-def scan_leaf_bytes_per_subtree(n, m):
-    """Algorithmic HBM bytes of scan_leaf_kernel per 4-knot subtree: 4 flat knot blocks read; one boundary entry and
-    three separator records [f_L | f_R | zs] written."""
+def scan_leaf_bytes_per_subtree(n, m, dual=False):
+    """Algorithmic HBM bytes of the leaf kernel per 4-knot subtree: 4 flat knot blocks read; one entry and three
+    separator records [f_L | f_R | zs] written. The entry is the (2n+m)-row boundary entry of kernels_scan.cuh, or
+    (dual) the Schur-complement element of kernels_dual.cuh: 3 blocks of np x (np+2) + 2 np, np = n rounded up to 4."""
     stride = 2 * n + 2 * m + 1 + n * n + n * m + n
-    ent = (2 * (2 * n + m) * n + (2 * n + m) + n + 1) & ~1
+    np_ = (n + 3) & ~3
+    ent = 3 * np_ * (np_ + 2) + 2 * np_ if dual else (2 * (2 * n + m) * n + (2 * n + m) + n + 1) & ~1
     return 8 * (4 * stride + ent + 3 * (2 * n + 1) * n)
 
 
@@ -354,7 +356,8 @@ def run_reference(args, rank, world):
 def run_ours(args, rank, world, local_rank):
     import rslqr_b200 as R
     from rslqr_b200.lib import pinned_array
-    n, m, N, B = N_STATES, N_INPUTS, HORIZON, args.batch
+    n, m, N, B = args.n, args.m, HORIZON, args.batch
+    dual = (n, m) != (12, 4) or bool(int(os.environ.get("RSLQR_DUAL", "0") or 0))
     dist = None
     cpu_binding = bind_to_gpu_cpus(local_rank) if world > 1 and not os.environ.get("RSLQR_BENCH_NO_BIND") else "not bound (one rank)"
     if world > 1:
@@ -449,14 +452,15 @@ def run_ours(args, rank, world, local_rank):
         # dominant kernel of the scan path: scan_leaf_kernel (levels 0 and 1 = 3/4 of all separators), one launch per
         # step, timed with CUDA events on the launching stream by the C-ABI (rslqr_cuda_kernel_timing)
         nsub = B * (N // 4)
-        by_sub = scan_leaf_bytes_per_subtree(n, m)
+        by_sub = scan_leaf_bytes_per_subtree(n, m, dual)
         fl_sub = scan_leaf_flops_per_subtree(n, m)
         k_avg_ms = k_ms if k_n else ms_per_step
         ach = nsub * by_sub / (k_avg_ms * 1e-3) / 1e9
         fp64 = fp64_peak()
-        roof = {"kernel": f"scan_leaf_kernel<{n},{m}> (one warp per 4-knot subtree: leaf factors + levels 0..1 on boundary entries)",
+        roof = {"kernel": (f"dual_leaf_kernel<{n},{m}> (one warp per 4-knot subtree: leaf elements + levels 0..1 in dual form)" if dual else
+                           f"scan_leaf_kernel<{n},{m}> (one warp per 4-knot subtree: leaf factors + levels 0..1 on boundary entries)"),
                 "bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ach / pk["hbm_gbs"],
-                "traffic": SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM * B if SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM and (n, m, N) == (12, 4, 256) else None,
+                "traffic": SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM * B if SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM and (n, m, N) == (12, 4, 256) and not dual else None,
                 "peak_kind": pk_kind, "algorithmic_bytes_per_launch": nsub * by_sub, "bytes_per_subtree": by_sub,
                 "avg_launch_ms": k_avg_ms, "kernel_launches_timed": k_n, "kernel_share_of_step": k_avg_ms / ms_per_step,
                 "binding_unit": "LSU data pipe (shared-memory + shuffle wavefronts) at 75 % of peak and dependent-chain latency at 12 warps/SM; "
@@ -486,10 +490,13 @@ def run_ours(args, rank, world, local_rank):
                 "reference_count_tflops_whole_step": flop_model(n, m, N) * B / (ms_per_step * 1e-3) / 1e12,
                 "note": "achieved = FLOPs tier0 executes (DESIGN.md section 5) / its CUDA-event time; "
                         "reference_count = SURVEY 8d figure (32.2 MFLOP/solve as the reference executes it) over the whole step"}
-    line = {"metric": METRIC, "value": value, "unit": "solves/s", "n_gpus": world, "steps": args.steps,
+    metric = METRIC if (n, m) == (12, 4) else f"LQR solves/sec (n={n},m={m},N={N} batched)"
+    workload = WORKLOAD if (n, m) == (12, 4) else f"batched synthetic LQR n={n} m={m} N={N} (shape sweep, not a BASELINE config)"
+    line = {"metric": metric, "value": value, "unit": "solves/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic", "value_kind": VALUE_KIND,
-            "config": {"workload": WORKLOAD, "batch_per_gpu": B, "global_batch": B * world, "seed": SEED,
+            "config": {"workload": workload, "batch_per_gpu": B, "global_batch": B * world, "seed": SEED,
+                       "entry_form": "dual (Schur-complement elements)" if dual and s.mode == R.MODE_SCAN else "boundary rows",
                        "mode": {R.MODE_STAGED: "staged", R.MODE_FUSED: "fused (tiered)", R.MODE_SCAN: "scan"}[s.mode], "parallelism": f"batch-shard x{world}, no collective",
                        "l2": "inputs (%.2f GB/GPU) larger than L2; no explicit flush" % (B * N * st * 8 / 1e9),
                        "host_cpu_binding": cpu_binding},
@@ -511,9 +518,18 @@ def run_ours(args, rank, world, local_rank):
             line["riccati_gpu"] = gpu_riccati_comparison(R, s, B)
         except Exception as e:  # a comparison figure must never take the bench line down
             line["riccati_gpu"] = {"unavailable": repr(e)}
+    s.close()
+    if dist is not None and (n, m) == (12, 4) and not os.environ.get("RSLQR_BENCH_NO_LONG"):
+        # SURVEY 8e row 2 on the same ranks (after every timed region of the batch workload)
+        try:
+            rec = long_horizon_record(R, dist, rank, world, local_rank)
+            if rank == 0:
+                line["long_horizon"] = rec
+        except Exception as e:  # never take the headline line down; all ranks reach this point together or not at all
+            if rank == 0:
+                line["long_horizon"] = {"unavailable": repr(e)}
     if rank == 0:
         print(json.dumps(line), flush=True)
-    s.close()
     if dist is not None:
         dist.destroy_process_group()
 
@@ -853,6 +869,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=4096)
+    ap.add_argument("--n", type=int, default=N_STATES, help="states (batch workload; default = the BASELINE shape)")
+    ap.add_argument("--m", type=int, default=N_INPUTS, help="inputs (batch workload)")
     ap.add_argument("--mode", default="auto", choices=["auto", "staged", "fused", "scan"])
     ap.add_argument("--workload", default="batch", choices=["batch", "long", "large", "single"],
                     help="batch = BASELINE configs[2] (default, the headline metric); long = configs[3] single long horizon")

@@ -1,0 +1,451 @@
+// kernels_dual.cuh -- the scan path in DUAL form, for any (n, m) with n <= 16, m <= 16.
+//
+// Eliminating x_k, u_k at the leaves (ndlqr_SolveLeaf, reference src/nested_dissection.c:10-105; Q_k, R_k are
+// diagonal) leaves a block-tridiagonal SPD system in the multipliers alone:
+//     M lambda = rho,   M(k+1,k+1) = A_k Q_k^-1 A_k^T + B_k R_k^-1 B_k^T + Q_{k+1}^-1,   M(k+1,k+2) = -Q_{k+1}^-1 A_{k+1}^T
+// whose diagonal blocks are exactly the separator matrices S the reference factors (ndlqr_FactorInnerProduct at the
+// leaf level, src/nested_dissection.c:114-134), and the reference's nested dissection is block cyclic reduction on it.
+// A subtree [a,b] is carried as its Schur complement onto the two multipliers bounding it (lambda_a, lambda_{b+1}):
+//     element matrix [[Saa, Sab], [Sab^T, Sbb]] (n x n blocks),  element rhs [sa; sb]
+// instead of as the (2n+m)-row boundary entry of kernels_scan.cuh. Merging [a,i] and [i+1,b] over lambda_{i+1}:
+//     S = SbbL + SaaR,  S_L = SabL^T,  S_R = SabR,  s = sbL + saR       (the reference's S, S_L, S_R, s)
+//     [f_L f_R zs] = S^-1 [S_L S_R s]                                    (Cholesky + ndlqr_SolveCholeskyFactor)
+//     Saa' = SaaL - S_L^T f_L,  Sab' = -S_L^T f_R,  Sbb' = SbbR - S_R^T f_R,  sa' = saL - S_L^T zs,  sb' = sbR - S_R^T zs
+// Same separators, same S, same records [f_L | f_R | zs] as the other paths (and as the reference up to rounding);
+// what differs is that the product with [A_b | B_b] that every later inner product applies to the boundary rows
+// X(b), U(b) is applied once, at the leaves, so a merge above the leaves is n x n blocks only: no input rows, no
+// P1 product, and m only appears in the leaf kernel and in the down pass. tools/dual_prototype.py is the numpy
+// statement of the same recurrences, checked against the oracle.
+//
+// Entry of a subtree, ORIENTED by the side it will be merged from (left child: L-type, right child: R-type):
+//     [ Kp | Cp | Sp | ks | ss ]     Kp, Cp, Sp: NP x LD row-major (NP = n rounded up to a multiple of 4, LD = NP + 2)
+//     L-type: Kp = Saa, Cp = Sab,   Sp = Sbb, ks = sa, ss = sb      (the parent's S_L columns are the rows of Cp)
+//     R-type: Kp = Sbb, Cp = Sab^T, Sp = Saa, ks = sb, ss = sa      (the parent's S_R columns are the rows of Cp)
+// so that a merge reads S = Sp(L) + Sp(R), the right-hand sides as ROWS of Cp(L), Cp(R) and s = ss(L) + ss(R), and
+// writes  [Cp(L); Cp(R)] [f_L f_R zs]  subtracted from the keep parts. Padded rows/columns (n not a multiple of 4)
+// are zero except for 0.5 on the diagonal of Sp, which makes the padded part of S the identity.
+#pragma once
+#include "kernels_scan.cuh"
+
+namespace rslqr {
+
+template <int NS>
+struct DualDim {
+  static constexpr int NP = (NS + 3) & ~3;          // padded block size (multiple of 4: DMMA k-steps, 16-byte rows)
+  static constexpr int LD = NP + 2;                 // row stride of a block (rows 16-byte aligned, bank-staggered)
+  static constexpr int BLK = NP * LD;
+  static constexpr int OK = 0, OC = BLK, OS = 2 * BLK, OKS = 3 * BLK, OSS = 3 * BLK + NP;
+  static constexpr int ENT = 3 * BLK + 2 * NP;      // even -> entries stay 16-byte aligned
+  static constexpr int WSZ = (2 * NS + 1) * NS;     // separator record [f_L | f_R | zs], column-major ld NS
+  static constexpr int WP = (2 * NP + 1) * NP;      // the same in shared memory, ld NP
+  static constexpr int LR = NP * (NP + 2);          // factor scratch of spine_core2<NP>
+};
+
+inline size_t dual_ent_doubles(int n) { const int np = (n + 3) & ~3; return (size_t)3 * np * (np + 2) + 2 * np; }
+
+// ---------------------------------------------------------------------------------------------------------
+// One merge, one warp. EL: L-type entry of the left subtree, ER: R-type entry of the right one (shared memory).
+// Eout: the merged entry, R-type if out_right else L-type; may be EL itself (rows are consumed tile by tile before
+// they are overwritten) or a separate buffer, or nullptr (root: only the record is wanted).
+// W: [f_L | f_R | zs] column-major ld NP on return (WP doubles); Lr: factor scratch (LR doubles).
+// Returns non-zero (warp-uniform) when a pivot is <= 0 (the reference's Cholesky fails, src/linalg_custom.c:88).
+// ---------------------------------------------------------------------------------------------------------
+template <int NS>
+__device__ __forceinline__ int dual_merge(const double* EL, const double* ER, double* Eout, bool out_right, double* W,
+                                          double* Lr) {
+  using D = DualDim<NS>;
+  constexpr int NP = D::NP, LD = D::LD;
+  static_assert(2 * NP <= 32, "one warp per separator");
+  const int lane = threadIdx.x & 31, q = lane & 3, rr = lane >> 2;
+  int bad;
+  {
+    // lanes [0,NP): row c of S = Sp(L) + Sp(R) (symmetric: row = column); lanes [NP,2NP): row c of Cp(L) (= column c of
+    // S_L) and of Cp(R) (= column c of S_R); s rides in acc2 of lane 0
+    const bool isS = lane < NP;
+    const int c = isS ? lane : (lane < 2 * NP ? lane - NP : 0);
+    const double* pa = EL + (isS ? D::OS : D::OC) + c * LD;
+    const double* pb = ER + (isS ? D::OS : D::OC) + c * LD;
+    double acc[NP], acc2[NP];
+#pragma unroll
+    for (int r = 0; r < NP; r += 2) {
+      const double2 a = *reinterpret_cast<const double2*>(pa + r);
+      const double2 b = *reinterpret_cast<const double2*>(pb + r);
+      const double2 sl = *reinterpret_cast<const double2*>(EL + D::OSS + r);
+      const double2 sr = *reinterpret_cast<const double2*>(ER + D::OSS + r);
+      acc[r] = isS ? a.x + b.x : a.x;
+      acc[r + 1] = isS ? a.y + b.y : a.y;
+      acc2[r] = isS ? (lane == 0 ? sl.x + sr.x : 0.0) : b.x;
+      acc2[r + 1] = isS ? (lane == 0 ? sl.y + sr.y : 0.0) : b.y;
+    }
+    __syncwarp();  // (Lr / W may live where other lanes were still reading)
+    bad = spine_core2<NP, true>(acc, acc2, Lr, W);
+  }
+  if (!Eout) return bad;
+  // ---- [Cp(L); Cp(R)] (2NP x NP) times [f_L f_R zs] (NP x 2NP+1) on the fp64 tensor cores, subtracted from the keep
+  //      parts: rows < NP come from the left entry, rows >= NP from the right one ----
+  constexpr int MT = 2 * NP / 8, NT = 2 * NP / 8, KS = NP / 4;
+  double bneg[KS][NT], zq[KS];
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) bneg[ks][nt] = -W[(8 * nt + rr) * NP + 4 * ks + q];
+    zq[ks] = W[2 * NP * NP + 4 * ks + q];
+  }
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt) {
+    const int rho = 8 * mt + rr;
+    const bool isL = rho < NP;
+    const int r = isL ? rho : rho - NP;
+    const double* X = isL ? EL : ER;
+    double a[KS];
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) a[ks] = X[D::OC + r * LD + 4 * ks + q];
+    double c[NT][2];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      const int g = 8 * nt + 2 * q;                    // columns g, g+1: both in the same half (NP is even)
+      const bool colL = g < NP;
+      if (colL == isL) {                               // aa' (left rows, left columns) or bb': keep part
+        const double2 v = *reinterpret_cast<const double2*>(X + D::OK + r * LD + (colL ? g : g - NP));
+        c[nt][0] = v.x; c[nt][1] = v.y;
+      } else { c[nt][0] = 0.0; c[nt][1] = 0.0; }
+    }
+    const double z0 = X[D::OKS + r];
+    __syncwarp();  // every lane has read this tile's rows: they may be overwritten now (Eout == EL)
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks)
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) dmma884(c[nt][0], c[nt][1], a[ks], bneg[ks][nt]);
+    double part = 0.0;
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) part = fma(a[ks], zq[ks], part);
+    part += __shfl_xor_sync(0xffffffffu, part, 1);
+    part += __shfl_xor_sync(0xffffffffu, part, 2);
+    // destinations: the side that matches the output's orientation keeps [Kp | Cp | ks], the other one gives Sp, ss
+    const bool own = isL != out_right;                 // L rows of an L-type output, R rows of an R-type output
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      const int g = 8 * nt + 2 * q;
+      const bool colL = g < NP;
+      const bool diag = colL == isL;                   // aa' / bb' (else ab' / ba')
+      const int gc = colL ? g : g - NP;
+      if (own) {
+        *reinterpret_cast<double2*>(Eout + (diag ? D::OK : D::OC) + r * LD + gc) = make_double2(c[nt][0], c[nt][1]);
+      } else if (diag) {
+        double v0 = c[nt][0], v1 = c[nt][1];
+        if constexpr (NP > NS) {  // padded rows of Sp keep 0.5 on the diagonal (the next S gets the identity there)
+          if (r >= NS) { v0 = gc == r ? 0.5 : 0.0; v1 = gc + 1 == r ? 0.5 : 0.0; }
+        }
+        *reinterpret_cast<double2*>(Eout + D::OS + r * LD + gc) = make_double2(v0, v1);
+      }
+    }
+    if (q == 0) Eout[(own ? D::OKS : D::OSS) + r] = z0 - part;
+    __syncwarp();
+  }
+  return bad;
+}
+
+// record [f_L | f_R | zs]: shared memory (ld NP) -> global (ld NS, the layout topdown / down read)
+template <int NS>
+__device__ __forceinline__ void dual_store_record(double* rec, const double* W) {
+  using D = DualDim<NS>;
+  constexpr int NP = D::NP;
+  const int lane = threadIdx.x & 31;
+  for (int e = lane; e < D::WSZ; e += 32) {
+    const int col = e / NS, row = e - col * NS;
+    const int wc = col < NS ? col : (col < 2 * NS ? NP + col - NS : 2 * NP);
+    rec[e] = W[wc * NP + row];
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Leaf elements of two neighbouring knots at once, straight from their transformed blocks (leaf_transform):
+// lanes [0,NS) build the L-type element of knot kL into EL, lanes [NS,2NS) the R-type element of knot kR into ER.
+//   element of knot k:  Saa = Q^-1,  Sab = -Q^-1 A^T,  Sbb = A Q^-1 A^T + B R^-1 B^T,
+//                       sa = -z_x - z_lambda,  sb = A z_x + B z_u          (z: the leaf-solved rhs)
+//   knot 0 (x_0 is fixed, lambda_0 is no unknown of the dual system): Q^-1 -> 0 in Saa, Sab, Sbb
+//   last knot of the horizon: only Saa, sa (its R, A, B, d are ignored)
+// One row per lane; all stores are contiguous rows.
+// ---------------------------------------------------------------------------------------------------------
+template <int NS, int NI>
+__device__ __forceinline__ void dual_leaf_pair(const double* BL, const double* zlL, const double* BR, const double* zlR,
+                                               bool first0, bool lastR, double* EL, double* ER) {
+  using D = DualDim<NS>;
+  using RD = RawDim<NS, NI>;
+  constexpr int NP = D::NP, LD = D::LD, XU = NS + NI;
+  const int lane = threadIdx.x & 31;
+  const bool right = lane >= NS;
+  const int c = right ? lane - NS : lane;
+  const bool act = lane < 2 * NS;
+  const double* B = right ? BR : BL;
+  const double* zl = right ? zlR : zlL;
+  double* E = right ? ER : EL;
+  const double* AB = B + RD::OA;
+  const bool noQ = !right && first0;     // knot 0
+  const bool dead = right && lastR;      // last knot: no b side
+  const int cs = act ? c : 0;
+  // w[l] = AB(c, l) * D(l): row c of [A | B] scaled by the leaf diagonals
+  double w[XU];
+  double sb = 0.0;
+#pragma unroll
+  for (int l = 0; l < XU; ++l) {
+    const double d = (l < NS && noQ) ? 0.0 : B[l];
+    const double abv = AB[cs + NS * l];
+    w[l] = dead ? 0.0 : abv * d;
+    sb = fma(dead ? 0.0 : abv, B[RD::OZ + l], sb);
+  }
+  double g[NP];  // row c of Sbb = [A | B] D [A | B]^T
+#pragma unroll
+  for (int r = 0; r < NP; ++r) g[r] = 0.0;
+#pragma unroll
+  for (int l = 0; l < XU; ++l) {
+#pragma unroll
+    for (int r = 0; r < NS; ++r) g[r] = fma(w[l], AB[r + NS * l], g[r]);
+  }
+  const double dq = noQ ? 0.0 : B[cs];                 // 1 / Q(c)
+  const double sa = -B[RD::OZ + cs] - zl[cs];
+  if (act) {
+    double* kp = E + D::OK + c * LD;
+    double* cp = E + D::OC + c * LD;
+    double* sp = E + D::OS + c * LD;
+    // L-type: Kp = Saa (diagonal), Cp = Sab row c = -A(:, c)^T / Q(c), Sp = Sbb;  R-type: Kp = Sbb,
+    // Cp = Sab^T row c = -A(c, :) / Q(:), Sp = Saa
+#pragma unroll
+    for (int r = 0; r < NP; r += 2) {
+      double cx = 0.0, cy = 0.0;
+      if (r < NS) cx = right ? (dead ? 0.0 : -AB[c + NS * r] * B[r]) : -AB[r + NS * c] * dq;
+      if (r + 1 < NS) cy = right ? (dead ? 0.0 : -AB[c + NS * (r + 1)] * B[r + 1]) : -AB[r + 1 + NS * c] * dq;
+      const double dx = r == c ? dq : 0.0, dy = r + 1 == c ? dq : 0.0;
+      *reinterpret_cast<double2*>(cp + r) = make_double2(cx, cy);
+      *reinterpret_cast<double2*>(kp + r) = right ? make_double2(g[r], g[r + 1]) : make_double2(dx, dy);
+      *reinterpret_cast<double2*>(sp + r) = right ? make_double2(dx, dy) : make_double2(g[r], g[r + 1]);
+    }
+    E[D::OKS + c] = right ? sb : sa;
+    E[D::OSS + c] = right ? sa : sb;
+  }
+  // padding rows NS..NP-1 of both elements: zero, 0.5 on the diagonal of Sp (S of the merge gets the identity there)
+  if constexpr (NP > NS) {
+    for (int it = lane; it < 2 * (NP - NS); it += 32) {
+      double* Ep = it < NP - NS ? EL : ER;
+      const int r = NS + (it < NP - NS ? it : it - (NP - NS));
+      for (int k = 0; k < NP; ++k) {
+        Ep[D::OK + r * LD + k] = 0.0;
+        Ep[D::OC + r * LD + k] = 0.0;
+        Ep[D::OS + r * LD + k] = k == r ? 0.5 : 0.0;
+      }
+      Ep[D::OKS + r] = 0.0;
+      Ep[D::OSS + r] = 0.0;
+    }
+  }
+  __syncwarp();
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Leaf kernel: one warp = 4 consecutive knots (a subtree of the two lowest levels). One TMA bulk copy brings the flat
+// knot blocks in, leaf_transform rewrites them in place (1/Q, 1/R, leaf-solved rhs), then
+//   knots (0,1) -> merge -> X (L-type),  knots (2,3) -> merge -> Y (R-type),  X + Y -> the subtree's entry
+// Output per subtree: three separator records (slots 0, 1, 2 = separators after local knots 0, 1, 2) and the entry,
+// L-type for an even subtree index, R-type for an odd one.
+// per warp: [NSE | 4 knot blocks | X | Y | Z | W | Lr]
+// ---------------------------------------------------------------------------------------------------------
+constexpr int DUAL_WPC = 4;
+
+template <int NS, int NI>
+__host__ __device__ constexpr int dual_leaf_warp_doubles() {
+  using D = DualDim<NS>;
+  return ((NS + 1) & ~1) + ((SCAN_LEAF * RawDim<NS, NI>::STRIDE + 1) & ~1) + 3 * D::ENT + ((D::WP + 1) & ~1) + D::LR;
+}
+
+template <int NS, int NI>
+__global__ void __launch_bounds__(32 * DUAL_WPC) dual_leaf_kernel(Shape s, Bufs b, double* ent0, double* sep_in, int pack_rhs,
+                                                                   int M0, long long nsub) {
+  using D = DualDim<NS>;
+  using RD = RawDim<NS, NI>;
+  constexpr int NSE = (NS + 1) & ~1, RAW = (SCAN_LEAF * RD::STRIDE + 1) & ~1;
+  constexpr int RAWB = SCAN_LEAF * RD::STRIDE * (int)sizeof(double);
+  static_assert(RAWB % 16 == 0 && D::ENT % 2 == 0 && D::LR % 2 == 0, "TMA / 128-bit alignment");
+  extern __shared__ __align__(16) double smf[];
+  __shared__ __align__(8) unsigned long long mbar[DUAL_WPC];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long sub = (long long)blockIdx.x * DUAL_WPC + warp;
+  if (sub >= nsub) return;
+  double* R0 = smf + warp * dual_leaf_warp_doubles<NS, NI>();
+  double* R = R0 + (NSE - NS);            // leaf_transform's region: R[0..NS) = z_lambda of block 0, blocks at R + NS
+  double* X = R0 + NSE + RAW;
+  double* Y = X + D::ENT;
+  double* Z = Y + D::ENT;
+  double* W = Z + D::ENT;
+  double* Lr = W + ((D::WP + 1) & ~1);
+  const int prob = (int)(sub / M0), grp = (int)(sub - (long long)prob * M0);
+  const int k0 = grp * SCAN_LEAF;
+  const int N = s.N;
+  if (lane == 0) {
+    mbar_init(&mbar[warp], 1);
+    fence_mbar_init();
+    mbar_expect_tx(&mbar[warp], RAWB);
+    bulk_g2s(R + NS, knot_ptr(s, b, prob, k0), RAWB, &mbar[warp]);
+  }
+  __syncwarp();
+  const double zl0 = leaf_zl0<NS, NI>(s, b, prob, k0, pack_rhs);
+  mbar_wait(&mbar[warp], 0);
+  leaf_transform<NS, NI, SCAN_LEAF>(s, b, prob, k0, pack_rhs, R, zl0);
+  double* rec = sep_in + ((size_t)prob * M0 + grp) * 3 * D::WSZ;
+  auto blk = [&](int j) { return R + NS + j * RD::STRIDE; };
+  auto zlam = [&](int j) { return R + j * RD::STRIDE; };
+  int bad;
+  // knots (0,1): separator after local knot 0
+  dual_leaf_pair<NS, NI>(blk(0), zlam(0), blk(1), zlam(1), s.kofs + k0 == 0, s.kofs + k0 + 1 == s.Ng - 1, X, Z);
+  bad = dual_merge<NS>(X, Z, X, false, W, Lr);
+  dual_store_record<NS>(rec, W);
+  if (bad && lane == 0) { b.status[(size_t)prob * 3 * N + rs_slot_S(k0 >> 1, 0, N)] = -1; b.flags[prob] = 1; }
+  __syncwarp();
+  // knots (2,3): separator after local knot 2
+  dual_leaf_pair<NS, NI>(blk(2), zlam(2), blk(3), zlam(3), false, s.kofs + k0 + 3 == s.Ng - 1, Y, Z);
+  bad = dual_merge<NS>(Y, Z, Y, true, W, Lr);
+  dual_store_record<NS>(rec + 2 * D::WSZ, W);
+  if (bad && lane == 0) { b.status[(size_t)prob * 3 * N + rs_slot_S((k0 >> 1) + 1, 0, N)] = -1; b.flags[prob] = 1; }
+  __syncwarp();
+  // level 1: separator after local knot 1
+  bad = dual_merge<NS>(X, Y, M0 > 1 ? X : nullptr, (grp & 1) != 0, W, Lr);
+  dual_store_record<NS>(rec + D::WSZ, W);
+  if (bad && lane == 0) { b.status[(size_t)prob * 3 * N + rs_slot_S(k0 >> 2, 1, N)] = -1; b.flags[prob] = 1; }
+  if (M0 > 1) {
+    fence_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+      bulk_s2g(ent0 + ((size_t)prob * M0 + grp) * D::ENT, X, D::ENT * (int)sizeof(double));
+      bulk_commit();
+      bulk_wait_read0();  // shared memory must stay valid until the copy engine has read it
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Tier kernel: one CTA = (problem, `ecount` consecutive entries), log2(ecount) more levels, one warp per merge, merged
+// in place. Entry e of a tier is L-type for even e, R-type for odd e. Records go to `sep` (slot = index of the 4-knot
+// subtree that starts right after the separator), the CTA's merged entry to `out`.
+// ---------------------------------------------------------------------------------------------------------
+struct DualTierArgs {
+  const double* in;   // [batch][Min][ENT]
+  double* out;        // [batch][Min / ecount][ENT] or nullptr (last tier)
+  double* sep;        // [batch][M0][WSZ]
+  int Min, ecount, M0;
+  int span4;          // 4-knot subtrees per input entry (record slot of the separator after entry e: (e + 1) * span4)
+};
+
+template <int NS>
+__host__ __device__ constexpr int dual_tier_warp_scratch() { return ((DualDim<NS>::WP + 1) & ~1) + DualDim<NS>::LR; }
+
+template <int NS>
+__global__ void __launch_bounds__(128) dual_tier_kernel(Shape s, Bufs b, DualTierArgs a) {
+  using D = DualDim<NS>;
+  extern __shared__ __align__(16) double smf[];
+  __shared__ __align__(8) unsigned long long mbar;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int ecount = a.ecount, ncta = a.Min / ecount;
+  const int prob = blockIdx.x / ncta, sg = blockIdx.x % ncta;
+  double* ents = smf;
+  double* scr = ents + ecount * D::ENT + warp * dual_tier_warp_scratch<NS>();
+  double* W = scr;
+  double* Lr = scr + ((D::WP + 1) & ~1);
+  const double* in = a.in + ((size_t)prob * a.Min + (size_t)sg * ecount) * D::ENT;
+  if (tid == 0) {
+    mbar_init(&mbar, 1);
+    fence_mbar_init();
+    mbar_expect_tx(&mbar, ecount * D::ENT * (int)sizeof(double));
+    bulk_g2s(ents, in, ecount * D::ENT * (int)sizeof(double), &mbar);
+  }
+  __syncthreads();
+  mbar_wait(&mbar, 0);
+  int levels = 0;
+  while ((1 << levels) < ecount) ++levels;
+  for (int l = 0; l < levels; ++l) {
+    if (l > 0) __syncthreads();
+    const int nsep = ecount >> (l + 1);
+    if (warp < nsep) {
+      const int el = (2 * warp) << l, er = el + (1 << l);   // merged entries live in the slot of their first entry
+      const int ge_last = sg * ecount + er - 1;             // last input entry of the left subtree
+      const int oidx = (sg * ecount + el) >> (l + 1);       // index of the merged subtree at its level
+      const bool root = a.Min == ecount && l == levels - 1;
+      double* EL = ents + el * D::ENT;
+      const int bad = dual_merge<NS>(EL, ents + er * D::ENT, root ? nullptr : EL, (oidx & 1) != 0, W, Lr);
+      const int slot = (ge_last + 1) * a.span4;
+      dual_store_record<NS>(a.sep + ((size_t)prob * a.M0 + slot) * D::WSZ, W);
+      if (bad && lane == 0) {
+        const int i = slot * SCAN_LEAF - 1;                 // local knot index of the separator
+        int lev = 0;
+        while ((i >> lev) & 1) ++lev;
+        b.status[(size_t)prob * 3 * s.N + rs_slot_S(i >> (lev + 1), lev, s.N)] = -1;
+        b.flags[prob] = 1;
+      }
+    }
+  }
+  if (a.out) {
+    __syncthreads();
+    fence_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      bulk_s2g(a.out + ((size_t)prob * ncta + sg) * D::ENT, ents, D::ENT * (int)sizeof(double));
+      bulk_commit();
+      bulk_wait_read0();
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------------
+inline bool dual_shape_ok(int n, int m) {
+  return (n == 6 && m == 3) || (n == 12 && m == 4) || (n == 12 && m == 6) || (n == 8 && m == 4) || (n == 16 && m == 8) ||
+         (n == 4 && m == 2);
+}
+
+template <int NS, int NI>
+inline cudaError_t dual_launch_t(ScanPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st,
+                                 cudaEvent_t k0, cudaEvent_t k1) {
+  using D = DualDim<NS>;
+  FusedPlan& f = p.f;
+  const int smem = DUAL_WPC * dual_leaf_warp_doubles<NS, NI>() * (int)sizeof(double);
+  cudaError_t e = smem_optin(dual_leaf_kernel<NS, NI>, smem);
+  if (e != cudaSuccess) return e;
+  const long long nsub = (long long)batch * f.M0;
+  f.launches = 1;
+  if (k0) cudaEventRecord(k0, st);
+  dual_leaf_kernel<NS, NI><<<(unsigned)((nsub + DUAL_WPC - 1) / DUAL_WPC), 32 * DUAL_WPC, smem, st>>>(s, b, p.sb.ent0, p.sb.sep_in,
+                                                                                                        pack_rhs, f.M0, nsub);
+  if (k1) cudaEventRecord(k1, st);
+  e = smem_optin(dual_tier_kernel<NS>, (8 * D::ENT + 4 * dual_tier_warp_scratch<NS>()) * (int)sizeof(double));
+  if (e != cudaSuccess) return e;
+  for (int t = 0; t < f.ntiers; ++t) {
+    const FusedTier& T = f.tiers[t];
+    DualTierArgs a{};
+    a.in = f.fb.ent[t];
+    a.out = t == f.ntiers - 1 ? nullptr : f.fb.ent[t + 1];
+    a.sep = f.fb.sep;
+    a.Min = T.Min; a.ecount = T.ecount; a.M0 = f.M0; a.span4 = T.span / SCAN_LEAF;
+    const int warps = T.ecount / 2 > 0 ? T.ecount / 2 : 1;
+    const int sm = (T.ecount * D::ENT + warps * dual_tier_warp_scratch<NS>()) * (int)sizeof(double);
+    dual_tier_kernel<NS><<<(unsigned)((size_t)batch * (T.Min / T.ecount)), 32 * warps, sm, st>>>(s, b, a);
+    ++f.launches;
+  }
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  return launch_scan_down<NS, NI>(p, s, b, batch, pack_rhs, st, nullptr, nullptr);
+}
+
+inline int dual_launch(ScanPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st, std::string& err,
+                       cudaEvent_t k0, cudaEvent_t k1) {
+  if (!p.f.available || !p.dual) { err = "shape not covered by the dual-form scan kernels"; return -5; }
+  cudaError_t e;
+  if (s.n == 6 && s.m == 3) e = dual_launch_t<6, 3>(p, s, b, batch, pack_rhs, st, k0, k1);
+  else if (s.n == 12 && s.m == 4) e = dual_launch_t<12, 4>(p, s, b, batch, pack_rhs, st, k0, k1);
+  else if (s.n == 12 && s.m == 6) e = dual_launch_t<12, 6>(p, s, b, batch, pack_rhs, st, k0, k1);
+  else if (s.n == 8 && s.m == 4) e = dual_launch_t<8, 4>(p, s, b, batch, pack_rhs, st, k0, k1);
+  else if (s.n == 16 && s.m == 8) e = dual_launch_t<16, 8>(p, s, b, batch, pack_rhs, st, k0, k1);
+  else if (s.n == 4 && s.m == 2) e = dual_launch_t<4, 2>(p, s, b, batch, pack_rhs, st, k0, k1);
+  else { err = "shape not covered by the dual-form scan kernels"; return -5; }
+  if (e != cudaSuccess) { err = std::string("dual launch: ") + cudaGetErrorString(e); return -3; }
+  return 0;
+}
+
+}  // namespace rslqr

@@ -138,9 +138,11 @@ __host__ __device__ constexpr int factor_scratch_doubles() { return NS * factor_
 // On return Wout = [f_L | f_R | zs] (column-major, ld NS) and acc / acc2 still hold the lane's solved columns.
 // Same S = Lt D Lt^T as clap_CholeskyFactorize (src/linalg_custom.c:88) up to the diagonal scaling.
 // ---------------------------------------------------------------------------------------------------------
-template <int NS>
+//   S0 (dual path, kernels_dual.cuh): the right-hand side s rides in acc2 of lane 0 instead of in acc of lane 2NS, so
+//   that 2 NS lanes suffice (NS = 16 fits in one warp); zs then comes out of lane 0's acc2.
+template <int NS, bool S0 = false>
 __device__ __forceinline__ int spine_core2(double (&acc)[NS], double (&acc2)[NS], double* Lr, double* Wout) {
-  static_assert(NS % 2 == 0 && 2 * NS + 1 <= 32, "pairs; one warp per separator");
+  static_assert(NS % 2 == 0 && 2 * NS + (S0 ? 0 : 1) <= 32, "pairs; one warp per separator");
   constexpr int LDF = factor_ld<NS>();
   const int lane = threadIdx.x & 31;
   int bad = 0;
@@ -178,6 +180,21 @@ __device__ __forceinline__ int spine_core2(double (&acc)[NS], double (&acc2)[NS]
     }
   }
   // a lane's solved column is contiguous in W (column-major, ld NS): 128-bit stores (Wout is 16-byte aligned)
+  if constexpr (S0) {
+    if (lane >= NS && lane < 2 * NS) {
+      const int c = lane - NS;
+#pragma unroll
+      for (int r = 0; r < NS; r += 2) {
+        *reinterpret_cast<double2*>(Wout + c * NS + r) = make_double2(acc[r], acc[r + 1]);
+        *reinterpret_cast<double2*>(Wout + (NS + c) * NS + r) = make_double2(acc2[r], acc2[r + 1]);
+      }
+    } else if (lane == 0) {
+#pragma unroll
+      for (int r = 0; r < NS; r += 2) *reinterpret_cast<double2*>(Wout + 2 * NS * NS + r) = make_double2(acc2[r], acc2[r + 1]);
+    }
+    __syncwarp();
+    return bad;
+  }
   if (lane >= NS && lane <= 2 * NS) {
     const int c = lane - NS;  // lane 2NS: c = NS -> column 2NS of W (zs)
     double* w1 = lane < 2 * NS ? Wout + c * NS : Wout + 2 * NS * NS;
@@ -1118,10 +1135,10 @@ inline int launch_topdown(const double* sep, double* lam, int M0, int batch, con
   static const int force = [] { const char* v = getenv("RSLQR_TOPDOWN_SMEM"); return v ? atoi(v) : -1; }();
   auto pass = [&](int span, int step) {
     const int nloc = span / step, ctas = batch * (M0 / span);
-    const bool smem_ok = nloc >= 2 && nloc <= H;
+    const int bytes = ((nloc - 1) * WSZ + (nloc + 1) * NS) * (int)sizeof(double);
+    const bool smem_ok = nloc >= 2 && nloc <= H && bytes <= 200 * 1024;  // (63 records of n = 16 would not fit)
     const bool use_smem = smem_ok && (force >= 0 ? force != 0 : ctas <= 1024);
     if (use_smem) {
-      const int bytes = ((nloc - 1) * WSZ + (nloc + 1) * NS) * (int)sizeof(double);
       smem_optin(topdown_smem_kernel<NS>, bytes);
       topdown_smem_kernel<NS><<<ctas, 128, bytes, st>>>(sep, lam, M0, left, right, span, step);
     } else {

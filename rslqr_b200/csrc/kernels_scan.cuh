@@ -68,7 +68,6 @@ template <int NS, int NI, int NK>
 __device__ __forceinline__ void leaf_transform(const Shape& s, const Bufs& b, int prob, int k0, int pack_rhs, double* R, double zl0) {
   using RD = RawDim<NS, NI>;
   constexpr int XU = NS + NI;
-  static_assert(XU == 16, "one half-warp per knot");
   const int lane = threadIdx.x & 31;
   const int N = s.N;
   // z_lambda: -d in place, or the caller's rhs
@@ -84,7 +83,7 @@ __device__ __forceinline__ void leaf_transform(const Shape& s, const Bufs& b, in
   __syncwarp();
 #pragma unroll 1
   for (int it = lane; it < NK * XU; it += 32) {
-    const int j = it >> 4, l = it & 15;
+    const int j = it / XU, l = it - j * XU;  // (XU is a compile-time constant: a shift for XU == 16)
     const int k = k0 + j, kg = s.kofs + k;
     const bool last = kg == s.Ng - 1, isR = l >= NS;
     double* B = R + NS + j * RD::STRIDE;
@@ -414,17 +413,19 @@ template <int NS, int NI>
 __global__ void __launch_bounds__(128) scan_down_kernel(Shape s, Bufs b, ScanBufs sb, const double* lam_all, int pack_rhs,
                                                          int M0, long long nsub) {
   using D = Dim<NS, NI>;
-  constexpr int WSZ = D::WSZ;
-  static_assert(NS + NI <= 16 && NS <= 16, "two knots per warp pass");
+  constexpr int WSZ = D::WSZ, XU = NS + NI;
+  // two knots per warp pass (lanes 0..15 / 16..31) when the X and U rows of a knot fit in a half-warp, else one
+  constexpr bool TWO = XU <= 16;
+  static_assert(XU <= 32 && NS <= 16, "rows of a knot fit in a warp, multipliers in a half-warp");
   const int lane = threadIdx.x & 31;
   const long long sub = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (sub >= nsub) return;
   const int prob = (int)(sub / M0), grp = (int)(sub - (long long)prob * M0);
   const double* la_p = lam_all + ((size_t)prob * (M0 + 1) + grp) * NS;
   const double* rec = sb.sep_in + ((size_t)prob * M0 + grp) * 3 * WSZ;
-  const int half = lane >> 4, r = lane & 15;
-  const int rc = r < NS ? r : 0;
-  // multipliers, one entry per lane r < NS (both halves hold copies)
+  const int half = lane >> 4, r16 = lane & 15;
+  const int rc = r16 < NS ? r16 : 0;
+  // multipliers, one entry per lane r16 < NS (both halves hold copies)
   const double la = la_p[rc], lb = la_p[NS + rc];
   auto sepmul = [&](const double* R, double left, double right) -> double {
     double v = R[2 * NS * NS + rc];
@@ -440,9 +441,12 @@ __global__ void __launch_bounds__(128) scan_down_kernel(Shape s, Bufs b, ScanBuf
   // half 0 computes l1 (record 0: la | l2), half 1 computes l3 (record 2: l2 | lb)
   const double l13 = sepmul(rec + (half ? 2 * WSZ : 0), half ? l2 : la, half ? lb : l2);
   const double l1 = __shfl_sync(0xffffffffu, l13, rc), l3 = __shfl_sync(0xffffffffu, l13, 16 + rc);
+  constexpr int PASSES = TWO ? 2 : 4;
 #pragma unroll 1
-  for (int pass = 0; pass < 2; ++pass) {
-    const int j = 2 * pass + half;  // local knot of this half-warp
+  for (int pass = 0; pass < PASSES; ++pass) {
+    const int j = TWO ? 2 * pass + half : pass;  // local knot of this (half-)warp
+    const int r = TWO ? r16 : lane;              // row of [x; u] this lane produces
+    const int base = TWO ? (lane & 16) : 0;      // where this knot's copy of the multipliers sits
     const int k = grp * SCAN_LEAF + j;
     const int kg = s.kofs + k;
     const double lk = j == 0 ? la : (j == 1 ? l1 : (j == 2 ? l2 : l3));
@@ -451,13 +455,15 @@ __global__ void __launch_bounds__(128) scan_down_kernel(Shape s, Bufs b, ScanBuf
     double* out = soln_ptr(s, b, prob, k);
     const bool last = kg == s.Ng - 1;
     double acc = 0.0;  // row r of [A|B]^T ln
-    const double* col = kn + s.oA + (r < NS + NI ? r : 0) * NS;
+    const double* col = kn + s.oA + (r < XU ? r : 0) * NS;
 #pragma unroll
     for (int c = 0; c < NS; ++c) {
-      const double lc = __shfl_sync(0xffffffffu, ln, (lane & 16) + c);
+      const double lc = __shfl_sync(0xffffffffu, ln, base + c);
       acc = fma(last ? 0.0 : __ldg(col + c), lc, acc);
     }
-    if (r < NS + NI) {
+    // (a lane with r >= NS holds a copy of multiplier entry r16 < NS or of entry 0: its own lk is only used for r < NS,
+    //  where r == r16 in both layouts)
+    if (r < XU) {
       const double d = __ldg(kn + r);
       const double rx = scan_rhs(s, b, prob, k, NS + r, pack_rhs);
       if (r < NS) {
@@ -481,9 +487,19 @@ __global__ void __launch_bounds__(128) scan_down_kernel(Shape s, Bufs b, ScanBuf
 struct ScanPlan {
   FusedPlan f;     // G0 = SCAN_LEAF; only sep / lamhat / ent[t >= 1] / xsep / xlam of f.fb are allocated
   ScanBufs sb;
+  bool dual;       // entries are the Schur-complement elements of kernels_dual.cuh (any covered shape), else the boundary
+                   // entries of this file (n = 12, m = 4)
+  size_t ent;      // doubles per entry
 };
 
-inline bool scan_shape_ok(int n, int m) { return n == 12 && m == 4; }
+inline bool dual_shape_ok(int n, int m);       // kernels_dual.cuh
+inline size_t dual_ent_doubles(int n);
+// RSLQR_DUAL=1 routes n = 12, m = 4 through the dual-form kernels too (A/B runs)
+inline bool scan_classic_ok(int n, int m) {
+  const char* v = getenv("RSLQR_DUAL");  // (read at plan time: a handle keeps the form it was created with)
+  return n == 12 && m == 4 && !(v && atoi(v));
+}
+inline bool scan_shape_ok(int n, int m) { return scan_classic_ok(n, m) || dual_shape_ok(n, m); }
 
 inline void scan_free(ScanPlan* p) {
   cudaFree(p->sb.ent0); cudaFree(p->sb.sep_in);
@@ -496,6 +512,8 @@ inline int scan_plan(const Shape& s, int batch, ScanPlan* p, std::string& err) {
   memset(p, 0, sizeof(*p));
   if (!scan_shape_ok(s.n, s.m) || s.N < SCAN_LEAF) return 0;
   FusedPlan& f = p->f;
+  p->dual = !scan_classic_ok(s.n, s.m);
+  p->ent = p->dual ? dual_ent_doubles(s.n) : fused_ent_doubles(s.n, s.m);
   f.ns = s.n; f.ni = s.m; f.G0 = SCAN_LEAF; f.M0 = s.N / SCAN_LEAF; f.use_dmma = 1;
   // entries per tier CTA: 4 for batches (2 then 1 of 2 warps active over a CTA's two levels, measured +1.7 % over 8),
   // 8 for a single long horizon (fewer dependent launches); RSLQR_TIER_E = 2, 4 or 8 overrides. Falls back to 8 when a
@@ -517,7 +535,7 @@ inline int scan_plan(const Shape& s, int batch, ScanPlan* p, std::string& err) {
     if (tier_e == 8) { memset(p, 0, sizeof(*p)); return 0; }
     tier_e = 8;
   }
-  const size_t n = s.n, ent = fused_ent_doubles(s.n, s.m), wsz = (2 * n + 1) * n;
+  const size_t n = s.n, ent = p->ent, wsz = (2 * n + 1) * n;
   auto alloc = [&](double** ptr, size_t cnt) {
     f.bytes += cnt * sizeof(double);
     return cudaMalloc((void**)ptr, cnt * sizeof(double)) == cudaSuccess;
@@ -560,9 +578,13 @@ inline cudaError_t launch_scan_down(ScanPlan& p, const Shape& s, const Bufs& b, 
   return cudaGetLastError();
 }
 
+inline int dual_launch(ScanPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st, std::string& err,
+                       cudaEvent_t k0, cudaEvent_t k1);  // kernels_dual.cuh
+
 inline int scan_launch(ScanPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st, std::string& err,
                        cudaEvent_t k0 = nullptr, cudaEvent_t k1 = nullptr) {
   if (!p.f.available) { err = "shape not covered by the scan kernels"; return -5; }
+  if (p.dual) return dual_launch(p, s, b, batch, pack_rhs, st, err, k0, k1);
   p.f.launches = 1;
   if (k0) cudaEventRecord(k0, st);  // k0..k1 bracket the dominant kernel (leaf) only
   cudaError_t e = launch_scan_leaf<12, 4>(p, s, b, batch, pack_rhs, st);

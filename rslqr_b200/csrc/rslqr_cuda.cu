@@ -13,6 +13,7 @@
 
 #include "kernels_fused.cuh"
 #include "kernels_scan.cuh"
+#include "kernels_dual.cuh"
 #include "kernels_riccati.cuh"
 #include "kernels_staged.cuh"
 #include "kernels_staged_mma.cuh"
@@ -527,7 +528,7 @@ extern "C" int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs) {
     b.status += f * 3 * s.N; b.flags += f; b.leafd += f * s.N * (s.n + s.m);
     ScanPlan q = h->scan;
     {
-      const size_t ent = fused_ent_doubles(s.n, s.m), wsz = (2 * (size_t)s.n + 1) * s.n;
+      const size_t ent = q.ent, wsz = (2 * (size_t)s.n + 1) * s.n;
       q.f.fb.sep += f * q.f.M0 * wsz; q.f.fb.lamhat += f * (q.f.M0 + 1) * s.n;
       q.sb.sep_in += f * q.f.M0 * 3 * wsz; q.sb.ent0 += f * q.f.M0 * ent;
       q.f.fb.ent[0] = q.sb.ent0;
@@ -881,6 +882,16 @@ extern "C" int rslqr_cuda_create_shard(int n, int m, int nhorizon, int first_kno
   int rc = rslqr_cuda_create(n, m, shard_knots, 1, device, flags & ~RSLQR_KEEP_FACT, out);
   if (rc) return rc;
   rslqr_cuda_solver* h = *out;
+  if (h->scan.dual) {
+    // the shard kernels exist for the boundary-entry form only: a shape the scan path covers in dual form runs its
+    // shards on the tiered kernels
+    scan_free(&h->scan);
+    if (!h->fused.available && fused_plan(h->s, h->batch, h->g0_pref, &h->fused, g_err)) {
+      rslqr_cuda_destroy(h);
+      *out = nullptr;
+      return RSLQR_E_NOMEM;
+    }
+  }
   if (!(h->scan.f.available && h->scan.f.ntiers >= 1) && !(h->fused.available && h->fused.ntiers >= 1)) {
     rslqr_cuda_destroy(h);
     *out = nullptr;

@@ -197,6 +197,61 @@ def test_scan_path_all_horizons(N):
     s.close()
 
 
+@pytest.mark.parametrize("N", [4, 8, 64, 256, 2048])
+@pytest.mark.parametrize("shape", [(6, 3), (12, 6), (8, 4), (16, 8), (4, 2), (12, 4)])
+def test_dual_form_scan_path_shapes(shape, N, monkeypatch):
+    # the scan path in dual form (kernels_dual.cuh: a subtree = its Schur complement onto the two multipliers bounding
+    # it) for every covered shape, against the oracle; n = 12, m = 4 is routed through it with RSLQR_DUAL=1
+    n, m = shape
+    B = 5
+    monkeypatch.setenv("RSLQR_DUAL", "1")
+    kn, x0 = R.synth_problems(n, m, N, 41, 0, B)
+    s = R.CudaSolver(n, m, N, batch=B, flags=0)
+    assert s.mode == R.MODE_SCAN
+    s.upload(kn, x0)
+    s.solve()
+    z = s.solution().copy()
+    assert not s.flags().any()
+    s.solve()
+    assert np.array_equal(s.solution(), z)          # re-solve on the same handle: bit-identical
+    for p in range(B):
+        want, _ = O.port_solve(n, m, N, kn[p], x0[p], threads=2)
+        assert max(rel_err_classes(z[p], want, n, m, N)) < TOL, (shape, N, p)
+        assert O.kkt_residual(n, m, N, kn[p], x0[p], z[p]) < 1e-10 * max(1.0, np.linalg.norm(z[p]))
+    # a caller-supplied right-hand side (pack_rhs = 0) takes the same path
+    rhs = np.zeros((B, N, 2 * n + m))
+    for p in range(B):
+        ps = O.PortSolver(n, m, N)
+        ps.init(kn[p], x0[p])
+        rhs[p] = ps.soln
+        ps.close()
+    s.upload_rhs(rhs)
+    s.solve(pack_rhs=False)
+    assert np.linalg.norm(s.solution() - z) <= 1e-12 * np.linalg.norm(z)
+    # a non-positive Q entry raises the status word of that leaf factor
+    bad = kn.copy()
+    bad[2, N // 2, 1] = -1.0
+    s.upload(bad, x0)
+    s.solve()
+    assert list(s.flags()) == [0, 0, 1, 0, 0] and s.status(2)[2 * (N // 2)] == -1
+    s.close()
+
+
+def test_shipped_n6_problem_runs_in_scan_mode():
+    # lqr_prob_256.json (n=6, m=3: the only shape the reference ships) takes the scan path by default
+    n, m, N, kn, x0 = R.load_problem_json(os.path.join(GOLDEN, "lqr_prob_256.json"))
+    want = np.array(golden_json("lqr_prob_256.json")["soln"]).reshape(-1)
+    s = R.CudaSolver(n, m, N, batch=1, flags=0)
+    assert s.mode == R.MODE_SCAN
+    s.upload(kn[None], x0[None])
+    s.solve()
+    z = s.solution()[0]
+    assert np.linalg.norm(z[:want.size] - want) < 1e-6
+    ref, _ = O.port_solve(n, m, N, kn, x0)
+    assert max(rel_err_classes(z, ref, n, m, N)) < TOL
+    s.close()
+
+
 def test_scan_path_is_bit_reproducible():
     # warp-synchronous shared-memory code with TMA copies: a data race would show up as run-to-run differences.
     # 40 repeated solves of the same resident batch (more warps than one wave of the GPU) must be bit-identical,
