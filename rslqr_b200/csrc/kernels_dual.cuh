@@ -29,20 +29,6 @@
 
 namespace rslqr {
 
-template <int NS>
-struct DualDim {
-  static constexpr int NP = (NS + 3) & ~3;          // padded block size (multiple of 4: DMMA k-steps, 16-byte rows)
-  static constexpr int LD = NP + 2;                 // row stride of a block (rows 16-byte aligned, bank-staggered)
-  static constexpr int BLK = NP * LD;
-  static constexpr int OK = 0, OC = BLK, OS = 2 * BLK, OKS = 3 * BLK, OSS = 3 * BLK + NP;
-  static constexpr int ENT = 3 * BLK + 2 * NP;      // even -> entries stay 16-byte aligned
-  static constexpr int WSZ = (2 * NS + 1) * NS;     // separator record [f_L | f_R | zs], column-major ld NS
-  static constexpr int WP = (2 * NP + 1) * NP;      // the same in shared memory, ld NP
-  static constexpr int LR = NP * (NP + 2);          // factor scratch of spine_core2<NP>
-};
-
-inline size_t dual_ent_doubles(int n) { const int np = (n + 3) & ~3; return (size_t)3 * np * (np + 2) + 2 * np; }
-
 // ---------------------------------------------------------------------------------------------------------
 // One merge, one warp. EL: L-type entry of the left subtree, ER: R-type entry of the right one (shared memory).
 // Eout: the merged entry, R-type if out_right else L-type; may be EL itself (rows are consumed tile by tile before
@@ -405,14 +391,23 @@ inline cudaError_t dual_launch_t(ScanPlan& p, const Shape& s, const Bufs& b, int
                                  cudaEvent_t k0, cudaEvent_t k1) {
   using D = DualDim<NS>;
   FusedPlan& f = p.f;
-  const int smem = DUAL_WPC * dual_leaf_warp_doubles<NS, NI>() * (int)sizeof(double);
-  cudaError_t e = smem_optin(dual_leaf_kernel<NS, NI>, smem);
-  if (e != cudaSuccess) return e;
-  const long long nsub = (long long)batch * f.M0;
+  cudaError_t e;
   f.launches = 1;
   if (k0) cudaEventRecord(k0, st);
-  dual_leaf_kernel<NS, NI><<<(unsigned)((nsub + DUAL_WPC - 1) / DUAL_WPC), 32 * DUAL_WPC, smem, st>>>(s, b, p.sb.ent0, p.sb.sep_in,
-                                                                                                        pack_rhs, f.M0, nsub);
+  if constexpr (NS == 12 && NI == 4) {
+    if (p.hybrid) {  // boundary-row leaf kernel (levels 0..1), dual elements out
+      e = launch_scan_leaf<12, 4>(p, s, b, batch, pack_rhs, st);
+      if (e != cudaSuccess) return e;
+    }
+  }
+  if (!p.hybrid) {
+    const int smem = DUAL_WPC * dual_leaf_warp_doubles<NS, NI>() * (int)sizeof(double);
+    e = smem_optin(dual_leaf_kernel<NS, NI>, smem);
+    if (e != cudaSuccess) return e;
+    const long long nsub = (long long)batch * f.M0;
+    dual_leaf_kernel<NS, NI><<<(unsigned)((nsub + DUAL_WPC - 1) / DUAL_WPC), 32 * DUAL_WPC, smem, st>>>(s, b, p.sb.ent0, p.sb.sep_in,
+                                                                                                          pack_rhs, f.M0, nsub);
+  }
   if (k1) cudaEventRecord(k1, st);
   e = smem_optin(dual_tier_kernel<NS>, (8 * D::ENT + 4 * dual_tier_warp_scratch<NS>()) * (int)sizeof(double));
   if (e != cudaSuccess) return e;
@@ -435,7 +430,7 @@ inline cudaError_t dual_launch_t(ScanPlan& p, const Shape& s, const Bufs& b, int
 
 inline int dual_launch(ScanPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st, std::string& err,
                        cudaEvent_t k0, cudaEvent_t k1) {
-  if (!p.f.available || !p.dual) { err = "shape not covered by the dual-form scan kernels"; return -5; }
+  if (!p.f.available || !(p.dual || p.hybrid)) { err = "shape not covered by the dual-form scan kernels"; return -5; }
   cudaError_t e;
   if (s.n == 6 && s.m == 3) e = dual_launch_t<6, 3>(p, s, b, batch, pack_rhs, st, k0, k1);
   else if (s.n == 12 && s.m == 4) e = dual_launch_t<12, 4>(p, s, b, batch, pack_rhs, st, k0, k1);

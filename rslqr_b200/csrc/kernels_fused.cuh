@@ -59,6 +59,21 @@ struct Dim {
   static constexpr int ENT = (2 * SLOT + ZS + NS + 1) & ~1;
 };
 
+// ---- layout of the dual-form entries (kernels_dual.cuh; also written by scan_leaf_kernel) ----
+template <int NS>
+struct DualDim {
+  static constexpr int NP = (NS + 3) & ~3;          // padded block size (multiple of 4: DMMA k-steps, 16-byte rows)
+  static constexpr int LD = NP + 2;                 // row stride of a block (rows 16-byte aligned, bank-staggered)
+  static constexpr int BLK = NP * LD;
+  static constexpr int OK = 0, OC = BLK, OS = 2 * BLK, OKS = 3 * BLK, OSS = 3 * BLK + NP;
+  static constexpr int ENT = 3 * BLK + 2 * NP;      // even -> entries stay 16-byte aligned
+  static constexpr int WSZ = (2 * NS + 1) * NS;     // separator record [f_L | f_R | zs], column-major ld NS
+  static constexpr int WP = (2 * NP + 1) * NP;      // the same in shared memory, ld NP
+  static constexpr int LR = NP * (NP + 2);          // factor scratch of spine_core2<NP>
+};
+
+inline size_t dual_ent_doubles(int n) { const int np = (n + 3) & ~3; return (size_t)3 * np * (np + 2) + 2 * np; }
+
 // ---- TMA 1-D bulk copies (cp.async.bulk) and the mbarrier that tracks them ----
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {

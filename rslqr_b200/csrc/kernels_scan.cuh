@@ -292,6 +292,80 @@ __device__ __forceinline__ int merge_raw(const double* Bl, const double* Br, con
 }
 
 
+// ---------------------------------------------------------------------------------------------------------
+// Boundary entry of a subtree [a,b] (rows [X(a) | X(b) | U(b)] of L, R, z and z_lambda(a)) -> its dual-form element
+// (kernels_dual.cuh), so that the levels above the leaf kernel run on n x n blocks only. With
+//   soln(k) = z(k) - L(k) lambda_a - R(k) lambda_{b+1}
+// the rows of the multiplier system the subtree contributes to are
+//   lambda_a     :  x_a                       ->  Saa = -L_X(a), Sab = -R_X(a), sa = -z_x(a) - z_lambda(a)
+//   lambda_{b+1} : -(A_b x_b + B_b u_b)       ->  [Sba | Sbb | sb] = [A_b | B_b] [L | R | z]_{X,U rows of b}
+// the second being the product every later ndlqr_FactorInnerProduct (src/nested_dissection.c:114) would apply to
+// these rows: it is applied here once. E: entry (Dim layout), AB: [A_b | B_b] in global memory, Eo: dual entry
+// (DualDim layout, R-type if `right` else L-type; must not alias E). One warp.
+// ---------------------------------------------------------------------------------------------------------
+template <int NS, int NI>
+__device__ __forceinline__ void entry_to_dual(const double* E, const double* __restrict__ AB, double* Eo, bool right) {
+  using D = Dim<NS, NI>;
+  using DD = DualDim<NS>;
+  constexpr int SLOT = D::SLOT, ZS = D::ZS, LD = DD::LD, KS = (NS + NI) / 4;
+  static_assert(NS % 4 == 0 && (NS + NI) % 4 == 0 && NS > 8 && NS <= 16 && DD::NP == NS, "tile shapes");
+  const int lane = threadIdx.x & 31, q = lane & 3, rr = lane >> 2;
+  const double* LX = E + NS * NS;            // rows X(b), U(b) of the L block
+  const double* RX = E + SLOT + NS * NS;
+  const double* zx = E + 2 * SLOT + NS;
+  double d[2][4][2];
+#pragma unroll
+  for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) d[mt][nt][0] = d[mt][nt][1] = 0.0;
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+    const int l = 4 * ks + q;
+    const double a0 = __ldg(AB + l * NS + rr);
+    const double a1 = (8 + rr < NS) ? __ldg(AB + l * NS + 8 + rr) : 0.0;
+    double bf[4];
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+      const int n = 8 * nt + rr;
+      bf[nt] = n < NS ? LX[l * NS + n] : (n < 2 * NS ? RX[l * NS + n - NS] : (n == 2 * NS ? zx[l] : 0.0));
+    }
+#pragma unroll
+    for (int nt = 0; nt < 4; ++nt) {
+      dmma884(d[0][nt][0], d[0][nt][1], a0, bf[nt]);
+      dmma884(d[1][nt][0], d[1][nt][1], a1, bf[nt]);
+    }
+  }
+  // [Sba | Sbb | sb]: an R-type element keeps all three (Cp, Kp, ks), an L-type one only Sbb, sb (Sp, ss)
+#pragma unroll
+  for (int mt = 0; mt < 2; ++mt) {
+    const int row = 8 * mt + rr;
+    if (row < NS) {
+#pragma unroll
+      for (int nt = 0; nt < 3; ++nt) {
+        const int col = 8 * nt + 2 * q;
+        const double2 v = make_double2(d[mt][nt][0], d[mt][nt][1]);
+        if (col < NS) {
+          if (right) *reinterpret_cast<double2*>(Eo + DD::OC + row * LD + col) = v;
+        } else {
+          *reinterpret_cast<double2*>(Eo + (right ? DD::OK : DD::OS) + row * LD + col - NS) = v;
+        }
+      }
+      if (q == 0) Eo[(right ? DD::OKS : DD::OSS) + row] = d[mt][3][0];
+    }
+  }
+  // Saa = -L_X(a) (Kp of an L-type element, Sp of an R-type one), Sab = -R_X(a) (Cp, L-type only), sa
+  for (int e = lane; e < NS * NS / 2; e += 32) {
+    const int row = e / (NS / 2), col = 2 * (e - row * (NS / 2));
+    const double2 l = *reinterpret_cast<const double2*>(E + row * NS + col);
+    *reinterpret_cast<double2*>(Eo + (right ? DD::OS : DD::OK) + row * LD + col) = make_double2(-l.x, -l.y);
+    if (!right) {
+      const double2 r2 = *reinterpret_cast<const double2*>(E + SLOT + row * NS + col);
+      *reinterpret_cast<double2*>(Eo + DD::OC + row * LD + col) = make_double2(-r2.x, -r2.y);
+    }
+  }
+  if (lane < NS) Eo[(right ? DD::OSS : DD::OKS) + lane] = -E[2 * SLOT + lane] - E[2 * SLOT + ZS + lane];
+}
+
 struct ScanBufs {
   double* ent0;    // [batch][M0][ENT]   entries of the 4-knot subtrees (input of the first tier)
   double* sep_in;  // [batch][M0][3][WSZ] records of the interior separators of a subtree: local knots 1, 2, 3
@@ -312,7 +386,7 @@ __host__ __device__ constexpr int scan_leaf_smem_doubles() { return SCAN_WPC * s
 
 template <int NS, int NI>
 __global__ void __launch_bounds__(32 * SCAN_WPC, 2) scan_leaf_kernel(Shape s, Bufs b, ScanBufs sb, int pack_rhs, int M0,
-                                                                      long long nsub) {
+                                                                      long long nsub, int dual_out) {
   using D = Dim<NS, NI>;
   using RD = RawDim<NS, NI>;
   constexpr int ZS = D::ZS, SLOT = D::SLOT, WSZ = D::WSZ, ENT = D::ENT;
@@ -388,11 +462,26 @@ __global__ void __launch_bounds__(32 * SCAN_WPC, 2) scan_leaf_kernel(Shape s, Bu
   }
   if (M0 > 1) {  // (a single subtree is the whole problem: only the records are needed)
     lean_schur_dmma<NS, NI>(E0, E1, E0, E0, Wf);
-    fence_async_smem();
-    __syncwarp();
-    if (lane == 0) {
-      bulk_s2g(sb.ent0 + ((size_t)prob * M0 + grp) * ENT, E0, ENT * (int)sizeof(double));
-      bulk_commit();
+    if (dual_out) {
+      // the levels above run in dual form (kernels_dual.cuh): hand the subtree up as its Schur-complement element,
+      // built in the now dead right entry
+      using DD = DualDim<NS>;
+      static_assert(DD::ENT <= ENT, "the dual element fits in the dead entry");
+      __syncwarp();
+      entry_to_dual<NS, NI>(E0, knot_ptr(s, b, prob, k0 + SCAN_LEAF - 1) + s.oA, E1, (grp & 1) != 0);
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        bulk_s2g(sb.ent0 + ((size_t)prob * M0 + grp) * DD::ENT, E1, DD::ENT * (int)sizeof(double));
+        bulk_commit();
+      }
+    } else {
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        bulk_s2g(sb.ent0 + ((size_t)prob * M0 + grp) * ENT, E0, ENT * (int)sizeof(double));
+        bulk_commit();
+      }
     }
   }
   if (lane == 0) bulk_wait_read0();  // shared memory must stay valid until the copy engine has read it
@@ -489,6 +578,7 @@ struct ScanPlan {
   ScanBufs sb;
   bool dual;       // entries are the Schur-complement elements of kernels_dual.cuh (any covered shape), else the boundary
                    // entries of this file (n = 12, m = 4)
+  bool hybrid;     // n = 12, m = 4: scan_leaf_kernel (boundary rows, levels 0..1) hands dual elements up, the tiers run dual
   size_t ent;      // doubles per entry
 };
 
@@ -508,12 +598,17 @@ inline void scan_free(ScanPlan* p) {
   memset(p, 0, sizeof(*p));
 }
 
-inline int scan_plan(const Shape& s, int batch, ScanPlan* p, std::string& err) {
+// allow_hybrid: false for shards (their exchange and cross-GPU tier work on boundary entries)
+inline int scan_plan(const Shape& s, int batch, ScanPlan* p, std::string& err, bool allow_hybrid = true) {
   memset(p, 0, sizeof(*p));
   if (!scan_shape_ok(s.n, s.m) || s.N < SCAN_LEAF) return 0;
   FusedPlan& f = p->f;
   p->dual = !scan_classic_ok(s.n, s.m);
-  p->ent = p->dual ? dual_ent_doubles(s.n) : fused_ent_doubles(s.n, s.m);
+  {
+    const char* v = getenv("RSLQR_NO_HYBRID");  // A/B: boundary entries at every level, as in round 1
+    p->hybrid = !p->dual && allow_hybrid && !(v && atoi(v));
+  }
+  p->ent = (p->dual || p->hybrid) ? dual_ent_doubles(s.n) : fused_ent_doubles(s.n, s.m);
   f.ns = s.n; f.ni = s.m; f.G0 = SCAN_LEAF; f.M0 = s.N / SCAN_LEAF; f.use_dmma = 1;
   // entries per tier CTA: 4 for batches (2 then 1 of 2 warps active over a CTA's two levels, measured +1.7 % over 8),
   // 8 for a single long horizon (fewer dependent launches); RSLQR_TIER_E = 2, 4 or 8 overrides. Falls back to 8 when a
@@ -563,7 +658,8 @@ inline cudaError_t launch_scan_leaf(ScanPlan& p, const Shape& s, const Bufs& b, 
   cudaError_t e = smem_optin(scan_leaf_kernel<NS, NI>, smem);
   if (e != cudaSuccess) return e;
   const long long nsub = (long long)batch * p.f.M0;
-  scan_leaf_kernel<NS, NI><<<(unsigned)((nsub + SCAN_WPC - 1) / SCAN_WPC), 32 * SCAN_WPC, smem, st>>>(s, b, p.sb, pack_rhs, p.f.M0, nsub);
+  scan_leaf_kernel<NS, NI><<<(unsigned)((nsub + SCAN_WPC - 1) / SCAN_WPC), 32 * SCAN_WPC, smem, st>>>(s, b, p.sb, pack_rhs, p.f.M0, nsub,
+                                                                                                       p.hybrid ? 1 : 0);
   return cudaGetLastError();
 }
 
@@ -584,7 +680,7 @@ inline int dual_launch(ScanPlan& p, const Shape& s, const Bufs& b, int batch, in
 inline int scan_launch(ScanPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st, std::string& err,
                        cudaEvent_t k0 = nullptr, cudaEvent_t k1 = nullptr) {
   if (!p.f.available) { err = "shape not covered by the scan kernels"; return -5; }
-  if (p.dual) return dual_launch(p, s, b, batch, pack_rhs, st, err, k0, k1);
+  if (p.dual || p.hybrid) return dual_launch(p, s, b, batch, pack_rhs, st, err, k0, k1);
   p.f.launches = 1;
   if (k0) cudaEventRecord(k0, st);  // k0..k1 bracket the dominant kernel (leaf) only
   cudaError_t e = launch_scan_leaf<12, 4>(p, s, b, batch, pack_rhs, st);

@@ -33,6 +33,10 @@ static int fail(int code, const std::string& msg) {
                   std::string(#call) + ": " + cudaGetErrorString(e_));                   \
   } while (0)
 
+// create() flag used by rslqr_cuda_create_shard only: plan the scan path on boundary entries at every level (the
+// shard exchange and the cross-GPU tier work on them)
+static const unsigned RSLQR_INTERNAL_SHARD = 1u << 31;
+
 struct PhaseSpan { int phase; cudaEvent_t t0, t1; };
 
 struct rslqr_cuda_solver {
@@ -130,7 +134,7 @@ extern "C" int rslqr_cuda_create(int n, int m, int N, int batch, int device, uns
     h->force_dfma = fd ? atoi(fd) : 0;
     memset(&h->scan, 0, sizeof(h->scan));
     memset(&h->fused, 0, sizeof(h->fused));
-    if (scan_plan(h->s, h->batch, &h->scan, g_err)) {
+    if (scan_plan(h->s, h->batch, &h->scan, g_err, !(flags & RSLQR_INTERNAL_SHARD))) {
       rslqr_cuda_destroy(h);
       return RSLQR_E_NOMEM;
     }
@@ -879,7 +883,7 @@ extern "C" int rslqr_cuda_create_shard(int n, int m, int nhorizon, int first_kno
   if (nhorizon < 2 || (nhorizon & (nhorizon - 1)) || shard_knots < 16 || (shard_knots & (shard_knots - 1)) ||
       first_knot < 0 || first_knot % shard_knots || first_knot + shard_knots > nhorizon)
     return fail(RSLQR_E_ARG, "shard: need power-of-two horizon and shard size (>= 16), first_knot a multiple of the shard size");
-  int rc = rslqr_cuda_create(n, m, shard_knots, 1, device, flags & ~RSLQR_KEEP_FACT, out);
+  int rc = rslqr_cuda_create(n, m, shard_knots, 1, device, (flags & ~RSLQR_KEEP_FACT) | RSLQR_INTERNAL_SHARD, out);
   if (rc) return rc;
   rslqr_cuda_solver* h = *out;
   if (h->scan.dual) {
