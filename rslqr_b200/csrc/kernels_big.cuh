@@ -1,0 +1,433 @@
+// kernels_big.cuh -- the dual-form nested dissection (see kernels_dual.cuh for the formulation) for LARGE blocks,
+// n = 64, m = 16 (BASELINE configs[4]): an element [Saa | Sab | Sbb | sa | sb] is 99 KB and a merge touches three of
+// them plus a 66 KB record, so elements live in HBM / L2 and a CTA (not a warp) owns a merge.
+//
+// Per level, two launches over all (problem, merge) pairs:
+//   big_spine_kernel : S = SbbL + SaaR, then ONE elimination sweep with the 2n+1 right-hand sides riding along as extra
+//                      rows, one row per THREAD in registers (rows of S | columns of S_L | columns of S_R | s; the same
+//                      scheme as spine_core2, with the pivot rows broadcast through shared memory), then the backward
+//                      sweep; [f_L | f_R | zs] goes straight from registers to the separator's record.
+//                      (= ndlqr_FactorInnerProduct + Cholesky + ndlqr_SolveCholeskyFactor, src/nested_dissection.c:114-152)
+//   big_schur_kernel : Saa' = SaaL - SabL f_L, Sab' = -SabL f_R, sa' = saL - SabL zs,
+//                      Sbb' = SbbR - SabR^T f_R, sb' = sbR - SabR^T zs      on mma.sync.m8n8k4.f64
+//                      (= ndlqr_UpdateShurFactor restricted to what a later inner product reads, :154-171)
+// then one top-down launch per level (lambda of the separators from the records) and big_down_kernel (x_k, u_k from the
+// leaf equations, as scan_down_kernel). Against the staged path on this shape (every knot updated at every level, dense
+// `fact` array of 755 MB per problem): 3.4 instead of 23.6 GFLOP per solve, 0.22 instead of 0.76 GB per problem.
+#pragma once
+#include "kernels_fused.cuh"
+
+namespace rslqr {
+
+template <int NS>
+struct BigDim {
+  static constexpr int BLK = NS * NS;
+  static constexpr int OAA = 0, OAB = BLK, OBB = 2 * BLK, OSA = 3 * BLK, OSB = 3 * BLK + NS;
+  static constexpr int ENT = 3 * BLK + 2 * NS;   // [Saa | Sab | Sbb | sa | sb], blocks row-major ld NS
+  static constexpr int WSZ = (2 * NS + 1) * NS;  // record [f_L | f_R | zs], column-major ld NS
+};
+
+struct BigBufs {
+  double* entA;  // [batch][N][ENT]      elements of the even levels (level l has N >> l of them, packed at the front)
+  double* entB;  // [batch][N/2][ENT]    elements of the odd levels
+  double* rec;   // [batch][N][WSZ]      record of the separator after knot i at slot i (slot N-1 unused)
+  double* lam;   // [batch][N+1][NS]     multipliers lambda_k; slots 0 and N stay zero
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// Leaf elements (ndlqr_SolveLeaf on diagonal Q, R, src/nested_dissection.c:10-105, with the rhs packing of
+// src/solver.c:138-190), one CTA per (problem, knot):
+//   Saa = Q^-1, Sab = -Q^-1 A^T, Sbb = A Q^-1 A^T + B R^-1 B^T, sa = -z_x - z_lambda, sb = A z_x + B z_u
+//   knot 0: x_0 is fixed (z_x = x0) and lambda_0 is no unknown: Q^-1 -> 0 in the blocks; last knot: only Saa, sa.
+// dynamic smem: (NS*(NS+NI) + 2*(NS+NI) + 2*NS) doubles
+// ---------------------------------------------------------------------------------------------------------
+template <int NS, int NI>
+__global__ void __launch_bounds__(256) big_leaf_kernel(Shape s, Bufs b, BigBufs bb, int pack_rhs) {
+  using D = BigDim<NS>;
+  constexpr int XU = NS + NI;
+  extern __shared__ __align__(16) double smf[];
+  double* AB = smf;                 // [NS x XU] column-major, as in the flat knot block
+  double* dv = AB + NS * XU;        // 1/Q, 1/R (as used in the products: 0 for Q of knot 0 and for the last knot)
+  double* zv = dv + XU;             // leaf-solved z_x, z_u
+  double* sc = zv + XU;             // 1/Q of this knot (also for knot 0), then z_lambda
+  const int N = s.N;
+  const int prob = blockIdx.x / N, k = blockIdx.x % N;
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const double* kn = knot_ptr(s, b, prob, k);
+  const bool first = k == 0, last = k == N - 1;
+  for (int e = tid; e < NS * XU; e += nthr) AB[e] = last ? 0.0 : kn[s.oA + e];
+  for (int l = tid; l < XU; l += nthr) {
+    const bool isR = l >= NS;
+    const double d = kn[l];  // Q then R lead the block
+    if (!(d > 0.0) && !(isR && last)) {
+      b.status[(size_t)prob * 3 * N + (isR ? rs_slot_R(k) : rs_slot_Q(k))] = -1;
+      b.flags[prob] = 1;
+    }
+    const double dinv = (isR && last) ? 0.0 : 1.0 / d;
+    double rx;  // negated rhs of row l of [x; u]
+    if (!pack_rhs) rx = soln_ptr(s, b, prob, k)[NS + l];
+    else rx = isR ? (last ? 0.0 : -kn[s.orr + l - NS]) : -kn[s.oq + l];
+    double z;
+    if (first && !isR) {
+      const double rl = pack_rhs ? -b.x0[(size_t)prob * NS + l] : soln_ptr(s, b, prob, k)[l];
+      z = -rl;  // z_x(0) = x0
+    } else {
+      z = (isR && last) ? rx : rx * dinv;
+    }
+    zv[l] = z;
+    dv[l] = (last || (first && !isR)) ? 0.0 : dinv;
+    if (!isR) {
+      sc[l] = first ? 0.0 : dinv;
+      double zl = 0.0;  // z_lambda(k) = negated rhs of the lambda row (unused for knot 0)
+      if (!first) zl = pack_rhs ? -(kn - s.stride)[s.od + l] : soln_ptr(s, b, prob, k)[l];
+      sc[NS + l] = zl;
+    }
+  }
+  __syncthreads();
+  double* E = bb.entA + ((size_t)prob * N + k) * D::ENT;
+  for (int e = tid; e < NS * NS; e += nthr) {
+    const int r = e / NS, c = e - r * NS;
+    E[D::OAA + e] = r == c ? sc[r] : 0.0;
+    E[D::OAB + e] = -sc[r] * AB[c + NS * r];  // -A(c, r) / Q(r)   (AB is zero for the last knot)
+    double g = 0.0;
+#pragma unroll 8
+    for (int l = 0; l < XU; ++l) g = fma(AB[r + NS * l] * dv[l], AB[c + NS * l], g);
+    E[D::OBB + e] = g;
+  }
+  for (int r = tid; r < NS; r += nthr) {
+    E[D::OSA + r] = -zv[r] - sc[NS + r];
+    double v = 0.0;
+    for (int l = 0; l < XU; ++l) v = fma(AB[r + NS * l], zv[l], v);
+    E[D::OSB + r] = v;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Spine of one merge, one CTA of 3 NS + 1 (rounded up to warps) threads, one row of NS doubles per thread in registers:
+//   threads [0,NS)      : row t of S = SbbL + SaaR
+//   threads [NS,2NS)    : column c of S_L = row c of SabL
+//   threads [2NS,3NS)   : column c of S_R = column c of SabR
+//   thread  3NS         : s = sbL + saR
+// Step j: thread j scales its row by 1/d_j and publishes [1/d_j | U(j, j+1..)] in shared memory; everybody eliminates
+// with its own unscaled element (an appended row ends up holding D^-1 Lt^-1 y). The backward sweep x_j = y_j -
+// sum_{k>j} U(j,k) x_k reads the same rows. Returns the solved columns straight into the record.
+// dynamic smem: NS * (NS + 2) doubles.
+// ---------------------------------------------------------------------------------------------------------
+template <int NS>
+__host__ __device__ constexpr int big_spine_threads() { return ((3 * NS + 1 + 31) / 32) * 32; }
+
+template <int NS>
+__global__ void __launch_bounds__(big_spine_threads<NS>()) big_spine_kernel(Shape s, Bufs b, const double* ein, double* rec_all,
+                                                                            int level, int M) {
+  using D = BigDim<NS>;
+  constexpr int LD = NS + 2;
+  extern __shared__ __align__(16) double Ur[];
+  __shared__ int s_bad;
+  const int N = s.N;
+  const int prob = blockIdx.x / M, t = blockIdx.x % M;
+  const int tid = threadIdx.x;
+  const int Min = 2 * M;                                   // elements of this level per problem
+  const double* EL = ein + ((size_t)prob * Min + 2 * t) * D::ENT;
+  const double* ER = EL + D::ENT;
+  const int i_sep = ((2 * t + 1) << level) - 1;            // knot index of the separator
+  double row[NS];
+  if (tid == 0) s_bad = 0;
+  if (tid < NS) {
+    const double2* pa = reinterpret_cast<const double2*>(EL + D::OBB + tid * NS);
+    const double2* pb = reinterpret_cast<const double2*>(ER + D::OAA + tid * NS);
+#pragma unroll
+    for (int k = 0; k < NS; k += 2) {
+      const double2 a = __ldg(pa + k / 2), c = __ldg(pb + k / 2);
+      row[k] = a.x + c.x; row[k + 1] = a.y + c.y;
+    }
+  } else if (tid < 2 * NS) {
+    const double2* pa = reinterpret_cast<const double2*>(EL + D::OAB + (tid - NS) * NS);
+#pragma unroll
+    for (int k = 0; k < NS; k += 2) { const double2 a = __ldg(pa + k / 2); row[k] = a.x; row[k + 1] = a.y; }
+  } else if (tid < 3 * NS) {
+    const double* pc = ER + D::OAB + (tid - 2 * NS);
+#pragma unroll
+    for (int k = 0; k < NS; ++k) row[k] = __ldg(pc + k * NS);
+  } else {
+#pragma unroll
+    for (int k = 0; k < NS; ++k) row[k] = tid == 3 * NS ? __ldg(EL + D::OSB + k) + __ldg(ER + D::OSA + k) : 0.0;
+  }
+#pragma unroll
+  for (int j = 0; j < NS; ++j) {
+    const int j0 = j & ~1;
+    if (tid == j) {
+      const double d = row[j];
+      if (!(d > 0.0)) s_bad = 1;
+      const double dinv = 1.0 / d;
+#pragma unroll
+      for (int k = j0; k < NS; k += 2) {
+        const double u0 = k < j ? 0.0 : (k == j ? dinv : row[k] * dinv);
+        const double u1 = k + 1 == j ? dinv : row[k + 1] * dinv;
+        *reinterpret_cast<double2*>(Ur + j * LD + k) = make_double2(u0, u1);
+      }
+    }
+    __syncthreads();
+    const double m1 = row[j];
+    double dinv = 0.0;
+#pragma unroll
+    for (int k = j0; k < NS; k += 2) {
+      const double2 u = *reinterpret_cast<const double2*>(Ur + j * LD + k);
+      if (k == j) dinv = u.x;
+      else if (k > j) row[k] = fma(-m1, u.x, row[k]);
+      if (k + 1 == j) dinv = u.y;
+      else if (k + 1 > j) row[k + 1] = fma(-m1, u.y, row[k + 1]);
+    }
+    row[j] = m1 * dinv;
+  }
+  if (tid >= NS && tid <= 3 * NS) {
+#pragma unroll
+    for (int j = NS - 2; j >= 0; --j) {
+      const int k0 = (j + 1) & ~1;
+#pragma unroll
+      for (int k = NS - 2; k >= k0; k -= 2) {  // the latest x last: one dependent FMA per step
+        const double2 u = *reinterpret_cast<const double2*>(Ur + j * LD + k);
+        row[j] = fma(-u.y, row[k + 1], row[j]);
+        if (k > j) row[j] = fma(-u.x, row[k], row[j]);
+      }
+    }
+    double* rec = rec_all + ((size_t)prob * N + i_sep) * D::WSZ + (size_t)(tid - NS) * NS;  // column tid - NS of [f_L | f_R | zs]
+#pragma unroll
+    for (int k = 0; k < NS; k += 2) *reinterpret_cast<double2*>(rec + k) = make_double2(row[k], row[k + 1]);
+  }
+  __syncthreads();
+  if (tid == 0 && s_bad) {
+    b.status[(size_t)prob * 3 * N + rs_slot_S(t, level, N)] = -1;
+    b.flags[prob] = 1;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Schur update of one merge on the fp64 tensor cores, one CTA of 8 warps. F = [f_L | f_R | zs] is staged in shared
+// memory (ld NS + 4: the B fragments of a warp fall into two wavefronts); warp w owns rows 8w..8w+7 of the left half
+// (SabL rows -> [Saa' | Sab' | sa']) and rows 8w..8w+7 of the right half (SabR^T rows -> [Sbb' | sb']); its A fragments
+// stay in registers across all column tiles. NS = 64: 8 warps x 8 rows.
+// dynamic smem: (2 NS + 1) * (NS + 4) doubles.
+// ---------------------------------------------------------------------------------------------------------
+template <int NS>
+__global__ void __launch_bounds__(256) big_schur_kernel(Shape s, const double* ein, double* eout, const double* rec_all, int level,
+                                                         int M) {
+  using D = BigDim<NS>;
+  static_assert(NS == 64, "8 warps x 8 rows per half");
+  constexpr int LDF = NS + 4, KS = NS / 4;
+  extern __shared__ __align__(16) double Fs[];  // column c of F at Fs + c * LDF
+  const int N = s.N;
+  const int prob = blockIdx.x / M, t = blockIdx.x % M;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, q = lane & 3, rr = lane >> 2;
+  const int Min = 2 * M;
+  const double* EL = ein + ((size_t)prob * Min + 2 * t) * D::ENT;
+  const double* ER = EL + D::ENT;
+  double* EO = eout + ((size_t)prob * M + t) * D::ENT;
+  const int i_sep = ((2 * t + 1) << level) - 1;
+  const double* rec = rec_all + ((size_t)prob * N + i_sep) * D::WSZ;
+  for (int e = tid; e < D::WSZ / 2; e += blockDim.x) {
+    const int c = (2 * e) / NS, k = 2 * e - c * NS;
+    *reinterpret_cast<double2*>(Fs + c * LDF + k) = __ldg(reinterpret_cast<const double2*>(rec) + e);
+  }
+  __syncthreads();
+  const int r = 8 * warp + rr;  // row within a half
+#pragma unroll 1
+  for (int half = 0; half < 2; ++half) {
+    // A fragments: left half: SabL(r, k); right half: SabR(k, r)
+    double a[KS];
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+      const int k = 4 * ks + q;
+      a[ks] = half ? __ldg(ER + D::OAB + k * NS + r) : __ldg(EL + D::OAB + r * NS + k);
+    }
+    // zs column: keep - a . zs
+    {
+      double part = 0.0;
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks) part = fma(a[ks], Fs[2 * NS * LDF + 4 * ks + q], part);
+      part += __shfl_xor_sync(0xffffffffu, part, 1);
+      part += __shfl_xor_sync(0xffffffffu, part, 2);
+      if (q == 0) EO[(half ? D::OSB : D::OSA) + r] = (half ? ER[D::OSB + r] : EL[D::OSA + r]) - part;
+    }
+    // column tiles: left half: 2NS columns (f_L -> Saa', f_R -> Sab'); right half: NS columns (f_R -> Sbb')
+    const int ntiles = half ? NS / 8 : 2 * NS / 8;
+#pragma unroll 1
+    for (int nt0 = 0; nt0 < ntiles; nt0 += 4) {
+      double c[4][2];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int col = 8 * (nt0 + u) + 2 * q;  // column of this half's output
+        double2 v = make_double2(0.0, 0.0);
+        if (half) v = __ldg(reinterpret_cast<const double2*>(ER + D::OBB + r * NS + col));
+        else if (col < NS) v = __ldg(reinterpret_cast<const double2*>(EL + D::OAA + r * NS + col));
+        c[u][0] = -v.x; c[u][1] = -v.y;  // accumulate a.F - keep, negate on the way out
+      }
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int fc = (half ? NS : 0) + 8 * (nt0 + u) + rr;  // column of F: f_L 0..NS-1, f_R NS..2NS-1
+          dmma884(c[u][0], c[u][1], a[ks], Fs[fc * LDF + 4 * ks + q]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int col = 8 * (nt0 + u) + 2 * q;
+        double* dst = half ? EO + D::OBB + r * NS + col : (col < NS ? EO + D::OAA + r * NS + col : EO + D::OAB + r * NS + col - NS);
+        *reinterpret_cast<double2*>(dst) = make_double2(-c[u][0], -c[u][1]);
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Top-down, one launch per level (coarsest first): lambda_{i+1} = zs - f_L lambda_a - f_R lambda_{b+1} for the separators
+// of that level ([a,b] = the merged subtree). One CTA of NS threads per (problem, separator).
+// ---------------------------------------------------------------------------------------------------------
+template <int NS>
+__global__ void __launch_bounds__(NS) big_topdown_kernel(int N, const double* rec_all, double* lam_all, int level, int M) {
+  using D = BigDim<NS>;
+  __shared__ double la[NS], lb[NS];
+  const int prob = blockIdx.x / M, t = blockIdx.x % M;
+  const int i_sep = ((2 * t + 1) << level) - 1;
+  const int a = i_sep + 1 - (1 << level), b1 = i_sep + 1 + (1 << level);
+  double* lam = lam_all + (size_t)prob * (N + 1) * NS;
+  const int r = threadIdx.x;
+  la[r] = a == 0 ? 0.0 : lam[(size_t)a * NS + r];  // (lambda_0 does not couple: f_L is zero there)
+  lb[r] = lam[(size_t)b1 * NS + r];                // slot N is zero
+  __syncthreads();
+  const double* rec = rec_all + ((size_t)prob * N + i_sep) * D::WSZ;
+  double v = rec[2 * NS * NS + r];
+#pragma unroll 8
+  for (int c = 0; c < NS; ++c) v = fma(-rec[c * NS + r], la[c], fma(-rec[(NS + c) * NS + r], lb[c], v));
+  lam[(size_t)(i_sep + 1) * NS + r] = v;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Down: x_k = Q_k^-1 (rhs_x + lambda_k - A_k^T lambda_{k+1}), u_k = R_k^-1 (rhs_u - B_k^T lambda_{k+1}) from the leaf
+// equations (the reference's rhs propagation src/solve.c:175-180 telescoped); knot 0: x_0 = x0 and
+// lambda_0 = Q_0 x0 + q_0 + A_0^T lambda_1 (src/nested_dissection.c:24-59). One CTA per (problem, knot), one thread per row.
+// ---------------------------------------------------------------------------------------------------------
+template <int NS, int NI>
+__global__ void __launch_bounds__(NS + NI) big_down_kernel(Shape s, Bufs b, const double* lam_all, int pack_rhs) {
+  constexpr int XU = NS + NI;
+  __shared__ double ln[NS];
+  const int N = s.N;
+  const int prob = blockIdx.x / N, k = blockIdx.x % N;
+  const int r = threadIdx.x;
+  const double* lam = lam_all + (size_t)prob * (N + 1) * NS;
+  const bool first = k == 0, last = k == N - 1;
+  if (r < NS) ln[r] = lam[(size_t)(k + 1) * NS + r];
+  __syncthreads();
+  if (r >= XU) return;
+  const double* kn = knot_ptr(s, b, prob, k);
+  double* out = soln_ptr(s, b, prob, k);
+  double acc = 0.0;  // row r of [A | B]^T lambda_{k+1}
+  if (!last) {
+    const double* col = kn + s.oA + r * NS;
+#pragma unroll 8
+    for (int c = 0; c < NS; ++c) acc = fma(__ldg(col + c), ln[c], acc);
+  }
+  const double d = kn[r];
+  double rx;
+  if (!pack_rhs) rx = out[NS + r];
+  else rx = r < NS ? -kn[s.oq + r] : (last ? 0.0 : -kn[s.orr + r - NS]);
+  if (r < NS) {
+    const double lk = first ? 0.0 : lam[(size_t)k * NS + r];
+    double xv, lv;
+    if (first) {
+      const double rl = pack_rhs ? -b.x0[(size_t)prob * NS + r] : out[r];
+      xv = -rl;
+      lv = -d * rl - rx + acc;
+    } else {
+      xv = (rx + lk - acc) / d;
+      lv = lk;
+    }
+    out[r] = lv;
+    out[NS + r] = xv;
+  } else {
+    out[NS + r] = last ? rx : (rx - acc) / d;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------------
+struct BigPlan {
+  bool covered;    // the shape has these kernels
+  bool allocated;
+  BigBufs bb;
+  size_t bytes;
+  int launches;
+};
+
+inline bool big_shape_ok(int n, int m, int N) { return n == 64 && m == 16 && N >= 2; }
+
+inline void big_free(BigPlan* p) {
+  cudaFree(p->bb.entA); cudaFree(p->bb.entB); cudaFree(p->bb.rec); cudaFree(p->bb.lam);
+  const bool cov = p->covered;
+  memset(p, 0, sizeof(*p));
+  p->covered = cov;
+}
+
+inline int big_alloc(const Shape& s, int batch, BigPlan* p, std::string& err) {
+  if (p->allocated) return 0;
+  const size_t ent = BigDim<64>::ENT, wsz = BigDim<64>::WSZ;
+  auto alloc = [&](double** ptr, size_t cnt) {
+    p->bytes += cnt * sizeof(double);
+    return cudaMalloc((void**)ptr, cnt * sizeof(double)) == cudaSuccess;
+  };
+  const bool ok = alloc(&p->bb.entA, (size_t)batch * s.N * ent) && alloc(&p->bb.entB, (size_t)batch * (s.N / 2) * ent) &&
+                  alloc(&p->bb.rec, (size_t)batch * s.N * wsz) && alloc(&p->bb.lam, (size_t)batch * (s.N + 1) * s.n);
+  if (!ok) {
+    cudaGetLastError();
+    big_free(p);
+    err = "device allocation for the large-block dual path failed";
+    return -4;
+  }
+  p->allocated = true;
+  return 0;
+}
+
+// problems [first, first + count) of the handle (the kernels index problems from 0: views start at `first`)
+inline int big_launch(BigPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st, std::string& err) {
+  constexpr int NS = 64, NI = 16;
+  using D = BigDim<NS>;
+  const int N = s.N;
+  p.launches = 0;
+  cudaError_t e = cudaMemsetAsync(p.bb.lam, 0, sizeof(double) * (size_t)batch * (N + 1) * NS, st);
+  if (e != cudaSuccess) { err = std::string("big launch: ") + cudaGetErrorString(e); return -3; }
+  const int leaf_smem = (NS * (NS + NI) + 2 * (NS + NI) + 2 * NS) * (int)sizeof(double);
+  const int spine_smem = NS * (NS + 2) * (int)sizeof(double);
+  const int schur_smem = (2 * NS + 1) * (NS + 4) * (int)sizeof(double);
+  if ((e = smem_optin(big_leaf_kernel<NS, NI>, leaf_smem)) != cudaSuccess || (e = smem_optin(big_spine_kernel<NS>, spine_smem)) != cudaSuccess ||
+      (e = smem_optin(big_schur_kernel<NS>, schur_smem)) != cudaSuccess) {
+    err = std::string("big launch: ") + cudaGetErrorString(e);
+    return -3;
+  }
+  big_leaf_kernel<NS, NI><<<(unsigned)((size_t)batch * N), 256, leaf_smem, st>>>(s, b, p.bb, pack_rhs);
+  ++p.launches;
+  const double* ein = p.bb.entA;
+  for (int level = 0; level < s.K; ++level) {
+    const int M = N >> (level + 1);
+    double* eout = (level & 1) ? p.bb.entA : p.bb.entB;
+    big_spine_kernel<NS><<<(unsigned)((size_t)batch * M), big_spine_threads<NS>(), spine_smem, st>>>(s, b, ein, p.bb.rec, level, M);
+    ++p.launches;
+    if (level < s.K - 1) {
+      big_schur_kernel<NS><<<(unsigned)((size_t)batch * M), 256, schur_smem, st>>>(s, ein, eout, p.bb.rec, level, M);
+      ++p.launches;
+    }
+    ein = eout;
+  }
+  for (int level = s.K - 1; level >= 0; --level) {
+    const int M = N >> (level + 1);
+    big_topdown_kernel<NS><<<(unsigned)((size_t)batch * M), NS, 0, st>>>(N, p.bb.rec, p.bb.lam, level, M);
+    ++p.launches;
+  }
+  big_down_kernel<NS, NI><<<(unsigned)((size_t)batch * N), NS + NI, 0, st>>>(s, b, p.bb.lam, pack_rhs);
+  ++p.launches;
+  e = cudaGetLastError();
+  if (e != cudaSuccess) { err = std::string("big launch: ") + cudaGetErrorString(e); return -3; }
+  return 0;
+}
+
+}  // namespace rslqr

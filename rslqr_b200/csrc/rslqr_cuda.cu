@@ -14,6 +14,7 @@
 #include "kernels_fused.cuh"
 #include "kernels_scan.cuh"
 #include "kernels_dual.cuh"
+#include "kernels_big.cuh"
 #include "kernels_riccati.cuh"
 #include "kernels_staged.cuh"
 #include "kernels_staged_mma.cuh"
@@ -56,6 +57,7 @@ struct rslqr_cuda_solver {
   bool ktime_on; std::vector<std::pair<cudaEvent_t, cudaEvent_t>> kspans; double k_ms; int k_n;
   FusedPlan fused; int force_dfma;
   ScanPlan scan; int g0_pref;
+  BigPlan big{};  // dual-form path for large blocks (n = 64, m = 16): buffers allocated on the first solve
   int factored = 0;  // `fact` holds a finished staged factorization of the uploaded problems
   bool prof_keep = false;  // keep the profile spans across enqueues (the chunks of solve_host)
   double* ric_gain = nullptr;  // [batch][N][K | dv | P | p] of the Riccati comparison solver (allocated on first use)
@@ -134,6 +136,7 @@ extern "C" int rslqr_cuda_create(int n, int m, int N, int batch, int device, uns
     h->force_dfma = fd ? atoi(fd) : 0;
     memset(&h->scan, 0, sizeof(h->scan));
     memset(&h->fused, 0, sizeof(h->fused));
+    h->big.covered = big_shape_ok(n, m, N) && !(flags & RSLQR_INTERNAL_SHARD);
     if (scan_plan(h->s, h->batch, &h->scan, g_err, !(flags & RSLQR_INTERNAL_SHARD))) {
       rslqr_cuda_destroy(h);
       return RSLQR_E_NOMEM;
@@ -160,6 +163,7 @@ extern "C" int rslqr_cuda_destroy(rslqr_cuda_solver* h) {
   cudaFree(h->b.status); cudaFree(h->b.leafd); cudaFree(h->ric_gain);
   fused_free(&h->fused);
   scan_free(&h->scan);
+  big_free(&h->big);
   for (auto ev : h->evpool) cudaEventDestroy(ev);
   for (auto& pr : h->kspans) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
   if (h->marks_made) for (auto ev : h->marks) cudaEventDestroy(ev);
@@ -276,7 +280,8 @@ extern "C" int rslqr_cuda_set_mode(rslqr_cuda_solver* h, int mode) {
     if (fused_plan(h->s, h->batch, h->g0_pref, &h->fused, g_err)) return RSLQR_E_NOMEM;
     if (!h->fused.available) return fail(RSLQR_E_UNSUPPORTED, "shape is not covered by the tiered (fused) kernels");
   }
-  if (mode == RSLQR_MODE_SCAN && !h->scan.f.available) return fail(RSLQR_E_UNSUPPORTED, "shape is not covered by the scan kernels");
+  if (mode == RSLQR_MODE_SCAN && !h->scan.f.available && !h->big.covered)
+    return fail(RSLQR_E_UNSUPPORTED, "shape is not covered by the scan kernels");
   h->mode = mode;
   return RSLQR_OK;
 }
@@ -284,7 +289,7 @@ extern "C" int rslqr_cuda_set_mode(rslqr_cuda_solver* h, int mode) {
 extern "C" int rslqr_cuda_get_mode(rslqr_cuda_solver* h) {
   if (!h) return fail(RSLQR_E_ARG, "handle is NULL");
   if (h->mode != RSLQR_MODE_AUTO) return h->mode;
-  if (h->scan.f.available) return RSLQR_MODE_SCAN;
+  if (h->scan.f.available || h->big.covered) return RSLQR_MODE_SCAN;
   if (h->fused.available) return RSLQR_MODE_FUSED;
   return RSLQR_MODE_STAGED;
 }
@@ -522,6 +527,21 @@ extern "C" int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs) {
     if (rc) return rc;
   }
   const int mode = rslqr_cuda_get_mode(h);
+  if (mode == RSLQR_MODE_SCAN && !h->scan.f.available) {  // large blocks: elements in HBM, a CTA per merge (kernels_big.cuh)
+    if (big_alloc(h->s, h->batch, &h->big, g_err)) return RSLQR_E_NOMEM;
+    const Shape& s = h->s;
+    const size_t f = (size_t)h->r_first;
+    Bufs b = h->b;
+    b.knots += f * s.N * s.stride; b.x0 += f * s.n; b.soln += f * s.N * s.zs;
+    b.status += f * 3 * s.N; b.flags += f;
+    BigPlan q = h->big;
+    q.bb.entA += f * s.N * BigDim<64>::ENT; q.bb.entB += f * (s.N / 2) * BigDim<64>::ENT;
+    q.bb.rec += f * s.N * BigDim<64>::WSZ; q.bb.lam += f * (s.N + 1) * s.n;
+    int rc = big_launch(q, s, b, h->r_count, pack_rhs, h->stream, g_err);
+    if (rc) return rc;
+    h->launches = q.launches;
+    return RSLQR_OK;
+  }
   if (mode == RSLQR_MODE_SCAN) {
     std::pair<cudaEvent_t, cudaEvent_t> kt;
     if (h->ktime_on) { cudaEventCreate(&kt.first); cudaEventCreate(&kt.second); }
