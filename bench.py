@@ -82,8 +82,28 @@ def scan_leaf_bytes_per_subtree(n, m, dual=False):
     return 8 * (4 * stride + ent + 3 * (2 * n + 1) * n)
 
 
+def whole_step_bytes(n, m, N, dual):
+    """Algorithmic HBM bytes of one whole scan-path solve: the leaf kernel's bytes, every tier's elements in and out and its
+    records, the top-down pass (records + multipliers) and the down pass (records, knot blocks, multipliers in, solution out)."""
+    stride = 2 * n + 2 * m + 1 + n * n + n * m + n
+    np_ = (n + 3) & ~3
+    ent = 3 * np_ * (np_ + 2) + 2 * np_ if dual else (2 * (2 * n + m) * n + (2 * n + m) + n + 1) & ~1
+    wsz = (2 * n + 1) * n
+    M0 = N // 4
+    leaf = M0 * (4 * stride + ent + 3 * wsz)
+    tiers, M = 0, M0
+    while M > 1:
+        e = min(4, M)
+        tiers += M * ent + (M // e) * ent + (M - M // e) * wsz
+        M //= e
+    top = (M0 - 1) * wsz + 2 * M0 * n
+    down = M0 * (3 * wsz + 4 * stride + 2 * n) + N * (2 * n + m)
+    return 8 * (leaf + tiers + top + down)
+
+
 # dram__bytes_read.sum + dram__bytes_write.sum of scan_leaf_kernel per problem from the committed ncu --set full capture
-SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM = (497.240576e6 + 788.572672e6) / 1024   # profiles/r01_ncu_scan_v9.md
+# (profiles/r02_ncu_full.md: 497.2 MB + 698.1 MB at batch 1024, hybrid leaf kernel)
+SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM = (497.2e6 + 698.1e6) / 1024
 
 # dram__bytes_read.sum + dram__bytes_write.sum of tier0_kernel per problem, from the committed ncu --set full capture
 # (profiles/r01_ncu_tier0_v1.md: 0.995 GB + 4.060 GB at batch 2048)
@@ -358,6 +378,7 @@ def run_ours(args, rank, world, local_rank):
     from rslqr_b200.lib import pinned_array
     n, m, N, B = args.n, args.m, HORIZON, args.batch
     dual = (n, m) != (12, 4) or bool(int(os.environ.get("RSLQR_DUAL", "0") or 0))
+    hybrid = (n, m) == (12, 4) and not dual and not int(os.environ.get("RSLQR_NO_HYBRID", "0") or 0)
     dist = None
     cpu_binding = bind_to_gpu_cpus(local_rank) if world > 1 and not os.environ.get("RSLQR_BENCH_NO_BIND") else "not bound (one rank)"
     if world > 1:
@@ -452,7 +473,7 @@ def run_ours(args, rank, world, local_rank):
         # dominant kernel of the scan path: scan_leaf_kernel (levels 0 and 1 = 3/4 of all separators), one launch per
         # step, timed with CUDA events on the launching stream by the C-ABI (rslqr_cuda_kernel_timing)
         nsub = B * (N // 4)
-        by_sub = scan_leaf_bytes_per_subtree(n, m, dual)
+        by_sub = scan_leaf_bytes_per_subtree(n, m, dual or hybrid)
         fl_sub = scan_leaf_flops_per_subtree(n, m)
         k_avg_ms = k_ms if k_n else ms_per_step
         ach = nsub * by_sub / (k_avg_ms * 1e-3) / 1e9
@@ -461,10 +482,11 @@ def run_ours(args, rank, world, local_rank):
                            f"scan_leaf_kernel<{n},{m}> (one warp per 4-knot subtree: leaf factors + levels 0..1 on boundary entries)"),
                 "bound": "hbm", "achieved": ach, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": ach / pk["hbm_gbs"],
                 "traffic": SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM * B if SCAN_LEAF_TRAFFIC_BYTES_PER_PROBLEM and (n, m, N) == (12, 4, 256) and not dual else None,
+                "whole_step_hbm_frac": whole_step_bytes(n, m, N, dual or hybrid) * B / (ms_per_step * 1e-3) / 1e9 / pk["hbm_gbs"],
                 "peak_kind": pk_kind, "algorithmic_bytes_per_launch": nsub * by_sub, "bytes_per_subtree": by_sub,
                 "avg_launch_ms": k_avg_ms, "kernel_launches_timed": k_n, "kernel_share_of_step": k_avg_ms / ms_per_step,
-                "binding_unit": "LSU data pipe (shared-memory + shuffle wavefronts) at 75 % of peak and dependent-chain latency at 12 warps/SM; "
-                                "DRAM 25 % busy (ncu --set full, profiles/r01_ncu_scan_v9.md)",
+                "binding_unit": "dependent chains of the 12 pivot steps at 12 warps/SM (LSU data pipe 74 % of peak, DRAM 22 % busy; "
+                                "ncu --set full, profiles/r02_ncu_full.md)",
                 "fp64_tflops_executed": nsub * fl_sub / (k_avg_ms * 1e-3) / 1e12, "fp64_frac_of_dmma_peak": nsub * fl_sub / (k_avg_ms * 1e-3) / 1e12 / fp64["tflops"],
                 "flops_per_subtree": fl_sub,
                 "reference_count_tflops_whole_step": flop_model(n, m, N) * B / (ms_per_step * 1e-3) / 1e12,

@@ -89,10 +89,34 @@ __global__ void __launch_bounds__(256) big_leaf_kernel(Shape s, Bufs b, BigBufs 
     const int r = e / NS, c = e - r * NS;
     E[D::OAA + e] = r == c ? sc[r] : 0.0;
     E[D::OAB + e] = -sc[r] * AB[c + NS * r];  // -A(c, r) / Q(r)   (AB is zero for the last knot)
-    double g = 0.0;
-#pragma unroll 8
-    for (int l = 0; l < XU; ++l) g = fma(AB[r + NS * l] * dv[l], AB[c + NS * l], g);
-    E[D::OBB + e] = g;
+  }
+  // Sbb = [A | B] D [A | B]^T: every thread a 4 x 4 tile of it in registers (rows r0.., columns c0..: 4 + 4 operand loads
+  // per 16 FMA), tiles (NS / 4)^2 over the CTA's threads
+  static_assert(NS % 4 == 0, "4 x 4 register tiles");
+  for (int tile = tid; tile < (NS / 4) * (NS / 4); tile += nthr) {
+    const int r0 = 4 * (tile / (NS / 4)), c0 = 4 * (tile % (NS / 4));
+    double g[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) g[i][j] = 0.0;
+#pragma unroll 4
+    for (int l = 0; l < XU; ++l) {
+      const double d = dv[l];
+      const double2 ra = *reinterpret_cast<const double2*>(AB + r0 + NS * l), rb = *reinterpret_cast<const double2*>(AB + r0 + 2 + NS * l);
+      const double2 ca = *reinterpret_cast<const double2*>(AB + c0 + NS * l), cb = *reinterpret_cast<const double2*>(AB + c0 + 2 + NS * l);
+      const double rv[4] = {ra.x * d, ra.y * d, rb.x * d, rb.y * d};
+      const double cv[4] = {ca.x, ca.y, cb.x, cb.y};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) g[i][j] = fma(rv[i], cv[j], g[i][j]);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      *reinterpret_cast<double2*>(E + D::OBB + (r0 + i) * NS + c0) = make_double2(g[i][0], g[i][1]);
+      *reinterpret_cast<double2*>(E + D::OBB + (r0 + i) * NS + c0 + 2) = make_double2(g[i][2], g[i][3]);
+    }
   }
   for (int r = tid; r < NS; r += nthr) {
     E[D::OSA + r] = -zv[r] - sc[NS + r];

@@ -312,11 +312,20 @@ __global__ void __launch_bounds__(32 * DUAL_WPC) dual_leaf_kernel(Shape s, Bufs 
 // subtree that starts right after the separator), the CTA's merged entry to `out`.
 // ---------------------------------------------------------------------------------------------------------
 struct DualTierArgs {
-  const double* in;   // [batch][Min][ENT]
-  double* out;        // [batch][Min / ecount][ENT] or nullptr (last tier)
-  double* sep;        // [batch][M0][WSZ]
-  int Min, ecount, M0;
-  int span4;          // 4-knot subtrees per input entry (record slot of the separator after entry e: (e + 1) * span4)
+  const double* in;      // element e of problem p: in + (p*Min + e)*in_stride
+  long long in_stride;   // ENT when the elements are packed (one bulk copy per CTA), else one copy per element
+  double* out;           // merged element of CTA c of problem p: out + (p*ncta + c)*out_stride; nullptr = none
+  long long out_stride;
+  double* sep;           // record of the separator after element e: sep + p*sep_pstride + (e+1)*sep_mul*WSZ
+  long long sep_pstride;
+  int sep_mul;
+  int Min, ecount;
+  int span;              // knots per input element (status words only; 0 = cross-GPU tier: flags only)
+  int root_out;          // the last merge of a single-CTA tier also produces its element (a shard's contribution), R-type
+  int root_right;        // if root_right (the shard's rank is odd)
+  // cross-GPU tier fed by peer stores over NVLink (shard_push_kernel): element e is complete once wait_flags[e] >= wait_epoch
+  const unsigned long long* wait_flags;
+  unsigned long long wait_epoch;
 };
 
 template <int NS>
@@ -334,14 +343,29 @@ __global__ void __launch_bounds__(128) dual_tier_kernel(Shape s, Bufs b, DualTie
   double* scr = ents + ecount * D::ENT + warp * dual_tier_warp_scratch<NS>();
   double* W = scr;
   double* Lr = scr + ((D::WP + 1) & ~1);
-  const double* in = a.in + ((size_t)prob * a.Min + (size_t)sg * ecount) * D::ENT;
+  const double* in = a.in + ((size_t)prob * a.Min + (size_t)sg * ecount) * a.in_stride;
   if (tid == 0) {
     mbar_init(&mbar, 1);
     fence_mbar_init();
-    mbar_expect_tx(&mbar, ecount * D::ENT * (int)sizeof(double));
-    bulk_g2s(ents, in, ecount * D::ENT * (int)sizeof(double), &mbar);
   }
   __syncthreads();
+  if (a.wait_flags) {  // elements arrive by peer stores: wait for their flags (bounded: a lost peer must not hang the GPU)
+    if (tid < a.Min) {
+      const unsigned long long t0 = global_ns();
+      while (ld_acquire_sys(a.wait_flags + tid) < a.wait_epoch) {
+        if (global_ns() - t0 > 4000000000ull) { b.flags[prob] = 2; break; }
+        __nanosleep(64);
+      }
+    }
+    __syncthreads();
+    asm volatile("fence.proxy.async;" ::: "memory");  // the TMA (async proxy) reads what the acquire made visible
+  }
+  if (tid == 0) {
+    mbar_expect_tx(&mbar, ecount * D::ENT * (int)sizeof(double));
+    if (a.in_stride == D::ENT) bulk_g2s(ents, in, ecount * D::ENT * (int)sizeof(double), &mbar);
+    else
+      for (int e = 0; e < ecount; ++e) bulk_g2s(ents + e * D::ENT, in + e * a.in_stride, D::ENT * (int)sizeof(double), &mbar);
+  }
   mbar_wait(&mbar, 0);
   int levels = 0;
   while ((1 << levels) < ecount) ++levels;
@@ -349,19 +373,21 @@ __global__ void __launch_bounds__(128) dual_tier_kernel(Shape s, Bufs b, DualTie
     if (l > 0) __syncthreads();
     const int nsep = ecount >> (l + 1);
     if (warp < nsep) {
-      const int el = (2 * warp) << l, er = el + (1 << l);   // merged entries live in the slot of their first entry
-      const int ge_last = sg * ecount + er - 1;             // last input entry of the left subtree
+      const int el = (2 * warp) << l, er = el + (1 << l);   // merged elements live in the slot of their first element
+      const int ge_last = sg * ecount + er - 1;             // last input element of the left subtree
       const int oidx = (sg * ecount + el) >> (l + 1);       // index of the merged subtree at its level
       const bool root = a.Min == ecount && l == levels - 1;
       double* EL = ents + el * D::ENT;
-      const int bad = dual_merge<NS>(EL, ents + er * D::ENT, root ? nullptr : EL, (oidx & 1) != 0, W, Lr);
-      const int slot = (ge_last + 1) * a.span4;
-      dual_store_record<NS>(a.sep + ((size_t)prob * a.M0 + slot) * D::WSZ, W);
+      const bool oright = root ? a.root_right != 0 : (oidx & 1) != 0;
+      const int bad = dual_merge<NS>(EL, ents + er * D::ENT, (root && !a.root_out) ? nullptr : EL, oright, W, Lr);
+      dual_store_record<NS>(a.sep + (size_t)prob * a.sep_pstride + (size_t)(ge_last + 1) * a.sep_mul * D::WSZ, W);
       if (bad && lane == 0) {
-        const int i = slot * SCAN_LEAF - 1;                 // local knot index of the separator
-        int lev = 0;
-        while ((i >> lev) & 1) ++lev;
-        b.status[(size_t)prob * 3 * s.N + rs_slot_S(i >> (lev + 1), lev, s.N)] = -1;
+        if (a.span > 0) {
+          const int i = (ge_last + 1) * a.span - 1;         // local knot index of the separator
+          int lev = 0;
+          while ((i >> lev) & 1) ++lev;
+          b.status[(size_t)prob * 3 * s.N + rs_slot_S(i >> (lev + 1), lev, s.N)] = -1;
+        }
         b.flags[prob] = 1;
       }
     }
@@ -371,7 +397,7 @@ __global__ void __launch_bounds__(128) dual_tier_kernel(Shape s, Bufs b, DualTie
     fence_async_smem();
     __syncthreads();
     if (tid == 0) {
-      bulk_s2g(a.out + ((size_t)prob * ncta + sg) * D::ENT, ents, D::ENT * (int)sizeof(double));
+      bulk_s2g(a.out + ((size_t)prob * ncta + sg) * a.out_stride, ents, D::ENT * (int)sizeof(double));
       bulk_commit();
       bulk_wait_read0();
     }
@@ -384,6 +410,39 @@ __global__ void __launch_bounds__(128) dual_tier_kernel(Shape s, Bufs b, DualTie
 inline bool dual_shape_ok(int n, int m) {
   return (n == 6 && m == 3) || (n == 12 && m == 4) || (n == 12 && m == 6) || (n == 8 && m == 4) || (n == 16 && m == 8) ||
          (n == 4 && m == 2);
+}
+
+template <int NS>
+inline void dual_launch_tier(const Shape& s, const Bufs& b, const DualTierArgs& a, int batch, cudaStream_t st) {
+  using D = DualDim<NS>;
+  const int warps = a.ecount / 2 > 0 ? a.ecount / 2 : 1;
+  const int sm = (a.ecount * D::ENT + warps * dual_tier_warp_scratch<NS>()) * (int)sizeof(double);
+  dual_tier_kernel<NS><<<(unsigned)((size_t)batch * (a.Min / a.ecount)), 32 * warps, sm, st>>>(s, b, a);
+}
+
+// the local tiers of the plan. last_out: where the last tier puts the merged element of the whole local tree (a shard's
+// contribution to the exchange), R-type if root_right; nullptr = the local tree is the whole problem.
+template <int NS>
+inline cudaError_t dual_launch_tiers(ScanPlan& p, const Shape& s, const Bufs& b, int batch, cudaStream_t st, double* last_out,
+                                     long long last_out_stride, int root_right) {
+  using D = DualDim<NS>;
+  FusedPlan& f = p.f;
+  cudaError_t e = smem_optin(dual_tier_kernel<NS>, (8 * D::ENT + 4 * dual_tier_warp_scratch<NS>()) * (int)sizeof(double));
+  if (e != cudaSuccess) return e;
+  for (int t = 0; t < f.ntiers; ++t) {
+    const FusedTier& T = f.tiers[t];
+    const bool last = t == f.ntiers - 1;
+    DualTierArgs a{};
+    a.in = f.fb.ent[t]; a.in_stride = D::ENT;
+    a.out = last ? last_out : f.fb.ent[t + 1];
+    a.out_stride = last ? last_out_stride : D::ENT;
+    a.sep = f.fb.sep; a.sep_pstride = (long long)f.M0 * D::WSZ; a.sep_mul = T.span / SCAN_LEAF;
+    a.Min = T.Min; a.ecount = T.ecount; a.span = T.span;
+    a.root_out = last && last_out ? 1 : 0; a.root_right = root_right;
+    dual_launch_tier<NS>(s, b, a, batch, st);
+    ++f.launches;
+  }
+  return cudaGetLastError();
 }
 
 template <int NS, int NI>
@@ -409,21 +468,7 @@ inline cudaError_t dual_launch_t(ScanPlan& p, const Shape& s, const Bufs& b, int
                                                                                                           pack_rhs, f.M0, nsub);
   }
   if (k1) cudaEventRecord(k1, st);
-  e = smem_optin(dual_tier_kernel<NS>, (8 * D::ENT + 4 * dual_tier_warp_scratch<NS>()) * (int)sizeof(double));
-  if (e != cudaSuccess) return e;
-  for (int t = 0; t < f.ntiers; ++t) {
-    const FusedTier& T = f.tiers[t];
-    DualTierArgs a{};
-    a.in = f.fb.ent[t];
-    a.out = t == f.ntiers - 1 ? nullptr : f.fb.ent[t + 1];
-    a.sep = f.fb.sep;
-    a.Min = T.Min; a.ecount = T.ecount; a.M0 = f.M0; a.span4 = T.span / SCAN_LEAF;
-    const int warps = T.ecount / 2 > 0 ? T.ecount / 2 : 1;
-    const int sm = (T.ecount * D::ENT + warps * dual_tier_warp_scratch<NS>()) * (int)sizeof(double);
-    dual_tier_kernel<NS><<<(unsigned)((size_t)batch * (T.Min / T.ecount)), 32 * warps, sm, st>>>(s, b, a);
-    ++f.launches;
-  }
-  e = cudaGetLastError();
+  e = dual_launch_tiers<NS>(p, s, b, batch, st, nullptr, 0, 0);
   if (e != cudaSuccess) return e;
   return launch_scan_down<NS, NI>(p, s, b, batch, pack_rhs, st, nullptr, nullptr);
 }
@@ -440,6 +485,47 @@ inline int dual_launch(ScanPlan& p, const Shape& s, const Bufs& b, int batch, in
   else if (s.n == 4 && s.m == 2) e = dual_launch_t<4, 2>(p, s, b, batch, pack_rhs, st, k0, k1);
   else { err = "shape not covered by the dual-form scan kernels"; return -5; }
   if (e != cudaSuccess) { err = std::string("dual launch: ") + cudaGetErrorString(e); return -3; }
+  return 0;
+}
+
+// ---- shards of one long horizon in hybrid form (n = 12, m = 4): the exchange payload is the shard's dual element (its
+//      Schur complement onto lambda of its first knot and of the first knot of the next shard), nothing else ----
+inline int dual_shard_reduce(ScanPlan& p, const Shape& s, const Bufs& b, int pack_rhs, cudaStream_t st, double* payload,
+                             std::string& err) {
+  using D = DualDim<12>;
+  if (!p.f.available || !p.hybrid || p.f.ntiers < 1) { err = "shard needs the hybrid scan kernels and at least two subtrees"; return -5; }
+  p.f.launches = 1;
+  cudaError_t e = launch_scan_leaf<12, 4>(p, s, b, 1, pack_rhs, st);
+  if (e == cudaSuccess) e = dual_launch_tiers<12>(p, s, b, 1, st, payload, D::ENT, (s.kofs / s.N) & 1);
+  if (e != cudaSuccess) { err = std::string("shard reduce: ") + cudaGetErrorString(e); return -3; }
+  return 0;
+}
+
+inline int dual_shard_finish(ScanPlan& p, const Shape& s, const Bufs& b, int pack_rhs, cudaStream_t st, const double* gathered,
+                             int rank, int nranks, std::string& err, const unsigned long long* wait_flags = nullptr,
+                             unsigned long long wait_epoch = 0) {
+  using D = DualDim<12>;
+  if (!p.f.available || !p.hybrid || p.f.ntiers < 1) { err = "shard needs the hybrid scan kernels"; return -5; }
+  const double *left = nullptr, *right = nullptr;
+  cudaError_t e = cudaSuccess;
+  if (nranks > 1) {
+    e = smem_optin(dual_tier_kernel<12>, (8 * D::ENT + 4 * dual_tier_warp_scratch<12>()) * (int)sizeof(double));
+    if (e == cudaSuccess) {
+      DualTierArgs a{};
+      a.in = gathered; a.in_stride = D::ENT;
+      a.out = nullptr; a.out_stride = 0;
+      a.sep = p.f.xsep; a.sep_pstride = 0; a.sep_mul = 1;
+      a.Min = nranks; a.ecount = nranks; a.span = 0;
+      a.wait_flags = wait_flags; a.wait_epoch = wait_epoch;
+      dual_launch_tier<12>(s, b, a, 1, st);  // every rank runs the top log2(nranks) levels redundantly, bit-identically
+      topdown_kernel<12><<<1, 128, 0, st>>>(p.f.xsep, p.f.xlam, nranks, nullptr, nullptr, nranks, 1);
+      p.f.launches += 2;
+      left = p.f.xlam + (size_t)rank * 12;
+      right = p.f.xlam + (size_t)(rank + 1) * 12;
+    }
+  }
+  if (e == cudaSuccess) e = launch_scan_down<12, 4>(p, s, b, 1, pack_rhs, st, left, right);
+  if (e != cudaSuccess) { err = std::string("shard finish: ") + cudaGetErrorString(e); return -3; }
   return 0;
 }
 

@@ -300,11 +300,11 @@ __device__ __forceinline__ int merge_raw(const double* Bl, const double* Br, con
 //   lambda_a     :  x_a                       ->  Saa = -L_X(a), Sab = -R_X(a), sa = -z_x(a) - z_lambda(a)
 //   lambda_{b+1} : -(A_b x_b + B_b u_b)       ->  [Sba | Sbb | sb] = [A_b | B_b] [L | R | z]_{X,U rows of b}
 // the second being the product every later ndlqr_FactorInnerProduct (src/nested_dissection.c:114) would apply to
-// these rows: it is applied here once. E: entry (Dim layout), AB: [A_b | B_b] in global memory, Eo: dual entry
+// these rows: it is applied here once. E: entry (Dim layout), AB: [A_b | B_b] (global memory if LDG, else shared), Eo: dual entry
 // (DualDim layout, R-type if `right` else L-type; must not alias E). One warp.
 // ---------------------------------------------------------------------------------------------------------
-template <int NS, int NI>
-__device__ __forceinline__ void entry_to_dual(const double* E, const double* __restrict__ AB, double* Eo, bool right) {
+template <int NS, int NI, bool LDG = true>
+__device__ __forceinline__ void entry_to_dual(const double* E, const double* __restrict__ AB, double* Eo, bool right, bool lastb) {
   using D = Dim<NS, NI>;
   using DD = DualDim<NS>;
   constexpr int SLOT = D::SLOT, ZS = D::ZS, LD = DD::LD, KS = (NS + NI) / 4;
@@ -321,8 +321,9 @@ __device__ __forceinline__ void entry_to_dual(const double* E, const double* __r
 #pragma unroll
   for (int ks = 0; ks < KS; ++ks) {
     const int l = 4 * ks + q;
-    const double a0 = __ldg(AB + l * NS + rr);
-    const double a1 = (8 + rr < NS) ? __ldg(AB + l * NS + 8 + rr) : 0.0;
+    // (b = last knot of the horizon: its A, B are ignored, SURVEY A.1 -- there is no multiplier behind it to couple to)
+    const double a0 = lastb ? 0.0 : (LDG ? __ldg(AB + l * NS + rr) : AB[l * NS + rr]);
+    const double a1 = (8 + rr < NS && !lastb) ? (LDG ? __ldg(AB + l * NS + 8 + rr) : AB[l * NS + 8 + rr]) : 0.0;
     double bf[4];
 #pragma unroll
     for (int nt = 0; nt < 4; ++nt) {
@@ -451,10 +452,26 @@ __global__ void __launch_bounds__(32 * SCAN_WPC, 2) scan_leaf_kernel(Shape s, Bu
       b.flags[prob] = 1;
     }
   }
-  // ---- level 1: E0 + E1 -> E0 (separator after knot k0+1); W and the factor scratch in the dead blocks 2, 3 ----
-  double* Wf = B23;
+  // ---- level 1: E0 + E1 -> E0 (separator after knot k0+1); W and the factor scratch in the dead blocks 0, 1 (the
+  //      [A | B] of block 1 is the last thing read there: the hook syncs the warp before the first write). Block 3
+  //      keeps its [A | B] for the conversion of the merged entry below. ----
+  double* Wf = R + NS;
+  static_assert((NS * 8) % 16 == 0, "W is 16-byte aligned behind the z_lambda slot");
+  // [A | B] of the subtree's last knot was overwritten by the record of merge (k0, k0+1): once the copy engine has read
+  // that record, fetch it again (8-byte cp.async, it is L2-resident) into its old place; it lands while the
+  // factorization below runs and is what entry_to_dual multiplies the boundary rows with
+  double* ABlast = R + NS + (SCAN_LEAF - 1) * RD::STRIDE + RD::OA;
+  auto hook1 = [&]() {
+    rec_done();
+    if (dual_out && M0 > 1) {
+      const double* src = knot_ptr(s, b, prob, k0 + SCAN_LEAF - 1) + s.oA;
+      for (int e = lane; e < RD::AB; e += 32)
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(ABlast + e)), "l"(src + e) : "memory");
+      asm volatile("cp.async.commit_group;" ::: "memory");
+    }
+  };
   bad = spine_merge<NS, NI, false, true>(R + NS + RD::STRIDE + RD::OA, E0 + NS * NS, E0 + SLOT + NS * NS, E0 + 2 * SLOT + NS, E1,
-                                         E1 + SLOT, E1 + 2 * SLOT, E1 + 2 * SLOT + ZS, B23 + WSZ, Wf, rec_done);
+                                         E1 + SLOT, E1 + 2 * SLOT, E1 + 2 * SLOT + ZS, Wf + WSZ, Wf, hook1);
   store_rec(1, Wf);
   if (bad && lane == 0) {
     b.status[(size_t)prob * 3 * N + rs_slot_S(k0 >> 2, 1, N)] = -1;
@@ -467,8 +484,10 @@ __global__ void __launch_bounds__(32 * SCAN_WPC, 2) scan_leaf_kernel(Shape s, Bu
       // built in the now dead right entry
       using DD = DualDim<NS>;
       static_assert(DD::ENT <= ENT, "the dual element fits in the dead entry");
+      asm volatile("cp.async.wait_all;" ::: "memory");
       __syncwarp();
-      entry_to_dual<NS, NI>(E0, knot_ptr(s, b, prob, k0 + SCAN_LEAF - 1) + s.oA, E1, (grp & 1) != 0);
+      entry_to_dual<NS, NI, false>(E0, ABlast, E1, (grp & 1) != 0,
+                                   s.kofs + k0 + SCAN_LEAF - 1 == s.Ng - 1);
       fence_async_smem();
       __syncwarp();
       if (lane == 0) {

@@ -137,7 +137,10 @@ extern "C" int rslqr_cuda_create(int n, int m, int N, int batch, int device, uns
     memset(&h->scan, 0, sizeof(h->scan));
     memset(&h->fused, 0, sizeof(h->fused));
     h->big.covered = big_shape_ok(n, m, N) && !(flags & RSLQR_INTERNAL_SHARD);
-    if (scan_plan(h->s, h->batch, &h->scan, g_err, !(flags & RSLQR_INTERNAL_SHARD))) {
+    // shards take the hybrid form too (their exchange payload is then the shard's dual element); RSLQR_SHARD_CLASSIC=1
+    // keeps the boundary-entry shard path of round 1 (A/B runs)
+    const char* sc = getenv("RSLQR_SHARD_CLASSIC");
+    if (scan_plan(h->s, h->batch, &h->scan, g_err, !((flags & RSLQR_INTERNAL_SHARD) && sc && atoi(sc)))) {
       rslqr_cuda_destroy(h);
       return RSLQR_E_NOMEM;
     }
@@ -927,9 +930,10 @@ extern "C" int rslqr_cuda_create_shard(int n, int m, int nhorizon, int first_kno
   return RSLQR_OK;
 }
 
-extern "C" size_t rslqr_cuda_shard_payload_doubles(rslqr_cuda_solver* h) {
-  return h ? fused_payload_doubles(h->s.n, h->s.m) : 0;
+static size_t shard_payload(const rslqr_cuda_solver* h) {
+  return (h->scan.f.available && h->scan.hybrid) ? dual_ent_doubles(h->s.n) : fused_payload_doubles(h->s.n, h->s.m);
 }
+extern "C" size_t rslqr_cuda_shard_payload_doubles(rslqr_cuda_solver* h) { return h ? shard_payload(h) : 0; }
 
 extern "C" int rslqr_cuda_shard_reduce(rslqr_cuda_solver* h, double* d_payload) {
   if (!h || !d_payload || !h->shard) return fail(RSLQR_E_ARG, "shard_reduce: bad argument");
@@ -939,7 +943,8 @@ extern "C" int rslqr_cuda_shard_reduce(rslqr_cuda_solver* h, double* d_payload) 
     if (rc) return rc;
   }
   if (rslqr_cuda_get_mode(h) == RSLQR_MODE_SCAN) {
-    int rc = scan_shard_reduce(h->scan, h->s, h->b, 1, h->stream, d_payload, g_err);
+    int rc = h->scan.hybrid ? dual_shard_reduce(h->scan, h->s, h->b, 1, h->stream, d_payload, g_err)
+                            : scan_shard_reduce(h->scan, h->s, h->b, 1, h->stream, d_payload, g_err);
     h->launches = h->scan.f.launches;
     return rc;
   }
@@ -954,7 +959,8 @@ extern "C" int rslqr_cuda_shard_finish(rslqr_cuda_solver* h, const double* d_gat
     return fail(RSLQR_E_ARG, "shard_finish: bad argument (rank / nranks must match the shard's position; nranks <= 8)");
   CU(cudaSetDevice(h->device));
   if (rslqr_cuda_get_mode(h) == RSLQR_MODE_SCAN) {
-    int rc = scan_shard_finish(h->scan, h->s, h->b, 1, h->stream, d_gathered, rank, nranks, g_err);
+    int rc = h->scan.hybrid ? dual_shard_finish(h->scan, h->s, h->b, 1, h->stream, d_gathered, rank, nranks, g_err)
+                            : scan_shard_finish(h->scan, h->s, h->b, 1, h->stream, d_gathered, rank, nranks, g_err);
     h->launches = h->scan.f.launches;
     return rc;
   }
@@ -975,7 +981,7 @@ extern "C" int rslqr_cuda_shard_push(rslqr_cuda_solver* h, const double* d_paylo
   PeerPtrs pp;
   memset(&pp, 0, sizeof(pp));
   for (int r = 0; r < nranks; ++r) { pp.gathered[r] = peer_gathered[r]; pp.flags[r] = peer_flags[r]; }
-  const int pay = (int)fused_payload_doubles(h->s.n, h->s.m);
+  const int pay = (int)shard_payload(h);
   shard_push_kernel<<<nranks, 256, 0, h->stream>>>(d_payload, pp, rank, pay, epoch);
   CU(cudaGetLastError());
   ++h->launches;
@@ -989,7 +995,8 @@ extern "C" int rslqr_cuda_shard_finish_wait(rslqr_cuda_solver* h, const double* 
     return fail(RSLQR_E_ARG, "shard_finish_wait: bad argument");
   if (rslqr_cuda_get_mode(h) != RSLQR_MODE_SCAN) return fail(RSLQR_E_UNSUPPORTED, "the peer-to-peer exchange needs the scan kernels");
   CU(cudaSetDevice(h->device));
-  int rc = scan_shard_finish(h->scan, h->s, h->b, 1, h->stream, d_gathered, rank, nranks, g_err, d_flags, epoch);
+  int rc = h->scan.hybrid ? dual_shard_finish(h->scan, h->s, h->b, 1, h->stream, d_gathered, rank, nranks, g_err, d_flags, epoch)
+                          : scan_shard_finish(h->scan, h->s, h->b, 1, h->stream, d_gathered, rank, nranks, g_err, d_flags, epoch);
   h->launches = h->scan.f.launches;
   return rc;
 }
@@ -1009,7 +1016,7 @@ extern "C" int rslqr_cuda_set_stream(rslqr_cuda_solver* h, void* stream) {
 // d_payload[r] / d_gathered[r] are device buffers on shard r's device (payload / nranks * payload doubles).
 extern "C" int rslqr_cuda_shard_exchange(rslqr_cuda_solver** hs, int nranks, double** d_payload, double** d_gathered) {
   if (!hs || !d_payload || !d_gathered || nranks < 1) return fail(RSLQR_E_ARG, "shard_exchange: bad argument");
-  const size_t pay = rslqr_cuda_shard_payload_doubles(hs[0]);
+  const size_t pay = shard_payload(hs[0]);
   for (int r = 0; r < nranks; ++r) {  // payloads complete
     CU(cudaSetDevice(hs[r]->device));
     CU(cudaStreamSynchronize(hs[r]->stream));

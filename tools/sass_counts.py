@@ -23,7 +23,7 @@ def main():
             fn = fn.replace("void rslqr::", "")
             counts[fn] = collections.Counter()
             continue
-        m = re.match(r"\s+/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_]+)((?:\.[A-Z0-9_]+)*)", line)
+        m = re.match(r"\s+/\*[0-9a-f]{4,}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_]+)((?:\.[A-Z0-9_]+)*)", line)
         if m and fn:
             counts[fn][m.group(1)] += 1
             counts[fn]["_total"] += 1
