@@ -32,6 +32,7 @@ struct BigBufs {
   double* entB;  // [batch][N/2][ENT]    elements of the odd levels
   double* rec;   // [batch][N][WSZ]      record of the separator after knot i at slot i (slot N-1 unused)
   double* lam;   // [batch][N+1][NS]     multipliers lambda_k; slots 0 and N stay zero
+  double* ufac;  // [batch][N/2][BigFac::SIZE] factor U, block inverses and 1/d of the merges of the level in flight
 };
 
 // ---------------------------------------------------------------------------------------------------------
@@ -42,7 +43,7 @@ struct BigBufs {
 // dynamic smem: (NS*(NS+NI) + 2*(NS+NI) + 2*NS) doubles
 // ---------------------------------------------------------------------------------------------------------
 template <int NS, int NI>
-__global__ void __launch_bounds__(256) big_leaf_kernel(Shape s, Bufs b, BigBufs bb, int pack_rhs) {
+__global__ void __launch_bounds__(256, 2) big_leaf_kernel(Shape s, Bufs b, BigBufs bb, int pack_rhs) {
   using D = BigDim<NS>;
   constexpr int XU = NS + NI;
   extern __shared__ __align__(16) double smf[];
@@ -100,7 +101,7 @@ __global__ void __launch_bounds__(256) big_leaf_kernel(Shape s, Bufs b, BigBufs 
     for (int i = 0; i < 4; ++i)
 #pragma unroll
       for (int j = 0; j < 4; ++j) g[i][j] = 0.0;
-#pragma unroll 4
+#pragma unroll 2
     for (int l = 0; l < XU; ++l) {
       const double d = dv[l];
       const double2 ra = *reinterpret_cast<const double2*>(AB + r0 + NS * l), rb = *reinterpret_cast<const double2*>(AB + r0 + 2 + NS * l);
@@ -222,6 +223,256 @@ __global__ void __launch_bounds__(big_spine_threads<NS>()) big_spine_kernel(Shap
   if (tid == 0 && s_bad) {
     b.status[(size_t)prob * 3 * N + rs_slot_S(t, level, N)] = -1;
     b.flags[prob] = 1;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// The same spine as big_spine_kernel, split so that the 2n+1 solves run on the fp64 tensor cores (RSLQR_BIG_SPINE=1
+// selects the single-kernel variant above for A/B runs):
+//
+//   big_factor_kernel : ONE WARP per merge. S = SbbL + SaaR is built in shared memory and factored in place,
+//                       S = U^T D U (right-looking LDL^T, the warp's lanes own the rows below the pivot; no CTA barrier,
+//                       so the pivot chains of the merges of a CTA overlap). Output per merge (`ufac`): U (unit upper,
+//                       row-major ld NS), the inverses X_b of the 8 x 8 diagonal blocks of L = U^T, and 1/d.
+//   big_solve_kernel  : one CTA of 8 warps per merge. Y = [S_L | S_R | s] (NS x 2NS+1, padded to 17 column tiles of 8) and U
+//                       are staged in shared memory; a warp owns column tiles and runs BOTH blocked substitution sweeps
+//                       for them without any CTA barrier: for block row b,
+//                           W_b = X_b (Y_b - sum_{b' < b} L_bb' W_b'),   then   F_b = X_b^T (D^-1 W_b - sum_{b' > b} U_bb' F_b')
+//                       every product an m8n8k4 DMMA pair (the 8 x 8 blocks are the A operands, the column tile of Y the B
+//                       operand, read back from shared memory in B-fragment layout). [f_L | f_R | zs] = F goes to the record.
+// ---------------------------------------------------------------------------------------------------------
+template <int NS>
+struct BigFac {
+  static constexpr int NB = NS / 8;
+  static constexpr int OU = 0, OX = NS * NS, OD = NS * NS + NB * 64, SIZE = NS * NS + NB * 64 + NS;  // doubles per merge in `ufac`
+};
+
+constexpr int BIG_FACTOR_WPC = 12;  // merges (warps) per CTA of big_factor_kernel
+
+// packed lower triangle: element (i, k), k <= i, at i (i + 1) / 2 + k
+__device__ __forceinline__ int big_tri(int i) { return (i * (i + 1)) >> 1; }
+
+template <int NS>
+__host__ __device__ constexpr int big_factor_warp_doubles() { return ((NS * (NS + 1) / 2) + 1) & ~1; }
+
+template <int NS>
+__global__ void __launch_bounds__(32 * BIG_FACTOR_WPC) big_factor_kernel(Shape s, Bufs b, const double* ein, double* ufac, int level,
+                                                                          int M, long long nmerge) {
+  using D = BigDim<NS>;
+  using F = BigFac<NS>;
+  static_assert(NS == 64, "two trailing columns per lane");
+  extern __shared__ __align__(16) double smf[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long mi = (long long)blockIdx.x * BIG_FACTOR_WPC + warp;
+  if (mi >= nmerge) return;
+  const int N = s.N;
+  const int prob = (int)(mi / M), t = (int)(mi % M);
+  double* A = smf + (size_t)warp * big_factor_warp_doubles<NS>();   // lower triangle of S, packed by rows
+  const double* EL = ein + ((size_t)prob * 2 * M + 2 * t) * D::ENT;
+  const double* ER = EL + D::ENT;
+  for (int e = lane; e < NS * NS; e += 32) {
+    const int r = e / NS, c = e - r * NS;
+    if (c <= r) A[big_tri(r) + c] = __ldg(EL + D::OBB + e) + __ldg(ER + D::OAA + e);
+  }
+  __syncwarp();
+  double* U = ufac + (size_t)mi * F::SIZE;
+  int bad = 0;
+  // right-looking LDL^T on the lower triangle: after step j column j holds the multipliers l(i,j) = S'(i,j) / d_j.
+  // A lane owns the trailing COLUMNS k0 = j + 1 + lane and k1 = k0 + 32: the update S'(i,k) -= l(i,j) S'(k,j) walks down
+  // the rows i >= k with S'(k,j) in a register, l(i,j) a broadcast load and S'(i, k0..) one contiguous run per row.
+#pragma unroll 1
+  for (int j = 0; j < NS; ++j) {
+    const double d = A[big_tri(j) + j];
+    if (!(d > 0.0)) bad = 1;
+    const double dinv = 1.0 / d;
+    const int k0 = j + 1 + lane, k1 = k0 + 32;
+    const bool two = j + 33 < NS;                                    // (warp-uniform) a second column per lane exists
+    const double c0 = k0 < NS ? A[big_tri(k0) + j] : 0.0, c1 = k1 < NS ? A[big_tri(k1) + j] : 0.0;  // unscaled S'(k, j)
+    __syncwarp();
+    if (k0 < NS) A[big_tri(k0) + j] = c0 * dinv;
+    if (k1 < NS) A[big_tri(k1) + j] = c1 * dinv;
+    if (lane == 0) A[big_tri(j) + j] = dinv;
+    __syncwarp();
+#pragma unroll 1
+    for (int i = j + 1; i < NS; i += 4) {
+      double li[4], a0[4], a1[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {  // all loads of the group before any store (the compiler cannot tell they do not alias)
+        const int r = i + u < NS ? i + u : NS - 1;
+        const int base = big_tri(r);
+        li[u] = A[base + j];
+        a0[u] = k0 <= r ? A[base + k0] : 0.0;
+        a1[u] = (two && k1 <= r) ? A[base + k1] : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int r = i + u;
+        const int base = big_tri(r < NS ? r : NS - 1);
+        if (r < NS && k0 <= r) A[base + k0] = fma(-li[u], c0, a0[u]);
+        if (two && r < NS && k1 <= r) A[base + k1] = fma(-li[u], c1, a1[u]);
+      }
+    }
+    __syncwarp();
+  }
+  // U(j,k) = l(k,j) for k > j (row-major, ld NS), unit diagonal implied; 1/d
+  for (int e = lane; e < NS * NS; e += 32) {
+    const int j = e / NS, k = e - j * NS;
+    U[F::OU + e] = k > j ? A[big_tri(k) + j] : (k == j ? 1.0 : 0.0);
+  }
+  for (int j = lane; j < NS; j += 32) U[F::OD + j] = A[big_tri(j) + j];
+  // X_b = inverse of the unit lower 8 x 8 diagonal block of L = U^T: lane = (4 blocks per round) x 8 columns
+#pragma unroll 1
+  for (int round = 0; round < F::NB / 4; ++round) {
+    const int blk = 4 * round + (lane >> 3), c = lane & 7;
+    double x[8];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+      double v = r == c ? 1.0 : 0.0;
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        if (k < r) v = fma(-A[big_tri(8 * blk + r) + 8 * blk + k], x[k], v);   // T(r, k) = l(8blk + r, 8blk + k)
+      x[r] = r < c ? 0.0 : v;
+    }
+#pragma unroll
+    for (int r = 0; r < 8; ++r) U[F::OX + blk * 64 + r * 8 + c] = x[r];
+  }
+  if (bad && lane == 0) {
+    b.status[(size_t)prob * 3 * N + rs_slot_S(t, level, N)] = -1;
+    b.flags[prob] = 1;
+  }
+}
+
+// Both substitution sweeps for T column tiles at once, RIGHT-LOOKING: the 8 block rows of a tile stay in registers as
+// DMMA accumulators (C fragments); once block row b is final it goes through shared memory once (C layout -> B
+// fragment) and every other block row still to be solved is updated with it, so a B fragment is loaded once per block
+// and an A fragment (8 x 8 block of U) once per DMMA pair of T tiles. The solved tile leaves from registers straight
+// to the record.
+//   forward : W_b = X_b Y_b, then Y_c -= L_cb W_b for c > b          (L_cb (r, k) = U(8b + k, 8c + r))
+//   scaling : V = D^-1 W
+//   backward: F_b = X_b^T V_b, then V_c -= U_cb F_b for c < b
+template <int NS, int T>
+__device__ __forceinline__ void big_solve_tiles(const double* Us, const double* Xs, const double* ds, double* const (&Yt)[T],
+                                                double* const (&rec)[T], const int (&ncols)[T]) {
+  constexpr int NB = NS / 8, LDU = NS + 4, LDY = 2 * NS + 8;
+  const int lane = threadIdx.x & 31, q = lane & 3, rr = lane >> 2;
+  double c[NB][T][2];
+#pragma unroll
+  for (int bk = 0; bk < NB; ++bk)
+#pragma unroll
+    for (int u = 0; u < T; ++u) {
+      const double2 cv = *reinterpret_cast<const double2*>(Yt[u] + (8 * bk + rr) * LDY + 2 * q);
+      c[bk][u][0] = cv.x; c[bk][u][1] = cv.y;
+    }
+  __syncwarp();
+  // C fragment of block row `bk` -> shared memory -> product with an 8 x 8 block (A fragments a0, a1) -> C fragment
+  auto through = [&](int bk, double (&v)[T][2], double a0, double a1) {
+#pragma unroll
+    for (int u = 0; u < T; ++u) *reinterpret_cast<double2*>(Yt[u] + (8 * bk + rr) * LDY + 2 * q) = make_double2(v[u][0], v[u][1]);
+    __syncwarp();
+#pragma unroll
+    for (int u = 0; u < T; ++u) {
+      const double b0 = Yt[u][(8 * bk + q) * LDY + rr], b1 = Yt[u][(8 * bk + 4 + q) * LDY + rr];
+      v[u][0] = v[u][1] = 0.0;
+      dmma884(v[u][0], v[u][1], a0, b0);
+      dmma884(v[u][0], v[u][1], a1, b1);
+    }
+    __syncwarp();
+  };
+  // block row `bk` (final) as B fragments
+  auto as_b = [&](int bk, const double (&v)[T][2], double (&bf)[T][2]) {
+#pragma unroll
+    for (int u = 0; u < T; ++u) *reinterpret_cast<double2*>(Yt[u] + (8 * bk + rr) * LDY + 2 * q) = make_double2(v[u][0], v[u][1]);
+    __syncwarp();
+#pragma unroll
+    for (int u = 0; u < T; ++u) { bf[u][0] = Yt[u][(8 * bk + q) * LDY + rr]; bf[u][1] = Yt[u][(8 * bk + 4 + q) * LDY + rr]; }
+    __syncwarp();
+  };
+#pragma unroll
+  for (int bk = 0; bk < NB; ++bk) {
+    through(bk, c[bk], Xs[bk * 64 + rr * 8 + q], Xs[bk * 64 + rr * 8 + 4 + q]);  // W_b = X_b Y_b
+    if (bk + 1 < NB) {
+      double bf[T][2];
+      as_b(bk, c[bk], bf);
+#pragma unroll
+      for (int b2 = bk + 1; b2 < NB; ++b2) {
+        const double a0 = -Us[(8 * bk + q) * LDU + 8 * b2 + rr], a1 = -Us[(8 * bk + 4 + q) * LDU + 8 * b2 + rr];
+#pragma unroll
+        for (int u = 0; u < T; ++u) { dmma884(c[b2][u][0], c[b2][u][1], a0, bf[u][0]); dmma884(c[b2][u][0], c[b2][u][1], a1, bf[u][1]); }
+      }
+    }
+  }
+#pragma unroll
+  for (int bk = 0; bk < NB; ++bk) {  // V = D^-1 W
+    const double dr = ds[8 * bk + rr];
+#pragma unroll
+    for (int u = 0; u < T; ++u) { c[bk][u][0] *= dr; c[bk][u][1] *= dr; }
+  }
+#pragma unroll
+  for (int bk = NB - 1; bk >= 0; --bk) {
+    through(bk, c[bk], Xs[bk * 64 + q * 8 + rr], Xs[bk * 64 + (4 + q) * 8 + rr]);  // F_b = X_b^T V_b
+    // the solved block row: straight from the C fragment to the record (column-major, ld NS: 8 consecutive k per column)
+#pragma unroll
+    for (int u = 0; u < T; ++u) {
+      if (2 * q < ncols[u]) rec[u][(size_t)(2 * q) * NS + 8 * bk + rr] = c[bk][u][0];
+      if (2 * q + 1 < ncols[u]) rec[u][(size_t)(2 * q + 1) * NS + 8 * bk + rr] = c[bk][u][1];
+    }
+    if (bk > 0) {
+      double bf[T][2];
+      as_b(bk, c[bk], bf);
+#pragma unroll
+      for (int b2 = 0; b2 < bk; ++b2) {
+        const double a0 = -Us[(8 * b2 + rr) * LDU + 8 * bk + q], a1 = -Us[(8 * b2 + rr) * LDU + 8 * bk + 4 + q];
+#pragma unroll
+        for (int u = 0; u < T; ++u) { dmma884(c[b2][u][0], c[b2][u][1], a0, bf[u][0]); dmma884(c[b2][u][0], c[b2][u][1], a1, bf[u][1]); }
+      }
+    }
+  }
+}
+
+constexpr int BIG_SOLVE_THREADS = 288;  // 9 warps: 8 take two column tiles each, the ninth the tile with the zs column
+
+template <int NS>
+__global__ void __launch_bounds__(BIG_SOLVE_THREADS) big_solve_kernel(Shape s, const double* ein, const double* ufac, double* rec_all,
+                                                                       int level, int M) {
+  using D = BigDim<NS>;
+  using F = BigFac<NS>;
+  static_assert(NS == 64, "8 block rows, 17 column tiles over 9 warps");
+  constexpr int NB = NS / 8, LDU = NS + 4, LDY = 2 * NS + 8;
+  extern __shared__ __align__(16) double smf[];
+  double* Us = smf;                      // U, row-major ld LDU
+  double* Ys = Us + NS * LDU;            // Y / W / F, row k at Ys + k * LDY, column = right-hand side
+  double* Xs = Ys + NS * LDY;            // X_b, 8 x 8 row-major each
+  double* ds = Xs + NB * 64;             // 1/d
+  const int N = s.N;
+  const int prob = blockIdx.x / M, t = blockIdx.x % M;
+  const int tid = threadIdx.x, warp = tid >> 5, nthr = blockDim.x;
+  const double* EL = ein + ((size_t)prob * 2 * M + 2 * t) * D::ENT;
+  const double* ER = EL + D::ENT;
+  const double* Uf = ufac + ((size_t)prob * M + t) * F::SIZE;
+  const int i_sep = ((2 * t + 1) << level) - 1;
+  for (int e = tid; e < NS * NS; e += nthr) {
+    const int r = e / NS, c = e - r * NS;
+    Us[r * LDU + c] = __ldg(Uf + F::OU + e);
+    Ys[r * LDY + c] = __ldg(EL + D::OAB + c * NS + r);   // S_L(k = r, col = c) = SabL(c, r): strided read, conflict-free store
+    Ys[r * LDY + NS + c] = __ldg(ER + D::OAB + e);       // S_R(k, c) = SabR(k, c)
+  }
+  for (int e = tid; e < NB * 64 + NS; e += nthr) Xs[e] = __ldg(Uf + F::OX + e);  // X blocks, then 1/d (contiguous)
+  for (int e = tid; e < NS * 8; e += nthr) {
+    const int k = e >> 3, c = e & 7;
+    Ys[k * LDY + 2 * NS + c] = c == 0 ? __ldg(EL + D::OSB + k) + __ldg(ER + D::OSA + k) : 0.0;
+  }
+  __syncthreads();
+  double* rec = rec_all + ((size_t)prob * N + i_sep) * D::WSZ;  // [f_L | f_R | zs], column-major ld NS
+  if (warp < 8) {
+    double* const Yt[2] = {Ys + 8 * warp, Ys + 8 * (warp + 8)};
+    double* const rc[2] = {rec + (size_t)8 * warp * NS, rec + (size_t)8 * (warp + 8) * NS};
+    const int nc[2] = {8, 8};
+    big_solve_tiles<NS, 2>(Us, Xs, ds, Yt, rc, nc);
+  } else {
+    double* const Yt[1] = {Ys + 8 * 16};
+    double* const rc[1] = {rec + (size_t)8 * 16 * NS};
+    const int nc[1] = {1};
+    big_solve_tiles<NS, 1>(Us, Xs, ds, Yt, rc, nc);
   }
 }
 
@@ -387,7 +638,7 @@ struct BigPlan {
 inline bool big_shape_ok(int n, int m, int N) { return n == 64 && m == 16 && N >= 2; }
 
 inline void big_free(BigPlan* p) {
-  cudaFree(p->bb.entA); cudaFree(p->bb.entB); cudaFree(p->bb.rec); cudaFree(p->bb.lam);
+  cudaFree(p->bb.entA); cudaFree(p->bb.entB); cudaFree(p->bb.rec); cudaFree(p->bb.lam); cudaFree(p->bb.ufac);
   const bool cov = p->covered;
   memset(p, 0, sizeof(*p));
   p->covered = cov;
@@ -401,7 +652,8 @@ inline int big_alloc(const Shape& s, int batch, BigPlan* p, std::string& err) {
     return cudaMalloc((void**)ptr, cnt * sizeof(double)) == cudaSuccess;
   };
   const bool ok = alloc(&p->bb.entA, (size_t)batch * s.N * ent) && alloc(&p->bb.entB, (size_t)batch * (s.N / 2) * ent) &&
-                  alloc(&p->bb.rec, (size_t)batch * s.N * wsz) && alloc(&p->bb.lam, (size_t)batch * (s.N + 1) * s.n);
+                  alloc(&p->bb.rec, (size_t)batch * s.N * wsz) && alloc(&p->bb.lam, (size_t)batch * (s.N + 1) * s.n) &&
+                  alloc(&p->bb.ufac, (size_t)batch * (s.N / 2) * BigFac<64>::SIZE);
   if (!ok) {
     cudaGetLastError();
     big_free(p);
@@ -423,6 +675,13 @@ inline int big_launch(BigPlan& p, const Shape& s, const Bufs& b, int batch, int 
   const int leaf_smem = (NS * (NS + NI) + 2 * (NS + NI) + 2 * NS) * (int)sizeof(double);
   const int spine_smem = NS * (NS + 2) * (int)sizeof(double);
   const int schur_smem = (2 * NS + 1) * (NS + 4) * (int)sizeof(double);
+  const int factor_smem = BIG_FACTOR_WPC * big_factor_warp_doubles<NS>() * (int)sizeof(double);
+  const int solve_smem = (NS * (NS + 4) + NS * (2 * NS + 8) + (NS / 8) * 64 + NS) * (int)sizeof(double);
+  static const int one_kernel_spine = [] { const char* v = getenv("RSLQR_BIG_SPINE"); return v ? atoi(v) : 0; }();
+  if ((e = smem_optin(big_factor_kernel<NS>, factor_smem)) != cudaSuccess || (e = smem_optin(big_solve_kernel<NS>, solve_smem)) != cudaSuccess) {
+    err = std::string("big launch: ") + cudaGetErrorString(e);
+    return -3;
+  }
   if ((e = smem_optin(big_leaf_kernel<NS, NI>, leaf_smem)) != cudaSuccess || (e = smem_optin(big_spine_kernel<NS>, spine_smem)) != cudaSuccess ||
       (e = smem_optin(big_schur_kernel<NS>, schur_smem)) != cudaSuccess) {
     err = std::string("big launch: ") + cudaGetErrorString(e);
@@ -434,8 +693,16 @@ inline int big_launch(BigPlan& p, const Shape& s, const Bufs& b, int batch, int 
   for (int level = 0; level < s.K; ++level) {
     const int M = N >> (level + 1);
     double* eout = (level & 1) ? p.bb.entA : p.bb.entB;
-    big_spine_kernel<NS><<<(unsigned)((size_t)batch * M), big_spine_threads<NS>(), spine_smem, st>>>(s, b, ein, p.bb.rec, level, M);
-    ++p.launches;
+    if (one_kernel_spine) {
+      big_spine_kernel<NS><<<(unsigned)((size_t)batch * M), big_spine_threads<NS>(), spine_smem, st>>>(s, b, ein, p.bb.rec, level, M);
+      ++p.launches;
+    } else {
+      const long long nmerge = (long long)batch * M;
+      big_factor_kernel<NS><<<(unsigned)((nmerge + BIG_FACTOR_WPC - 1) / BIG_FACTOR_WPC), 32 * BIG_FACTOR_WPC, factor_smem, st>>>(
+          s, b, ein, p.bb.ufac, level, M, nmerge);
+      big_solve_kernel<NS><<<(unsigned)nmerge, BIG_SOLVE_THREADS, solve_smem, st>>>(s, ein, p.bb.ufac, p.bb.rec, level, M);
+      p.launches += 2;
+    }
     if (level < s.K - 1) {
       big_schur_kernel<NS><<<(unsigned)((size_t)batch * M), 256, schur_smem, st>>>(s, ein, eout, p.bb.rec, level, M);
       ++p.launches;
