@@ -40,15 +40,16 @@ struct BigBufs {
 // src/solver.c:138-190), one CTA per (problem, knot):
 //   Saa = Q^-1, Sab = -Q^-1 A^T, Sbb = A Q^-1 A^T + B R^-1 B^T, sa = -z_x - z_lambda, sb = A z_x + B z_u
 //   knot 0: x_0 is fixed (z_x = x0) and lambda_0 is no unknown: Q^-1 -> 0 in the blocks; last knot: only Saa, sa.
-// dynamic smem: (NS*(NS+NI) + 2*(NS+NI) + 2*NS) doubles
+// dynamic smem: ((NS+8)*(NS+NI) + 2*(NS+NI) + 2*NS + 3*NS) doubles
 // ---------------------------------------------------------------------------------------------------------
 template <int NS, int NI>
 __global__ void __launch_bounds__(256, 2) big_leaf_kernel(Shape s, Bufs b, BigBufs bb, int pack_rhs) {
   using D = BigDim<NS>;
-  constexpr int XU = NS + NI;
+  constexpr int XU = NS + NI, LDA = NS + 8;  // (LDA = 8 mod 16: the DMMA fragments of a warp fall into two wavefronts)
+  static_assert(NS == 64 && XU % 4 == 0, "8 warps x 8 rows; k-steps of 4");
   extern __shared__ __align__(16) double smf[];
-  double* AB = smf;                 // [NS x XU] column-major, as in the flat knot block
-  double* dv = AB + NS * XU;        // 1/Q, 1/R (as used in the products: 0 for Q of knot 0 and for the last knot)
+  double* AB = smf;                 // [NS x XU] column-major with leading dimension LDA
+  double* dv = AB + LDA * XU;       // 1/Q, 1/R (as used in the products: 0 for Q of knot 0 and for the last knot)
   double* zv = dv + XU;             // leaf-solved z_x, z_u
   double* sc = zv + XU;             // 1/Q of this knot (also for knot 0), then z_lambda
   const int N = s.N;
@@ -56,7 +57,17 @@ __global__ void __launch_bounds__(256, 2) big_leaf_kernel(Shape s, Bufs b, BigBu
   const int tid = threadIdx.x, nthr = blockDim.x;
   const double* kn = knot_ptr(s, b, prob, k);
   const bool first = k == 0, last = k == N - 1;
-  for (int e = tid; e < NS * XU; e += nthr) AB[e] = last ? 0.0 : kn[s.oA + e];
+  static_assert((NS * XU) % (4 * 256) == 0, "staging loop: 4 loads in flight per thread");
+  for (int e0 = tid; e0 < NS * XU; e0 += 4 * nthr) {
+    double v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v[u] = last ? 0.0 : __ldg(kn + s.oA + e0 + u * nthr);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int e = e0 + u * nthr, l = e / NS, r = e - l * NS;
+      AB[r + LDA * l] = v[u];
+    }
+  }
   for (int l = tid; l < XU; l += nthr) {
     const bool isR = l >= NS;
     const double d = kn[l];  // Q then R lead the block
@@ -89,41 +100,43 @@ __global__ void __launch_bounds__(256, 2) big_leaf_kernel(Shape s, Bufs b, BigBu
   for (int e = tid; e < NS * NS; e += nthr) {
     const int r = e / NS, c = e - r * NS;
     E[D::OAA + e] = r == c ? sc[r] : 0.0;
-    E[D::OAB + e] = -sc[r] * AB[c + NS * r];  // -A(c, r) / Q(r)   (AB is zero for the last knot)
+    E[D::OAB + e] = -sc[r] * AB[c + LDA * r];  // -A(c, r) / Q(r)   (AB is zero for the last knot)
   }
-  // Sbb = [A | B] D [A | B]^T: every thread a 4 x 4 tile of it in registers (rows r0.., columns c0..: 4 + 4 operand loads
-  // per 16 FMA), tiles (NS / 4)^2 over the CTA's threads
-  static_assert(NS % 4 == 0, "4 x 4 register tiles");
-  for (int tile = tid; tile < (NS / 4) * (NS / 4); tile += nthr) {
-    const int r0 = 4 * (tile / (NS / 4)), c0 = 4 * (tile % (NS / 4));
-    double g[4][4];
+  // Sbb = [A | B] D [A | B]^T on the fp64 tensor cores: warp w owns rows 8w..8w+7; its A fragments (scaled by D) stay in
+  // registers across the 8 column tiles, 4 column tiles in flight at a time
+  {
+    const int warp = tid >> 5, lane = tid & 31, q = lane & 3, rr = lane >> 2;
+    constexpr int KS = XU / 4;
+    double a[KS];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int ks = 0; ks < KS; ++ks) a[ks] = AB[8 * warp + rr + LDA * (4 * ks + q)] * dv[4 * ks + q];
+#pragma unroll 1
+    for (int nt0 = 0; nt0 < NS / 8; nt0 += 4) {
+      double c[4][2];
 #pragma unroll
-      for (int j = 0; j < 4; ++j) g[i][j] = 0.0;
-#pragma unroll 2
-    for (int l = 0; l < XU; ++l) {
-      const double d = dv[l];
-      const double2 ra = *reinterpret_cast<const double2*>(AB + r0 + NS * l), rb = *reinterpret_cast<const double2*>(AB + r0 + 2 + NS * l);
-      const double2 ca = *reinterpret_cast<const double2*>(AB + c0 + NS * l), cb = *reinterpret_cast<const double2*>(AB + c0 + 2 + NS * l);
-      const double rv[4] = {ra.x * d, ra.y * d, rb.x * d, rb.y * d};
-      const double cv[4] = {ca.x, ca.y, cb.x, cb.y};
+      for (int u = 0; u < 4; ++u) c[u][0] = c[u][1] = 0.0;
 #pragma unroll
-      for (int i = 0; i < 4; ++i)
+      for (int ks = 0; ks < KS; ++ks) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) g[i][j] = fma(rv[i], cv[j], g[i][j]);
-    }
+        for (int u = 0; u < 4; ++u) dmma884(c[u][0], c[u][1], a[ks], AB[8 * (nt0 + u) + rr + LDA * (4 * ks + q)]);
+      }
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      *reinterpret_cast<double2*>(E + D::OBB + (r0 + i) * NS + c0) = make_double2(g[i][0], g[i][1]);
-      *reinterpret_cast<double2*>(E + D::OBB + (r0 + i) * NS + c0 + 2) = make_double2(g[i][2], g[i][3]);
+      for (int u = 0; u < 4; ++u)
+        *reinterpret_cast<double2*>(E + D::OBB + (8 * warp + rr) * NS + 8 * (nt0 + u) + 2 * q) = make_double2(c[u][0], c[u][1]);
     }
   }
-  for (int r = tid; r < NS; r += nthr) {
-    E[D::OSA + r] = -zv[r] - sc[NS + r];
+  {  // sb = [A | B] z: four threads per row, a quarter of the XU terms each (thread = 64 part + row)
+    const int r = tid & (NS - 1), part = tid / NS;
     double v = 0.0;
-    for (int l = 0; l < XU; ++l) v = fma(AB[r + NS * l], zv[l], v);
-    E[D::OSB + r] = v;
+#pragma unroll 4
+    for (int l = part * (XU / 4); l < (part + 1) * (XU / 4); ++l) v = fma(AB[r + LDA * l], zv[l], v);
+    double* ps = sc + 2 * NS;  // partial sums
+    if (part > 0) ps[(part - 1) * NS + r] = v;
+    __syncthreads();
+    if (part == 0) {
+      E[D::OSA + r] = -zv[r] - sc[NS + r];
+      E[D::OSB + r] = v + ps[r] + ps[NS + r] + ps[2 * NS + r];
+    }
   }
 }
 
@@ -445,16 +458,47 @@ __global__ void __launch_bounds__(BIG_SOLVE_THREADS) big_solve_kernel(Shape s, c
   double* ds = Xs + NB * 64;             // 1/d
   const int N = s.N;
   const int prob = blockIdx.x / M, t = blockIdx.x % M;
-  const int tid = threadIdx.x, warp = tid >> 5, nthr = blockDim.x;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nthr = blockDim.x;
   const double* EL = ein + ((size_t)prob * 2 * M + 2 * t) * D::ENT;
   const double* ER = EL + D::ENT;
   const double* Uf = ufac + ((size_t)prob * M + t) * F::SIZE;
   const int i_sep = ((2 * t + 1) << level) - 1;
-  for (int e = tid; e < NS * NS; e += nthr) {
-    const int r = e / NS, c = e - r * NS;
-    Us[r * LDU + c] = __ldg(Uf + F::OU + e);
-    Ys[r * LDY + c] = __ldg(EL + D::OAB + c * NS + r);   // S_L(k = r, col = c) = SabL(c, r): strided read, conflict-free store
-    Ys[r * LDY + NS + c] = __ldg(ER + D::OAB + e);       // S_R(k, c) = SabR(k, c)
+  for (int e0 = 2 * tid; e0 < NS * NS; e0 += 8 * nthr) {  // 128-bit loads, 4 + 4 in flight per thread
+    double2 uv[4], yv[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int e = e0 + 2 * u * nthr;
+      if (e < NS * NS) {
+        uv[u] = __ldg(reinterpret_cast<const double2*>(Uf + F::OU + e));
+        yv[u] = __ldg(reinterpret_cast<const double2*>(ER + D::OAB + e));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int e = e0 + 2 * u * nthr;
+      if (e < NS * NS) {
+        const int r = e / NS, c = e - r * NS;
+        *reinterpret_cast<double2*>(Us + r * LDU + c) = uv[u];
+        *reinterpret_cast<double2*>(Ys + r * LDY + NS + c) = yv[u];   // S_R(k, c) = SabR(k, c)
+      }
+    }
+  }
+  // S_L(k, c) = SabL(c, k): a warp moves tiles of 8 k x 4 c (lane = 4 kk + cc): 64-byte runs of a SabL row in, a 4-way
+  // conflicted store out (a plain transpose would be 16-way with this row stride)
+  for (int t0 = warp; t0 < (NS / 8) * (NS / 4); t0 += 4 * (nthr >> 5)) {
+    double v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int tile = t0 + u * (nthr >> 5);
+      const int k = 8 * (tile % (NS / 8)) + (lane >> 2), c = 4 * (tile / (NS / 8)) + (lane & 3);
+      v[u] = tile < (NS / 8) * (NS / 4) ? __ldg(EL + D::OAB + c * NS + k) : 0.0;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int tile = t0 + u * (nthr >> 5);
+      const int k = 8 * (tile % (NS / 8)) + (lane >> 2), c = 4 * (tile / (NS / 8)) + (lane & 3);
+      if (tile < (NS / 8) * (NS / 4)) Ys[k * LDY + c] = v[u];
+    }
   }
   for (int e = tid; e < NB * 64 + NS; e += nthr) Xs[e] = __ldg(Uf + F::OX + e);  // X blocks, then 1/d (contiguous)
   for (int e = tid; e < NS * 8; e += nthr) {
@@ -672,7 +716,7 @@ inline int big_launch(BigPlan& p, const Shape& s, const Bufs& b, int batch, int 
   p.launches = 0;
   cudaError_t e = cudaMemsetAsync(p.bb.lam, 0, sizeof(double) * (size_t)batch * (N + 1) * NS, st);
   if (e != cudaSuccess) { err = std::string("big launch: ") + cudaGetErrorString(e); return -3; }
-  const int leaf_smem = (NS * (NS + NI) + 2 * (NS + NI) + 2 * NS) * (int)sizeof(double);
+  const int leaf_smem = ((NS + 8) * (NS + NI) + 2 * (NS + NI) + 2 * NS + 3 * NS) * (int)sizeof(double);
   const int spine_smem = NS * (NS + 2) * (int)sizeof(double);
   const int schur_smem = (2 * NS + 1) * (NS + 4) * (int)sizeof(double);
   const int factor_smem = BIG_FACTOR_WPC * big_factor_warp_doubles<NS>() * (int)sizeof(double);
