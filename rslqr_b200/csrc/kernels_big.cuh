@@ -355,6 +355,114 @@ __global__ void __launch_bounds__(32 * BIG_FACTOR_WPC) big_factor_kernel(Shape s
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// big_factor_reg_kernel: the same outputs as big_factor_kernel, with the matrix held in REGISTERS as DMMA accumulator
+// fragments (lower block triangle: 36 blocks of 8 x 8, two doubles per lane each) and a blocked right-looking LDL^T:
+//   for block column b:  S_bb = L_bb D_b L_bb^T by row elimination on [S_bb | I] inside the warp (shuffles; gives
+//                         X_b = L_bb^-1 directly),
+//                        panel  R_c = S_cb X_b^T (= L_cb D_b),  L_cb = R_c D_b^-1          (2 DMMAs per block)
+//                        trailing S_cc' -= L_cb (L_c'b D_b)^T                                (2 DMMAs per block)
+// C fragments become A / B operands through four 64-bit shuffles (frag_c2a). One warp per merge, no shared memory, no
+// barrier; about 2.5 k warp instructions per matrix against 78 k for the packed-triangle kernel above.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int BIG_FACTOR_REG_WPC = 4;
+
+// C fragment (lane (g, q): C[g][2q], C[g][2q+1]) -> A fragments of the same block (a0 = C[g][q], a1 = C[g][4+q]);
+// read as a B operand this is the block's transpose
+__device__ __forceinline__ void frag_c2a(double c0, double c1, double& a0, double& a1, int lane) {
+  const int g4 = lane & ~3, q = lane & 3, src = g4 | (q >> 1);
+  const double x0 = shfl_d(c0, src), x1 = shfl_d(c1, src);
+  const double y0 = shfl_d(c0, src | 2), y1 = shfl_d(c1, src | 2);
+  a0 = (q & 1) ? x1 : x0;
+  a1 = (q & 1) ? y1 : y0;
+}
+
+template <int NS>
+__global__ void __launch_bounds__(32 * BIG_FACTOR_REG_WPC) big_factor_reg_kernel(Shape s, Bufs b, const double* ein, double* ufac,
+                                                                                  int level, int M, long long nmerge) {
+  using D = BigDim<NS>;
+  using F = BigFac<NS>;
+  constexpr int NB = NS / 8;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, q = lane & 3;
+  const long long mi = (long long)blockIdx.x * BIG_FACTOR_REG_WPC + warp;
+  if (mi >= nmerge) return;
+  const int N = s.N;
+  const int prob = (int)(mi / M), t = (int)(mi % M);
+  const double* EL = ein + ((size_t)prob * 2 * M + 2 * t) * D::ENT;
+  const double* ER = EL + D::ENT;
+  double* U = ufac + (size_t)mi * F::SIZE;
+  double S[NB][NB][2];  // block (c, c'), c >= c', as a C fragment
+#pragma unroll
+  for (int c = 0; c < NB; ++c)
+#pragma unroll
+    for (int c2 = 0; c2 <= c; ++c2) {
+      const int off = (8 * c + g) * NS + 8 * c2 + 2 * q;
+      const double2 x = __ldg(reinterpret_cast<const double2*>(EL + D::OBB + off));
+      const double2 y = __ldg(reinterpret_cast<const double2*>(ER + D::OAA + off));
+      S[c][c2][0] = x.x + y.x;
+      S[c][c2][1] = x.y + y.y;
+    }
+  int bad = 0;
+#pragma unroll
+  for (int bk = 0; bk < NB; ++bk) {
+    // --- diagonal block: row elimination on [S_bb | I]
+    double s0 = S[bk][bk][0], s1 = S[bk][bk][1];
+    double x0 = (g == 2 * q) ? 1.0 : 0.0, x1 = (g == 2 * q + 1) ? 1.0 : 0.0;
+    double dq0 = 0.0, dq1 = 0.0;   // 1/d of columns 2q, 2q+1 of the block
+    double da0 = 0.0, da1 = 0.0;   // 1/d of columns q, 4+q
+    double* Ud = U + F::OU + (size_t)(8 * bk) * NS + 8 * bk;
+#pragma unroll 1
+    for (int j = 0; j < 8; ++j) {
+      const double v = (j & 1) ? s1 : s0;
+      const double colv = shfl_d(v, (lane & ~3) | (j >> 1));  // S'(g, j)
+      const double d = shfl_d(v, (j << 2) | (j >> 1));        // S'(j, j)
+      const int rowj = (j << 2) | q;
+      const double rs0 = shfl_d(s0, rowj), rs1 = shfl_d(s1, rowj), rx0 = shfl_d(x0, rowj), rx1 = shfl_d(x1, rowj);
+      if (!(d > 0.0)) bad = 1;
+      const double dinv = fast_rcp(d);
+      const double l = g > j ? colv * dinv : 0.0;
+      s0 = fma(-l, rs0, s0); s1 = fma(-l, rs1, s1);
+      x0 = fma(-l, rx0, x0); x1 = fma(-l, rx1, x1);
+      if (q == (j >> 1)) { if (j & 1) dq1 = dinv; else dq0 = dinv; }
+      if (q == (j & 3)) { if (j >> 2) da1 = dinv; else da0 = dinv; }
+      if (q == 0) Ud[(size_t)j * NS + g] = g > j ? l : (g == j ? 1.0 : 0.0);  // U(8b + j, 8b + g) = l(g, j)
+    }
+    *reinterpret_cast<double2*>(U + F::OX + bk * 64 + g * 8 + 2 * q) = make_double2(x0, x1);
+    if (g == 0) *reinterpret_cast<double2*>(U + F::OD + 8 * bk + 2 * q) = make_double2(dq0, dq1);
+    if (bk + 1 < NB) {
+      double xa0, xa1;
+      frag_c2a(x0, x1, xa0, xa1, lane);  // X_b as a B operand = X_b^T
+      double nl[NB][2], rd[NB][2];       // -L_cb as A fragments, (L_cb D_b)^T as B fragments
+#pragma unroll
+      for (int c = bk + 1; c < NB; ++c) {
+        double pa0, pa1;
+        frag_c2a(S[c][bk][0], S[c][bk][1], pa0, pa1, lane);
+        double r0 = 0.0, r1 = 0.0;
+        dmma884(r0, r1, pa0, xa0);
+        dmma884(r0, r1, pa1, xa1);
+        // U(8b + k, 8c + g) = L_cb(g, k); the block below the diagonal of U is zero
+        U[F::OU + (size_t)(8 * bk + 2 * q) * NS + 8 * c + g] = r0 * dq0;
+        U[F::OU + (size_t)(8 * bk + 2 * q + 1) * NS + 8 * c + g] = r1 * dq1;
+        *reinterpret_cast<double2*>(U + F::OU + (size_t)(8 * c + g) * NS + 8 * bk + 2 * q) = make_double2(0.0, 0.0);
+        frag_c2a(r0, r1, rd[c][0], rd[c][1], lane);
+        nl[c][0] = -rd[c][0] * da0;
+        nl[c][1] = -rd[c][1] * da1;
+      }
+#pragma unroll
+      for (int c = bk + 1; c < NB; ++c)
+#pragma unroll
+        for (int c2 = bk + 1; c2 <= c; ++c2) {
+          dmma884(S[c][c2][0], S[c][c2][1], nl[c][0], rd[c2][0]);
+          dmma884(S[c][c2][0], S[c][c2][1], nl[c][1], rd[c2][1]);
+        }
+    }
+  }
+  if (bad && lane == 0) {
+    b.status[(size_t)prob * 3 * N + rs_slot_S(t, level, N)] = -1;
+    b.flags[prob] = 1;
+  }
+}
+
 // Both substitution sweeps for T column tiles at once, RIGHT-LOOKING: the 8 block rows of a tile stay in registers as
 // DMMA accumulators (C fragments); once block row b is final it goes through shared memory once (C layout -> B
 // fragment) and every other block row still to be solved is updated with it, so a B fragment is loaded once per block
@@ -722,6 +830,7 @@ inline int big_launch(BigPlan& p, const Shape& s, const Bufs& b, int batch, int 
   const int factor_smem = BIG_FACTOR_WPC * big_factor_warp_doubles<NS>() * (int)sizeof(double);
   const int solve_smem = (NS * (NS + 4) + NS * (2 * NS + 8) + (NS / 8) * 64 + NS) * (int)sizeof(double);
   static const int one_kernel_spine = [] { const char* v = getenv("RSLQR_BIG_SPINE"); return v ? atoi(v) : 0; }();
+  static const int packed_factor = [] { const char* v = getenv("RSLQR_BIG_FACTOR_PACKED"); return v ? atoi(v) : 0; }();  // A/B
   if ((e = smem_optin(big_factor_kernel<NS>, factor_smem)) != cudaSuccess || (e = smem_optin(big_solve_kernel<NS>, solve_smem)) != cudaSuccess) {
     err = std::string("big launch: ") + cudaGetErrorString(e);
     return -3;
@@ -742,8 +851,12 @@ inline int big_launch(BigPlan& p, const Shape& s, const Bufs& b, int batch, int 
       ++p.launches;
     } else {
       const long long nmerge = (long long)batch * M;
-      big_factor_kernel<NS><<<(unsigned)((nmerge + BIG_FACTOR_WPC - 1) / BIG_FACTOR_WPC), 32 * BIG_FACTOR_WPC, factor_smem, st>>>(
-          s, b, ein, p.bb.ufac, level, M, nmerge);
+      if (packed_factor)
+        big_factor_kernel<NS><<<(unsigned)((nmerge + BIG_FACTOR_WPC - 1) / BIG_FACTOR_WPC), 32 * BIG_FACTOR_WPC, factor_smem, st>>>(
+            s, b, ein, p.bb.ufac, level, M, nmerge);
+      else
+        big_factor_reg_kernel<NS><<<(unsigned)((nmerge + BIG_FACTOR_REG_WPC - 1) / BIG_FACTOR_REG_WPC), 32 * BIG_FACTOR_REG_WPC, 0, st>>>(
+            s, b, ein, p.bb.ufac, level, M, nmerge);
       big_solve_kernel<NS><<<(unsigned)nmerge, BIG_SOLVE_THREADS, solve_smem, st>>>(s, ein, p.bb.ufac, p.bb.rec, level, M);
       p.launches += 2;
     }
