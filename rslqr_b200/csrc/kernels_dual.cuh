@@ -245,6 +245,7 @@ __host__ __device__ constexpr int dual_leaf_warp_doubles() {
 template <int NS, int NI>
 __global__ void __launch_bounds__(32 * DUAL_WPC) dual_leaf_kernel(Shape s, Bufs b, double* ent0, double* sep_in, int pack_rhs,
                                                                    int M0, long long nsub) {
+  pdl_sync();
   using D = DualDim<NS>;
   using RD = RawDim<NS, NI>;
   constexpr int NSE = (NS + 1) & ~1, RAW = (SCAN_LEAF * RD::STRIDE + 1) & ~1;
@@ -326,6 +327,7 @@ struct DualTierArgs {
   // cross-GPU tier fed by peer stores over NVLink (shard_push_kernel): element e is complete once wait_flags[e] >= wait_epoch
   const unsigned long long* wait_flags;
   unsigned long long wait_epoch;
+  double* top_lam;       // single-CTA tier: also resolve the multipliers of its separators top-down (topdown_levels) into top_lam
 };
 
 template <int NS>
@@ -333,6 +335,7 @@ __host__ __device__ constexpr int dual_tier_warp_scratch() { return ((DualDim<NS
 
 template <int NS>
 __global__ void __launch_bounds__(128) dual_tier_kernel(Shape s, Bufs b, DualTierArgs a) {
+  pdl_sync();
   using D = DualDim<NS>;
   extern __shared__ __align__(16) double smf[];
   __shared__ __align__(8) unsigned long long mbar;
@@ -392,6 +395,10 @@ __global__ void __launch_bounds__(128) dual_tier_kernel(Shape s, Bufs b, DualTie
       }
     }
   }
+  if (a.top_lam) {  // (the records of this CTA's separators are in global memory: visible to the CTA after the barrier)
+    __syncthreads();
+    topdown_levels<NS>(a.sep, a.top_lam, a.Min, nullptr, nullptr, a.Min, 1, 0);
+  }
   if (a.out) {
     __syncthreads();
     fence_async_smem();
@@ -417,7 +424,7 @@ inline void dual_launch_tier(const Shape& s, const Bufs& b, const DualTierArgs& 
   using D = DualDim<NS>;
   const int warps = a.ecount / 2 > 0 ? a.ecount / 2 : 1;
   const int sm = (a.ecount * D::ENT + warps * dual_tier_warp_scratch<NS>()) * (int)sizeof(double);
-  dual_tier_kernel<NS><<<(unsigned)((size_t)batch * (a.Min / a.ecount)), 32 * warps, sm, st>>>(s, b, a);
+  launch_k(dual_tier_kernel<NS>, dim3((unsigned)((size_t)batch * (a.Min / a.ecount))), dim3(32 * warps), (size_t)sm, st, s, b, a);
 }
 
 // the local tiers of the plan. last_out: where the last tier puts the merged element of the whole local tree (a shard's
@@ -464,8 +471,8 @@ inline cudaError_t dual_launch_t(ScanPlan& p, const Shape& s, const Bufs& b, int
     e = smem_optin(dual_leaf_kernel<NS, NI>, smem);
     if (e != cudaSuccess) return e;
     const long long nsub = (long long)batch * f.M0;
-    dual_leaf_kernel<NS, NI><<<(unsigned)((nsub + DUAL_WPC - 1) / DUAL_WPC), 32 * DUAL_WPC, smem, st>>>(s, b, p.sb.ent0, p.sb.sep_in,
-                                                                                                          pack_rhs, f.M0, nsub);
+    launch_k(dual_leaf_kernel<NS, NI>, dim3((unsigned)((nsub + DUAL_WPC - 1) / DUAL_WPC)), dim3(32 * DUAL_WPC), (size_t)smem, st, s, b,
+             p.sb.ent0, p.sb.sep_in, pack_rhs, f.M0, nsub);
   }
   if (k1) cudaEventRecord(k1, st);
   e = dual_launch_tiers<NS>(p, s, b, batch, st, nullptr, 0, 0);
@@ -517,9 +524,9 @@ inline int dual_shard_finish(ScanPlan& p, const Shape& s, const Bufs& b, int pac
       a.sep = p.f.xsep; a.sep_pstride = 0; a.sep_mul = 1;
       a.Min = nranks; a.ecount = nranks; a.span = 0;
       a.wait_flags = wait_flags; a.wait_epoch = wait_epoch;
+      a.top_lam = p.f.xlam;                  // ... and the multipliers of those separators (same CTA, no second launch)
       dual_launch_tier<12>(s, b, a, 1, st);  // every rank runs the top log2(nranks) levels redundantly, bit-identically
-      topdown_kernel<12><<<1, 128, 0, st>>>(p.f.xsep, p.f.xlam, nranks, nullptr, nullptr, nranks, 1);
-      p.f.launches += 2;
+      p.f.launches += 1;
       left = p.f.xlam + (size_t)rank * 12;
       right = p.f.xlam + (size_t)(rank + 1) * 12;
     }

@@ -926,6 +926,7 @@ __device__ __forceinline__ unsigned long long global_ns() {
 // CTA r stores this rank's payload into rank r's gathered buffer (slot `rank`) with plain peer stores over NVLink,
 // then publishes it: system-scope fence, release store of the epoch into rank r's flag word for this source.
 __global__ void shard_push_kernel(const double* src, PeerPtrs peers, int rank, int pay, unsigned long long epoch) {
+  pdl_sync();
   const int r = blockIdx.x;
   double* dst = peers.gathered[r] + (size_t)rank * pay;
   if (dst != src) {
@@ -943,6 +944,7 @@ __host__ __device__ constexpr int tier_warp_scratch() { return ((2 * NS + 1) * (
 
 template <int NS, int NI>
 __global__ void __launch_bounds__(128, 4) tier_kernel(Shape s, Bufs b, TierArgs a) {
+  pdl_sync();
   using D = Dim<NS, NI>;
   constexpr int ZS = D::ZS, SLOT = D::SLOT, WSZ = D::WSZ, ENT = D::ENT;
   static_assert(ZS <= 32, "lean Schur update maps one row per lane");
@@ -1040,15 +1042,15 @@ __global__ void __launch_bounds__(128, 4) tier_kernel(Shape s, Bufs b, TierArgs 
 // Slots 0 and M0 of fb.lamhat hold zeros (no separator outside the horizon). One CTA per problem.
 // ---------------------------------------------------------------------------------------------------------
 template <int NS>
-__global__ void topdown_kernel(const double* sep_all, double* lam_all, int M0, const double* left, const double* right,
-                               int span, int step) {
+__device__ __forceinline__ void topdown_levels(const double* sep_all, double* lam_all, int M0, const double* left, const double* right,
+                                               int span, int step, int cta) {
   // left/right: multipliers of the separators bounding the range (a shard's neighbours), nullptr = none.
   // A CTA covers the `span` slots after slot blk*span and resolves the separators at multiples of `step` inside it
   // (coarsest first); the multipliers at both ends of its range are already final, or (span == M0) set here.
   // Long horizons run two passes: (span = M0, step = H) with one CTA, then (span = H, step = 1) with M0/H CTAs.
   constexpr int WSZ = (2 * NS + 1) * NS;
   const int nblk = M0 / span;
-  const int prob = blockIdx.x / nblk, base = (blockIdx.x % nblk) * span;
+  const int prob = cta / nblk, base = (cta % nblk) * span;
   double* lam = lam_all + (size_t)prob * (M0 + 1) * NS;
   const double* sep = sep_all + (size_t)prob * M0 * WSZ;
   if (span == M0 && threadIdx.x < NS) {
@@ -1075,6 +1077,13 @@ __global__ void topdown_kernel(const double* sep_all, double* lam_all, int M0, c
   }
 }
 
+template <int NS>
+__global__ void topdown_kernel(const double* sep_all, double* lam_all, int M0, const double* left, const double* right,
+                               int span, int step) {
+  pdl_sync();
+  topdown_levels<NS>(sep_all, lam_all, M0, left, right, span, step, (int)blockIdx.x);
+}
+
 // Latency variant of topdown_kernel for few CTAs (one long horizon): the records of the CTA's range (at most 63) come
 // into shared memory by TMA bulk copies up front and the multipliers of the range live in shared memory too, so the
 // log2(span/step) dependent levels cost shared-memory round trips instead of L2 / HBM ones. Same arithmetic, same
@@ -1082,6 +1091,7 @@ __global__ void topdown_kernel(const double* sep_all, double* lam_all, int M0, c
 template <int NS>
 __global__ void __launch_bounds__(128) topdown_smem_kernel(const double* sep_all, double* lam_all, int M0, const double* left,
                                                             const double* right, int span, int step) {
+  pdl_sync();
   constexpr int WSZ = (2 * NS + 1) * NS;
   extern __shared__ __align__(16) double tsm[];
   __shared__ __align__(8) unsigned long long mbar;
@@ -1155,9 +1165,9 @@ inline int launch_topdown(const double* sep, double* lam, int M0, int batch, con
     const bool use_smem = smem_ok && (force >= 0 ? force != 0 : ctas <= 1024);
     if (use_smem) {
       smem_optin(topdown_smem_kernel<NS>, bytes);
-      topdown_smem_kernel<NS><<<ctas, 128, bytes, st>>>(sep, lam, M0, left, right, span, step);
+      launch_k(topdown_smem_kernel<NS>, dim3(ctas), dim3(128), (size_t)bytes, st, sep, lam, M0, left, right, span, step);
     } else {
-      topdown_kernel<NS><<<ctas, 128, 0, st>>>(sep, lam, M0, left, right, span, step);
+      launch_k(topdown_kernel<NS>, dim3(ctas), dim3(128), (size_t)0, st, sep, lam, M0, left, right, span, step);
     }
   };
   if (M0 <= H) {
@@ -1287,7 +1297,7 @@ inline void launch_tier(const Shape& s, const Bufs& b, const TierArgs& a, int ba
   using D = Dim<NS, NI>;
   const int warps = a.ecount / 2 > 0 ? a.ecount / 2 : 1;
   const int smem = (a.ecount * D::ENT + warps * tier_warp_scratch<NS>()) * (int)sizeof(double);
-  tier_kernel<NS, NI><<<(unsigned)((size_t)batch * (a.Min / a.ecount)), 32 * warps, smem, st>>>(s, b, a);
+  launch_k(tier_kernel<NS, NI>, dim3((unsigned)((size_t)batch * (a.Min / a.ecount))), dim3(32 * warps), (size_t)smem, st, s, b, a);
 }
 
 // tiers >= 1 of the local tree. `last_out`: where the last tier puts its merged entry (shards), nullptr = nowhere.

@@ -388,6 +388,7 @@ __host__ __device__ constexpr int scan_leaf_smem_doubles() { return SCAN_WPC * s
 template <int NS, int NI>
 __global__ void __launch_bounds__(32 * SCAN_WPC, 2) scan_leaf_kernel(Shape s, Bufs b, ScanBufs sb, int pack_rhs, int M0,
                                                                       long long nsub, int dual_out) {
+  pdl_sync();
   using D = Dim<NS, NI>;
   using RD = RawDim<NS, NI>;
   constexpr int ZS = D::ZS, SLOT = D::SLOT, WSZ = D::WSZ, ENT = D::ENT;
@@ -520,6 +521,7 @@ __global__ void __launch_bounds__(32 * SCAN_WPC, 2) scan_leaf_kernel(Shape s, Bu
 template <int NS, int NI>
 __global__ void __launch_bounds__(128) scan_down_kernel(Shape s, Bufs b, ScanBufs sb, const double* lam_all, int pack_rhs,
                                                          int M0, long long nsub) {
+  pdl_sync();
   using D = Dim<NS, NI>;
   constexpr int WSZ = D::WSZ, XU = NS + NI;
   // two knots per warp pass (lanes 0..15 / 16..31) when the X and U rows of a knot fit in a half-warp, else one
@@ -677,9 +679,8 @@ inline cudaError_t launch_scan_leaf(ScanPlan& p, const Shape& s, const Bufs& b, 
   cudaError_t e = smem_optin(scan_leaf_kernel<NS, NI>, smem);
   if (e != cudaSuccess) return e;
   const long long nsub = (long long)batch * p.f.M0;
-  scan_leaf_kernel<NS, NI><<<(unsigned)((nsub + SCAN_WPC - 1) / SCAN_WPC), 32 * SCAN_WPC, smem, st>>>(s, b, p.sb, pack_rhs, p.f.M0, nsub,
-                                                                                                       p.hybrid ? 1 : 0);
-  return cudaGetLastError();
+  return launch_k(scan_leaf_kernel<NS, NI>, dim3((unsigned)((nsub + SCAN_WPC - 1) / SCAN_WPC)), dim3(32 * SCAN_WPC), (size_t)smem, st, s, b,
+                  p.sb, pack_rhs, p.f.M0, nsub, p.hybrid ? 1 : 0);
 }
 
 // top-down over the separators above the subtrees, then multipliers inside the subtrees + solution
@@ -688,7 +689,8 @@ inline cudaError_t launch_scan_down(ScanPlan& p, const Shape& s, const Bufs& b, 
                                     const double* left, const double* right) {
   p.f.launches += launch_topdown<NS>(p.f.fb.sep, p.f.fb.lamhat, p.f.M0, batch, left, right, st);
   const long long nsub = (long long)batch * p.f.M0;
-  scan_down_kernel<NS, NI><<<(unsigned)((nsub + 3) / 4), 128, 0, st>>>(s, b, p.sb, p.f.fb.lamhat, pack_rhs, p.f.M0, nsub);
+  launch_k(scan_down_kernel<NS, NI>, dim3((unsigned)((nsub + 3) / 4)), dim3(128), (size_t)0, st, s, b, p.sb, (const double*)p.f.fb.lamhat,
+           pack_rhs, p.f.M0, nsub);
   ++p.f.launches;
   return cudaGetLastError();
 }
@@ -744,7 +746,8 @@ inline int scan_shard_finish(ScanPlan& p, const Shape& s, const Bufs& b, int pac
       a.out = nullptr; a.out_stride = 0;
       a.Min = nranks; a.ecount = nranks; a.span = 0;
       launch_tier<12, 4>(s, b, a, 1, st);
-      topdown_kernel<12><<<1, 128, 0, st>>>(p.f.xsep, p.f.xlam, nranks, nullptr, nullptr, nranks, 1);
+      launch_k(topdown_kernel<12>, dim3(1), dim3(128), (size_t)0, st, (const double*)p.f.xsep, p.f.xlam, nranks, (const double*)nullptr,
+               (const double*)nullptr, nranks, 1);
       p.f.launches += 2;
       left = p.f.xlam + (size_t)rank * 12;
       right = p.f.xlam + (size_t)(rank + 1) * 12;

@@ -37,6 +37,41 @@ inline cudaError_t smem_optin(Kernel kernel, int bytes) {
   return e;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Programmatic dependent launch (latency mode: one long horizon, few CTAs per kernel). A kernel launched through
+// launch_k while pdl_mode() is on carries cudaLaunchAttributeProgrammaticStreamSerialization: it may become resident
+// while its predecessor in the stream still runs, and waits in pdl_sync() (griddepcontrol.wait: the predecessor grid
+// complete, its writes visible) before it touches any global memory. Launch latency and the CTA prologue then overlap
+// the predecessor instead of following it. Every kernel launched through launch_k MUST start with pdl_sync(); without
+// the attribute both instructions are no-ops.
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void pdl_sync() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+inline bool& pdl_mode() {
+  static thread_local bool on = false;
+  return on;
+}
+struct PdlScope {
+  bool prev;
+  explicit PdlScope(bool on) : prev(pdl_mode()) { pdl_mode() = on; }
+  ~PdlScope() { pdl_mode() = prev; }
+  PdlScope(const PdlScope&) = delete;
+  PdlScope& operator=(const PdlScope&) = delete;
+};
+template <typename... KA, typename... A>
+inline cudaError_t launch_k(void (*kern)(KA...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, A&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at{};
+  at.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at.val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = &at;
+  cfg.numAttrs = pdl_mode() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KA>(std::forward<A>(args))...);
+}
+
 struct Shape {
   int n, m, N, K;
   int fs;      // (2n+m)*n

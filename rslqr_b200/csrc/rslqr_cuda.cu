@@ -57,6 +57,7 @@ struct rslqr_cuda_solver {
   bool ktime_on; std::vector<std::pair<cudaEvent_t, cudaEvent_t>> kspans; double k_ms; int k_n;
   FusedPlan fused; int force_dfma;
   ScanPlan scan; int g0_pref;
+  bool pdl;   // latency mode (batch < 64): kernels are chained by programmatic dependent launch (kernels_staged.cuh)
   BigPlan big{};  // dual-form path for large blocks (n = 64, m = 16): buffers allocated on the first solve
   int factored = 0;  // `fact` holds a finished staged factorization of the uploaded problems
   bool prof_keep = false;  // keep the profile spans across enqueues (the chunks of solve_host)
@@ -147,6 +148,8 @@ extern "C" int rslqr_cuda_create(int n, int m, int N, int batch, int device, uns
     // the tiered buffers (dense state of every knot) are allocated up front only for shapes the scan kernels
     // do not cover; otherwise on the first set_mode(RSLQR_MODE_FUSED)
     h->g0_pref = g0 ? atoi(g0) : 8;
+    const char* pv = getenv("RSLQR_PDL");   // 0 switches programmatic dependent launch off (A/B runs)
+    h->pdl = batch < 64 && !(pv && !atoi(pv));
     if (!h->scan.f.available && fused_plan(h->s, h->batch, h->g0_pref, &h->fused, g_err)) {
       rslqr_cuda_destroy(h);
       return RSLQR_E_NOMEM;
@@ -547,6 +550,7 @@ extern "C" int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs) {
     return RSLQR_OK;
   }
   if (mode == RSLQR_MODE_SCAN) {
+    PdlScope pdl(h->pdl && !h->ktime_on);
     std::pair<cudaEvent_t, cudaEvent_t> kt;
     if (h->ktime_on) { cudaEventCreate(&kt.first); cudaEventCreate(&kt.second); }
     const Shape& s = h->s;
@@ -939,6 +943,7 @@ extern "C" size_t rslqr_cuda_shard_payload_doubles(rslqr_cuda_solver* h) { retur
 extern "C" int rslqr_cuda_shard_reduce(rslqr_cuda_solver* h, double* d_payload) {
   if (!h || !d_payload || !h->shard) return fail(RSLQR_E_ARG, "shard_reduce: bad argument");
   CU(cudaSetDevice(h->device));
+  PdlScope pdl(h->pdl);
   {
     int rc = clear_status(h);  // (a time-out or failure of the previous solve must not stick)
     if (rc) return rc;
@@ -959,6 +964,7 @@ extern "C" int rslqr_cuda_shard_finish(rslqr_cuda_solver* h, const double* d_gat
       (nranks > 1 && !d_gathered) || h->s.kofs != rank * h->s.N || h->s.Ng != nranks * h->s.N)
     return fail(RSLQR_E_ARG, "shard_finish: bad argument (rank / nranks must match the shard's position; nranks <= 8)");
   CU(cudaSetDevice(h->device));
+  PdlScope pdl(h->pdl);
   if (rslqr_cuda_get_mode(h) == RSLQR_MODE_SCAN) {
     int rc = h->scan.hybrid ? dual_shard_finish(h->scan, h->s, h->b, 1, h->stream, d_gathered, rank, nranks, g_err)
                             : scan_shard_finish(h->scan, h->s, h->b, 1, h->stream, d_gathered, rank, nranks, g_err);
@@ -983,7 +989,8 @@ extern "C" int rslqr_cuda_shard_push(rslqr_cuda_solver* h, const double* d_paylo
   memset(&pp, 0, sizeof(pp));
   for (int r = 0; r < nranks; ++r) { pp.gathered[r] = peer_gathered[r]; pp.flags[r] = peer_flags[r]; }
   const int pay = (int)shard_payload(h);
-  shard_push_kernel<<<nranks, 256, 0, h->stream>>>(d_payload, pp, rank, pay, epoch);
+  PdlScope pdl(h->pdl);
+  launch_k(shard_push_kernel, dim3(nranks), dim3(256), (size_t)0, h->stream, d_payload, pp, rank, pay, epoch);
   CU(cudaGetLastError());
   ++h->launches;
   return RSLQR_OK;
@@ -996,6 +1003,7 @@ extern "C" int rslqr_cuda_shard_finish_wait(rslqr_cuda_solver* h, const double* 
     return fail(RSLQR_E_ARG, "shard_finish_wait: bad argument");
   if (rslqr_cuda_get_mode(h) != RSLQR_MODE_SCAN) return fail(RSLQR_E_UNSUPPORTED, "the peer-to-peer exchange needs the scan kernels");
   CU(cudaSetDevice(h->device));
+  PdlScope pdl(h->pdl);
   int rc = h->scan.hybrid ? dual_shard_finish(h->scan, h->s, h->b, 1, h->stream, d_gathered, rank, nranks, g_err, d_flags, epoch)
                           : scan_shard_finish(h->scan, h->s, h->b, 1, h->stream, d_gathered, rank, nranks, g_err, d_flags, epoch);
   h->launches = h->scan.f.launches;
