@@ -19,6 +19,16 @@
 
 namespace rslqr {
 
+// Ampere-style asynchronous copies global -> shared (LDGSTS): no staging registers, every copy of a prologue in flight
+// at once. 16-byte copies bypass L1 (.cg); 8-byte ones serve transposes and sources that are only 8-byte aligned.
+__device__ __forceinline__ void cp_async8(double* sdst, const double* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_u32(sdst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async16(double* sdst, const double* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(sdst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 template <int NS>
 struct BigDim {
   static constexpr int BLK = NS * NS;
@@ -57,16 +67,12 @@ __global__ void __launch_bounds__(256, 2) big_leaf_kernel(Shape s, Bufs b, BigBu
   const int tid = threadIdx.x, nthr = blockDim.x;
   const double* kn = knot_ptr(s, b, prob, k);
   const bool first = k == 0, last = k == N - 1;
-  static_assert((NS * XU) % (4 * 256) == 0, "staging loop: 4 loads in flight per thread");
-  for (int e0 = tid; e0 < NS * XU; e0 += 4 * nthr) {
-    double v[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) v[u] = last ? 0.0 : __ldg(kn + s.oA + e0 + u * nthr);
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int e = e0 + u * nthr, l = e / NS, r = e - l * NS;
-      AB[r + LDA * l] = v[u];
-    }
+  // [A | B] -> shared memory by 8-byte asynchronous copies (the knot block is only 8-byte aligned), in flight while the
+  // diagonal / right-hand-side part below is computed
+  for (int e = tid; e < NS * XU; e += nthr) {
+    const int l = e / NS, r = e - l * NS;
+    if (last) AB[r + LDA * l] = 0.0;
+    else cp_async8(AB + r + LDA * l, kn + s.oA + e);
   }
   for (int l = tid; l < XU; l += nthr) {
     const bool isR = l >= NS;
@@ -95,6 +101,7 @@ __global__ void __launch_bounds__(256, 2) big_leaf_kernel(Shape s, Bufs b, BigBu
       sc[NS + l] = zl;
     }
   }
+  cp_async_wait_all();
   __syncthreads();
   double* E = bb.entA + ((size_t)prob * N + k) * D::ENT;
   for (int e = tid; e < NS * NS; e += nthr) {
@@ -571,48 +578,24 @@ __global__ void __launch_bounds__(BIG_SOLVE_THREADS) big_solve_kernel(Shape s, c
   const double* ER = EL + D::ENT;
   const double* Uf = ufac + ((size_t)prob * M + t) * F::SIZE;
   const int i_sep = ((2 * t + 1) << level) - 1;
-  for (int e0 = 2 * tid; e0 < NS * NS; e0 += 8 * nthr) {  // 128-bit loads, 4 + 4 in flight per thread
-    double2 uv[4], yv[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int e = e0 + 2 * u * nthr;
-      if (e < NS * NS) {
-        uv[u] = __ldg(reinterpret_cast<const double2*>(Uf + F::OU + e));
-        yv[u] = __ldg(reinterpret_cast<const double2*>(ER + D::OAB + e));
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int e = e0 + 2 * u * nthr;
-      if (e < NS * NS) {
-        const int r = e / NS, c = e - r * NS;
-        *reinterpret_cast<double2*>(Us + r * LDU + c) = uv[u];
-        *reinterpret_cast<double2*>(Ys + r * LDY + NS + c) = yv[u];   // S_R(k, c) = SabR(k, c)
-      }
-    }
+  // staging by asynchronous copies: everything in flight at once, no staging registers
+  for (int e = 2 * tid; e < NS * NS; e += 2 * nthr) {
+    const int r = e / NS, c = e - r * NS;
+    cp_async16(Us + r * LDU + c, Uf + F::OU + e);
+    cp_async16(Ys + r * LDY + NS + c, ER + D::OAB + e);   // S_R(k, c) = SabR(k, c)
   }
   // S_L(k, c) = SabL(c, k): a warp moves tiles of 8 k x 4 c (lane = 4 kk + cc): 64-byte runs of a SabL row in, a 4-way
   // conflicted store out (a plain transpose would be 16-way with this row stride)
-  for (int t0 = warp; t0 < (NS / 8) * (NS / 4); t0 += 4 * (nthr >> 5)) {
-    double v[4];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int tile = t0 + u * (nthr >> 5);
-      const int k = 8 * (tile % (NS / 8)) + (lane >> 2), c = 4 * (tile / (NS / 8)) + (lane & 3);
-      v[u] = tile < (NS / 8) * (NS / 4) ? __ldg(EL + D::OAB + c * NS + k) : 0.0;
-    }
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int tile = t0 + u * (nthr >> 5);
-      const int k = 8 * (tile % (NS / 8)) + (lane >> 2), c = 4 * (tile / (NS / 8)) + (lane & 3);
-      if (tile < (NS / 8) * (NS / 4)) Ys[k * LDY + c] = v[u];
-    }
+  for (int tile = warp; tile < (NS / 8) * (NS / 4); tile += nthr >> 5) {
+    const int k = 8 * (tile % (NS / 8)) + (lane >> 2), c = 4 * (tile / (NS / 8)) + (lane & 3);
+    cp_async8(Ys + k * LDY + c, EL + D::OAB + c * NS + k);
   }
-  for (int e = tid; e < NB * 64 + NS; e += nthr) Xs[e] = __ldg(Uf + F::OX + e);  // X blocks, then 1/d (contiguous)
+  for (int e = 2 * tid; e < NB * 64 + NS; e += 2 * nthr) cp_async16(Xs + e, Uf + F::OX + e);  // X blocks, then 1/d (contiguous)
   for (int e = tid; e < NS * 8; e += nthr) {
     const int k = e >> 3, c = e & 7;
     Ys[k * LDY + 2 * NS + c] = c == 0 ? __ldg(EL + D::OSB + k) + __ldg(ER + D::OSA + k) : 0.0;
   }
+  cp_async_wait_all();
   __syncthreads();
   double* rec = rec_all + ((size_t)prob * N + i_sep) * D::WSZ;  // [f_L | f_R | zs], column-major ld NS
   if (warp < 8) {
@@ -636,7 +619,7 @@ __global__ void __launch_bounds__(BIG_SOLVE_THREADS) big_solve_kernel(Shape s, c
 // dynamic smem: (2 NS + 1) * (NS + 4) doubles.
 // ---------------------------------------------------------------------------------------------------------
 template <int NS>
-__global__ void __launch_bounds__(256) big_schur_kernel(Shape s, const double* ein, double* eout, const double* rec_all, int level,
+__global__ void __launch_bounds__(256, 3) big_schur_kernel(Shape s, const double* ein, double* eout, const double* rec_all, int level,
                                                          int M) {
   using D = BigDim<NS>;
   static_assert(NS == 64, "8 warps x 8 rows per half");
@@ -653,18 +636,20 @@ __global__ void __launch_bounds__(256) big_schur_kernel(Shape s, const double* e
   const double* rec = rec_all + ((size_t)prob * N + i_sep) * D::WSZ;
   for (int e = tid; e < D::WSZ / 2; e += blockDim.x) {
     const int c = (2 * e) / NS, k = 2 * e - c * NS;
-    *reinterpret_cast<double2*>(Fs + c * LDF + k) = __ldg(reinterpret_cast<const double2*>(rec) + e);
+    cp_async16(Fs + c * LDF + k, rec + 2 * e);
   }
-  __syncthreads();
   const int r = 8 * warp + rr;  // row within a half
+  // A fragments: left half: SabL(r, k); right half: SabR(k, r). Those of the left half are requested while F is in flight.
+  double a[KS];
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) a[ks] = __ldg(EL + D::OAB + r * NS + 4 * ks + q);
+  cp_async_wait_all();
+  __syncthreads();
 #pragma unroll 1
   for (int half = 0; half < 2; ++half) {
-    // A fragments: left half: SabL(r, k); right half: SabR(k, r)
-    double a[KS];
+    if (half) {
 #pragma unroll
-    for (int ks = 0; ks < KS; ++ks) {
-      const int k = 4 * ks + q;
-      a[ks] = half ? __ldg(ER + D::OAB + k * NS + r) : __ldg(EL + D::OAB + r * NS + k);
+      for (int ks = 0; ks < KS; ++ks) a[ks] = __ldg(ER + D::OAB + (4 * ks + q) * NS + r);
     }
     // zs column: keep - a . zs
     {
@@ -677,17 +662,24 @@ __global__ void __launch_bounds__(256) big_schur_kernel(Shape s, const double* e
     }
     // column tiles: left half: 2NS columns (f_L -> Saa', f_R -> Sab'); right half: NS columns (f_R -> Sbb')
     const int ntiles = half ? NS / 8 : 2 * NS / 8;
+    // keep part of a group of 4 column tiles (requested one group ahead of its use)
+    auto keep = [&](int nt0, double2 (&v)[4]) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int col = 8 * (nt0 + u) + 2 * q;  // column of this half's output
+        v[u] = make_double2(0.0, 0.0);
+        if (half) v[u] = __ldg(reinterpret_cast<const double2*>(ER + D::OBB + r * NS + col));
+        else if (col < NS) v[u] = __ldg(reinterpret_cast<const double2*>(EL + D::OAA + r * NS + col));
+      }
+    };
+    double2 kv[4];
+    keep(0, kv);
 #pragma unroll 1
     for (int nt0 = 0; nt0 < ntiles; nt0 += 4) {
       double c[4][2];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int col = 8 * (nt0 + u) + 2 * q;  // column of this half's output
-        double2 v = make_double2(0.0, 0.0);
-        if (half) v = __ldg(reinterpret_cast<const double2*>(ER + D::OBB + r * NS + col));
-        else if (col < NS) v = __ldg(reinterpret_cast<const double2*>(EL + D::OAA + r * NS + col));
-        c[u][0] = -v.x; c[u][1] = -v.y;  // accumulate a.F - keep, negate on the way out
-      }
+      for (int u = 0; u < 4; ++u) { c[u][0] = -kv[u].x; c[u][1] = -kv[u].y; }  // accumulate a.F - keep, negate on the way out
+      if (nt0 + 4 < ntiles) keep(nt0 + 4, kv);
 #pragma unroll
       for (int ks = 0; ks < KS; ++ks) {
 #pragma unroll
