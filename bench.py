@@ -815,7 +815,7 @@ def run_large(args, rank, world, local_rank):
                               "note": "rhs phase only (pack + leaf scaling + K rhs levels) on the stored staged factorization; per rank x world"}
     else:
         tf = big_flops_per_solve(n, m, N) * value / 1e12
-        line["roofline"] = {"kernel": "whole step (big_spine_kernel + big_schur_kernel per level)", "bound": "tensor", "achieved": tf,
+        line["roofline"] = {"kernel": "whole step (big_leaf_kernel, then big_factor_reg_kernel + big_solve_kernel + big_schur_kernel per level; profiles/r02_ncu_big.md)", "bound": "tensor", "achieved": tf,
                             "peak": fp64["tflops"], "unit": "TFLOP/s", "frac": tf / fp64["tflops"], "traffic": None, "peak_kind": fp64["kind"],
                             "flops_per_solve_executed": big_flops_per_solve(n, m, N),
                             "reference_count_tflops": ref_tf, "reference_count_frac": ref_tf / fp64["tflops"],

@@ -252,6 +252,29 @@ def test_shipped_n6_problem_runs_in_scan_mode():
     s.close()
 
 
+def test_latency_mode_dependent_launch_is_bit_identical(monkeypatch):
+    # batch < 64: kernels are chained by programmatic dependent launch (pdl_sync / launch_k, kernels_staged.cuh). A kernel
+    # that touched global memory before its griddepcontrol.wait would race with its predecessor: 30 back-to-back solves
+    # with the chain on must reproduce the solve with the chain off bit for bit (RSLQR_PDL is read when a handle is made).
+    for (n, m, N) in ((12, 4, 2048), (6, 3, 256), (12, 6, 64)):
+        kn, x0 = R.synth_problems(n, m, N, 21, 0, 2)
+        monkeypatch.setenv("RSLQR_PDL", "0")
+        s0 = R.CudaSolver(n, m, N, batch=2, flags=0)
+        s0.upload(kn, x0)
+        s0.solve()
+        want = s0.solution().copy()
+        s0.close()
+        monkeypatch.setenv("RSLQR_PDL", "1")
+        s1 = R.CudaSolver(n, m, N, batch=2, flags=0)
+        s1.upload(kn, x0)
+        for _ in range(30):
+            s1.solve_async(True)
+        s1.sync()
+        assert np.array_equal(s1.solution(), want)
+        assert not s1.flags().any()
+        s1.close()
+
+
 def test_scan_path_is_bit_reproducible():
     # warp-synchronous shared-memory code with TMA copies: a data race would show up as run-to-run differences.
     # 40 repeated solves of the same resident batch (more warps than one wave of the GPU) must be bit-identical,
