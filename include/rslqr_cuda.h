@@ -214,6 +214,23 @@ int rslqr_cuda_la_cholesky(double* A, int n, int* info);          /* in-place lo
 int rslqr_cuda_la_trisolve(const double* L, int n, double* b, int m, int which); /* 0: L^-1 b, 1: L^-T b, 2: both */
 
 /* pinned host memory helpers so that callers can stage uploads at full PCIe rate */
+/* Solve without any allocation. No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same kernels and launch order as rslqr_cuda_solve_async in RSLQR_MODE_SCAN with the rhs packed from the problem
+ * data, but without a handle: the caller passes DEVICE buffers on `device` (16-byte aligned)
+ *     d_knots [batch][N][stride]  flat knot blocks (rslqr_cuda_knot_stride)     d_x0   [batch][n]
+ *     d_soln  [batch][N][2n+m]    out, [lambda_k, x_k, u_k]                      d_flags [batch] out, 0 = solved
+ * and everything the kernels keep between launches lives in one static device array of RSLQR_STATIC_SCRATCH_BYTES
+ * (32 MiB; every GPU that loads the library holds it until exit). The call enqueues on `stream` (NULL = the legacy
+ * default stream) and calls no cudaMalloc / cudaFree or any other allocating routine. Shapes: those of the scan
+ * path ((12,4), (6,3), (12,6), (8,4), (16,8), (4,2)), power-of-two N >= 8; about 0.98 MB of scratch per problem at
+ * n=12, m=4, N=256 (33 problems fit). A size beyond the array is rejected with RSLQR_E_ARG and a message that
+ * states the bytes needed. ALL calls on a device share the array: calls that overlap on the GPU (different streams,
+ * or graphs replayed concurrently) race; serialise them. */
+#define RSLQR_STATIC_SCRATCH_BYTES 33554432u /* 32 MiB */
+int rslqr_cuda_solve_static(int n, int m, int nhorizon, int batch, int device, const double* d_knots,
+                            const double* d_x0, double* d_soln, int* d_flags, void* stream);
+
 void* rslqr_cuda_host_alloc(size_t bytes);
 void rslqr_cuda_host_free(void* p);
 /* page-lock (and later release) memory the caller already owns, e.g. the malloc'ed mirrors behind solver->fact /

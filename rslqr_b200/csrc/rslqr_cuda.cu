@@ -1038,3 +1038,114 @@ extern "C" int rslqr_cuda_shard_exchange(rslqr_cuda_solver** hs, int nranks, dou
   }
   return RSLQR_OK;
 }
+
+// ------------------------------------------------------------------ solve without any allocation
+// rslqr_cuda_solve_static: the scan-path solve (the launches of rslqr_cuda_solve_async in RSLQR_MODE_SCAN, same
+// kernels, same order) for callers that cannot allocate: code under CUDA graph capture, tight serving loops. No handle:
+// the caller passes the device buffers of the problems, the solutions and the per-problem flags; everything the
+// kernels keep between launches (elements of the subtrees, separator records, multipliers of the upper separators,
+// status words) lives in ONE file-scope device array of RSLQR_STATIC_SCRATCH_BYTES that every GPU loading the library
+// holds until exit. In host code `g_static_scratch` is only the host-side stand-in of that array: its device address
+// comes from cudaGetSymbolAddress, once per device, with that device current (static_scratch_base).
+// All calls on a device share the array: calls that overlap on the GPU (different streams) race.
+static __device__ __align__(256) unsigned char g_static_scratch[RSLQR_STATIC_SCRATCH_BYTES];
+
+static int static_scratch_base(int device, unsigned char** out) {
+  constexpr int MAXDEV = 64;
+  static std::mutex mu;
+  static unsigned char* base[MAXDEV] = {};
+  if (device < 0 || device >= MAXDEV) return fail(RSLQR_E_ARG, "solve_static: device index out of range");
+  std::lock_guard<std::mutex> lock(mu);
+  if (!base[device]) {  // (the caller made `device` current)
+    unsigned char* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, g_static_scratch);
+    if (e != cudaSuccess || !p) {
+      cudaGetLastError();
+      return fail(RSLQR_E_CUDA, std::string("solve_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+    }
+    base[device] = p;
+  }
+  *out = base[device];
+  return RSLQR_OK;
+}
+
+extern "C" int rslqr_cuda_solve_static(int n, int m, int nhorizon, int batch, int device, const double* d_knots,
+                                       const double* d_x0, double* d_soln, int* d_flags, void* stream) {
+  if (!d_knots || !d_x0 || !d_soln || !d_flags) return fail(RSLQR_E_ARG, "solve_static: a buffer is NULL");
+  if (batch <= 0 || nhorizon < 2 * SCAN_LEAF || (nhorizon & (nhorizon - 1)))
+    return fail(RSLQR_E_ARG, "solve_static: need batch > 0 and a power-of-two horizon >= 8");
+  if (!dual_shape_ok(n, m)) return fail(RSLQR_E_UNSUPPORTED, "solve_static: shape not covered by the scan kernels");
+  const int ndev = rslqr_cuda_device_count();
+  if (ndev <= 0) return fail(RSLQR_E_NODEVICE, "no CUDA device available (there is no CPU fallback)");
+  if (device < 0 || device >= ndev) return fail(RSLQR_E_ARG, "solve_static: device index out of range");
+  CU(cudaSetDevice(device));
+  const Shape s = make_shape(n, m, nhorizon);
+  // the plan scan_plan would make, with its buffers carved out of the static array instead of allocated
+  ScanPlan p;
+  memset(&p, 0, sizeof(p));
+  FusedPlan& f = p.f;
+  p.hybrid = n == 12 && m == 4;
+  p.dual = !p.hybrid;
+  p.ent = dual_ent_doubles(n);
+  f.ns = n; f.ni = m; f.G0 = SCAN_LEAF; f.M0 = nhorizon / SCAN_LEAF; f.use_dmma = 1;
+  {
+    int tier_e = batch >= 64 ? 4 : 8;  // (scan_plan's rule)
+    for (;;) {
+      int M = f.M0, span = f.G0;
+      f.ntiers = 0;
+      bool fits = true;
+      while (M > 1) {
+        if (f.ntiers == 8) { fits = false; break; }
+        const int e = M < tier_e ? M : tier_e;
+        f.tiers[f.ntiers++] = FusedTier{M, e, span};
+        M /= e; span *= e;
+      }
+      if (fits) break;
+      if (tier_e == 8) return fail(RSLQR_E_UNSUPPORTED, "solve_static: horizon too long for the tier slots");
+      tier_e = 8;
+    }
+  }
+  const size_t wsz = (2 * (size_t)n + 1) * n, B = (size_t)batch;
+  size_t need = 0;  // bytes, every piece 256-byte aligned (the bulk copies need 16)
+  auto piece = [&](size_t bytes) { const size_t at = need; need += (bytes + 255) & ~(size_t)255; return at; };
+  const size_t o_sep = piece(sizeof(double) * B * f.M0 * wsz);
+  const size_t o_lam = piece(sizeof(double) * B * (f.M0 + 1) * n);
+  const size_t o_sin = piece(sizeof(double) * B * f.M0 * 3 * wsz);
+  const size_t o_ent0 = piece(sizeof(double) * B * f.M0 * p.ent);
+  size_t o_ent[8] = {};
+  for (int t = 1; t < f.ntiers; ++t) o_ent[t] = piece(sizeof(double) * B * f.tiers[t].Min * p.ent);
+  const size_t status_bytes = sizeof(int) * B * 3 * nhorizon;
+  const size_t o_status = piece(status_bytes);
+  if (need > (size_t)RSLQR_STATIC_SCRATCH_BYTES) {
+    char msg[256];
+    snprintf(msg, sizeof(msg),
+             "solve_static: n=%d m=%d N=%d batch=%d needs %zu bytes of scratch, the static array holds %zu "
+             "(RSLQR_STATIC_SCRATCH_BYTES); use a handle (rslqr_cuda_create) for larger problems",
+             n, m, nhorizon, batch, need, (size_t)RSLQR_STATIC_SCRATCH_BYTES);
+    return fail(RSLQR_E_ARG, msg);
+  }
+  unsigned char* base = nullptr;
+  {
+    int rc = static_scratch_base(device, &base);
+    if (rc) return rc;
+  }
+  f.fb.sep = reinterpret_cast<double*>(base + o_sep);
+  f.fb.lamhat = reinterpret_cast<double*>(base + o_lam);
+  p.sb.sep_in = reinterpret_cast<double*>(base + o_sin);
+  p.sb.ent0 = reinterpret_cast<double*>(base + o_ent0);
+  f.fb.ent[0] = p.sb.ent0;
+  for (int t = 1; t < f.ntiers; ++t) f.fb.ent[t] = reinterpret_cast<double*>(base + o_ent[t]);
+  f.bytes = need;
+  f.available = true;
+  Bufs b;
+  memset(&b, 0, sizeof(b));
+  b.knots = d_knots; b.x0 = d_x0; b.soln = d_soln; b.flags = d_flags;
+  b.status = reinterpret_cast<int*>(base + o_status);
+  cudaStream_t st = (cudaStream_t)stream;
+  // the array keeps the last call's contents: status words and flags must start at zero, the rest is written before
+  // it is read
+  CU(cudaMemsetAsync(b.status, 0, status_bytes, st));
+  CU(cudaMemsetAsync(d_flags, 0, sizeof(int) * B, st));
+  PdlScope pdl(false);
+  return scan_launch(p, s, b, batch, 1, st, g_err);
+}

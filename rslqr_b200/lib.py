@@ -58,6 +58,8 @@ _sig("rslqr_cuda_factor_async", C.c_int, C.c_void_p)
 _sig("rslqr_cuda_riccati_solve_async", C.c_int, C.c_void_p)
 _sig("rslqr_cuda_solve_rhs_async", C.c_int, C.c_void_p, C.c_int)
 _sig("rslqr_cuda_solve_host", C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int)
+_sig("rslqr_cuda_solve_static", C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p,
+     C.c_void_p, C.c_void_p)
 _sig("rslqr_cuda_stage", C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int)
 _sig("rslqr_cuda_schur_task", C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int)
 _sig("rslqr_cuda_download_solution", C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int)
