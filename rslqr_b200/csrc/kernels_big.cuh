@@ -53,7 +53,7 @@ struct BigBufs {
 // dynamic smem: ((NS+8)*(NS+NI) + 2*(NS+NI) + 2*NS + 3*NS) doubles
 // ---------------------------------------------------------------------------------------------------------
 template <int NS, int NI>
-__global__ void __launch_bounds__(256, 2) big_leaf_kernel(Shape s, Bufs b, BigBufs bb, int pack_rhs) {
+__global__ void __launch_bounds__(256, 2) big_leaf_kernel(Shape s, Bufs b, BigBufs bb, int pack_rhs, int sym) {
   using D = BigDim<NS>;
   constexpr int XU = NS + NI, LDA = NS + 8;  // (LDA = 8 mod 16: the DMMA fragments of a warp fall into two wavefronts)
   static_assert(NS == 64 && XU % 4 == 0, "8 warps x 8 rows; k-steps of 4");
@@ -104,32 +104,44 @@ __global__ void __launch_bounds__(256, 2) big_leaf_kernel(Shape s, Bufs b, BigBu
   cp_async_wait_all();
   __syncthreads();
   double* E = bb.entA + ((size_t)prob * N + k) * D::ENT;
+  // sym: the readers of Saa, Sbb (factorization, keep part of the Schur update) take the lower block triangle only
+  // (8 x 8 tiles with column tile <= row tile): the tiles above it are neither computed nor written
   for (int e = tid; e < NS * NS; e += nthr) {
     const int r = e / NS, c = e - r * NS;
-    E[D::OAA + e] = r == c ? sc[r] : 0.0;
+    if (!sym || (c >> 3) <= (r >> 3)) E[D::OAA + e] = r == c ? sc[r] : 0.0;
     E[D::OAB + e] = -sc[r] * AB[c + LDA * r];  // -A(c, r) / Q(r)   (AB is zero for the last knot)
   }
-  // Sbb = [A | B] D [A | B]^T on the fp64 tensor cores: warp w owns rows 8w..8w+7; its A fragments (scaled by D) stay in
-  // registers across the 8 column tiles, 4 column tiles in flight at a time
+  // Sbb = [A | B] D [A | B]^T on the fp64 tensor cores, 8 x 8 output tiles. sym: the 36 tiles of the lower block triangle,
+  // dealt round-robin to the 8 warps (4 or 5 each, all in flight); else all 64 tiles, 8 per warp in two groups of 4.
   {
     const int warp = tid >> 5, lane = tid & 31, q = lane & 3, rr = lane >> 2;
-    constexpr int KS = XU / 4;
-    double a[KS];
-#pragma unroll
-    for (int ks = 0; ks < KS; ++ks) a[ks] = AB[8 * warp + rr + LDA * (4 * ks + q)] * dv[4 * ks + q];
+    constexpr int KS = XU / 4, NT = NS / 8, G = 5;
+    const int ntask = sym ? NT * (NT + 1) / 2 : NT * NT;
 #pragma unroll 1
-    for (int nt0 = 0; nt0 < NS / 8; nt0 += 4) {
-      double c[4][2];
+    for (int i0 = warp; i0 < ntask; i0 += 8 * G) {
+      int tr[G], tc[G];
+      double c[G][2];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) c[u][0] = c[u][1] = 0.0;
-#pragma unroll
+      for (int u = 0; u < G; ++u) {
+        const int i = i0 + 8 * u;
+        int t = 0, jj = i;
+        if (sym) { while (jj > t) { ++t; jj -= t; } }   // i = t (t + 1) / 2 + jj, jj <= t
+        else { t = i / NT; jj = i - t * NT; }
+        tr[u] = i < ntask ? t : 0; tc[u] = i < ntask ? jj : 0;
+        c[u][0] = c[u][1] = 0.0;
+      }
+      const int nact = (ntask - i0 + 7) / 8;  // (warp-uniform) tasks of this group
+#pragma unroll 4
       for (int ks = 0; ks < KS; ++ks) {
+        const double dk = dv[4 * ks + q];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) dmma884(c[u][0], c[u][1], a[ks], AB[8 * (nt0 + u) + rr + LDA * (4 * ks + q)]);
+        for (int u = 0; u < G; ++u)
+          if (u < nact)
+            dmma884(c[u][0], c[u][1], AB[8 * tr[u] + rr + LDA * (4 * ks + q)] * dk, AB[8 * tc[u] + rr + LDA * (4 * ks + q)]);
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u)
-        *reinterpret_cast<double2*>(E + D::OBB + (8 * warp + rr) * NS + 8 * (nt0 + u) + 2 * q) = make_double2(c[u][0], c[u][1]);
+      for (int u = 0; u < G; ++u)
+        if (u < nact) *reinterpret_cast<double2*>(E + D::OBB + (8 * tr[u] + rr) * NS + 8 * tc[u] + 2 * q) = make_double2(c[u][0], c[u][1]);
     }
   }
   {  // sb = [A | B] z: four threads per row, a quarter of the XU terms each (thread = 64 part + row)
@@ -618,12 +630,52 @@ __global__ void __launch_bounds__(BIG_SOLVE_THREADS) big_solve_kernel(Shape s, c
 // stay in registers across all column tiles. NS = 64: 8 warps x 8 rows.
 // dynamic smem: (2 NS + 1) * (NS + 4) doubles.
 // ---------------------------------------------------------------------------------------------------------
+// One run of column tiles of the Schur update for the 8 rows of a warp: out(r, 8j..8j+7) = keep(r, .) - a(r, :) F(:, fcol0 + 8j..)
+// for j < cnt, four tiles in flight, the keep part requested one group ahead of its use. a: A fragments of the rows
+// (registers); Fcols: F column fcol0 in shared memory (ld LDF); keep_row: row r of the block that is updated, nullptr =
+// zero; dst_row: row r of the output block.
+template <int NS>
+__device__ __forceinline__ void big_schur_run(const double (&a)[NS / 4], const double* Fcols, const double* keep_row, double* dst_row,
+                                              int cnt, int q, int rr) {
+  constexpr int LDF = NS + 4, KS = NS / 4;
+  auto keep = [&](int nt0, double2 (&v)[4]) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      v[u] = make_double2(0.0, 0.0);
+      if (keep_row && nt0 + u < cnt) v[u] = __ldg(reinterpret_cast<const double2*>(keep_row + 8 * (nt0 + u) + 2 * q));
+    }
+  };
+  double2 kv[4];
+  keep(0, kv);
+#pragma unroll 1
+  for (int nt0 = 0; nt0 < cnt; nt0 += 4) {
+    double c[4][2];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) { c[u][0] = -kv[u].x; c[u][1] = -kv[u].y; }  // accumulate a.F - keep, negate on the way out
+    if (nt0 + 4 < cnt) keep(nt0 + 4, kv);
+    const int nact = cnt - nt0;  // (warp-uniform) tiles of this group: 1..4
+#pragma unroll
+    for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (u < nact) dmma884(c[u][0], c[u][1], a[ks], Fcols[(8 * (nt0 + u) + rr) * LDF + 4 * ks + q]);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (u < nact) *reinterpret_cast<double2*>(dst_row + 8 * (nt0 + u) + 2 * q) = make_double2(-c[u][0], -c[u][1]);
+  }
+}
+
+// sym: Saa' and Sbb' are symmetric and every reader (the factorization, this kernel's keep part) takes the lower block
+// triangle only, so only the column tiles up to the diagonal one are computed: 136 instead of 192 tiles per merge. Warp w
+// takes row tile w of the left half and row tile 7 - w of the right half: 17 tiles each. sym = 0 (the single-kernel spine
+// variant reads full rows): all tiles, row tile w in both halves.
 template <int NS>
 __global__ void __launch_bounds__(256, 3) big_schur_kernel(Shape s, const double* ein, double* eout, const double* rec_all, int level,
-                                                         int M) {
+                                                         int M, int sym) {
   using D = BigDim<NS>;
   static_assert(NS == 64, "8 warps x 8 rows per half");
-  constexpr int LDF = NS + 4, KS = NS / 4;
+  constexpr int LDF = NS + 4, KS = NS / 4, NT = NS / 8;
   extern __shared__ __align__(16) double Fs[];  // column c of F at Fs + c * LDF
   const int N = s.N;
   const int prob = blockIdx.x / M, t = blockIdx.x % M;
@@ -638,63 +690,39 @@ __global__ void __launch_bounds__(256, 3) big_schur_kernel(Shape s, const double
     const int c = (2 * e) / NS, k = 2 * e - c * NS;
     cp_async16(Fs + c * LDF + k, rec + 2 * e);
   }
-  const int r = 8 * warp + rr;  // row within a half
+  const int tL = warp, tR = sym ? NT - 1 - warp : warp;  // row tiles of this warp in the left / right half
   // A fragments: left half: SabL(r, k); right half: SabR(k, r). Those of the left half are requested while F is in flight.
   double a[KS];
+  {
+    const int r = 8 * tL + rr;
 #pragma unroll
-  for (int ks = 0; ks < KS; ++ks) a[ks] = __ldg(EL + D::OAB + r * NS + 4 * ks + q);
+    for (int ks = 0; ks < KS; ++ks) a[ks] = __ldg(EL + D::OAB + r * NS + 4 * ks + q);
+  }
   cp_async_wait_all();
   __syncthreads();
-#pragma unroll 1
-  for (int half = 0; half < 2; ++half) {
-    if (half) {
+  const double* zs = Fs + 2 * NS * LDF;
+  {  // left half: [Saa' | Sab' | sa'] rows of row tile tL
+    const int r = 8 * tL + rr;
+    double part = 0.0;
 #pragma unroll
-      for (int ks = 0; ks < KS; ++ks) a[ks] = __ldg(ER + D::OAB + (4 * ks + q) * NS + r);
-    }
-    // zs column: keep - a . zs
-    {
-      double part = 0.0;
+    for (int ks = 0; ks < KS; ++ks) part = fma(a[ks], zs[4 * ks + q], part);
+    part += __shfl_xor_sync(0xffffffffu, part, 1);
+    part += __shfl_xor_sync(0xffffffffu, part, 2);
+    if (q == 0) EO[D::OSA + r] = EL[D::OSA + r] - part;
+    big_schur_run<NS>(a, Fs, EL + D::OAA + r * NS, EO + D::OAA + r * NS, sym ? tL + 1 : NT, q, rr);   // f_L -> Saa'
+    big_schur_run<NS>(a, Fs + NS * LDF, nullptr, EO + D::OAB + r * NS, NT, q, rr);                    // f_R -> Sab'
+  }
+  {  // right half: [Sbb' | sb'] rows of row tile tR
+    const int r = 8 * tR + rr;
 #pragma unroll
-      for (int ks = 0; ks < KS; ++ks) part = fma(a[ks], Fs[2 * NS * LDF + 4 * ks + q], part);
-      part += __shfl_xor_sync(0xffffffffu, part, 1);
-      part += __shfl_xor_sync(0xffffffffu, part, 2);
-      if (q == 0) EO[(half ? D::OSB : D::OSA) + r] = (half ? ER[D::OSB + r] : EL[D::OSA + r]) - part;
-    }
-    // column tiles: left half: 2NS columns (f_L -> Saa', f_R -> Sab'); right half: NS columns (f_R -> Sbb')
-    const int ntiles = half ? NS / 8 : 2 * NS / 8;
-    // keep part of a group of 4 column tiles (requested one group ahead of its use)
-    auto keep = [&](int nt0, double2 (&v)[4]) {
+    for (int ks = 0; ks < KS; ++ks) a[ks] = __ldg(ER + D::OAB + (4 * ks + q) * NS + r);
+    double part = 0.0;
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int col = 8 * (nt0 + u) + 2 * q;  // column of this half's output
-        v[u] = make_double2(0.0, 0.0);
-        if (half) v[u] = __ldg(reinterpret_cast<const double2*>(ER + D::OBB + r * NS + col));
-        else if (col < NS) v[u] = __ldg(reinterpret_cast<const double2*>(EL + D::OAA + r * NS + col));
-      }
-    };
-    double2 kv[4];
-    keep(0, kv);
-#pragma unroll 1
-    for (int nt0 = 0; nt0 < ntiles; nt0 += 4) {
-      double c[4][2];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) { c[u][0] = -kv[u].x; c[u][1] = -kv[u].y; }  // accumulate a.F - keep, negate on the way out
-      if (nt0 + 4 < ntiles) keep(nt0 + 4, kv);
-#pragma unroll
-      for (int ks = 0; ks < KS; ++ks) {
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const int fc = (half ? NS : 0) + 8 * (nt0 + u) + rr;  // column of F: f_L 0..NS-1, f_R NS..2NS-1
-          dmma884(c[u][0], c[u][1], a[ks], Fs[fc * LDF + 4 * ks + q]);
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int col = 8 * (nt0 + u) + 2 * q;
-        double* dst = half ? EO + D::OBB + r * NS + col : (col < NS ? EO + D::OAA + r * NS + col : EO + D::OAB + r * NS + col - NS);
-        *reinterpret_cast<double2*>(dst) = make_double2(-c[u][0], -c[u][1]);
-      }
-    }
+    for (int ks = 0; ks < KS; ++ks) part = fma(a[ks], zs[4 * ks + q], part);
+    part += __shfl_xor_sync(0xffffffffu, part, 1);
+    part += __shfl_xor_sync(0xffffffffu, part, 2);
+    if (q == 0) EO[D::OSB + r] = ER[D::OSB + r] - part;
+    big_schur_run<NS>(a, Fs + NS * LDF, ER + D::OBB + r * NS, EO + D::OBB + r * NS, sym ? tR + 1 : NT, q, rr);  // f_R -> Sbb'
   }
 }
 
@@ -727,25 +755,37 @@ __global__ void __launch_bounds__(NS) big_topdown_kernel(int N, const double* re
 // lambda_0 = Q_0 x0 + q_0 + A_0^T lambda_1 (src/nested_dissection.c:24-59). One CTA per (problem, knot), one thread per row.
 // ---------------------------------------------------------------------------------------------------------
 template <int NS, int NI>
-__global__ void __launch_bounds__(NS + NI) big_down_kernel(Shape s, Bufs b, const double* lam_all, int pack_rhs) {
-  constexpr int XU = NS + NI;
-  __shared__ double ln[NS];
+__global__ void __launch_bounds__(256) big_down_kernel(Shape s, Bufs b, const double* lam_all, int pack_rhs) {
+  constexpr int XU = NS + NI, CPW = XU / 8;
+  static_assert(NS == 64 && XU % 8 == 0, "two k per lane; columns dealt to 8 warps");
+  __shared__ double dot[XU];
   const int N = s.N;
   const int prob = blockIdx.x / N, k = blockIdx.x % N;
-  const int r = threadIdx.x;
+  const int r = threadIdx.x, warp = r >> 5, lane = r & 31;
   const double* lam = lam_all + (size_t)prob * (N + 1) * NS;
   const bool first = k == 0, last = k == N - 1;
-  if (r < NS) ln[r] = lam[(size_t)(k + 1) * NS + r];
+  const double* kn = knot_ptr(s, b, prob, k);
+  // [A | B]^T lambda_{k+1}: warp w takes columns w, w + 8, ...: a lane reads two consecutive-by-lane elements of a column
+  // (coalesced), all 2 CPW loads of the warp in flight, then a shuffle reduction per column
+  {
+    const double l0 = lam[(size_t)(k + 1) * NS + lane], l1 = lam[(size_t)(k + 1) * NS + 32 + lane];
+    double part[CPW];
+#pragma unroll
+    for (int u = 0; u < CPW; ++u) {
+      const double* col = kn + s.oA + (size_t)(warp + 8 * u) * NS;
+      part[u] = last ? 0.0 : fma(__ldg(col + lane), l0, __ldg(col + 32 + lane) * l1);
+    }
+#pragma unroll
+    for (int u = 0; u < CPW; ++u) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) part[u] += __shfl_xor_sync(0xffffffffu, part[u], o);
+      if (lane == 0) dot[warp + 8 * u] = part[u];
+    }
+  }
   __syncthreads();
   if (r >= XU) return;
-  const double* kn = knot_ptr(s, b, prob, k);
   double* out = soln_ptr(s, b, prob, k);
-  double acc = 0.0;  // row r of [A | B]^T lambda_{k+1}
-  if (!last) {
-    const double* col = kn + s.oA + r * NS;
-#pragma unroll 8
-    for (int c = 0; c < NS; ++c) acc = fma(__ldg(col + c), ln[c], acc);
-  }
+  const double acc = dot[r];  // row r of [A | B]^T lambda_{k+1}
   const double d = kn[r];
   double rx;
   if (!pack_rhs) rx = out[NS + r];
@@ -832,7 +872,7 @@ inline int big_launch(BigPlan& p, const Shape& s, const Bufs& b, int batch, int 
     err = std::string("big launch: ") + cudaGetErrorString(e);
     return -3;
   }
-  big_leaf_kernel<NS, NI><<<(unsigned)((size_t)batch * N), 256, leaf_smem, st>>>(s, b, p.bb, pack_rhs);
+  big_leaf_kernel<NS, NI><<<(unsigned)((size_t)batch * N), 256, leaf_smem, st>>>(s, b, p.bb, pack_rhs, one_kernel_spine ? 0 : 1);
   ++p.launches;
   const double* ein = p.bb.entA;
   for (int level = 0; level < s.K; ++level) {
@@ -853,7 +893,8 @@ inline int big_launch(BigPlan& p, const Shape& s, const Bufs& b, int batch, int 
       p.launches += 2;
     }
     if (level < s.K - 1) {
-      big_schur_kernel<NS><<<(unsigned)((size_t)batch * M), 256, schur_smem, st>>>(s, ein, eout, p.bb.rec, level, M);
+      big_schur_kernel<NS><<<(unsigned)((size_t)batch * M), 256, schur_smem, st>>>(s, ein, eout, p.bb.rec, level, M,
+                                                                                     one_kernel_spine ? 0 : 1);
       ++p.launches;
     }
     ein = eout;
@@ -863,7 +904,7 @@ inline int big_launch(BigPlan& p, const Shape& s, const Bufs& b, int batch, int 
     big_topdown_kernel<NS><<<(unsigned)((size_t)batch * M), NS, 0, st>>>(N, p.bb.rec, p.bb.lam, level, M);
     ++p.launches;
   }
-  big_down_kernel<NS, NI><<<(unsigned)((size_t)batch * N), NS + NI, 0, st>>>(s, b, p.bb.lam, pack_rhs);
+  big_down_kernel<NS, NI><<<(unsigned)((size_t)batch * N), 256, 0, st>>>(s, b, p.bb.lam, pack_rhs);
   ++p.launches;
   e = cudaGetLastError();
   if (e != cudaSuccess) { err = std::string("big launch: ") + cudaGetErrorString(e); return -3; }
