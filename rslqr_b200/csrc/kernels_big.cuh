@@ -2,18 +2,17 @@
 // n = 64, m = 16 (BASELINE configs[4]): an element [Saa | Sab | Sbb | sa | sb] is 99 KB and a merge touches three of
 // them plus a 66 KB record, so elements live in HBM / L2 and a CTA (not a warp) owns a merge.
 //
-// Per level, two launches over all (problem, merge) pairs:
-//   big_spine_kernel : S = SbbL + SaaR, then ONE elimination sweep with the 2n+1 right-hand sides riding along as extra
-//                      rows, one row per THREAD in registers (rows of S | columns of S_L | columns of S_R | s; the same
-//                      scheme as spine_core2, with the pivot rows broadcast through shared memory), then the backward
-//                      sweep; [f_L | f_R | zs] goes straight from registers to the separator's record.
-//                      (= ndlqr_FactorInnerProduct + Cholesky + ndlqr_SolveCholeskyFactor, src/nested_dissection.c:114-152)
-//   big_schur_kernel : Saa' = SaaL - SabL f_L, Sab' = -SabL f_R, sa' = saL - SabL zs,
-//                      Sbb' = SbbR - SabR^T f_R, sb' = sbR - SabR^T zs      on mma.sync.m8n8k4.f64
-//                      (= ndlqr_UpdateShurFactor restricted to what a later inner product reads, :154-171)
-// then one top-down launch per level (lambda of the separators from the records) and big_down_kernel (x_k, u_k from the
-// leaf equations, as scan_down_kernel). Against the staged path on this shape (every knot updated at every level, dense
-// `fact` array of 755 MB per problem): 3.4 instead of 23.6 GFLOP per solve, 0.22 instead of 0.76 GB per problem.
+// Per level, three launches over all (problem, merge) pairs, all block arithmetic on mma.sync.m8n8k4.f64:
+//   big_factor_reg_kernel : S = SbbL + SaaR = U^T D U                  (ndlqr_FactorInnerProduct + the separator
+//                           Cholesky, src/nested_dissection.c:114-134, src/solve.c:87-98)
+//   big_solve_kernel      : W = U^-T [S_L | S_R | s]                   (the forward half of ndlqr_SolveCholeskyFactor, :136-152)
+//   big_schur_kernel      : Saa' = SaaL - W_L^T D^-1 W_L, Sab' = -W_L^T D^-1 W_R, sa' = saL - W_L^T D^-1 w_s,
+//                           Sbb' = SbbR - W_R^T D^-1 W_R, sb' = sbR - W_R^T D^-1 w_s
+//                           (= ndlqr_UpdateShurFactor restricted to what a later inner product reads, :154-171)
+// then one top-down launch per level (lambda of the separators: records, then one back-substitution with U) and
+// big_down_kernel (x_k, u_k from the leaf equations, as scan_down_kernel). Against the staged path on this shape (every
+// knot updated at every level, dense `fact` array of 755 MB per problem): 2.3 instead of 23.6 GFLOP per solve, 0.26
+// instead of 0.76 GB per problem.
 #pragma once
 #include "kernels_fused.cuh"
 
@@ -40,9 +39,9 @@ struct BigDim {
 struct BigBufs {
   double* entA;  // [batch][N][ENT]      elements of the even levels (level l has N >> l of them, packed at the front)
   double* entB;  // [batch][N/2][ENT]    elements of the odd levels
-  double* rec;   // [batch][N][WSZ]      record of the separator after knot i at slot i (slot N-1 unused)
+  double* rec;   // [batch][N][WSZ]      record [W_L | W_R | w_s] of the separator after knot i at slot i (slot N-1 unused)
   double* lam;   // [batch][N+1][NS]     multipliers lambda_k; slots 0 and N stay zero
-  double* ufac;  // [batch][N/2][BigFac::SIZE] factor U, block inverses and 1/d of the merges of the level in flight
+  double* ufac;  // [batch][N][BigFac::SIZE] factor U, block inverses and 1/d of the separator after knot i at slot i
 };
 
 // ---------------------------------------------------------------------------------------------------------
@@ -53,7 +52,7 @@ struct BigBufs {
 // dynamic smem: ((NS+8)*(NS+NI) + 2*(NS+NI) + 2*NS + 3*NS) doubles
 // ---------------------------------------------------------------------------------------------------------
 template <int NS, int NI>
-__global__ void __launch_bounds__(256, 2) big_leaf_kernel(Shape s, Bufs b, BigBufs bb, int pack_rhs, int sym) {
+__global__ void __launch_bounds__(256, 2) big_leaf_kernel(Shape s, Bufs b, BigBufs bb, int pack_rhs) {
   using D = BigDim<NS>;
   constexpr int XU = NS + NI, LDA = NS + 8;  // (LDA = 8 mod 16: the DMMA fragments of a warp fall into two wavefronts)
   static_assert(NS == 64 && XU % 4 == 0, "8 warps x 8 rows; k-steps of 4");
@@ -104,19 +103,19 @@ __global__ void __launch_bounds__(256, 2) big_leaf_kernel(Shape s, Bufs b, BigBu
   cp_async_wait_all();
   __syncthreads();
   double* E = bb.entA + ((size_t)prob * N + k) * D::ENT;
-  // sym: the readers of Saa, Sbb (factorization, keep part of the Schur update) take the lower block triangle only
+  // the readers of Saa, Sbb (factorization, keep part of the Schur update) take the lower block triangle only
   // (8 x 8 tiles with column tile <= row tile): the tiles above it are neither computed nor written
   for (int e = tid; e < NS * NS; e += nthr) {
     const int r = e / NS, c = e - r * NS;
-    if (!sym || (c >> 3) <= (r >> 3)) E[D::OAA + e] = r == c ? sc[r] : 0.0;
+    if ((c >> 3) <= (r >> 3)) E[D::OAA + e] = r == c ? sc[r] : 0.0;
     E[D::OAB + e] = -sc[r] * AB[c + LDA * r];  // -A(c, r) / Q(r)   (AB is zero for the last knot)
   }
-  // Sbb = [A | B] D [A | B]^T on the fp64 tensor cores, 8 x 8 output tiles. sym: the 36 tiles of the lower block triangle,
-  // dealt round-robin to the 8 warps (4 or 5 each, all in flight); else all 64 tiles, 8 per warp in two groups of 4.
+  // Sbb = [A | B] D [A | B]^T on the fp64 tensor cores, 8 x 8 output tiles: the 36 tiles of the lower block triangle,
+  // dealt round-robin to the 8 warps (4 or 5 each, all in flight).
   {
     const int warp = tid >> 5, lane = tid & 31, q = lane & 3, rr = lane >> 2;
     constexpr int KS = XU / 4, NT = NS / 8, G = 5;
-    const int ntask = sym ? NT * (NT + 1) / 2 : NT * NT;
+    constexpr int ntask = NT * (NT + 1) / 2;
 #pragma unroll 1
     for (int i0 = warp; i0 < ntask; i0 += 8 * G) {
       int tr[G], tc[G];
@@ -125,8 +124,7 @@ __global__ void __launch_bounds__(256, 2) big_leaf_kernel(Shape s, Bufs b, BigBu
       for (int u = 0; u < G; ++u) {
         const int i = i0 + 8 * u;
         int t = 0, jj = i;
-        if (sym) { while (jj > t) { ++t; jj -= t; } }   // i = t (t + 1) / 2 + jj, jj <= t
-        else { t = i / NT; jj = i - t * NT; }
+        while (jj > t) { ++t; jj -= t; }   // i = t (t + 1) / 2 + jj, jj <= t
         tr[u] = i < ntask ? t : 0; tc[u] = i < ntask ? jj : 0;
         c[u][0] = c[u][1] = 0.0;
       }
@@ -160,118 +158,20 @@ __global__ void __launch_bounds__(256, 2) big_leaf_kernel(Shape s, Bufs b, BigBu
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Spine of one merge, one CTA of 3 NS + 1 (rounded up to warps) threads, one row of NS doubles per thread in registers:
-//   threads [0,NS)      : row t of S = SbbL + SaaR
-//   threads [NS,2NS)    : column c of S_L = row c of SabL
-//   threads [2NS,3NS)   : column c of S_R = column c of SabR
-//   thread  3NS         : s = sbL + saR
-// Step j: thread j scales its row by 1/d_j and publishes [1/d_j | U(j, j+1..)] in shared memory; everybody eliminates
-// with its own unscaled element (an appended row ends up holding D^-1 Lt^-1 y). The backward sweep x_j = y_j -
-// sum_{k>j} U(j,k) x_k reads the same rows. Returns the solved columns straight into the record.
-// dynamic smem: NS * (NS + 2) doubles.
-// ---------------------------------------------------------------------------------------------------------
-template <int NS>
-__host__ __device__ constexpr int big_spine_threads() { return ((3 * NS + 1 + 31) / 32) * 32; }
-
-template <int NS>
-__global__ void __launch_bounds__(big_spine_threads<NS>()) big_spine_kernel(Shape s, Bufs b, const double* ein, double* rec_all,
-                                                                            int level, int M) {
-  using D = BigDim<NS>;
-  constexpr int LD = NS + 2;
-  extern __shared__ __align__(16) double Ur[];
-  __shared__ int s_bad;
-  const int N = s.N;
-  const int prob = blockIdx.x / M, t = blockIdx.x % M;
-  const int tid = threadIdx.x;
-  const int Min = 2 * M;                                   // elements of this level per problem
-  const double* EL = ein + ((size_t)prob * Min + 2 * t) * D::ENT;
-  const double* ER = EL + D::ENT;
-  const int i_sep = ((2 * t + 1) << level) - 1;            // knot index of the separator
-  double row[NS];
-  if (tid == 0) s_bad = 0;
-  if (tid < NS) {
-    const double2* pa = reinterpret_cast<const double2*>(EL + D::OBB + tid * NS);
-    const double2* pb = reinterpret_cast<const double2*>(ER + D::OAA + tid * NS);
-#pragma unroll
-    for (int k = 0; k < NS; k += 2) {
-      const double2 a = __ldg(pa + k / 2), c = __ldg(pb + k / 2);
-      row[k] = a.x + c.x; row[k + 1] = a.y + c.y;
-    }
-  } else if (tid < 2 * NS) {
-    const double2* pa = reinterpret_cast<const double2*>(EL + D::OAB + (tid - NS) * NS);
-#pragma unroll
-    for (int k = 0; k < NS; k += 2) { const double2 a = __ldg(pa + k / 2); row[k] = a.x; row[k + 1] = a.y; }
-  } else if (tid < 3 * NS) {
-    const double* pc = ER + D::OAB + (tid - 2 * NS);
-#pragma unroll
-    for (int k = 0; k < NS; ++k) row[k] = __ldg(pc + k * NS);
-  } else {
-#pragma unroll
-    for (int k = 0; k < NS; ++k) row[k] = tid == 3 * NS ? __ldg(EL + D::OSB + k) + __ldg(ER + D::OSA + k) : 0.0;
-  }
-#pragma unroll
-  for (int j = 0; j < NS; ++j) {
-    const int j0 = j & ~1;
-    if (tid == j) {
-      const double d = row[j];
-      if (!(d > 0.0)) s_bad = 1;
-      const double dinv = 1.0 / d;
-#pragma unroll
-      for (int k = j0; k < NS; k += 2) {
-        const double u0 = k < j ? 0.0 : (k == j ? dinv : row[k] * dinv);
-        const double u1 = k + 1 == j ? dinv : row[k + 1] * dinv;
-        *reinterpret_cast<double2*>(Ur + j * LD + k) = make_double2(u0, u1);
-      }
-    }
-    __syncthreads();
-    const double m1 = row[j];
-    double dinv = 0.0;
-#pragma unroll
-    for (int k = j0; k < NS; k += 2) {
-      const double2 u = *reinterpret_cast<const double2*>(Ur + j * LD + k);
-      if (k == j) dinv = u.x;
-      else if (k > j) row[k] = fma(-m1, u.x, row[k]);
-      if (k + 1 == j) dinv = u.y;
-      else if (k + 1 > j) row[k + 1] = fma(-m1, u.y, row[k + 1]);
-    }
-    row[j] = m1 * dinv;
-  }
-  if (tid >= NS && tid <= 3 * NS) {
-#pragma unroll
-    for (int j = NS - 2; j >= 0; --j) {
-      const int k0 = (j + 1) & ~1;
-#pragma unroll
-      for (int k = NS - 2; k >= k0; k -= 2) {  // the latest x last: one dependent FMA per step
-        const double2 u = *reinterpret_cast<const double2*>(Ur + j * LD + k);
-        row[j] = fma(-u.y, row[k + 1], row[j]);
-        if (k > j) row[j] = fma(-u.x, row[k], row[j]);
-      }
-    }
-    double* rec = rec_all + ((size_t)prob * N + i_sep) * D::WSZ + (size_t)(tid - NS) * NS;  // column tid - NS of [f_L | f_R | zs]
-#pragma unroll
-    for (int k = 0; k < NS; k += 2) *reinterpret_cast<double2*>(rec + k) = make_double2(row[k], row[k + 1]);
-  }
-  __syncthreads();
-  if (tid == 0 && s_bad) {
-    b.status[(size_t)prob * 3 * N + rs_slot_S(t, level, N)] = -1;
-    b.flags[prob] = 1;
-  }
-}
-
-// ---------------------------------------------------------------------------------------------------------
-// The same spine as big_spine_kernel, split so that the 2n+1 solves run on the fp64 tensor cores (RSLQR_BIG_SPINE=1
-// selects the single-kernel variant above for A/B runs):
-//
-//   big_factor_kernel : ONE WARP per merge. S = SbbL + SaaR is built in shared memory and factored in place,
-//                       S = U^T D U (right-looking LDL^T, the warp's lanes own the rows below the pivot; no CTA barrier,
-//                       so the pivot chains of the merges of a CTA overlap). Output per merge (`ufac`): U (unit upper,
-//                       row-major ld NS), the inverses X_b of the 8 x 8 diagonal blocks of L = U^T, and 1/d.
-//   big_solve_kernel  : one CTA of 8 warps per merge. Y = [S_L | S_R | s] (NS x 2NS+1, padded to 17 column tiles of 8) and U
-//                       are staged in shared memory; a warp owns column tiles and runs BOTH blocked substitution sweeps
-//                       for them without any CTA barrier: for block row b,
-//                           W_b = X_b (Y_b - sum_{b' < b} L_bb' W_b'),   then   F_b = X_b^T (D^-1 W_b - sum_{b' > b} U_bb' F_b')
-//                       every product an m8n8k4 DMMA pair (the 8 x 8 blocks are the A operands, the column tile of Y the B
-//                       operand, read back from shared memory in B-fragment layout). [f_L | f_R | zs] = F goes to the record.
+// Spine of a merge: S = SbbL + SaaR = U^T D U, then W = U^-T [S_L | S_R | s] (the forward substitution ONLY).
+//   big_factor_reg_kernel : one warp per merge, S in registers; output per separator (`ufac`, slot = the separator's
+//                           knot index): U (unit upper, row-major ld NS), the inverses X_b of the 8 x 8 diagonal blocks
+//                           of L = U^T, and 1/d.
+//   big_solve_kernel      : one CTA of 9 warps per merge. Y = [S_L | S_R | s] (NS x 2NS+1, padded to 17 column tiles of 8)
+//                           and U are staged in shared memory; a warp owns column tiles and runs the blocked forward
+//                           substitution for them without any CTA barrier: for block row b,
+//                               W_b = X_b (Y_b - sum_{b' < b} L_bb' W_b')
+//                           every product an m8n8k4 DMMA pair. W = [W_L | W_R | w_s] goes to the separator's record.
+// The backward substitution is never run on the 2n+1 columns: the Schur update only needs products of the form
+// S_x^T S^-1 S_y = W_x^T D^-1 W_y (big_schur_kernel), and the separator's multiplier
+//     lambda = S^-1 (s - S_L lambda_a - S_R lambda_b) = U^-1 D^-1 (w_s - W_L lambda_a - W_R lambda_b)
+// needs ONE back-substitution per separator, in the top-down pass (big_topdown_kernel), which is why U and 1/d of
+// every separator are kept.
 // ---------------------------------------------------------------------------------------------------------
 template <int NS>
 struct BigFac {
@@ -279,110 +179,16 @@ struct BigFac {
   static constexpr int OU = 0, OX = NS * NS, OD = NS * NS + NB * 64, SIZE = NS * NS + NB * 64 + NS;  // doubles per merge in `ufac`
 };
 
-constexpr int BIG_FACTOR_WPC = 12;  // merges (warps) per CTA of big_factor_kernel
-
-// packed lower triangle: element (i, k), k <= i, at i (i + 1) / 2 + k
-__device__ __forceinline__ int big_tri(int i) { return (i * (i + 1)) >> 1; }
-
-template <int NS>
-__host__ __device__ constexpr int big_factor_warp_doubles() { return ((NS * (NS + 1) / 2) + 1) & ~1; }
-
-template <int NS>
-__global__ void __launch_bounds__(32 * BIG_FACTOR_WPC) big_factor_kernel(Shape s, Bufs b, const double* ein, double* ufac, int level,
-                                                                          int M, long long nmerge) {
-  using D = BigDim<NS>;
-  using F = BigFac<NS>;
-  static_assert(NS == 64, "two trailing columns per lane");
-  extern __shared__ __align__(16) double smf[];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const long long mi = (long long)blockIdx.x * BIG_FACTOR_WPC + warp;
-  if (mi >= nmerge) return;
-  const int N = s.N;
-  const int prob = (int)(mi / M), t = (int)(mi % M);
-  double* A = smf + (size_t)warp * big_factor_warp_doubles<NS>();   // lower triangle of S, packed by rows
-  const double* EL = ein + ((size_t)prob * 2 * M + 2 * t) * D::ENT;
-  const double* ER = EL + D::ENT;
-  for (int e = lane; e < NS * NS; e += 32) {
-    const int r = e / NS, c = e - r * NS;
-    if (c <= r) A[big_tri(r) + c] = __ldg(EL + D::OBB + e) + __ldg(ER + D::OAA + e);
-  }
-  __syncwarp();
-  double* U = ufac + (size_t)mi * F::SIZE;
-  int bad = 0;
-  // right-looking LDL^T on the lower triangle: after step j column j holds the multipliers l(i,j) = S'(i,j) / d_j.
-  // A lane owns the trailing COLUMNS k0 = j + 1 + lane and k1 = k0 + 32: the update S'(i,k) -= l(i,j) S'(k,j) walks down
-  // the rows i >= k with S'(k,j) in a register, l(i,j) a broadcast load and S'(i, k0..) one contiguous run per row.
-#pragma unroll 1
-  for (int j = 0; j < NS; ++j) {
-    const double d = A[big_tri(j) + j];
-    if (!(d > 0.0)) bad = 1;
-    const double dinv = 1.0 / d;
-    const int k0 = j + 1 + lane, k1 = k0 + 32;
-    const bool two = j + 33 < NS;                                    // (warp-uniform) a second column per lane exists
-    const double c0 = k0 < NS ? A[big_tri(k0) + j] : 0.0, c1 = k1 < NS ? A[big_tri(k1) + j] : 0.0;  // unscaled S'(k, j)
-    __syncwarp();
-    if (k0 < NS) A[big_tri(k0) + j] = c0 * dinv;
-    if (k1 < NS) A[big_tri(k1) + j] = c1 * dinv;
-    if (lane == 0) A[big_tri(j) + j] = dinv;
-    __syncwarp();
-#pragma unroll 1
-    for (int i = j + 1; i < NS; i += 4) {
-      double li[4], a0[4], a1[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {  // all loads of the group before any store (the compiler cannot tell they do not alias)
-        const int r = i + u < NS ? i + u : NS - 1;
-        const int base = big_tri(r);
-        li[u] = A[base + j];
-        a0[u] = k0 <= r ? A[base + k0] : 0.0;
-        a1[u] = (two && k1 <= r) ? A[base + k1] : 0.0;
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const int r = i + u;
-        const int base = big_tri(r < NS ? r : NS - 1);
-        if (r < NS && k0 <= r) A[base + k0] = fma(-li[u], c0, a0[u]);
-        if (two && r < NS && k1 <= r) A[base + k1] = fma(-li[u], c1, a1[u]);
-      }
-    }
-    __syncwarp();
-  }
-  // U(j,k) = l(k,j) for k > j (row-major, ld NS), unit diagonal implied; 1/d
-  for (int e = lane; e < NS * NS; e += 32) {
-    const int j = e / NS, k = e - j * NS;
-    U[F::OU + e] = k > j ? A[big_tri(k) + j] : (k == j ? 1.0 : 0.0);
-  }
-  for (int j = lane; j < NS; j += 32) U[F::OD + j] = A[big_tri(j) + j];
-  // X_b = inverse of the unit lower 8 x 8 diagonal block of L = U^T: lane = (4 blocks per round) x 8 columns
-#pragma unroll 1
-  for (int round = 0; round < F::NB / 4; ++round) {
-    const int blk = 4 * round + (lane >> 3), c = lane & 7;
-    double x[8];
-#pragma unroll
-    for (int r = 0; r < 8; ++r) {
-      double v = r == c ? 1.0 : 0.0;
-#pragma unroll
-      for (int k = 0; k < 8; ++k)
-        if (k < r) v = fma(-A[big_tri(8 * blk + r) + 8 * blk + k], x[k], v);   // T(r, k) = l(8blk + r, 8blk + k)
-      x[r] = r < c ? 0.0 : v;
-    }
-#pragma unroll
-    for (int r = 0; r < 8; ++r) U[F::OX + blk * 64 + r * 8 + c] = x[r];
-  }
-  if (bad && lane == 0) {
-    b.status[(size_t)prob * 3 * N + rs_slot_S(t, level, N)] = -1;
-    b.flags[prob] = 1;
-  }
-}
-
 // ---------------------------------------------------------------------------------------------------------
-// big_factor_reg_kernel: the same outputs as big_factor_kernel, with the matrix held in REGISTERS as DMMA accumulator
+// big_factor_reg_kernel: the matrix is held in REGISTERS as DMMA accumulator
 // fragments (lower block triangle: 36 blocks of 8 x 8, two doubles per lane each) and a blocked right-looking LDL^T:
 //   for block column b:  S_bb = L_bb D_b L_bb^T by row elimination on [S_bb | I] inside the warp (shuffles; gives
 //                         X_b = L_bb^-1 directly),
 //                        panel  R_c = S_cb X_b^T (= L_cb D_b),  L_cb = R_c D_b^-1          (2 DMMAs per block)
 //                        trailing S_cc' -= L_cb (L_c'b D_b)^T                                (2 DMMAs per block)
 // C fragments become A / B operands through four 64-bit shuffles (frag_c2a). One warp per merge, no shared memory, no
-// barrier; about 2.5 k warp instructions per matrix against 78 k for the packed-triangle kernel above.
+// barrier; about 2.5 k warp instructions per matrix (a scalar one-warp factorization of a packed triangle in shared
+// memory, the first version of this kernel, executed 78 k).
 // ---------------------------------------------------------------------------------------------------------
 constexpr int BIG_FACTOR_REG_WPC = 4;
 
@@ -409,7 +215,7 @@ __global__ void __launch_bounds__(32 * BIG_FACTOR_REG_WPC) big_factor_reg_kernel
   const int prob = (int)(mi / M), t = (int)(mi % M);
   const double* EL = ein + ((size_t)prob * 2 * M + 2 * t) * D::ENT;
   const double* ER = EL + D::ENT;
-  double* U = ufac + (size_t)mi * F::SIZE;
+  double* U = ufac + ((size_t)prob * N + ((2 * t + 1) << level) - 1) * F::SIZE;  // slot = the separator's knot index
   double S[NB][NB][2];  // block (c, c'), c >= c', as a C fragment
 #pragma unroll
   for (int c = 0; c < NB; ++c)
@@ -482,17 +288,14 @@ __global__ void __launch_bounds__(32 * BIG_FACTOR_REG_WPC) big_factor_reg_kernel
   }
 }
 
-// Both substitution sweeps for T column tiles at once, RIGHT-LOOKING: the 8 block rows of a tile stay in registers as
-// DMMA accumulators (C fragments); once block row b is final it goes through shared memory once (C layout -> B
-// fragment) and every other block row still to be solved is updated with it, so a B fragment is loaded once per block
-// and an A fragment (8 x 8 block of U) once per DMMA pair of T tiles. The solved tile leaves from registers straight
-// to the record.
-//   forward : W_b = X_b Y_b, then Y_c -= L_cb W_b for c > b          (L_cb (r, k) = U(8b + k, 8c + r))
-//   scaling : V = D^-1 W
-//   backward: F_b = X_b^T V_b, then V_c -= U_cb F_b for c < b
+// Forward substitution for T column tiles at once, RIGHT-LOOKING: the 8 block rows of a tile stay in registers as DMMA
+// accumulators (C fragments); once block row b is final (W_b = X_b Y_b) it leaves for the record straight from the
+// registers, goes through shared memory once (C layout -> B fragment) and every block row below it is updated with it
+// (Y_c -= L_cb W_b, L_cb (r, k) = U(8b + k, 8c + r)), so a B fragment is loaded once per block and an A fragment (8 x 8
+// block of U) once per DMMA pair of T tiles.
 template <int NS, int T>
-__device__ __forceinline__ void big_solve_tiles(const double* Us, const double* Xs, const double* ds, double* const (&Yt)[T],
-                                                double* const (&rec)[T], const int (&ncols)[T]) {
+__device__ __forceinline__ void big_solve_tiles(const double* Us, const double* Xs, double* const (&Yt)[T], double* const (&rec)[T],
+                                                const int (&ncols)[T]) {
   constexpr int NB = NS / 8, LDU = NS + 4, LDY = 2 * NS + 8;
   const int lane = threadIdx.x & 31, q = lane & 3, rr = lane >> 2;
   double c[NB][T][2];
@@ -504,64 +307,38 @@ __device__ __forceinline__ void big_solve_tiles(const double* Us, const double* 
       c[bk][u][0] = cv.x; c[bk][u][1] = cv.y;
     }
   __syncwarp();
-  // C fragment of block row `bk` -> shared memory -> product with an 8 x 8 block (A fragments a0, a1) -> C fragment
-  auto through = [&](int bk, double (&v)[T][2], double a0, double a1) {
 #pragma unroll
-    for (int u = 0; u < T; ++u) *reinterpret_cast<double2*>(Yt[u] + (8 * bk + rr) * LDY + 2 * q) = make_double2(v[u][0], v[u][1]);
+  for (int bk = 0; bk < NB; ++bk) {
+    // W_b = X_b Y_b: C fragment -> shared memory -> B fragment -> product with the 8 x 8 block X_b
+    const double xa0 = Xs[bk * 64 + rr * 8 + q], xa1 = Xs[bk * 64 + rr * 8 + 4 + q];
+#pragma unroll
+    for (int u = 0; u < T; ++u) *reinterpret_cast<double2*>(Yt[u] + (8 * bk + rr) * LDY + 2 * q) = make_double2(c[bk][u][0], c[bk][u][1]);
     __syncwarp();
 #pragma unroll
     for (int u = 0; u < T; ++u) {
       const double b0 = Yt[u][(8 * bk + q) * LDY + rr], b1 = Yt[u][(8 * bk + 4 + q) * LDY + rr];
-      v[u][0] = v[u][1] = 0.0;
-      dmma884(v[u][0], v[u][1], a0, b0);
-      dmma884(v[u][0], v[u][1], a1, b1);
+      c[bk][u][0] = c[bk][u][1] = 0.0;
+      dmma884(c[bk][u][0], c[bk][u][1], xa0, b0);
+      dmma884(c[bk][u][0], c[bk][u][1], xa1, b1);
     }
     __syncwarp();
-  };
-  // block row `bk` (final) as B fragments
-  auto as_b = [&](int bk, const double (&v)[T][2], double (&bf)[T][2]) {
-#pragma unroll
-    for (int u = 0; u < T; ++u) *reinterpret_cast<double2*>(Yt[u] + (8 * bk + rr) * LDY + 2 * q) = make_double2(v[u][0], v[u][1]);
-    __syncwarp();
-#pragma unroll
-    for (int u = 0; u < T; ++u) { bf[u][0] = Yt[u][(8 * bk + q) * LDY + rr]; bf[u][1] = Yt[u][(8 * bk + 4 + q) * LDY + rr]; }
-    __syncwarp();
-  };
-#pragma unroll
-  for (int bk = 0; bk < NB; ++bk) {
-    through(bk, c[bk], Xs[bk * 64 + rr * 8 + q], Xs[bk * 64 + rr * 8 + 4 + q]);  // W_b = X_b Y_b
-    if (bk + 1 < NB) {
-      double bf[T][2];
-      as_b(bk, c[bk], bf);
-#pragma unroll
-      for (int b2 = bk + 1; b2 < NB; ++b2) {
-        const double a0 = -Us[(8 * bk + q) * LDU + 8 * b2 + rr], a1 = -Us[(8 * bk + 4 + q) * LDU + 8 * b2 + rr];
-#pragma unroll
-        for (int u = 0; u < T; ++u) { dmma884(c[b2][u][0], c[b2][u][1], a0, bf[u][0]); dmma884(c[b2][u][0], c[b2][u][1], a1, bf[u][1]); }
-      }
-    }
-  }
-#pragma unroll
-  for (int bk = 0; bk < NB; ++bk) {  // V = D^-1 W
-    const double dr = ds[8 * bk + rr];
-#pragma unroll
-    for (int u = 0; u < T; ++u) { c[bk][u][0] *= dr; c[bk][u][1] *= dr; }
-  }
-#pragma unroll
-  for (int bk = NB - 1; bk >= 0; --bk) {
-    through(bk, c[bk], Xs[bk * 64 + q * 8 + rr], Xs[bk * 64 + (4 + q) * 8 + rr]);  // F_b = X_b^T V_b
-    // the solved block row: straight from the C fragment to the record (column-major, ld NS: 8 consecutive k per column)
+    // the final block row: to the record (column-major, ld NS: 8 consecutive k per column) ...
 #pragma unroll
     for (int u = 0; u < T; ++u) {
       if (2 * q < ncols[u]) rec[u][(size_t)(2 * q) * NS + 8 * bk + rr] = c[bk][u][0];
       if (2 * q + 1 < ncols[u]) rec[u][(size_t)(2 * q + 1) * NS + 8 * bk + rr] = c[bk][u][1];
     }
-    if (bk > 0) {
+    if (bk + 1 < NB) {  // ... and as B fragments into the block rows below
       double bf[T][2];
-      as_b(bk, c[bk], bf);
 #pragma unroll
-      for (int b2 = 0; b2 < bk; ++b2) {
-        const double a0 = -Us[(8 * b2 + rr) * LDU + 8 * bk + q], a1 = -Us[(8 * b2 + rr) * LDU + 8 * bk + 4 + q];
+      for (int u = 0; u < T; ++u) *reinterpret_cast<double2*>(Yt[u] + (8 * bk + rr) * LDY + 2 * q) = make_double2(c[bk][u][0], c[bk][u][1]);
+      __syncwarp();
+#pragma unroll
+      for (int u = 0; u < T; ++u) { bf[u][0] = Yt[u][(8 * bk + q) * LDY + rr]; bf[u][1] = Yt[u][(8 * bk + 4 + q) * LDY + rr]; }
+      __syncwarp();
+#pragma unroll
+      for (int b2 = bk + 1; b2 < NB; ++b2) {
+        const double a0 = -Us[(8 * bk + q) * LDU + 8 * b2 + rr], a1 = -Us[(8 * bk + 4 + q) * LDU + 8 * b2 + rr];
 #pragma unroll
         for (int u = 0; u < T; ++u) { dmma884(c[b2][u][0], c[b2][u][1], a0, bf[u][0]); dmma884(c[b2][u][0], c[b2][u][1], a1, bf[u][1]); }
       }
@@ -580,16 +357,15 @@ __global__ void __launch_bounds__(BIG_SOLVE_THREADS) big_solve_kernel(Shape s, c
   constexpr int NB = NS / 8, LDU = NS + 4, LDY = 2 * NS + 8;
   extern __shared__ __align__(16) double smf[];
   double* Us = smf;                      // U, row-major ld LDU
-  double* Ys = Us + NS * LDU;            // Y / W / F, row k at Ys + k * LDY, column = right-hand side
+  double* Ys = Us + NS * LDU;            // Y / W, row k at Ys + k * LDY, column = right-hand side
   double* Xs = Ys + NS * LDY;            // X_b, 8 x 8 row-major each
-  double* ds = Xs + NB * 64;             // 1/d
   const int N = s.N;
   const int prob = blockIdx.x / M, t = blockIdx.x % M;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nthr = blockDim.x;
   const double* EL = ein + ((size_t)prob * 2 * M + 2 * t) * D::ENT;
   const double* ER = EL + D::ENT;
-  const double* Uf = ufac + ((size_t)prob * M + t) * F::SIZE;
   const int i_sep = ((2 * t + 1) << level) - 1;
+  const double* Uf = ufac + ((size_t)prob * N + i_sep) * F::SIZE;
   // staging by asynchronous copies: everything in flight at once, no staging registers
   for (int e = 2 * tid; e < NS * NS; e += 2 * nthr) {
     const int r = e / NS, c = e - r * NS;
@@ -602,37 +378,38 @@ __global__ void __launch_bounds__(BIG_SOLVE_THREADS) big_solve_kernel(Shape s, c
     const int k = 8 * (tile % (NS / 8)) + (lane >> 2), c = 4 * (tile / (NS / 8)) + (lane & 3);
     cp_async8(Ys + k * LDY + c, EL + D::OAB + c * NS + k);
   }
-  for (int e = 2 * tid; e < NB * 64 + NS; e += 2 * nthr) cp_async16(Xs + e, Uf + F::OX + e);  // X blocks, then 1/d (contiguous)
+  for (int e = 2 * tid; e < NB * 64; e += 2 * nthr) cp_async16(Xs + e, Uf + F::OX + e);  // X blocks
   for (int e = tid; e < NS * 8; e += nthr) {
     const int k = e >> 3, c = e & 7;
     Ys[k * LDY + 2 * NS + c] = c == 0 ? __ldg(EL + D::OSB + k) + __ldg(ER + D::OSA + k) : 0.0;
   }
   cp_async_wait_all();
   __syncthreads();
-  double* rec = rec_all + ((size_t)prob * N + i_sep) * D::WSZ;  // [f_L | f_R | zs], column-major ld NS
+  double* rec = rec_all + ((size_t)prob * N + i_sep) * D::WSZ;  // [W_L | W_R | w_s], column-major ld NS
   if (warp < 8) {
     double* const Yt[2] = {Ys + 8 * warp, Ys + 8 * (warp + 8)};
     double* const rc[2] = {rec + (size_t)8 * warp * NS, rec + (size_t)8 * (warp + 8) * NS};
     const int nc[2] = {8, 8};
-    big_solve_tiles<NS, 2>(Us, Xs, ds, Yt, rc, nc);
+    big_solve_tiles<NS, 2>(Us, Xs, Yt, rc, nc);
   } else {
     double* const Yt[1] = {Ys + 8 * 16};
     double* const rc[1] = {rec + (size_t)8 * 16 * NS};
     const int nc[1] = {1};
-    big_solve_tiles<NS, 1>(Us, Xs, ds, Yt, rc, nc);
+    big_solve_tiles<NS, 1>(Us, Xs, Yt, rc, nc);
   }
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Schur update of one merge on the fp64 tensor cores, one CTA of 8 warps. F = [f_L | f_R | zs] is staged in shared
-// memory (ld NS + 4: the B fragments of a warp fall into two wavefronts); warp w owns rows 8w..8w+7 of the left half
-// (SabL rows -> [Saa' | Sab' | sa']) and rows 8w..8w+7 of the right half (SabR^T rows -> [Sbb' | sb']); its A fragments
-// stay in registers across all column tiles. NS = 64: 8 warps x 8 rows.
+// Schur update of one merge on the fp64 tensor cores, one CTA of 8 warps. W = [W_L | W_R | w_s] (the record) is staged
+// in shared memory (ld NS + 4: the B fragments of a warp fall into two wavefronts) and is BOTH operands:
+//     out(r, c) = keep(r, c) - sum_k W_x(k, r) (1/d_k) W_y(k, c)
+// the A fragments of a warp's 8 rows (column r of W_L or W_R from the record, scaled by 1/d) stay in registers across
+// its column tiles. NS = 64: 8 warps x 8 rows per half.
 // dynamic smem: (2 NS + 1) * (NS + 4) doubles.
 // ---------------------------------------------------------------------------------------------------------
 // One run of column tiles of the Schur update for the 8 rows of a warp: out(r, 8j..8j+7) = keep(r, .) - a(r, :) F(:, fcol0 + 8j..)
-// for j < cnt, four tiles in flight, the keep part requested one group ahead of its use. a: A fragments of the rows
-// (registers); Fcols: F column fcol0 in shared memory (ld LDF); keep_row: row r of the block that is updated, nullptr =
+// for j < cnt (F = W here), four tiles in flight, the keep part requested one group ahead of its use. a: A fragments of
+// the rows (registers); Fcols: column fcol0 of W in shared memory (ld LDF); keep_row: row r of the block that is updated, nullptr =
 // zero; dst_row: row r of the output block.
 template <int NS>
 __device__ __forceinline__ void big_schur_run(const double (&a)[NS / 4], const double* Fcols, const double* keep_row, double* dst_row,
@@ -666,17 +443,17 @@ __device__ __forceinline__ void big_schur_run(const double (&a)[NS / 4], const d
   }
 }
 
-// sym: Saa' and Sbb' are symmetric and every reader (the factorization, this kernel's keep part) takes the lower block
-// triangle only, so only the column tiles up to the diagonal one are computed: 136 instead of 192 tiles per merge. Warp w
-// takes row tile w of the left half and row tile 7 - w of the right half: 17 tiles each. sym = 0 (the single-kernel spine
-// variant reads full rows): all tiles, row tile w in both halves.
+// Saa' and Sbb' are symmetric and every reader (the factorization, this kernel's keep part) takes the lower block triangle
+// only, so only the column tiles up to the diagonal one are computed: 136 instead of 192 tiles per merge. Warp w takes
+// row tile w of the left half and row tile 7 - w of the right half: 17 tiles each.
 template <int NS>
-__global__ void __launch_bounds__(256, 3) big_schur_kernel(Shape s, const double* ein, double* eout, const double* rec_all, int level,
-                                                         int M, int sym) {
+__global__ void __launch_bounds__(256, 3) big_schur_kernel(Shape s, const double* ein, double* eout, const double* rec_all,
+                                                         const double* ufac, int level, int M) {
   using D = BigDim<NS>;
+  using F = BigFac<NS>;
   static_assert(NS == 64, "8 warps x 8 rows per half");
   constexpr int LDF = NS + 4, KS = NS / 4, NT = NS / 8;
-  extern __shared__ __align__(16) double Fs[];  // column c of F at Fs + c * LDF
+  extern __shared__ __align__(16) double Fs[];  // column c of W at Fs + c * LDF
   const int N = s.N;
   const int prob = blockIdx.x / M, t = blockIdx.x % M;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, q = lane & 3, rr = lane >> 2;
@@ -686,67 +463,94 @@ __global__ void __launch_bounds__(256, 3) big_schur_kernel(Shape s, const double
   double* EO = eout + ((size_t)prob * M + t) * D::ENT;
   const int i_sep = ((2 * t + 1) << level) - 1;
   const double* rec = rec_all + ((size_t)prob * N + i_sep) * D::WSZ;
+  const double* dinv = ufac + ((size_t)prob * N + i_sep) * F::SIZE + F::OD;
   for (int e = tid; e < D::WSZ / 2; e += blockDim.x) {
     const int c = (2 * e) / NS, k = 2 * e - c * NS;
     cp_async16(Fs + c * LDF + k, rec + 2 * e);
   }
-  const int tL = warp, tR = sym ? NT - 1 - warp : warp;  // row tiles of this warp in the left / right half
-  // A fragments: left half: SabL(r, k); right half: SabR(k, r). Those of the left half are requested while F is in flight.
-  double a[KS];
-  {
-    const int r = 8 * tL + rr;
+  const int tL = warp, tR = NT - 1 - warp;  // row tiles of this warp in the left / right half
+  double di[KS];
 #pragma unroll
-    for (int ks = 0; ks < KS; ++ks) a[ks] = __ldg(EL + D::OAB + r * NS + 4 * ks + q);
-  }
+  for (int ks = 0; ks < KS; ++ks) di[ks] = __ldg(dinv + 4 * ks + q);
   cp_async_wait_all();
   __syncthreads();
-  const double* zs = Fs + 2 * NS * LDF;
-  {  // left half: [Saa' | Sab' | sa'] rows of row tile tL
+  const double* ws = Fs + 2 * NS * LDF;
+  double a[KS];
+  {  // left half: [Saa' | Sab' | sa'] rows of row tile tL; A fragments: W_L(k, r) / d_k
     const int r = 8 * tL + rr;
     double part = 0.0;
 #pragma unroll
-    for (int ks = 0; ks < KS; ++ks) part = fma(a[ks], zs[4 * ks + q], part);
+    for (int ks = 0; ks < KS; ++ks) {
+      a[ks] = Fs[r * LDF + 4 * ks + q] * di[ks];
+      part = fma(a[ks], ws[4 * ks + q], part);
+    }
     part += __shfl_xor_sync(0xffffffffu, part, 1);
     part += __shfl_xor_sync(0xffffffffu, part, 2);
     if (q == 0) EO[D::OSA + r] = EL[D::OSA + r] - part;
-    big_schur_run<NS>(a, Fs, EL + D::OAA + r * NS, EO + D::OAA + r * NS, sym ? tL + 1 : NT, q, rr);   // f_L -> Saa'
-    big_schur_run<NS>(a, Fs + NS * LDF, nullptr, EO + D::OAB + r * NS, NT, q, rr);                    // f_R -> Sab'
+    big_schur_run<NS>(a, Fs, EL + D::OAA + r * NS, EO + D::OAA + r * NS, tL + 1, q, rr);   // W_L -> Saa'
+    big_schur_run<NS>(a, Fs + NS * LDF, nullptr, EO + D::OAB + r * NS, NT, q, rr);        // W_R -> Sab'
   }
-  {  // right half: [Sbb' | sb'] rows of row tile tR
+  {  // right half: [Sbb' | sb'] rows of row tile tR; A fragments: W_R(k, r) / d_k
     const int r = 8 * tR + rr;
-#pragma unroll
-    for (int ks = 0; ks < KS; ++ks) a[ks] = __ldg(ER + D::OAB + (4 * ks + q) * NS + r);
     double part = 0.0;
 #pragma unroll
-    for (int ks = 0; ks < KS; ++ks) part = fma(a[ks], zs[4 * ks + q], part);
+    for (int ks = 0; ks < KS; ++ks) {
+      a[ks] = Fs[(NS + r) * LDF + 4 * ks + q] * di[ks];
+      part = fma(a[ks], ws[4 * ks + q], part);
+    }
     part += __shfl_xor_sync(0xffffffffu, part, 1);
     part += __shfl_xor_sync(0xffffffffu, part, 2);
     if (q == 0) EO[D::OSB + r] = ER[D::OSB + r] - part;
-    big_schur_run<NS>(a, Fs + NS * LDF, ER + D::OBB + r * NS, EO + D::OBB + r * NS, sym ? tR + 1 : NT, q, rr);  // f_R -> Sbb'
+    big_schur_run<NS>(a, Fs + NS * LDF, ER + D::OBB + r * NS, EO + D::OBB + r * NS, tR + 1, q, rr);  // W_R -> Sbb'
   }
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// Top-down, one launch per level (coarsest first): lambda_{i+1} = zs - f_L lambda_a - f_R lambda_{b+1} for the separators
-// of that level ([a,b] = the merged subtree). One CTA of NS threads per (problem, separator).
+// Top-down, one launch per level (coarsest first): the multiplier of every separator of that level ([a,b] = the merged
+// subtree),   lambda_{i+1} = U^-1 D^-1 (w_s - W_L lambda_a - W_R lambda_{b+1}).
+// One CTA of NS threads per (problem, separator): the strict upper triangle of U comes into shared memory by asynchronous
+// copies while the threads (one row each) read the record; the back-substitution then runs in one warp, two rows per lane,
+// the solved component broadcast by a shuffle per step.
 // ---------------------------------------------------------------------------------------------------------
 template <int NS>
-__global__ void __launch_bounds__(NS) big_topdown_kernel(int N, const double* rec_all, double* lam_all, int level, int M) {
+__global__ void __launch_bounds__(NS) big_topdown_kernel(int N, const double* rec_all, const double* ufac, double* lam_all, int level,
+                                                          int M) {
   using D = BigDim<NS>;
-  __shared__ double la[NS], lb[NS];
+  using F = BigFac<NS>;
+  static_assert(NS == 64, "two rows per lane in the back-substitution");
+  constexpr int LDU = NS + 1;
+  __shared__ double la[NS], lb[NS], vs[NS], Us[NS * LDU];
   const int prob = blockIdx.x / M, t = blockIdx.x % M;
   const int i_sep = ((2 * t + 1) << level) - 1;
   const int a = i_sep + 1 - (1 << level), b1 = i_sep + 1 + (1 << level);
   double* lam = lam_all + (size_t)prob * (N + 1) * NS;
   const int r = threadIdx.x;
-  la[r] = a == 0 ? 0.0 : lam[(size_t)a * NS + r];  // (lambda_0 does not couple: f_L is zero there)
+  const double* Uf = ufac + ((size_t)prob * N + i_sep) * F::SIZE;
+  for (int e = r; e < NS * NS; e += NS) {
+    const int j = e / NS, k = e - j * NS;
+    if (k > j) cp_async8(Us + j * LDU + k, Uf + F::OU + e);
+  }
+  la[r] = a == 0 ? 0.0 : lam[(size_t)a * NS + r];  // (lambda_0 does not couple: W_L is zero there)
   lb[r] = lam[(size_t)b1 * NS + r];                // slot N is zero
   __syncthreads();
   const double* rec = rec_all + ((size_t)prob * N + i_sep) * D::WSZ;
   double v = rec[2 * NS * NS + r];
 #pragma unroll 8
   for (int c = 0; c < NS; ++c) v = fma(-rec[c * NS + r], la[c], fma(-rec[(NS + c) * NS + r], lb[c], v));
-  lam[(size_t)(i_sep + 1) * NS + r] = v;
+  vs[r] = v * __ldg(Uf + F::OD + r);
+  cp_async_wait_all();
+  __syncthreads();
+  if (r < 32) {
+    double x0 = vs[r], x1 = vs[r + 32];  // rows r and r + 32
+#pragma unroll 4
+    for (int k = NS - 1; k > 0; --k) {
+      const double xk = __shfl_sync(0xffffffffu, k >= 32 ? x1 : x0, k & 31);
+      if (r < k) x0 = fma(-Us[r * LDU + k], xk, x0);
+      if (r + 32 < k) x1 = fma(-Us[(r + 32) * LDU + k], xk, x1);
+    }
+    lam[(size_t)(i_sep + 1) * NS + r] = x0;
+    lam[(size_t)(i_sep + 1) * NS + 32 + r] = x1;
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -837,7 +641,7 @@ inline int big_alloc(const Shape& s, int batch, BigPlan* p, std::string& err) {
   };
   const bool ok = alloc(&p->bb.entA, (size_t)batch * s.N * ent) && alloc(&p->bb.entB, (size_t)batch * (s.N / 2) * ent) &&
                   alloc(&p->bb.rec, (size_t)batch * s.N * wsz) && alloc(&p->bb.lam, (size_t)batch * (s.N + 1) * s.n) &&
-                  alloc(&p->bb.ufac, (size_t)batch * (s.N / 2) * BigFac<64>::SIZE);
+                  alloc(&p->bb.ufac, (size_t)batch * s.N * BigFac<64>::SIZE);
   if (!ok) {
     cudaGetLastError();
     big_free(p);
@@ -857,51 +661,33 @@ inline int big_launch(BigPlan& p, const Shape& s, const Bufs& b, int batch, int 
   cudaError_t e = cudaMemsetAsync(p.bb.lam, 0, sizeof(double) * (size_t)batch * (N + 1) * NS, st);
   if (e != cudaSuccess) { err = std::string("big launch: ") + cudaGetErrorString(e); return -3; }
   const int leaf_smem = ((NS + 8) * (NS + NI) + 2 * (NS + NI) + 2 * NS + 3 * NS) * (int)sizeof(double);
-  const int spine_smem = NS * (NS + 2) * (int)sizeof(double);
   const int schur_smem = (2 * NS + 1) * (NS + 4) * (int)sizeof(double);
-  const int factor_smem = BIG_FACTOR_WPC * big_factor_warp_doubles<NS>() * (int)sizeof(double);
-  const int solve_smem = (NS * (NS + 4) + NS * (2 * NS + 8) + (NS / 8) * 64 + NS) * (int)sizeof(double);
-  static const int one_kernel_spine = [] { const char* v = getenv("RSLQR_BIG_SPINE"); return v ? atoi(v) : 0; }();
-  static const int packed_factor = [] { const char* v = getenv("RSLQR_BIG_FACTOR_PACKED"); return v ? atoi(v) : 0; }();  // A/B
-  if ((e = smem_optin(big_factor_kernel<NS>, factor_smem)) != cudaSuccess || (e = smem_optin(big_solve_kernel<NS>, solve_smem)) != cudaSuccess) {
-    err = std::string("big launch: ") + cudaGetErrorString(e);
-    return -3;
-  }
-  if ((e = smem_optin(big_leaf_kernel<NS, NI>, leaf_smem)) != cudaSuccess || (e = smem_optin(big_spine_kernel<NS>, spine_smem)) != cudaSuccess ||
+  const int solve_smem = (NS * (NS + 4) + NS * (2 * NS + 8) + (NS / 8) * 64) * (int)sizeof(double);
+  if ((e = smem_optin(big_leaf_kernel<NS, NI>, leaf_smem)) != cudaSuccess || (e = smem_optin(big_solve_kernel<NS>, solve_smem)) != cudaSuccess ||
       (e = smem_optin(big_schur_kernel<NS>, schur_smem)) != cudaSuccess) {
     err = std::string("big launch: ") + cudaGetErrorString(e);
     return -3;
   }
-  big_leaf_kernel<NS, NI><<<(unsigned)((size_t)batch * N), 256, leaf_smem, st>>>(s, b, p.bb, pack_rhs, one_kernel_spine ? 0 : 1);
+  big_leaf_kernel<NS, NI><<<(unsigned)((size_t)batch * N), 256, leaf_smem, st>>>(s, b, p.bb, pack_rhs);
   ++p.launches;
   const double* ein = p.bb.entA;
   for (int level = 0; level < s.K; ++level) {
     const int M = N >> (level + 1);
     double* eout = (level & 1) ? p.bb.entA : p.bb.entB;
-    if (one_kernel_spine) {
-      big_spine_kernel<NS><<<(unsigned)((size_t)batch * M), big_spine_threads<NS>(), spine_smem, st>>>(s, b, ein, p.bb.rec, level, M);
-      ++p.launches;
-    } else {
-      const long long nmerge = (long long)batch * M;
-      if (packed_factor)
-        big_factor_kernel<NS><<<(unsigned)((nmerge + BIG_FACTOR_WPC - 1) / BIG_FACTOR_WPC), 32 * BIG_FACTOR_WPC, factor_smem, st>>>(
-            s, b, ein, p.bb.ufac, level, M, nmerge);
-      else
-        big_factor_reg_kernel<NS><<<(unsigned)((nmerge + BIG_FACTOR_REG_WPC - 1) / BIG_FACTOR_REG_WPC), 32 * BIG_FACTOR_REG_WPC, 0, st>>>(
-            s, b, ein, p.bb.ufac, level, M, nmerge);
-      big_solve_kernel<NS><<<(unsigned)nmerge, BIG_SOLVE_THREADS, solve_smem, st>>>(s, ein, p.bb.ufac, p.bb.rec, level, M);
-      p.launches += 2;
-    }
+    const long long nmerge = (long long)batch * M;
+    big_factor_reg_kernel<NS><<<(unsigned)((nmerge + BIG_FACTOR_REG_WPC - 1) / BIG_FACTOR_REG_WPC), 32 * BIG_FACTOR_REG_WPC, 0, st>>>(
+        s, b, ein, p.bb.ufac, level, M, nmerge);
+    big_solve_kernel<NS><<<(unsigned)nmerge, BIG_SOLVE_THREADS, solve_smem, st>>>(s, ein, p.bb.ufac, p.bb.rec, level, M);
+    p.launches += 2;
     if (level < s.K - 1) {
-      big_schur_kernel<NS><<<(unsigned)((size_t)batch * M), 256, schur_smem, st>>>(s, ein, eout, p.bb.rec, level, M,
-                                                                                     one_kernel_spine ? 0 : 1);
+      big_schur_kernel<NS><<<(unsigned)nmerge, 256, schur_smem, st>>>(s, ein, eout, p.bb.rec, p.bb.ufac, level, M);
       ++p.launches;
     }
     ein = eout;
   }
   for (int level = s.K - 1; level >= 0; --level) {
     const int M = N >> (level + 1);
-    big_topdown_kernel<NS><<<(unsigned)((size_t)batch * M), NS, 0, st>>>(N, p.bb.rec, p.bb.lam, level, M);
+    big_topdown_kernel<NS><<<(unsigned)((size_t)batch * M), NS, 0, st>>>(N, p.bb.rec, p.bb.ufac, p.bb.lam, level, M);
     ++p.launches;
   }
   big_down_kernel<NS, NI><<<(unsigned)((size_t)batch * N), 256, 0, st>>>(s, b, p.bb.lam, pack_rhs);

@@ -543,7 +543,7 @@ extern "C" int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs) {
     BigPlan q = h->big;
     q.bb.entA += f * s.N * BigDim<64>::ENT; q.bb.entB += f * (s.N / 2) * BigDim<64>::ENT;
     q.bb.rec += f * s.N * BigDim<64>::WSZ; q.bb.lam += f * (s.N + 1) * s.n;
-    q.bb.ufac += f * (s.N / 2) * BigFac<64>::SIZE;
+    q.bb.ufac += f * s.N * BigFac<64>::SIZE;
     int rc = big_launch(q, s, b, h->r_count, pack_rhs, h->stream, g_err);
     if (rc) return rc;
     h->launches = q.launches;
