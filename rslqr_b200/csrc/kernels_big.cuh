@@ -49,12 +49,12 @@ struct BigBufs {
 // src/solver.c:138-190), one CTA per (problem, knot):
 //   Saa = Q^-1, Sab = -Q^-1 A^T, Sbb = A Q^-1 A^T + B R^-1 B^T, sa = -z_x - z_lambda, sb = A z_x + B z_u
 //   knot 0: x_0 is fixed (z_x = x0) and lambda_0 is no unknown: Q^-1 -> 0 in the blocks; last knot: only Saa, sa.
-// dynamic smem: ((NS+8)*(NS+NI) + 2*(NS+NI) + 2*NS + 3*NS) doubles
+// dynamic smem: ((NS+4)*(NS+NI) + 2*(NS+NI) + 2*NS + 3*NS) doubles
 // ---------------------------------------------------------------------------------------------------------
 template <int NS, int NI>
-__global__ void __launch_bounds__(256, 2) big_leaf_kernel(Shape s, Bufs b, BigBufs bb, int pack_rhs) {
+__global__ void __launch_bounds__(256, 3) big_leaf_kernel(Shape s, Bufs b, BigBufs bb, int pack_rhs) {
   using D = BigDim<NS>;
-  constexpr int XU = NS + NI, LDA = NS + 8;  // (LDA = 8 mod 16: the DMMA fragments of a warp fall into two wavefronts)
+  constexpr int XU = NS + NI, LDA = NS + 4;  // (LDA = 4 mod 16: the DMMA fragments of a warp fall into two wavefronts)
   static_assert(NS == 64 && XU % 4 == 0, "8 warps x 8 rows; k-steps of 4");
   extern __shared__ __align__(16) double smf[];
   double* AB = smf;                 // [NS x XU] column-major with leading dimension LDA
@@ -105,10 +105,12 @@ __global__ void __launch_bounds__(256, 2) big_leaf_kernel(Shape s, Bufs b, BigBu
   double* E = bb.entA + ((size_t)prob * N + k) * D::ENT;
   // the readers of Saa, Sbb (factorization, keep part of the Schur update) take the lower block triangle only
   // (8 x 8 tiles with column tile <= row tile): the tiles above it are neither computed nor written
-  for (int e = tid; e < NS * NS; e += nthr) {
+  for (int e = 2 * tid; e < NS * NS; e += 2 * nthr) {  // two columns per thread: 128-bit loads and stores
     const int r = e / NS, c = e - r * NS;
-    if ((c >> 3) <= (r >> 3)) E[D::OAA + e] = r == c ? sc[r] : 0.0;
-    E[D::OAB + e] = -sc[r] * AB[c + LDA * r];  // -A(c, r) / Q(r)   (AB is zero for the last knot)
+    const double qi = sc[r];
+    if ((c >> 3) <= (r >> 3)) *reinterpret_cast<double2*>(E + D::OAA + e) = make_double2(r == c ? qi : 0.0, r == c + 1 ? qi : 0.0);
+    const double2 av = *reinterpret_cast<const double2*>(AB + c + LDA * r);  // -A(c, r) / Q(r)   (AB is zero for the last knot)
+    *reinterpret_cast<double2*>(E + D::OAB + e) = make_double2(-qi * av.x, -qi * av.y);
   }
   // Sbb = [A | B] D [A | B]^T on the fp64 tensor cores, 8 x 8 output tiles: the 36 tiles of the lower block triangle,
   // dealt round-robin to the 8 warps (4 or 5 each, all in flight).
@@ -660,7 +662,7 @@ inline int big_launch(BigPlan& p, const Shape& s, const Bufs& b, int batch, int 
   p.launches = 0;
   cudaError_t e = cudaMemsetAsync(p.bb.lam, 0, sizeof(double) * (size_t)batch * (N + 1) * NS, st);
   if (e != cudaSuccess) { err = std::string("big launch: ") + cudaGetErrorString(e); return -3; }
-  const int leaf_smem = ((NS + 8) * (NS + NI) + 2 * (NS + NI) + 2 * NS + 3 * NS) * (int)sizeof(double);
+  const int leaf_smem = ((NS + 4) * (NS + NI) + 2 * (NS + NI) + 2 * NS + 3 * NS) * (int)sizeof(double);
   const int schur_smem = (2 * NS + 1) * (NS + 4) * (int)sizeof(double);
   const int solve_smem = (NS * (NS + 4) + NS * (2 * NS + 8) + (NS / 8) * 64) * (int)sizeof(double);
   if ((e = smem_optin(big_leaf_kernel<NS, NI>, leaf_smem)) != cudaSuccess || (e = smem_optin(big_solve_kernel<NS>, solve_smem)) != cudaSuccess ||
