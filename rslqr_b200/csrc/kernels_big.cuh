@@ -44,6 +44,34 @@ struct BigBufs {
   double* ufac;  // [batch][N][BigFac::SIZE] factor U, block inverses and 1/d of the separator after knot i at slot i
 };
 
+// G output tiles of Sbb = [A | B] D [A | B]^T for one warp: tiles warp, warp + 8, ... of the lower block triangle in row-major
+// order (tile i = (t, j), j <= t, i = t (t + 1) / 2 + j). AB: [A | B] in shared memory (column-major, ld NS + 4), dv: D.
+template <int NS, int NI, int G>
+__device__ __forceinline__ void big_leaf_sbb(const double* AB, const double* dv, double* Sbb, int warp, int lane) {
+  constexpr int XU = NS + NI, LDA = NS + 4, KS = XU / 4;
+  const int q = lane & 3, rr = lane >> 2;
+  const double *pa[G], *pb[G];
+  double* po[G];
+  double c[G][2];
+#pragma unroll
+  for (int u = 0; u < G; ++u) {
+    int t = 0, jj = warp + 8 * u;
+    while (jj > t) { ++t; jj -= t; }
+    pa[u] = AB + 8 * t + rr + LDA * q;
+    pb[u] = AB + 8 * jj + rr + LDA * q;
+    po[u] = Sbb + (8 * t + rr) * NS + 8 * jj + 2 * q;
+    c[u][0] = c[u][1] = 0.0;
+  }
+#pragma unroll 4
+  for (int ks = 0; ks < KS; ++ks) {
+    const double dk = dv[4 * ks + q];
+#pragma unroll
+    for (int u = 0; u < G; ++u) dmma884(c[u][0], c[u][1], pa[u][4 * LDA * ks] * dk, pb[u][4 * LDA * ks]);
+  }
+#pragma unroll
+  for (int u = 0; u < G; ++u) *reinterpret_cast<double2*>(po[u]) = make_double2(c[u][0], c[u][1]);
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Leaf elements (ndlqr_SolveLeaf on diagonal Q, R, src/nested_dissection.c:10-105, with the rhs packing of
 // src/solver.c:138-190), one CTA per (problem, knot):
@@ -113,36 +141,11 @@ __global__ void __launch_bounds__(256, 3) big_leaf_kernel(Shape s, Bufs b, BigBu
     *reinterpret_cast<double2*>(E + D::OAB + e) = make_double2(-qi * av.x, -qi * av.y);
   }
   // Sbb = [A | B] D [A | B]^T on the fp64 tensor cores, 8 x 8 output tiles: the 36 tiles of the lower block triangle,
-  // dealt round-robin to the 8 warps (4 or 5 each, all in flight).
+  // dealt round-robin to the 8 warps (warps 0..3: 5 tiles, 4..7: 4 tiles, all in flight).
   {
-    const int warp = tid >> 5, lane = tid & 31, q = lane & 3, rr = lane >> 2;
-    constexpr int KS = XU / 4, NT = NS / 8, G = 5;
-    constexpr int ntask = NT * (NT + 1) / 2;
-#pragma unroll 1
-    for (int i0 = warp; i0 < ntask; i0 += 8 * G) {
-      int tr[G], tc[G];
-      double c[G][2];
-#pragma unroll
-      for (int u = 0; u < G; ++u) {
-        const int i = i0 + 8 * u;
-        int t = 0, jj = i;
-        while (jj > t) { ++t; jj -= t; }   // i = t (t + 1) / 2 + jj, jj <= t
-        tr[u] = i < ntask ? t : 0; tc[u] = i < ntask ? jj : 0;
-        c[u][0] = c[u][1] = 0.0;
-      }
-      const int nact = (ntask - i0 + 7) / 8;  // (warp-uniform) tasks of this group
-#pragma unroll 4
-      for (int ks = 0; ks < KS; ++ks) {
-        const double dk = dv[4 * ks + q];
-#pragma unroll
-        for (int u = 0; u < G; ++u)
-          if (u < nact)
-            dmma884(c[u][0], c[u][1], AB[8 * tr[u] + rr + LDA * (4 * ks + q)] * dk, AB[8 * tc[u] + rr + LDA * (4 * ks + q)]);
-      }
-#pragma unroll
-      for (int u = 0; u < G; ++u)
-        if (u < nact) *reinterpret_cast<double2*>(E + D::OBB + (8 * tr[u] + rr) * NS + 8 * tc[u] + 2 * q) = make_double2(c[u][0], c[u][1]);
-    }
+    const int warp = tid >> 5;
+    if (warp < 4) big_leaf_sbb<NS, NI, 5>(AB, dv, E + D::OBB, warp, tid & 31);
+    else big_leaf_sbb<NS, NI, 4>(AB, dv, E + D::OBB, warp, tid & 31);
   }
   {  // sb = [A | B] z: four threads per row, a quarter of the XU terms each (thread = 64 part + row)
     const int r = tid & (NS - 1), part = tid / NS;
@@ -413,35 +416,42 @@ __global__ void __launch_bounds__(BIG_SOLVE_THREADS) big_solve_kernel(Shape s, c
 // for j < cnt (F = W here), four tiles in flight, the keep part requested one group ahead of its use. a: A fragments of
 // the rows (registers); Fcols: column fcol0 of W in shared memory (ld LDF); keep_row: row r of the block that is updated, nullptr =
 // zero; dst_row: row r of the output block.
+struct BigKeep4 { double2 v0, v1, v2, v3; };
+
+template <int NS, int NACT>
+__device__ __forceinline__ void big_schur_group(const double (&a)[NS / 4], const double* Fcols, BigKeep4 kv, double* dst_row, int nt0,
+                                                int q, int rr) {
+  constexpr int LDF = NS + 4, KS = NS / 4;
+  const double* bp = Fcols + (8 * nt0 + rr) * LDF + q;   // B fragment of tile u, k-step ks: bp[u * 8 * LDF + 4 * ks]
+  double c[NACT][2];
+  c[0][0] = -kv.v0.x; c[0][1] = -kv.v0.y;                // accumulate a.F - keep, negate on the way out
+  if constexpr (NACT > 1) { c[1][0] = -kv.v1.x; c[1][1] = -kv.v1.y; }
+  if constexpr (NACT > 2) { c[2][0] = -kv.v2.x; c[2][1] = -kv.v2.y; }
+  if constexpr (NACT > 3) { c[3][0] = -kv.v3.x; c[3][1] = -kv.v3.y; }
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+#pragma unroll
+    for (int u = 0; u < NACT; ++u) dmma884(c[u][0], c[u][1], a[ks], bp[u * 8 * LDF + 4 * ks]);
+  }
+#pragma unroll
+  for (int u = 0; u < NACT; ++u) *reinterpret_cast<double2*>(dst_row + 8 * (nt0 + u) + 2 * q) = make_double2(-c[u][0], -c[u][1]);
+}
+
 template <int NS>
 __device__ __forceinline__ void big_schur_run(const double (&a)[NS / 4], const double* Fcols, const double* keep_row, double* dst_row,
                                               int cnt, int q, int rr) {
-  constexpr int LDF = NS + 4, KS = NS / 4;
-  auto keep = [&](int nt0, double2 (&v)[4]) {
-#pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      v[u] = make_double2(0.0, 0.0);
-      if (keep_row && nt0 + u < cnt) v[u] = __ldg(reinterpret_cast<const double2*>(keep_row + 8 * (nt0 + u) + 2 * q));
-    }
+  auto keep1 = [&](int tile) {
+    return (keep_row && tile < cnt) ? __ldg(reinterpret_cast<const double2*>(keep_row + 8 * tile + 2 * q)) : make_double2(0.0, 0.0);
   };
-  double2 kv[4];
-  keep(0, kv);
+  auto keep = [&](int nt0) { return BigKeep4{keep1(nt0), keep1(nt0 + 1), keep1(nt0 + 2), keep1(nt0 + 3)}; };
 #pragma unroll 1
   for (int nt0 = 0; nt0 < cnt; nt0 += 4) {
-    double c[4][2];
-#pragma unroll
-    for (int u = 0; u < 4; ++u) { c[u][0] = -kv[u].x; c[u][1] = -kv[u].y; }  // accumulate a.F - keep, negate on the way out
-    if (nt0 + 4 < cnt) keep(nt0 + 4, kv);
-    const int nact = cnt - nt0;  // (warp-uniform) tiles of this group: 1..4
-#pragma unroll
-    for (int ks = 0; ks < KS; ++ks) {
-#pragma unroll
-      for (int u = 0; u < 4; ++u)
-        if (u < nact) dmma884(c[u][0], c[u][1], a[ks], Fcols[(8 * (nt0 + u) + rr) * LDF + 4 * ks + q]);
-    }
-#pragma unroll
-    for (int u = 0; u < 4; ++u)
-      if (u < nact) *reinterpret_cast<double2*>(dst_row + 8 * (nt0 + u) + 2 * q) = make_double2(-c[u][0], -c[u][1]);
+    const BigKeep4 kv = keep(nt0);      // (zeros beyond cnt)
+    const int nact = cnt - nt0;         // (warp-uniform) tiles of this group; one instantiation per count: no guards inside
+    if (nact >= 4) big_schur_group<NS, 4>(a, Fcols, kv, dst_row, nt0, q, rr);
+    else if (nact == 3) big_schur_group<NS, 3>(a, Fcols, kv, dst_row, nt0, q, rr);
+    else if (nact == 2) big_schur_group<NS, 2>(a, Fcols, kv, dst_row, nt0, q, rr);
+    else big_schur_group<NS, 1>(a, Fcols, kv, dst_row, nt0, q, rr);
   }
 }
 
