@@ -1,12 +1,12 @@
 #!/usr/bin/env python3
 """Per-kernel SASS opcode counts of librslqr.so (cuobjdump -sass): the evidence for which units a kernel uses
-(DMMA = fp64 tensor path, UBLKCP = TMA bulk copies, SYNCS = mbarrier, SHFL / LDS / STS = LSU data pipe)."""
+(DMMA = fp64 tensor path, UBLKCP = TMA bulk copies, LDGSTS = cp.async, SYNCS = mbarrier, SHFL / LDS / STS = LSU data pipe)."""
 import collections
 import re
 import subprocess
 import sys
 
-WANT = ["DMMA", "DFMA", "DMUL", "DADD", "MUFU", "SHFL", "LDS", "STS", "LDG", "STG", "UBLKCP", "SYNCS", "BAR", "UTMALDG", "UTCHMMA", "LDTM"]
+WANT = ["DMMA", "DFMA", "DMUL", "DADD", "MUFU", "SHFL", "LDS", "STS", "LDG", "STG", "LDGSTS", "UBLKCP", "SYNCS", "BAR", "UTMALDG", "UTCHMMA", "LDTM"]
 
 
 def main():
