@@ -678,6 +678,29 @@ def test_solve_host_pipeline_matches_resident_solve(mode):
     s.close()
 
 
+@pytest.mark.parametrize("shape", [(64, 16, 16), (6, 3, 32), (16, 8, 16)])
+def test_solve_host_chunks_on_the_dual_form_paths(shape):
+    # chunks of the host-to-host call address the per-separator buffers of the dual-form paths (elements, records,
+    # factors of the large-block path) at an offset: every chunking must reproduce the resident solve bit for bit, twice
+    n, m, N = shape
+    B = 7
+    kn, x0 = R.synth_problems(n, m, N, 13, 0, B)
+    s = R.CudaSolver(n, m, N, batch=B, flags=0)
+    assert s.mode == R.MODE_SCAN
+    s.upload(kn, x0)
+    s.solve()
+    want = s.solution().copy()
+    ref, _ = O.port_solve(n, m, N, kn[B - 1], x0[B - 1])
+    assert max(rel_err_classes(want[B - 1], ref, n, m, N)) < TOL
+    for chunk in (3, 1, 0, 3):
+        out = np.zeros((B, N * s.zs))
+        s.upload(np.zeros_like(kn), np.zeros_like(x0))
+        s.solve_host(kn, x0, out, chunk=chunk)
+        s.sync()
+        assert np.array_equal(out, want), (shape, chunk)
+    s.close()
+
+
 @pytest.mark.parametrize("shape,nranks", [((12, 4, 256), 2), ((12, 4, 256), 8), ((12, 4, 2048), 4), ((6, 3, 128), 8),
                                           ((12, 4, 64), 1)])
 def test_long_horizon_shards_emulated_on_one_gpu(shape, nranks):
