@@ -11,7 +11,7 @@
 //                           (= ndlqr_UpdateShurFactor restricted to what a later inner product reads, :154-171)
 // then one top-down launch per level (lambda of the separators: records, then one back-substitution with U) and
 // big_down_kernel (x_k, u_k from the leaf equations, as scan_down_kernel). Against the staged path on this shape (every
-// knot updated at every level, dense `fact` array of 755 MB per problem): 2.3 instead of 23.6 GFLOP per solve, 0.26
+// knot updated at every level, dense `fact` array of 755 MB per problem): 2.2 instead of 23.6 GFLOP per solve, 0.26
 // instead of 0.76 GB per problem.
 #pragma once
 #include "kernels_fused.cuh"
@@ -33,7 +33,7 @@ struct BigDim {
   static constexpr int BLK = NS * NS;
   static constexpr int OAA = 0, OAB = BLK, OBB = 2 * BLK, OSA = 3 * BLK, OSB = 3 * BLK + NS;
   static constexpr int ENT = 3 * BLK + 2 * NS;   // [Saa | Sab | Sbb | sa | sb], blocks row-major ld NS
-  static constexpr int WSZ = (2 * NS + 1) * NS;  // record [f_L | f_R | zs], column-major ld NS
+  static constexpr int WSZ = (2 * NS + 1) * NS;  // record [W_L | W_R | w_s], column-major ld NS
 };
 
 struct BigBufs {
@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(256, 3) big_leaf_kernel(Shape s, Bufs b, BigBu
 // ---------------------------------------------------------------------------------------------------------
 // Spine of a merge: S = SbbL + SaaR = U^T D U, then W = U^-T [S_L | S_R | s] (the forward substitution ONLY).
 //   big_factor_reg_kernel : one warp per merge, S in registers; output per separator (`ufac`, slot = the separator's
-//                           knot index): U (unit upper, row-major ld NS), the inverses X_b of the 8 x 8 diagonal blocks
+//                           knot index): U (strict upper triangle, row-major ld NS), the inverses X_b of the 8 x 8 diagonal blocks
 //                           of L = U^T, and 1/d.
 //   big_solve_kernel      : one CTA of 9 warps per merge. Y = [S_L | S_R | s] (NS x 2NS+1, padded to 17 column tiles of 8)
 //                           and U are staged in shared memory; a warp owns column tiles and runs the blocked forward
@@ -255,7 +255,7 @@ __global__ void __launch_bounds__(32 * BIG_FACTOR_REG_WPC) big_factor_reg_kernel
       x0 = fma(-l, rx0, x0); x1 = fma(-l, rx1, x1);
       if (q == (j >> 1)) { if (j & 1) dq1 = dinv; else dq0 = dinv; }
       if (q == (j & 3)) { if (j >> 2) da1 = dinv; else da0 = dinv; }
-      if (q == 0) Ud[(size_t)j * NS + g] = g > j ? l : (g == j ? 1.0 : 0.0);  // U(8b + j, 8b + g) = l(g, j)
+      if (q == 0 && g > j) Ud[(size_t)j * NS + g] = l;  // U(8b + j, 8b + g) = l(g, j): only the strict upper triangle of U is kept
     }
     *reinterpret_cast<double2*>(U + F::OX + bk * 64 + g * 8 + 2 * q) = make_double2(x0, x1);
     if (g == 0) *reinterpret_cast<double2*>(U + F::OD + 8 * bk + 2 * q) = make_double2(dq0, dq1);
@@ -270,10 +270,9 @@ __global__ void __launch_bounds__(32 * BIG_FACTOR_REG_WPC) big_factor_reg_kernel
         double r0 = 0.0, r1 = 0.0;
         dmma884(r0, r1, pa0, xa0);
         dmma884(r0, r1, pa1, xa1);
-        // U(8b + k, 8c + g) = L_cb(g, k); the block below the diagonal of U is zero
+        // U(8b + k, 8c + g) = L_cb(g, k) (nothing is stored on or below the diagonal: no reader looks there)
         U[F::OU + (size_t)(8 * bk + 2 * q) * NS + 8 * c + g] = r0 * dq0;
         U[F::OU + (size_t)(8 * bk + 2 * q + 1) * NS + 8 * c + g] = r1 * dq1;
-        *reinterpret_cast<double2*>(U + F::OU + (size_t)(8 * c + g) * NS + 8 * bk + 2 * q) = make_double2(0.0, 0.0);
         frag_c2a(r0, r1, rd[c][0], rd[c][1], lane);
         nl[c][0] = -rd[c][0] * da0;
         nl[c][1] = -rd[c][1] * da1;
@@ -374,7 +373,7 @@ __global__ void __launch_bounds__(BIG_SOLVE_THREADS) big_solve_kernel(Shape s, c
   // staging by asynchronous copies: everything in flight at once, no staging registers
   for (int e = 2 * tid; e < NS * NS; e += 2 * nthr) {
     const int r = e / NS, c = e - r * NS;
-    cp_async16(Us + r * LDU + c, Uf + F::OU + e);
+    if (c >= 8 * (r / 8 + 1)) cp_async16(Us + r * LDU + c, Uf + F::OU + e);   // (the blocks right of the diagonal one: all that is read)
     cp_async16(Ys + r * LDY + NS + c, ER + D::OAB + e);   // S_R(k, c) = SabR(k, c)
   }
   // S_L(k, c) = SabL(c, k): a warp moves tiles of 8 k x 4 c (lane = 4 kk + cc): 64-byte runs of a SabL row in, a 4-way
