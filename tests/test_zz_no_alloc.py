@@ -48,7 +48,7 @@ def test_solve_static_matches_the_handle_solve_on_two_calls_in_a_row():
     n, m = 12, 4
     # call 1: 20 problems of N = 256 (19.6 MB of the 32 MiB array); call 2: other problems, another horizon and
     # batch, over the first call's leftovers; then the first ones again
-    cases = [(256, 20, 5), (64, 9, 6), (256, 20, 5)]
+    cases = [(256, 20, 5), (64, 9, 6), (16, 100, 7), (256, 20, 5)]  # (batch >= 64 takes the other tier arity)
     grew = []
     for N, B, seed in cases:
         kn, x0 = R.synth_problems(n, m, N, seed, 0, B)
