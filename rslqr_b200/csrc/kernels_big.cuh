@@ -167,11 +167,12 @@ __global__ void __launch_bounds__(256, 3) big_leaf_kernel(Shape s, Bufs b, BigBu
 //   big_factor_reg_kernel : one warp per merge, S in registers; output per separator (`ufac`, slot = the separator's
 //                           knot index): U (strict upper triangle, row-major ld NS), the inverses X_b of the 8 x 8 diagonal blocks
 //                           of L = U^T, and 1/d.
-//   big_solve_kernel      : one CTA of 9 warps per merge. Y = [S_L | S_R | s] (NS x 2NS+1, padded to 17 column tiles of 8)
-//                           and U are staged in shared memory; a warp owns column tiles and runs the blocked forward
-//                           substitution for them without any CTA barrier: for block row b,
-//                               W_b = X_b (Y_b - sum_{b' < b} L_bb' W_b')
-//                           every product an m8n8k4 DMMA pair. W = [W_L | W_R | w_s] goes to the separator's record.
+//   big_solve_kernel      : one CTA of 9 warps per merge. U and the X_b are staged in shared memory; a warp owns row tiles of
+//                           Y^T = [S_L | S_R | s]^T (8 right-hand sides each, 17 tiles) straight from global memory in its
+//                           accumulator registers and runs the blocked forward substitution in transposed form,
+//                               Z_b = (Y^T_b - sum_{b' < b} Z_b' U_b'b) X_b^T,      Z = W^T
+//                           every product an m8n8k4 DMMA pair, no shared-memory round trip for the right-hand sides.
+//                           W = [W_L | W_R | w_s] goes to the separator's record.
 // The backward substitution is never run on the 2n+1 columns: the Schur update only needs products of the form
 // S_x^T S^-1 S_y = W_x^T D^-1 W_y (big_schur_kernel), and the separator's multiplier
 //     lambda = S^-1 (s - S_L lambda_a - S_R lambda_b) = U^-1 D^-1 (w_s - W_L lambda_a - W_R lambda_b)
@@ -292,114 +293,102 @@ __global__ void __launch_bounds__(32 * BIG_FACTOR_REG_WPC) big_factor_reg_kernel
   }
 }
 
-// Forward substitution for T column tiles at once, RIGHT-LOOKING: the 8 block rows of a tile stay in registers as DMMA
-// accumulators (C fragments); once block row b is final (W_b = X_b Y_b) it leaves for the record straight from the
-// registers, goes through shared memory once (C layout -> B fragment) and every block row below it is updated with it
-// (Y_c -= L_cb W_b, L_cb (r, k) = U(8b + k, 8c + r)), so a B fragment is loaded once per block and an A fragment (8 x 8
-// block of U) once per DMMA pair of T tiles.
+// Forward substitution in TRANSPOSED form: Z = Y^T U^-1 (Z = W^T), T row tiles of 8 right-hand sides x NS per warp, the
+// 8 column blocks of a row tile as DMMA accumulators (C fragments) in registers, right-looking:
+//     Z_b = Zc_b X_b^T (final),   then   Zc_b2 -= Z_b U_{b,b2}  for b2 > b
+// The right-hand sides are the A operands (a C fragment becomes an A fragment by four 64-bit shuffles, frag_c2a: no shared
+// memory round trip), the 8 x 8 blocks of U and X_b^T are the B operands, loaded once per block for all T tiles. A final
+// block leaves for the record (W(:, c) = Z(c, :), column-major ld NS: 16-byte runs) straight from the registers.
 template <int NS, int T>
-__device__ __forceinline__ void big_solve_tiles(const double* Us, const double* Xs, double* const (&Yt)[T], double* const (&rec)[T],
-                                                const int (&ncols)[T]) {
-  constexpr int NB = NS / 8, LDU = NS + 4, LDY = 2 * NS + 8;
+__device__ __forceinline__ void big_solve_rows(const double* Us, const double* Xs, double (&c)[NS / 8][T][2], double* const (&rec)[T],
+                                               const int (&nrows)[T]) {
+  constexpr int NB = NS / 8, LDU = NS + 4;
   const int lane = threadIdx.x & 31, q = lane & 3, rr = lane >> 2;
-  double c[NB][T][2];
-#pragma unroll
-  for (int bk = 0; bk < NB; ++bk)
-#pragma unroll
-    for (int u = 0; u < T; ++u) {
-      const double2 cv = *reinterpret_cast<const double2*>(Yt[u] + (8 * bk + rr) * LDY + 2 * q);
-      c[bk][u][0] = cv.x; c[bk][u][1] = cv.y;
-    }
-  __syncwarp();
 #pragma unroll
   for (int bk = 0; bk < NB; ++bk) {
-    // W_b = X_b Y_b: C fragment -> shared memory -> B fragment -> product with the 8 x 8 block X_b
-    const double xa0 = Xs[bk * 64 + rr * 8 + q], xa1 = Xs[bk * 64 + rr * 8 + 4 + q];
-#pragma unroll
-    for (int u = 0; u < T; ++u) *reinterpret_cast<double2*>(Yt[u] + (8 * bk + rr) * LDY + 2 * q) = make_double2(c[bk][u][0], c[bk][u][1]);
-    __syncwarp();
+    const double xb0 = Xs[bk * 64 + rr * 8 + q], xb1 = Xs[bk * 64 + rr * 8 + 4 + q];  // B fragments of X_b^T
+    double na[T][2];
 #pragma unroll
     for (int u = 0; u < T; ++u) {
-      const double b0 = Yt[u][(8 * bk + q) * LDY + rr], b1 = Yt[u][(8 * bk + 4 + q) * LDY + rr];
+      double a0, a1;
+      frag_c2a(c[bk][u][0], c[bk][u][1], a0, a1, lane);
       c[bk][u][0] = c[bk][u][1] = 0.0;
-      dmma884(c[bk][u][0], c[bk][u][1], xa0, b0);
-      dmma884(c[bk][u][0], c[bk][u][1], xa1, b1);
+      dmma884(c[bk][u][0], c[bk][u][1], a0, xb0);
+      dmma884(c[bk][u][0], c[bk][u][1], a1, xb1);
+      if (rr < nrows[u]) *reinterpret_cast<double2*>(rec[u] + (size_t)rr * NS + 8 * bk + 2 * q) = make_double2(c[bk][u][0], c[bk][u][1]);
+      if (bk + 1 < NB) {
+        frag_c2a(c[bk][u][0], c[bk][u][1], a0, a1, lane);
+        na[u][0] = -a0; na[u][1] = -a1;
+      }
     }
-    __syncwarp();
-    // the final block row: to the record (column-major, ld NS: 8 consecutive k per column) ...
-#pragma unroll
-    for (int u = 0; u < T; ++u) {
-      if (2 * q < ncols[u]) rec[u][(size_t)(2 * q) * NS + 8 * bk + rr] = c[bk][u][0];
-      if (2 * q + 1 < ncols[u]) rec[u][(size_t)(2 * q + 1) * NS + 8 * bk + rr] = c[bk][u][1];
-    }
-    if (bk + 1 < NB) {  // ... and as B fragments into the block rows below
-      double bf[T][2];
-#pragma unroll
-      for (int u = 0; u < T; ++u) *reinterpret_cast<double2*>(Yt[u] + (8 * bk + rr) * LDY + 2 * q) = make_double2(c[bk][u][0], c[bk][u][1]);
-      __syncwarp();
-#pragma unroll
-      for (int u = 0; u < T; ++u) { bf[u][0] = Yt[u][(8 * bk + q) * LDY + rr]; bf[u][1] = Yt[u][(8 * bk + 4 + q) * LDY + rr]; }
-      __syncwarp();
+    if (bk + 1 < NB) {
 #pragma unroll
       for (int b2 = bk + 1; b2 < NB; ++b2) {
-        const double a0 = -Us[(8 * bk + q) * LDU + 8 * b2 + rr], a1 = -Us[(8 * bk + 4 + q) * LDU + 8 * b2 + rr];
+        const double ub0 = Us[(8 * bk + q) * LDU + 8 * b2 + rr], ub1 = Us[(8 * bk + 4 + q) * LDU + 8 * b2 + rr];
 #pragma unroll
-        for (int u = 0; u < T; ++u) { dmma884(c[b2][u][0], c[b2][u][1], a0, bf[u][0]); dmma884(c[b2][u][0], c[b2][u][1], a1, bf[u][1]); }
+        for (int u = 0; u < T; ++u) { dmma884(c[b2][u][0], c[b2][u][1], na[u][0], ub0); dmma884(c[b2][u][0], c[b2][u][1], na[u][1], ub1); }
       }
     }
   }
 }
 
-constexpr int BIG_SOLVE_THREADS = 288;  // 9 warps: 8 take two column tiles each, the ninth the tile with the zs column
+constexpr int BIG_SOLVE_THREADS = 288;  // 9 warps: 8 take a row tile of S_L^T and one of S_R^T each, the ninth the vector s
 
+// dynamic smem: (NS * (NS + 4) + (NS / 8) * 64) doubles: the blocks of U right of the diagonal, the X_b
 template <int NS>
 __global__ void __launch_bounds__(BIG_SOLVE_THREADS) big_solve_kernel(Shape s, const double* ein, const double* ufac, double* rec_all,
                                                                        int level, int M) {
   using D = BigDim<NS>;
   using F = BigFac<NS>;
-  static_assert(NS == 64, "8 block rows, 17 column tiles over 9 warps");
-  constexpr int NB = NS / 8, LDU = NS + 4, LDY = 2 * NS + 8;
+  static_assert(NS == 64, "8 column blocks, 17 row tiles over 9 warps");
+  constexpr int NB = NS / 8, LDU = NS + 4;
   extern __shared__ __align__(16) double smf[];
   double* Us = smf;                      // U, row-major ld LDU
-  double* Ys = Us + NS * LDU;            // Y / W, row k at Ys + k * LDY, column = right-hand side
-  double* Xs = Ys + NS * LDY;            // X_b, 8 x 8 row-major each
+  double* Xs = Us + NS * LDU;            // X_b, 8 x 8 row-major each
   const int N = s.N;
   const int prob = blockIdx.x / M, t = blockIdx.x % M;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nthr = blockDim.x;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, nthr = blockDim.x, q = lane & 3, rr = lane >> 2;
   const double* EL = ein + ((size_t)prob * 2 * M + 2 * t) * D::ENT;
   const double* ER = EL + D::ENT;
   const int i_sep = ((2 * t + 1) << level) - 1;
   const double* Uf = ufac + ((size_t)prob * N + i_sep) * F::SIZE;
-  // staging by asynchronous copies: everything in flight at once, no staging registers
   for (int e = 2 * tid; e < NS * NS; e += 2 * nthr) {
     const int r = e / NS, c = e - r * NS;
     if (c >= 8 * (r / 8 + 1)) cp_async16(Us + r * LDU + c, Uf + F::OU + e);   // (the blocks right of the diagonal one: all that is read)
-    cp_async16(Ys + r * LDY + NS + c, ER + D::OAB + e);   // S_R(k, c) = SabR(k, c)
   }
-  // S_L(k, c) = SabL(c, k): a warp moves tiles of 8 k x 4 c (lane = 4 kk + cc): 64-byte runs of a SabL row in, a 4-way
-  // conflicted store out (a plain transpose would be 16-way with this row stride)
-  for (int tile = warp; tile < (NS / 8) * (NS / 4); tile += nthr >> 5) {
-    const int k = 8 * (tile % (NS / 8)) + (lane >> 2), c = 4 * (tile / (NS / 8)) + (lane & 3);
-    cp_async8(Ys + k * LDY + c, EL + D::OAB + c * NS + k);
-  }
-  for (int e = 2 * tid; e < NB * 64; e += 2 * nthr) cp_async16(Xs + e, Uf + F::OX + e);  // X blocks
-  for (int e = tid; e < NS * 8; e += nthr) {
-    const int k = e >> 3, c = e & 7;
-    Ys[k * LDY + 2 * NS + c] = c == 0 ? __ldg(EL + D::OSB + k) + __ldg(ER + D::OSA + k) : 0.0;
-  }
-  cp_async_wait_all();
-  __syncthreads();
+  for (int e = 2 * tid; e < NB * 64; e += 2 * nthr) cp_async16(Xs + e, Uf + F::OX + e);
   double* rec = rec_all + ((size_t)prob * N + i_sep) * D::WSZ;  // [W_L | W_R | w_s], column-major ld NS
+  // the right-hand sides come straight from global memory into the accumulator fragments (row = right-hand side):
+  //   S_L^T = SabL: row c, 16-byte runs;  S_R^T(c, k) = SabR(k, c): 64-byte runs over the 8 rows of a tile
   if (warp < 8) {
-    double* const Yt[2] = {Ys + 8 * warp, Ys + 8 * (warp + 8)};
-    double* const rc[2] = {rec + (size_t)8 * warp * NS, rec + (size_t)8 * (warp + 8) * NS};
-    const int nc[2] = {8, 8};
-    big_solve_tiles<NS, 2>(Us, Xs, Yt, rc, nc);
+    double c[NB][2][2];
+    const double* pl = EL + D::OAB + (size_t)(8 * warp + rr) * NS + 2 * q;
+    const double* pr = ER + D::OAB + (size_t)(2 * q) * NS + 8 * warp + rr;
+#pragma unroll
+    for (int bk = 0; bk < NB; ++bk) {
+      const double2 v = __ldg(reinterpret_cast<const double2*>(pl + 8 * bk));
+      c[bk][0][0] = v.x; c[bk][0][1] = v.y;
+      c[bk][1][0] = __ldg(pr + (size_t)(8 * bk) * NS);
+      c[bk][1][1] = __ldg(pr + (size_t)(8 * bk + 1) * NS);
+    }
+    cp_async_wait_all();
+    __syncthreads();
+    double* const rc[2] = {rec + (size_t)8 * warp * NS, rec + (size_t)(NS + 8 * warp) * NS};
+    const int nr[2] = {8, 8};
+    big_solve_rows<NS, 2>(Us, Xs, c, rc, nr);
   } else {
-    double* const Yt[1] = {Ys + 8 * 16};
-    double* const rc[1] = {rec + (size_t)8 * 16 * NS};
-    const int nc[1] = {1};
-    big_solve_tiles<NS, 1>(Us, Xs, Yt, rc, nc);
+    double c[NB][1][2];
+#pragma unroll
+    for (int bk = 0; bk < NB; ++bk) {  // s = sbL + saR as row 0 of the tile
+      const int k = 8 * bk + 2 * q;
+      c[bk][0][0] = rr == 0 ? __ldg(EL + D::OSB + k) + __ldg(ER + D::OSA + k) : 0.0;
+      c[bk][0][1] = rr == 0 ? __ldg(EL + D::OSB + k + 1) + __ldg(ER + D::OSA + k + 1) : 0.0;
+    }
+    cp_async_wait_all();
+    __syncthreads();
+    double* const rc[1] = {rec + (size_t)2 * NS * NS};
+    const int nr[1] = {1};
+    big_solve_rows<NS, 1>(Us, Xs, c, rc, nr);
   }
 }
 
@@ -673,7 +662,7 @@ inline int big_launch(BigPlan& p, const Shape& s, const Bufs& b, int batch, int 
   if (e != cudaSuccess) { err = std::string("big launch: ") + cudaGetErrorString(e); return -3; }
   const int leaf_smem = ((NS + 4) * (NS + NI) + 2 * (NS + NI) + 2 * NS + 3 * NS) * (int)sizeof(double);
   const int schur_smem = (2 * NS + 1) * (NS + 4) * (int)sizeof(double);
-  const int solve_smem = (NS * (NS + 4) + NS * (2 * NS + 8) + (NS / 8) * 64) * (int)sizeof(double);
+  const int solve_smem = (NS * (NS + 4) + (NS / 8) * 64) * (int)sizeof(double);
   if ((e = smem_optin(big_leaf_kernel<NS, NI>, leaf_smem)) != cudaSuccess || (e = smem_optin(big_solve_kernel<NS>, solve_smem)) != cudaSuccess ||
       (e = smem_optin(big_schur_kernel<NS>, schur_smem)) != cudaSuccess) {
     err = std::string("big launch: ") + cudaGetErrorString(e);
