@@ -336,7 +336,7 @@ constexpr int BIG_SOLVE_THREADS = 288;  // 9 warps: 8 take a row tile of S_L^T a
 
 // dynamic smem: (NS * (NS + 4) + (NS / 8) * 64) doubles: the blocks of U right of the diagonal, the X_b
 template <int NS>
-__global__ void __launch_bounds__(BIG_SOLVE_THREADS) big_solve_kernel(Shape s, const double* ein, const double* ufac, double* rec_all,
+__global__ void __launch_bounds__(BIG_SOLVE_THREADS, 3) big_solve_kernel(Shape s, const double* ein, const double* ufac, double* rec_all,
                                                                        int level, int M) {
   using D = BigDim<NS>;
   using F = BigFac<NS>;
