@@ -253,7 +253,7 @@ __global__ void __launch_bounds__(32 * DUAL_WPC) dual_leaf_kernel(Shape s, Bufs 
   static_assert(RAWB % 16 == 0 && D::ENT % 2 == 0 && D::LR % 2 == 0, "TMA / 128-bit alignment");
   extern __shared__ __align__(16) double smf[];
   __shared__ __align__(8) unsigned long long mbar[DUAL_WPC];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = warp_index_sync(), lane = threadIdx.x & 31;
   const long long sub = (long long)blockIdx.x * DUAL_WPC + warp;
   if (sub >= nsub) return;
   double* R0 = smf + warp * dual_leaf_warp_doubles<NS, NI>();
@@ -339,7 +339,7 @@ __global__ void __launch_bounds__(128) dual_tier_kernel(Shape s, Bufs b, DualTie
   using D = DualDim<NS>;
   extern __shared__ __align__(16) double smf[];
   __shared__ __align__(8) unsigned long long mbar;
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int tid = threadIdx.x, warp = warp_index_sync(), lane = tid & 31;
   const int ecount = a.ecount, ncta = a.Min / ecount;
   const int prob = blockIdx.x / ncta, sg = blockIdx.x % ncta;
   double* ents = smf;

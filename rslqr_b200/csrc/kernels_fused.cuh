@@ -132,6 +132,10 @@ __device__ __forceinline__ void sts_pred(unsigned saddr, double v, int on) {
   asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.s32 p, %2, 0;\n\t@p st.shared.f64 [%0], %1;\n\t}" ::"r"(saddr), "d"(v), "r"(on) : "memory");
 }
 __device__ __forceinline__ double shfl_d(double v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+// warp index of the calling thread as a value the compiler KNOWS to be warp-uniform (broadcast from lane 0): branches on it
+// are then uniform branches, and the shuffles inside them need no WARPSYNC / ENDCOLLECTIVE wrappers (which also fence the
+// instruction scheduler around every shuffle of the elimination sweeps)
+__device__ __forceinline__ int warp_index_sync() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
 
 // factor scratch of spine_core2: Lt row-major (row j = Lt(j, .)) with leading dimension NS + 2: rows stay 16-byte
 // aligned for the 128-bit broadcast loads, and the 128-bit row stores of 8 neighbouring lanes (28 words apart for
@@ -703,7 +707,7 @@ __global__ void __launch_bounds__(16 * G, 512 / (16 * G)) tier0_kernel(Shape s, 
   double* zv = Rs + G * SLOT;
   double* W = zv + G * ZS;
   const int tid = threadIdx.x, nthr = blockDim.x;
-  const int warp = tid >> 5, lane = tid & 31;
+  const int warp = warp_index_sync(), lane = tid & 31;
   const int prob = blockIdx.x / M0, grp = blockIdx.x % M0;
   const int k0 = grp * G;
   const int N = s.N, Ng = s.Ng;
@@ -951,7 +955,7 @@ __global__ void __launch_bounds__(128, 4) tier_kernel(Shape s, Bufs b, TierArgs 
   extern __shared__ __align__(16) double smf[];
   double* sm = smf;
   const int tid = threadIdx.x, nthr = blockDim.x;
-  const int warp = tid >> 5, lane = tid & 31;
+  const int warp = warp_index_sync(), lane = tid & 31;
   const int ecount = a.ecount;
   const int ncta = a.Min / ecount;
   const int prob = blockIdx.x / ncta, sg = blockIdx.x % ncta;

@@ -396,7 +396,7 @@ __global__ void __launch_bounds__(32 * SCAN_WPC, 2) scan_leaf_kernel(Shape s, Bu
   static_assert(RAWB % 16 == 0 && (NS * 8) % 16 == 0 && scan_leaf_warp_doubles<NS, NI>() % 2 == 0 && (WSZ * 8) % 16 == 0, "TMA alignment");
   extern __shared__ __align__(16) double smf[];
   __shared__ __align__(8) unsigned long long mbar[SCAN_WPC];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = warp_index_sync(), lane = threadIdx.x & 31;
   const long long sub = (long long)blockIdx.x * SCAN_WPC + warp;
   if (sub >= nsub) return;
   double* R = smf + warp * scan_leaf_warp_doubles<NS, NI>();
@@ -528,7 +528,7 @@ __global__ void __launch_bounds__(128) scan_down_kernel(Shape s, Bufs b, ScanBuf
   constexpr bool TWO = XU <= 16;
   static_assert(XU <= 32 && NS <= 16, "rows of a knot fit in a warp, multipliers in a half-warp");
   const int lane = threadIdx.x & 31;
-  const long long sub = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const long long sub = (long long)blockIdx.x * (blockDim.x >> 5) + warp_index_sync();
   if (sub >= nsub) return;
   const int prob = (int)(sub / M0), grp = (int)(sub - (long long)prob * M0);
   const double* la_p = lam_all + ((size_t)prob * (M0 + 1) + grp) * NS;
