@@ -849,6 +849,36 @@ def test_long_horizon_16384_vs_reference():
         assert kkt <= 2 * ref_kkt + 1e-13 * np.linalg.norm(z), (what, kkt, ref_kkt)
 
 
+def test_full_baseline_batch_4096_properties():
+    # BASELINE configs[2] at its own size (the bench workload: n=12, m=4, N=256, seed 2024, problems 0..4095): no failure
+    # flag; samples against the oracle; KKT residual of a spread of problems no worse than 2x the oracle's; and a
+    # size-independent property: a problem solved inside the full batch is bit-identical to the same problem solved in a
+    # batch of 8 (other CTA / warp placement, other tier arity)
+    n, m, N, B = 12, 4, 256, 4096
+    kn, x0 = R.synth_problems(n, m, N, 2024, 0, B)
+    s = R.CudaSolver(n, m, N, batch=B, flags=0)
+    assert s.mode == R.MODE_SCAN
+    s.upload(kn, x0)
+    s.solve()
+    assert not s.flags().any()
+    z = s.solution().copy()
+    s.close()
+    assert np.isfinite(z).all()
+    for p in (0, 1, 2047, 4095):
+        ref, _ = O.port_solve(n, m, N, kn[p], x0[p])
+        assert max(rel_err_classes(z[p], ref, n, m, N)) < TOL, p
+        kkt_ref = O.kkt_residual(n, m, N, kn[p], x0[p], ref)
+        assert O.kkt_residual(n, m, N, kn[p], x0[p], z[p]) <= 2 * kkt_ref + 1e-13 * np.linalg.norm(ref), p
+    worst = max(O.kkt_residual(n, m, N, kn[p], x0[p], z[p]) / np.linalg.norm(z[p]) for p in range(0, B, 61))
+    assert worst < 1e-14 * N, worst
+    ids = [5, 700, 701, 1999, 2500, 3333, 4000, 4095]
+    small = R.CudaSolver(n, m, N, batch=len(ids), flags=0)
+    small.upload(np.ascontiguousarray(kn[ids]), np.ascontiguousarray(x0[ids]))
+    small.solve()
+    assert np.array_equal(small.solution(), z[ids])
+    small.close()
+
+
 def test_large_state_n64_N1024_vs_reference():
     # configs[4]: n=64, m=16, N=1024 (755 MB dense factor array per problem) against the reference's stored solution
     n, m, N = 64, 16, 1024
