@@ -414,9 +414,17 @@ __global__ void __launch_bounds__(128) dual_tier_kernel(Shape s, Bufs b, DualTie
 // ---------------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------------
+// shapes with a compiled instance of the dual-form kernels: even n <= 16 (the records are moved by 16-byte bulk copies),
+// m <= 16. One line here = one more shape on the scan path (kernels are templates on (n, m)).
+#define RSLQR_DUAL_SHAPES(X) \
+  X(6, 3) X(12, 4) X(12, 6) X(8, 4) X(16, 8) X(4, 2) /* round-2 list */ \
+  X(6, 2) X(8, 2) X(8, 3) X(10, 4) X(10, 5) X(12, 2) X(12, 3) X(12, 8) X(14, 4) X(14, 6) X(16, 4) X(16, 6)
+
 inline bool dual_shape_ok(int n, int m) {
-  return (n == 6 && m == 3) || (n == 12 && m == 4) || (n == 12 && m == 6) || (n == 8 && m == 4) || (n == 16 && m == 8) ||
-         (n == 4 && m == 2);
+#define RSLQR_X(N_, M_) if (n == N_ && m == M_) return true;
+  RSLQR_DUAL_SHAPES(RSLQR_X)
+#undef RSLQR_X
+  return false;
 }
 
 template <int NS>
@@ -484,13 +492,13 @@ inline int dual_launch(ScanPlan& p, const Shape& s, const Bufs& b, int batch, in
                        cudaEvent_t k0, cudaEvent_t k1) {
   if (!p.f.available || !(p.dual || p.hybrid)) { err = "shape not covered by the dual-form scan kernels"; return -5; }
   cudaError_t e;
-  if (s.n == 6 && s.m == 3) e = dual_launch_t<6, 3>(p, s, b, batch, pack_rhs, st, k0, k1);
-  else if (s.n == 12 && s.m == 4) e = dual_launch_t<12, 4>(p, s, b, batch, pack_rhs, st, k0, k1);
-  else if (s.n == 12 && s.m == 6) e = dual_launch_t<12, 6>(p, s, b, batch, pack_rhs, st, k0, k1);
-  else if (s.n == 8 && s.m == 4) e = dual_launch_t<8, 4>(p, s, b, batch, pack_rhs, st, k0, k1);
-  else if (s.n == 16 && s.m == 8) e = dual_launch_t<16, 8>(p, s, b, batch, pack_rhs, st, k0, k1);
-  else if (s.n == 4 && s.m == 2) e = dual_launch_t<4, 2>(p, s, b, batch, pack_rhs, st, k0, k1);
-  else { err = "shape not covered by the dual-form scan kernels"; return -5; }
+  bool found = false;
+  e = cudaSuccess;
+#define RSLQR_X(N_, M_) \
+  if (!found && s.n == N_ && s.m == M_) { found = true; e = dual_launch_t<N_, M_>(p, s, b, batch, pack_rhs, st, k0, k1); }
+  RSLQR_DUAL_SHAPES(RSLQR_X)
+#undef RSLQR_X
+  if (!found) { err = "shape not covered by the dual-form scan kernels"; return -5; }
   if (e != cudaSuccess) { err = std::string("dual launch: ") + cudaGetErrorString(e); return -3; }
   return 0;
 }

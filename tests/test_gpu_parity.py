@@ -237,6 +237,28 @@ def test_dual_form_scan_path_shapes(shape, N, monkeypatch):
     s.close()
 
 
+@pytest.mark.parametrize("shape", [(6, 2), (8, 2), (8, 3), (10, 4), (10, 5), (12, 2), (12, 3), (12, 8), (14, 4), (14, 6), (16, 4), (16, 6)])
+def test_dual_form_scan_path_more_shapes(shape):
+    # the further (even n <= 16, m) instances of the dual-form kernels (RSLQR_DUAL_SHAPES, kernels_dual.cuh): default
+    # mode is the scan path; two horizons (one tier / several tiers) against the oracle, plus the no-allocation entry
+    # point's shape list (it dispatches through the same table)
+    n, m = shape
+    for N in (8, 512):
+        B = 3
+        kn, x0 = R.synth_problems(n, m, N, 43, 0, B)
+        s = R.CudaSolver(n, m, N, batch=B, flags=0)
+        assert s.mode == R.MODE_SCAN
+        s.upload(kn, x0)
+        s.solve()
+        z = s.solution().copy()
+        assert not s.flags().any()
+        s.close()
+        for p in range(B):
+            want, _ = O.port_solve(n, m, N, kn[p], x0[p], threads=2)
+            assert max(rel_err_classes(z[p], want, n, m, N)) < TOL, (shape, N, p)
+            assert O.kkt_residual(n, m, N, kn[p], x0[p], z[p]) < 1e-10 * max(1.0, np.linalg.norm(z[p]))
+
+
 def test_shipped_n6_problem_runs_in_scan_mode():
     # lqr_prob_256.json (n=6, m=3: the only shape the reference ships) takes the scan path by default
     n, m, N, kn, x0 = R.load_problem_json(os.path.join(GOLDEN, "lqr_prob_256.json"))
