@@ -223,7 +223,7 @@ int rslqr_cuda_la_trisolve(const double* L, int n, double* b, int m, int which);
  * and everything the kernels keep between launches lives in one static device array of RSLQR_STATIC_SCRATCH_BYTES
  * (32 MiB; every GPU that loads the library holds it until exit). The call enqueues on `stream` (NULL = the legacy
  * default stream) and calls no cudaMalloc / cudaFree or any other allocating routine. Shapes: those of the scan
- * path (even n <= 16: the list RSLQR_DUAL_SHAPES in rslqr_b200/csrc/kernels_dual.cuh), power-of-two N >= 8; about 0.98 MB of scratch per problem at
+ * path (33 (n, m) pairs with n, m <= 16: the list RSLQR_DUAL_SHAPES in rslqr_b200/csrc/kernels_dual.cuh), power-of-two N >= 8; about 0.98 MB of scratch per problem at
  * n=12, m=4, N=256 (33 problems fit). A size beyond the array is rejected with RSLQR_E_ARG and a message that
  * states the bytes needed. ALL calls on a device share the array: calls that overlap on the GPU (different streams,
  * or graphs replayed concurrently) race; serialise them. */

@@ -414,11 +414,12 @@ __global__ void __launch_bounds__(128) dual_tier_kernel(Shape s, Bufs b, DualTie
 // ---------------------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------------------
-// shapes with a compiled instance of the dual-form kernels: even n <= 16 (the records are moved by 16-byte bulk copies),
-// m <= 16. One line here = one more shape on the scan path (kernels are templates on (n, m)).
+// shapes with a compiled instance of the dual-form kernels: n <= 16, m <= 16. One line here = one more shape on the scan path (kernels are templates on (n, m)).
 #define RSLQR_DUAL_SHAPES(X) \
   X(6, 3) X(12, 4) X(12, 6) X(8, 4) X(16, 8) X(4, 2) /* round-2 list */ \
-  X(6, 2) X(8, 2) X(8, 3) X(10, 4) X(10, 5) X(12, 2) X(12, 3) X(12, 8) X(14, 4) X(14, 6) X(16, 4) X(16, 6)
+  X(6, 2) X(8, 2) X(8, 3) X(10, 4) X(10, 5) X(12, 2) X(12, 3) X(12, 8) X(14, 4) X(14, 6) X(16, 4) X(16, 6) \
+  X(3, 1) X(5, 2) X(7, 3) X(9, 3) X(11, 4) X(13, 4) X(15, 5) /* odd n: blocks are padded to a multiple of 4 on chip */ \
+  X(2, 1) X(4, 1) X(4, 4) X(6, 6) X(7, 7) X(8, 8) X(14, 7) X(16, 16)
 
 inline bool dual_shape_ok(int n, int m) {
 #define RSLQR_X(N_, M_) if (n == N_ && m == M_) return true;

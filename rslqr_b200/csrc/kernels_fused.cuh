@@ -1165,7 +1165,8 @@ inline int launch_topdown(const double* sep, double* lam, int M0, int batch, con
   auto pass = [&](int span, int step) {
     const int nloc = span / step, ctas = batch * (M0 / span);
     const int bytes = ((nloc - 1) * WSZ + (nloc + 1) * NS) * (int)sizeof(double);
-    const bool smem_ok = nloc >= 2 && nloc <= H && bytes <= 200 * 1024;  // (63 records of n = 16 would not fit)
+    // (63 records of n = 16 would not fit; odd n: the records are only 8-byte aligned, no bulk copies)
+    const bool smem_ok = nloc >= 2 && nloc <= H && bytes <= 200 * 1024 && WSZ % 2 == 0;
     const bool use_smem = smem_ok && (force >= 0 ? force != 0 : ctas <= 1024);
     if (use_smem) {
       smem_optin(topdown_smem_kernel<NS>, bytes);

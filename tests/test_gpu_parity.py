@@ -237,9 +237,11 @@ def test_dual_form_scan_path_shapes(shape, N, monkeypatch):
     s.close()
 
 
-@pytest.mark.parametrize("shape", [(6, 2), (8, 2), (8, 3), (10, 4), (10, 5), (12, 2), (12, 3), (12, 8), (14, 4), (14, 6), (16, 4), (16, 6)])
+@pytest.mark.parametrize("shape", [(6, 2), (8, 2), (8, 3), (10, 4), (10, 5), (12, 2), (12, 3), (12, 8), (14, 4), (14, 6), (16, 4), (16, 6),
+                                   (3, 1), (5, 2), (7, 3), (9, 3), (11, 4), (13, 4), (15, 5),
+                                   (2, 1), (4, 1), (4, 4), (6, 6), (7, 7), (8, 8), (14, 7), (16, 16)])
 def test_dual_form_scan_path_more_shapes(shape):
-    # the further (even n <= 16, m) instances of the dual-form kernels (RSLQR_DUAL_SHAPES, kernels_dual.cuh): default
+    # the further (n <= 16, m <= 16; odd n too) instances of the dual-form kernels (RSLQR_DUAL_SHAPES, kernels_dual.cuh): default
     # mode is the scan path; two horizons (one tier / several tiers) against the oracle, plus the no-allocation entry
     # point's shape list (it dispatches through the same table)
     n, m = shape
