@@ -87,6 +87,7 @@ def test_solve_static_rejects_what_does_not_fit():
     assert rc == E_ARG
     msg = R.LIB.rslqr_cuda_last_error().decode()
     assert "RSLQR_STATIC_SCRATCH_BYTES" in msg and "bytes of scratch" in msg
-    assert R.LIB.rslqr_cuda_solve_static(13, 4, 256, 1, 0, one.data_ptr(), one.data_ptr(), one.data_ptr(), fl.data_ptr(), None) < 0
+    # (20, 7) has no instance of the scan kernels (RSLQR_DUAL_SHAPES): rejected before any launch
+    assert R.LIB.rslqr_cuda_solve_static(20, 7, 256, 1, 0, one.data_ptr(), one.data_ptr(), one.data_ptr(), fl.data_ptr(), None) == -5
     assert R.LIB.rslqr_cuda_solve_static(12, 4, 200, 1, 0, one.data_ptr(), one.data_ptr(), one.data_ptr(), fl.data_ptr(), None) == E_ARG
     assert R.LIB.rslqr_cuda_solve_static(12, 4, 256, 1, 0, None, one.data_ptr(), one.data_ptr(), fl.data_ptr(), None) == E_ARG
