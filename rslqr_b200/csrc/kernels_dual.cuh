@@ -144,6 +144,41 @@ __device__ __forceinline__ void dual_store_record(double* rec, const double* W) 
   }
 }
 
+// Sbb = [A | B] D [A | B]^T of one knot on the fp64 tensor cores, whole warp: AB = [A | B] (column-major ld NS) and
+// dv = the leaf diagonals [1/Q | 1/R] of the knot's transformed block; noQ: knot 0 (1/Q -> 0); dead: last knot (no b
+// side: zero). Writes rows [0, NS) of the NP x LD row-major block `dst`, zero in the padded columns [NS, NP).
+template <int NS, int NI>
+__device__ __forceinline__ void dual_leaf_sbb(const double* AB, const double* dv, bool noQ, bool dead, double* dst) {
+  using D = DualDim<NS>;
+  constexpr int NP = D::NP, LD = D::LD, XU = NS + NI, MT = (NS + 7) / 8, KS = (XU + 3) / 4;
+  const int lane = threadIdx.x & 31, q = lane & 3, rr = lane >> 2;
+  double a[MT][KS];  // A fragments [A | B](8 mt + rr, 4 ks + q) D(4 ks + q); unscaled they are the B fragments of the same tile index
+  double bq[MT][KS];
+#pragma unroll
+  for (int ks = 0; ks < KS; ++ks) {
+    const int l = 4 * ks + q;
+    const bool lv = l < XU;
+    const double d = (!lv || dead || (l < NS && noQ)) ? 0.0 : dv[lv ? l : 0];
+#pragma unroll
+    for (int mt = 0; mt < MT; ++mt) {
+      const int r = 8 * mt + rr;
+      const double v = (lv && r < NS) ? AB[r + NS * (lv ? l : 0)] : 0.0;
+      bq[mt][ks] = v;
+      a[mt][ks] = v * d;
+    }
+  }
+#pragma unroll
+  for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+    for (int nt = 0; nt < MT; ++nt) {
+      double c0 = 0.0, c1 = 0.0;
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks) dmma884(c0, c1, a[mt][ks], bq[nt][ks]);
+      const int row = 8 * mt + rr, col = 8 * nt + 2 * q;
+      if (row < NS && col < NP) *reinterpret_cast<double2*>(dst + row * LD + col) = make_double2(col < NS ? c0 : 0.0, col + 1 < NS ? c1 : 0.0);
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Leaf elements of two neighbouring knots at once, straight from their transformed blocks (leaf_transform):
 // lanes [0,NS) build the L-type element of knot kL into EL, lanes [NS,2NS) the R-type element of knot kR into ER.
@@ -151,7 +186,7 @@ __device__ __forceinline__ void dual_store_record(double* rec, const double* W) 
 //                       sa = -z_x - z_lambda,  sb = A z_x + B z_u          (z: the leaf-solved rhs)
 //   knot 0 (x_0 is fixed, lambda_0 is no unknown of the dual system): Q^-1 -> 0 in Saa, Sab, Sbb
 //   last knot of the horizon: only Saa, sa (its R, A, B, d are ignored)
-// One row per lane; all stores are contiguous rows.
+// Sbb on DMMA (dual_leaf_sbb); the rest one row per lane, all stores contiguous rows.
 // ---------------------------------------------------------------------------------------------------------
 template <int NS, int NI>
 __device__ __forceinline__ void dual_leaf_pair(const double* BL, const double* zlL, const double* BR, const double* zlR,
@@ -170,24 +205,12 @@ __device__ __forceinline__ void dual_leaf_pair(const double* BL, const double* z
   const bool noQ = !right && first0;     // knot 0
   const bool dead = right && lastR;      // last knot: no b side
   const int cs = act ? c : 0;
-  // w[l] = AB(c, l) * D(l): row c of [A | B] scaled by the leaf diagonals
-  double w[XU];
-  double sb = 0.0;
+  // Sbb of both knots on DMMA, straight into its place: Sp of the L-type element, Kp of the R-type one
+  dual_leaf_sbb<NS, NI>(BL + RD::OA, BL, first0, false, EL + D::OS);
+  dual_leaf_sbb<NS, NI>(BR + RD::OA, BR, false, lastR, ER + D::OK);
+  double sb = 0.0;     // row c of [A | B] z
 #pragma unroll
-  for (int l = 0; l < XU; ++l) {
-    const double d = (l < NS && noQ) ? 0.0 : B[l];
-    const double abv = AB[cs + NS * l];
-    w[l] = dead ? 0.0 : abv * d;
-    sb = fma(dead ? 0.0 : abv, B[RD::OZ + l], sb);
-  }
-  double g[NP];  // row c of Sbb = [A | B] D [A | B]^T
-#pragma unroll
-  for (int r = 0; r < NP; ++r) g[r] = 0.0;
-#pragma unroll
-  for (int l = 0; l < XU; ++l) {
-#pragma unroll
-    for (int r = 0; r < NS; ++r) g[r] = fma(w[l], AB[r + NS * l], g[r]);
-  }
+  for (int l = 0; l < XU; ++l) sb = fma(dead ? 0.0 : AB[cs + NS * l], B[RD::OZ + l], sb);
   const double dq = noQ ? 0.0 : B[cs];                 // 1 / Q(c)
   const double sa = -B[RD::OZ + cs] - zl[cs];
   if (act) {
@@ -203,8 +226,7 @@ __device__ __forceinline__ void dual_leaf_pair(const double* BL, const double* z
       if (r + 1 < NS) cy = right ? (dead ? 0.0 : -AB[c + NS * (r + 1)] * B[r + 1]) : -AB[r + 1 + NS * c] * dq;
       const double dx = r == c ? dq : 0.0, dy = r + 1 == c ? dq : 0.0;
       *reinterpret_cast<double2*>(cp + r) = make_double2(cx, cy);
-      *reinterpret_cast<double2*>(kp + r) = right ? make_double2(g[r], g[r + 1]) : make_double2(dx, dy);
-      *reinterpret_cast<double2*>(sp + r) = right ? make_double2(dx, dy) : make_double2(g[r], g[r + 1]);
+      *reinterpret_cast<double2*>((right ? sp : kp) + r) = make_double2(dx, dy);   // Saa (the other block holds Sbb already)
     }
     E[D::OKS + c] = right ? sb : sa;
     E[D::OSS + c] = right ? sa : sb;
