@@ -256,7 +256,6 @@ __device__ __forceinline__ void dual_leaf_pair(const double* BL, const double* z
 // L-type for an even subtree index, R-type for an odd one.
 // per warp: [NSE | 4 knot blocks | X | Y | Z | W | Lr]
 // ---------------------------------------------------------------------------------------------------------
-constexpr int DUAL_WPC = 4;
 
 template <int NS, int NI>
 __host__ __device__ constexpr int dual_leaf_warp_doubles() {
@@ -264,8 +263,24 @@ __host__ __device__ constexpr int dual_leaf_warp_doubles() {
   return ((NS + 1) & ~1) + ((SCAN_LEAF * RawDim<NS, NI>::STRIDE + 1) & ~1) + 3 * D::ENT + ((D::WP + 1) & ~1) + D::LR;
 }
 
+// warps per CTA of the leaf kernel: the count (3..8) that puts the most warps of this shape on an SM (227 KB of shared
+// memory, 1 KB reserved per CTA); the smaller count on a tie
 template <int NS, int NI>
-__global__ void __launch_bounds__(32 * DUAL_WPC) dual_leaf_kernel(Shape s, Bufs b, double* ent0, double* sep_in, int pack_rhs,
+__host__ __device__ constexpr int dual_leaf_wpc() {
+  const long long per_warp = (long long)dual_leaf_warp_doubles<NS, NI>() * 8;
+  int best = 3, best_warps = 0;
+  for (int w = 3; w <= 8; ++w) {
+    const long long cta = w * per_warp + 1024;
+    int ctas = (int)((227LL * 1024) / cta);
+    if (ctas > 32) ctas = 32;
+    const int warps = ctas * w > 64 ? 64 : ctas * w;
+    if (warps > best_warps) { best = w; best_warps = warps; }
+  }
+  return best;
+}
+
+template <int NS, int NI>
+__global__ void __launch_bounds__(32 * dual_leaf_wpc<NS, NI>()) dual_leaf_kernel(Shape s, Bufs b, double* ent0, double* sep_in, int pack_rhs,
                                                                    int M0, long long nsub) {
   pdl_sync();
   using D = DualDim<NS>;
@@ -274,6 +289,7 @@ __global__ void __launch_bounds__(32 * DUAL_WPC) dual_leaf_kernel(Shape s, Bufs 
   constexpr int RAWB = SCAN_LEAF * RD::STRIDE * (int)sizeof(double);
   static_assert(RAWB % 16 == 0 && D::ENT % 2 == 0 && D::LR % 2 == 0, "TMA / 128-bit alignment");
   extern __shared__ __align__(16) double smf[];
+  constexpr int DUAL_WPC = dual_leaf_wpc<NS, NI>();
   __shared__ __align__(8) unsigned long long mbar[DUAL_WPC];
   const int warp = warp_index_sync(), lane = threadIdx.x & 31;
   const long long sub = (long long)blockIdx.x * DUAL_WPC + warp;
@@ -498,6 +514,7 @@ inline cudaError_t dual_launch_t(ScanPlan& p, const Shape& s, const Bufs& b, int
     }
   }
   if (!p.hybrid) {
+    constexpr int DUAL_WPC = dual_leaf_wpc<NS, NI>();
     const int smem = DUAL_WPC * dual_leaf_warp_doubles<NS, NI>() * (int)sizeof(double);
     e = smem_optin(dual_leaf_kernel<NS, NI>, smem);
     if (e != cudaSuccess) return e;
