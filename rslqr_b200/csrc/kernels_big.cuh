@@ -44,15 +44,19 @@ struct BigBufs {
   double* ufac;  // [batch][N][BigFac::SIZE] factor U, block inverses and 1/d of the separator after knot i at slot i
 };
 
+constexpr int BIG_NI = 16;  // inputs the large-block kernels are laid out for (m <= BIG_NI)
+
 // G output tiles of Sbb = [A | B] D [A | B]^T for one warp: tiles warp, warp + 8, ... of the lower block triangle in row-major
 // order (tile i = (t, j), j <= t, i = t (t + 1) / 2 + j). AB: [A | B] in shared memory (column-major, ld NS + 4), dv: D.
-template <int NS, int NI, int G>
-__device__ __forceinline__ void big_leaf_sbb(const double* AB, const double* dv, double* Sbb, int warp, int lane) {
-  constexpr int XU = NS + NI, LDA = NS + 4, KS = XU / 4;
+// Rows / columns >= n are padding: 0.5 on the diagonal there (the S of a merge, SbbL + SaaR, gets the identity).
+template <int NS, int G>
+__device__ __forceinline__ void big_leaf_sbb(const double* AB, const double* dv, double* Sbb, int warp, int lane, int n) {
+  constexpr int XU = NS + BIG_NI, LDA = NS + 4, KS = XU / 4;
   const int q = lane & 3, rr = lane >> 2;
   const double *pa[G], *pb[G];
   double* po[G];
   double c[G][2];
+  int drow[G];  // row of the tile's lane if the tile is a diagonal one, else -1
 #pragma unroll
   for (int u = 0; u < G; ++u) {
     int t = 0, jj = warp + 8 * u;
@@ -60,6 +64,7 @@ __device__ __forceinline__ void big_leaf_sbb(const double* AB, const double* dv,
     pa[u] = AB + 8 * t + rr + LDA * q;
     pb[u] = AB + 8 * jj + rr + LDA * q;
     po[u] = Sbb + (8 * t + rr) * NS + 8 * jj + 2 * q;
+    drow[u] = t == jj ? 8 * t + rr : -1;
     c[u][0] = c[u][1] = 0.0;
   }
 #pragma unroll 4
@@ -69,7 +74,14 @@ __device__ __forceinline__ void big_leaf_sbb(const double* AB, const double* dv,
     for (int u = 0; u < G; ++u) dmma884(c[u][0], c[u][1], pa[u][4 * LDA * ks] * dk, pb[u][4 * LDA * ks]);
   }
 #pragma unroll
-  for (int u = 0; u < G; ++u) *reinterpret_cast<double2*>(po[u]) = make_double2(c[u][0], c[u][1]);
+  for (int u = 0; u < G; ++u) {
+    if (drow[u] >= n) {  // padded row of a diagonal tile (the products are zero there)
+      const int col = (drow[u] & ~7) + 2 * q;
+      if (col == drow[u]) c[u][0] = 0.5;
+      if (col + 1 == drow[u]) c[u][1] = 0.5;
+    }
+    *reinterpret_cast<double2*>(po[u]) = make_double2(c[u][0], c[u][1]);
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -77,44 +89,68 @@ __device__ __forceinline__ void big_leaf_sbb(const double* AB, const double* dv,
 // src/solver.c:138-190), one CTA per (problem, knot):
 //   Saa = Q^-1, Sab = -Q^-1 A^T, Sbb = A Q^-1 A^T + B R^-1 B^T, sa = -z_x - z_lambda, sb = A z_x + B z_u
 //   knot 0: x_0 is fixed (z_x = x0) and lambda_0 is no unknown: Q^-1 -> 0 in the blocks; last knot: only Saa, sa.
-// dynamic smem: ((NS+4)*(NS+NI) + 2*(NS+NI) + 2*NS + 3*NS) doubles
+// The blocks are NS x NS with NS = 32 or 64 >= n = s.n: a smaller n is padded on chip (zero rows / columns, 0.5 on the
+// padded diagonal of Saa and Sbb), m = s.m <= BIG_NI; everything above the leaves works on NS x NS blocks.
+// dynamic smem: big_leaf_smem_doubles<NS>()
 // ---------------------------------------------------------------------------------------------------------
-template <int NS, int NI>
+template <int NS>
+__host__ __device__ constexpr int big_leaf_smem_doubles() {
+  return (NS + 4) * (NS + BIG_NI) + 2 * (NS + BIG_NI) + 2 * NS + (256 / NS - 1) * NS;
+}
+
+template <int NS>
 __global__ void __launch_bounds__(256, 3) big_leaf_kernel(Shape s, Bufs b, BigBufs bb, int pack_rhs) {
   using D = BigDim<NS>;
-  constexpr int XU = NS + NI, LDA = NS + 4;  // (LDA = 4 mod 16: the DMMA fragments of a warp fall into two wavefronts)
-  static_assert(NS == 64 && XU % 4 == 0, "8 warps x 8 rows; k-steps of 4");
+  constexpr int XU = NS + BIG_NI, LDA = NS + 4;  // (LDA = 4 mod 16: the DMMA fragments of a warp fall into two wavefronts)
+  constexpr int NT = NS / 8, NTASK = NT * (NT + 1) / 2, PARTS = 256 / NS;
+  static_assert(NS % 32 == 0 && 256 % NS == 0 && XU % 4 == 0 && XU % PARTS == 0 && NTASK >= 8, "8 warps; k-steps of 4");
   extern __shared__ __align__(16) double smf[];
-  double* AB = smf;                 // [NS x XU] column-major with leading dimension LDA
-  double* dv = AB + LDA * XU;       // 1/Q, 1/R (as used in the products: 0 for Q of knot 0 and for the last knot)
+  double* AB = smf;                 // [NS x XU] column-major with leading dimension LDA: columns [0, NS) = A, [NS, XU) = B
+  double* dv = AB + LDA * XU;       // 1/Q, 1/R (as used in the products: 0 for Q of knot 0, for the last knot, for padding)
   double* zv = dv + XU;             // leaf-solved z_x, z_u
   double* sc = zv + XU;             // 1/Q of this knot (also for knot 0), then z_lambda
-  const int N = s.N;
+  const int N = s.N, n = s.n, m = s.m;
   const int prob = blockIdx.x / N, k = blockIdx.x % N;
   const int tid = threadIdx.x, nthr = blockDim.x;
   const double* kn = knot_ptr(s, b, prob, k);
   const bool first = k == 0, last = k == N - 1;
   // [A | B] -> shared memory by 8-byte asynchronous copies (the knot block is only 8-byte aligned), in flight while the
-  // diagonal / right-hand-side part below is computed
-  for (int e = tid; e < NS * XU; e += nthr) {
-    const int l = e / NS, r = e - l * NS;
-    if (last) AB[r + LDA * l] = 0.0;
-    else cp_async8(AB + r + LDA * l, kn + s.oA + e);
+  // diagonal / right-hand-side part below is computed; padding is zero
+  if (n == NS && m == BIG_NI) {  // nothing to pad: [A | B] is one contiguous run of the knot block
+    for (int e = tid; e < NS * XU; e += nthr) {
+      const int l = e / NS, r = e - l * NS;
+      if (last) AB[r + LDA * l] = 0.0;
+      else cp_async8(AB + r + LDA * l, kn + s.oA + e);
+    }
+  } else {
+    for (int e = tid; e < NS * XU; e += nthr) {
+      const int l = e / NS, r = e - l * NS;
+      const int lc = l < NS ? l : l - NS;                       // column of A, or of B
+      const bool valid = r < n && (l < NS ? lc < n : lc < m) && !last;
+      if (valid) cp_async8(AB + r + LDA * l, kn + (l < NS ? s.oA : s.oB) + (size_t)lc * n + r);
+      else AB[r + LDA * l] = 0.0;
+    }
   }
   for (int l = tid; l < XU; l += nthr) {
     const bool isR = l >= NS;
-    const double d = kn[l];  // Q then R lead the block
+    const int li = isR ? l - NS : l;
+    if (li >= (isR ? m : n)) {  // padding
+      zv[l] = 0.0; dv[l] = 0.0;
+      if (!isR) { sc[l] = 0.0; sc[NS + l] = 0.0; }
+      continue;
+    }
+    const double d = kn[isR ? n + li : li];  // Q then R lead the block
     if (!(d > 0.0) && !(isR && last)) {
       b.status[(size_t)prob * 3 * N + (isR ? rs_slot_R(k) : rs_slot_Q(k))] = -1;
       b.flags[prob] = 1;
     }
     const double dinv = (isR && last) ? 0.0 : 1.0 / d;
-    double rx;  // negated rhs of row l of [x; u]
-    if (!pack_rhs) rx = soln_ptr(s, b, prob, k)[NS + l];
-    else rx = isR ? (last ? 0.0 : -kn[s.orr + l - NS]) : -kn[s.oq + l];
+    double rx;  // negated rhs of row li of x, or of u
+    if (!pack_rhs) rx = soln_ptr(s, b, prob, k)[isR ? 2 * n + li : n + li];
+    else rx = isR ? (last ? 0.0 : -kn[s.orr + li]) : -kn[s.oq + li];
     double z;
     if (first && !isR) {
-      const double rl = pack_rhs ? -b.x0[(size_t)prob * NS + l] : soln_ptr(s, b, prob, k)[l];
+      const double rl = pack_rhs ? -b.x0[(size_t)prob * n + li] : soln_ptr(s, b, prob, k)[li];
       z = -rl;  // z_x(0) = x0
     } else {
       z = (isR && last) ? rx : rx * dinv;
@@ -124,7 +160,7 @@ __global__ void __launch_bounds__(256, 3) big_leaf_kernel(Shape s, Bufs b, BigBu
     if (!isR) {
       sc[l] = first ? 0.0 : dinv;
       double zl = 0.0;  // z_lambda(k) = negated rhs of the lambda row (unused for knot 0)
-      if (!first) zl = pack_rhs ? -(kn - s.stride)[s.od + l] : soln_ptr(s, b, prob, k)[l];
+      if (!first) zl = pack_rhs ? -(kn - s.stride)[s.od + li] : soln_ptr(s, b, prob, k)[li];
       sc[NS + l] = zl;
     }
   }
@@ -135,29 +171,32 @@ __global__ void __launch_bounds__(256, 3) big_leaf_kernel(Shape s, Bufs b, BigBu
   // (8 x 8 tiles with column tile <= row tile): the tiles above it are neither computed nor written
   for (int e = 2 * tid; e < NS * NS; e += 2 * nthr) {  // two columns per thread: 128-bit loads and stores
     const int r = e / NS, c = e - r * NS;
-    const double qi = sc[r];
-    if ((c >> 3) <= (r >> 3)) *reinterpret_cast<double2*>(E + D::OAA + e) = make_double2(r == c ? qi : 0.0, r == c + 1 ? qi : 0.0);
+    const double qi = sc[r], di = r < n ? qi : 0.5;    // (padded diagonal: 0.5)
+    if ((c >> 3) <= (r >> 3)) *reinterpret_cast<double2*>(E + D::OAA + e) = make_double2(r == c ? di : 0.0, r == c + 1 ? di : 0.0);
     const double2 av = *reinterpret_cast<const double2*>(AB + c + LDA * r);  // -A(c, r) / Q(r)   (AB is zero for the last knot)
     *reinterpret_cast<double2*>(E + D::OAB + e) = make_double2(-qi * av.x, -qi * av.y);
   }
-  // Sbb = [A | B] D [A | B]^T on the fp64 tensor cores, 8 x 8 output tiles: the 36 tiles of the lower block triangle,
-  // dealt round-robin to the 8 warps (warps 0..3: 5 tiles, 4..7: 4 tiles, all in flight).
+  // Sbb = [A | B] D [A | B]^T on the fp64 tensor cores, 8 x 8 output tiles: the tiles of the lower block triangle, dealt
+  // round-robin to the 8 warps, all of a warp in flight (NS = 64: 36 tiles, 5 or 4 per warp)
   {
     const int warp = tid >> 5;
-    if (warp < 4) big_leaf_sbb<NS, NI, 5>(AB, dv, E + D::OBB, warp, tid & 31);
-    else big_leaf_sbb<NS, NI, 4>(AB, dv, E + D::OBB, warp, tid & 31);
+    constexpr int GLO = NTASK / 8, REM = NTASK % 8;
+    if (warp < REM) big_leaf_sbb<NS, GLO + 1>(AB, dv, E + D::OBB, warp, tid & 31, n);
+    else big_leaf_sbb<NS, GLO>(AB, dv, E + D::OBB, warp, tid & 31, n);
   }
-  {  // sb = [A | B] z: four threads per row, a quarter of the XU terms each (thread = 64 part + row)
+  {  // sb = [A | B] z: PARTS threads per row, a share of the XU terms each (thread = NS part + row)
     const int r = tid & (NS - 1), part = tid / NS;
     double v = 0.0;
 #pragma unroll 4
-    for (int l = part * (XU / 4); l < (part + 1) * (XU / 4); ++l) v = fma(AB[r + LDA * l], zv[l], v);
+    for (int l = part * (XU / PARTS); l < (part + 1) * (XU / PARTS); ++l) v = fma(AB[r + LDA * l], zv[l], v);
     double* ps = sc + 2 * NS;  // partial sums
     if (part > 0) ps[(part - 1) * NS + r] = v;
     __syncthreads();
     if (part == 0) {
+#pragma unroll
+      for (int pp = 1; pp < PARTS; ++pp) v += ps[(pp - 1) * NS + r];
       E[D::OSA + r] = -zv[r] - sc[NS + r];
-      E[D::OSB + r] = v + ps[r] + ps[NS + r] + ps[2 * NS + r];
+      E[D::OSB + r] = v;
     }
   }
 }
@@ -332,15 +371,17 @@ __device__ __forceinline__ void big_solve_rows(const double* Us, const double* X
   }
 }
 
-constexpr int BIG_SOLVE_THREADS = 288;  // 9 warps: 8 take a row tile of S_L^T and one of S_R^T each, the ninth the vector s
+// NS / 8 + 1 warps: NS / 8 take a row tile of S_L^T and one of S_R^T each, the last one the vector s (NS = 64: 288 threads)
+template <int NS>
+__host__ __device__ constexpr int big_solve_threads() { return 32 * (NS / 8 + 1); }
 
 // dynamic smem: (NS * (NS + 4) + (NS / 8) * 64) doubles: the blocks of U right of the diagonal, the X_b
 template <int NS>
-__global__ void __launch_bounds__(BIG_SOLVE_THREADS, 3) big_solve_kernel(Shape s, const double* ein, const double* ufac, double* rec_all,
+__global__ void __launch_bounds__(big_solve_threads<NS>(), 3) big_solve_kernel(Shape s, const double* ein, const double* ufac, double* rec_all,
                                                                        int level, int M) {
   using D = BigDim<NS>;
   using F = BigFac<NS>;
-  static_assert(NS == 64, "8 column blocks, 17 row tiles over 9 warps");
+  static_assert(NS % 8 == 0, "NS / 8 column blocks, 2 NS / 8 + 1 row tiles over NS / 8 + 1 warps");
   constexpr int NB = NS / 8, LDU = NS + 4;
   extern __shared__ __align__(16) double smf[];
   double* Us = smf;                      // U, row-major ld LDU
@@ -360,7 +401,7 @@ __global__ void __launch_bounds__(BIG_SOLVE_THREADS, 3) big_solve_kernel(Shape s
   double* rec = rec_all + ((size_t)prob * N + i_sep) * D::WSZ;  // [W_L | W_R | w_s], column-major ld NS
   // the right-hand sides come straight from global memory into the accumulator fragments (row = right-hand side):
   //   S_L^T = SabL: row c, 16-byte runs;  S_R^T(c, k) = SabR(k, c): 64-byte runs over the 8 rows of a tile
-  if (warp < 8) {
+  if (warp < NB) {
     double c[NB][2][2];
     const double* pl = EL + D::OAB + (size_t)(8 * warp + rr) * NS + 2 * q;
     const double* pr = ER + D::OAB + (size_t)(2 * q) * NS + 8 * warp + rr;
@@ -447,11 +488,11 @@ __device__ __forceinline__ void big_schur_run(const double (&a)[NS / 4], const d
 // only, so only the column tiles up to the diagonal one are computed: 136 instead of 192 tiles per merge. Warp w takes
 // row tile w of the left half and row tile 7 - w of the right half: 17 tiles each.
 template <int NS>
-__global__ void __launch_bounds__(256, 3) big_schur_kernel(Shape s, const double* ein, double* eout, const double* rec_all,
+__global__ void __launch_bounds__(4 * NS, 3) big_schur_kernel(Shape s, const double* ein, double* eout, const double* rec_all,
                                                          const double* ufac, int level, int M) {
   using D = BigDim<NS>;
   using F = BigFac<NS>;
-  static_assert(NS == 64, "8 warps x 8 rows per half");
+  static_assert(NS % 16 == 0, "NS / 8 warps x 8 rows per half; LDF = 4 mod 16");
   constexpr int LDF = NS + 4, KS = NS / 4, NT = NS / 8;
   extern __shared__ __align__(16) double Fs[];  // column c of W at Fs + c * LDF
   const int N = s.N;
@@ -517,7 +558,8 @@ __global__ void __launch_bounds__(NS) big_topdown_kernel(int N, const double* re
                                                           int M) {
   using D = BigDim<NS>;
   using F = BigFac<NS>;
-  static_assert(NS == 64, "two rows per lane in the back-substitution");
+  static_assert(NS % 32 == 0, "NS / 32 rows per lane in the back-substitution");
+  constexpr int RPL = NS / 32;
   constexpr int LDU = NS + 1;
   __shared__ double la[NS], lb[NS], vs[NS], Us[NS * LDU];
   const int prob = blockIdx.x / M, t = blockIdx.x % M;
@@ -541,15 +583,21 @@ __global__ void __launch_bounds__(NS) big_topdown_kernel(int N, const double* re
   cp_async_wait_all();
   __syncthreads();
   if (r < 32) {
-    double x0 = vs[r], x1 = vs[r + 32];  // rows r and r + 32
+    double x[RPL];  // rows r, r + 32, ...
+#pragma unroll
+    for (int i = 0; i < RPL; ++i) x[i] = vs[r + 32 * i];
 #pragma unroll 4
     for (int k = NS - 1; k > 0; --k) {
-      const double xk = __shfl_sync(0xffffffffu, k >= 32 ? x1 : x0, k & 31);
-      if (r < k) x0 = fma(-Us[r * LDU + k], xk, x0);
-      if (r + 32 < k) x1 = fma(-Us[(r + 32) * LDU + k], xk, x1);
+      double own = x[0];
+#pragma unroll
+      for (int i = 1; i < RPL; ++i) own = k >= 32 * i ? x[i] : own;
+      const double xk = __shfl_sync(0xffffffffu, own, k & 31);
+#pragma unroll
+      for (int i = 0; i < RPL; ++i)
+        if (r + 32 * i < k) x[i] = fma(-Us[(r + 32 * i) * LDU + k], xk, x[i]);
     }
-    lam[(size_t)(i_sep + 1) * NS + r] = x0;
-    lam[(size_t)(i_sep + 1) * NS + 32 + r] = x1;
+#pragma unroll
+    for (int i = 0; i < RPL; ++i) lam[(size_t)(i_sep + 1) * NS + 32 * i + r] = x[i];
   }
 }
 
@@ -558,26 +606,35 @@ __global__ void __launch_bounds__(NS) big_topdown_kernel(int N, const double* re
 // equations (the reference's rhs propagation src/solve.c:175-180 telescoped); knot 0: x_0 = x0 and
 // lambda_0 = Q_0 x0 + q_0 + A_0^T lambda_1 (src/nested_dissection.c:24-59). One CTA per (problem, knot), one thread per row.
 // ---------------------------------------------------------------------------------------------------------
-template <int NS, int NI>
+template <int NS>
 __global__ void __launch_bounds__(256) big_down_kernel(Shape s, Bufs b, const double* lam_all, int pack_rhs) {
-  constexpr int XU = NS + NI, CPW = XU / 8;
-  static_assert(NS == 64 && XU % 8 == 0, "two k per lane; columns dealt to 8 warps");
+  constexpr int XU = NS + BIG_NI, CPW = XU / 8, RPL = NS / 32;
+  static_assert(NS % 32 == 0 && XU % 8 == 0, "NS / 32 elements of a column per lane; columns dealt to 8 warps");
   __shared__ double dot[XU];
-  const int N = s.N;
+  const int N = s.N, n = s.n, m = s.m;
   const int prob = blockIdx.x / N, k = blockIdx.x % N;
   const int r = threadIdx.x, warp = r >> 5, lane = r & 31;
-  const double* lam = lam_all + (size_t)prob * (N + 1) * NS;
+  const double* lam = lam_all + (size_t)prob * (N + 1) * NS;   // (rows >= n of a multiplier are padding: zero)
   const bool first = k == 0, last = k == N - 1;
   const double* kn = knot_ptr(s, b, prob, k);
-  // [A | B]^T lambda_{k+1}: warp w takes columns w, w + 8, ...: a lane reads two consecutive-by-lane elements of a column
-  // (coalesced), all 2 CPW loads of the warp in flight, then a shuffle reduction per column
+  // [A | B]^T lambda_{k+1}: warp w takes columns w, w + 8, ... (slots [0, NS) = columns of A, [NS, XU) = columns of B): a
+  // lane reads consecutive-by-lane elements of a column (coalesced), all loads of the warp in flight, then a shuffle
+  // reduction per column
   {
-    const double l0 = lam[(size_t)(k + 1) * NS + lane], l1 = lam[(size_t)(k + 1) * NS + 32 + lane];
+    double lv[RPL];
+#pragma unroll
+    for (int i = 0; i < RPL; ++i) lv[i] = lam[(size_t)(k + 1) * NS + 32 * i + lane];
     double part[CPW];
 #pragma unroll
     for (int u = 0; u < CPW; ++u) {
-      const double* col = kn + s.oA + (size_t)(warp + 8 * u) * NS;
-      part[u] = last ? 0.0 : fma(__ldg(col + lane), l0, __ldg(col + 32 + lane) * l1);
+      const int l = warp + 8 * u, lc = l < NS ? l : l - NS;
+      const bool valid = !last && (l < NS ? lc < n : lc < m);
+      const double* col = kn + (l < NS ? s.oA : s.oB) + (size_t)lc * n;
+      double v = 0.0;
+#pragma unroll
+      for (int i = 0; i < RPL; ++i)
+        if (valid && 32 * i + lane < n) v = fma(__ldg(col + 32 * i + lane), lv[i], v);
+      part[u] = v;
     }
 #pragma unroll
     for (int u = 0; u < CPW; ++u) {
@@ -588,27 +645,30 @@ __global__ void __launch_bounds__(256) big_down_kernel(Shape s, Bufs b, const do
   }
   __syncthreads();
   if (r >= XU) return;
+  const bool isR = r >= NS;
+  const int ri = isR ? r - NS : r;
+  if (ri >= (isR ? m : n)) return;   // padding
   double* out = soln_ptr(s, b, prob, k);
-  const double acc = dot[r];  // row r of [A | B]^T lambda_{k+1}
-  const double d = kn[r];
+  const double acc = dot[r];  // row of [A | B]^T lambda_{k+1}
+  const double d = kn[isR ? n + ri : ri];
   double rx;
-  if (!pack_rhs) rx = out[NS + r];
-  else rx = r < NS ? -kn[s.oq + r] : (last ? 0.0 : -kn[s.orr + r - NS]);
-  if (r < NS) {
-    const double lk = first ? 0.0 : lam[(size_t)k * NS + r];
+  if (!pack_rhs) rx = out[isR ? 2 * n + ri : n + ri];
+  else rx = isR ? (last ? 0.0 : -kn[s.orr + ri]) : -kn[s.oq + ri];
+  if (!isR) {
+    const double lk = first ? 0.0 : lam[(size_t)k * NS + ri];
     double xv, lv;
     if (first) {
-      const double rl = pack_rhs ? -b.x0[(size_t)prob * NS + r] : out[r];
+      const double rl = pack_rhs ? -b.x0[(size_t)prob * n + ri] : out[ri];
       xv = -rl;
       lv = -d * rl - rx + acc;
     } else {
       xv = (rx + lk - acc) / d;
       lv = lk;
     }
-    out[r] = lv;
-    out[NS + r] = xv;
+    out[ri] = lv;
+    out[n + ri] = xv;
   } else {
-    out[NS + r] = last ? rx : (rx - acc) / d;
+    out[2 * n + ri] = last ? rx : (rx - acc) / d;
   }
 }
 
@@ -618,30 +678,39 @@ __global__ void __launch_bounds__(256) big_down_kernel(Shape s, Bufs b, const do
 struct BigPlan {
   bool covered;    // the shape has these kernels
   bool allocated;
+  int ns;          // block size the kernels run at: 32 or 64 (n is padded up to it on chip)
   BigBufs bb;
   size_t bytes;
   int launches;
 };
 
-inline bool big_shape_ok(int n, int m, int N) { return n == 64 && m == 16 && N >= 2; }
+// any n <= 64 with m <= BIG_NI: blocks of 32 or 64 (the smallest that holds n)
+inline bool big_shape_ok(int n, int m, int N) { return n >= 1 && n <= 64 && m >= 1 && m <= BIG_NI && N >= 2; }
+inline int big_block_size(int n) { return n <= 32 ? 32 : 64; }
+inline size_t big_ent_doubles(int ns) { return (size_t)3 * ns * ns + 2 * ns; }
+inline size_t big_rec_doubles(int ns) { return ((size_t)2 * ns + 1) * ns; }
+inline size_t big_fac_doubles(int ns) { return (size_t)ns * ns + (ns / 8) * 64 + ns; }
 
 inline void big_free(BigPlan* p) {
   cudaFree(p->bb.entA); cudaFree(p->bb.entB); cudaFree(p->bb.rec); cudaFree(p->bb.lam); cudaFree(p->bb.ufac);
   const bool cov = p->covered;
+  const int ns = p->ns;
   memset(p, 0, sizeof(*p));
   p->covered = cov;
+  p->ns = ns;
 }
 
 inline int big_alloc(const Shape& s, int batch, BigPlan* p, std::string& err) {
   if (p->allocated) return 0;
-  const size_t ent = BigDim<64>::ENT, wsz = BigDim<64>::WSZ;
+  p->ns = big_block_size(s.n);
+  const size_t ns = (size_t)p->ns, ent = big_ent_doubles(p->ns), wsz = big_rec_doubles(p->ns);
   auto alloc = [&](double** ptr, size_t cnt) {
     p->bytes += cnt * sizeof(double);
     return cudaMalloc((void**)ptr, cnt * sizeof(double)) == cudaSuccess;
   };
   const bool ok = alloc(&p->bb.entA, (size_t)batch * s.N * ent) && alloc(&p->bb.entB, (size_t)batch * (s.N / 2) * ent) &&
-                  alloc(&p->bb.rec, (size_t)batch * s.N * wsz) && alloc(&p->bb.lam, (size_t)batch * (s.N + 1) * s.n) &&
-                  alloc(&p->bb.ufac, (size_t)batch * s.N * BigFac<64>::SIZE);
+                  alloc(&p->bb.rec, (size_t)batch * s.N * wsz) && alloc(&p->bb.lam, (size_t)batch * (s.N + 1) * ns) &&
+                  alloc(&p->bb.ufac, (size_t)batch * s.N * big_fac_doubles(p->ns));
   if (!ok) {
     cudaGetLastError();
     big_free(p);
@@ -653,22 +722,21 @@ inline int big_alloc(const Shape& s, int batch, BigPlan* p, std::string& err) {
 }
 
 // problems [first, first + count) of the handle (the kernels index problems from 0: views start at `first`)
-inline int big_launch(BigPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st, std::string& err) {
-  constexpr int NS = 64, NI = 16;
-  using D = BigDim<NS>;
+template <int NS>
+inline int big_launch_t(BigPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st, std::string& err) {
   const int N = s.N;
   p.launches = 0;
   cudaError_t e = cudaMemsetAsync(p.bb.lam, 0, sizeof(double) * (size_t)batch * (N + 1) * NS, st);
   if (e != cudaSuccess) { err = std::string("big launch: ") + cudaGetErrorString(e); return -3; }
-  const int leaf_smem = ((NS + 4) * (NS + NI) + 2 * (NS + NI) + 2 * NS + 3 * NS) * (int)sizeof(double);
+  const int leaf_smem = big_leaf_smem_doubles<NS>() * (int)sizeof(double);
   const int schur_smem = (2 * NS + 1) * (NS + 4) * (int)sizeof(double);
   const int solve_smem = (NS * (NS + 4) + (NS / 8) * 64) * (int)sizeof(double);
-  if ((e = smem_optin(big_leaf_kernel<NS, NI>, leaf_smem)) != cudaSuccess || (e = smem_optin(big_solve_kernel<NS>, solve_smem)) != cudaSuccess ||
+  if ((e = smem_optin(big_leaf_kernel<NS>, leaf_smem)) != cudaSuccess || (e = smem_optin(big_solve_kernel<NS>, solve_smem)) != cudaSuccess ||
       (e = smem_optin(big_schur_kernel<NS>, schur_smem)) != cudaSuccess) {
     err = std::string("big launch: ") + cudaGetErrorString(e);
     return -3;
   }
-  big_leaf_kernel<NS, NI><<<(unsigned)((size_t)batch * N), 256, leaf_smem, st>>>(s, b, p.bb, pack_rhs);
+  big_leaf_kernel<NS><<<(unsigned)((size_t)batch * N), 256, leaf_smem, st>>>(s, b, p.bb, pack_rhs);
   ++p.launches;
   const double* ein = p.bb.entA;
   for (int level = 0; level < s.K; ++level) {
@@ -677,10 +745,10 @@ inline int big_launch(BigPlan& p, const Shape& s, const Bufs& b, int batch, int 
     const long long nmerge = (long long)batch * M;
     big_factor_reg_kernel<NS><<<(unsigned)((nmerge + BIG_FACTOR_REG_WPC - 1) / BIG_FACTOR_REG_WPC), 32 * BIG_FACTOR_REG_WPC, 0, st>>>(
         s, b, ein, p.bb.ufac, level, M, nmerge);
-    big_solve_kernel<NS><<<(unsigned)nmerge, BIG_SOLVE_THREADS, solve_smem, st>>>(s, ein, p.bb.ufac, p.bb.rec, level, M);
+    big_solve_kernel<NS><<<(unsigned)nmerge, big_solve_threads<NS>(), solve_smem, st>>>(s, ein, p.bb.ufac, p.bb.rec, level, M);
     p.launches += 2;
     if (level < s.K - 1) {
-      big_schur_kernel<NS><<<(unsigned)nmerge, 256, schur_smem, st>>>(s, ein, eout, p.bb.rec, p.bb.ufac, level, M);
+      big_schur_kernel<NS><<<(unsigned)nmerge, 4 * NS, schur_smem, st>>>(s, ein, eout, p.bb.rec, p.bb.ufac, level, M);
       ++p.launches;
     }
     ein = eout;
@@ -690,11 +758,15 @@ inline int big_launch(BigPlan& p, const Shape& s, const Bufs& b, int batch, int 
     big_topdown_kernel<NS><<<(unsigned)((size_t)batch * M), NS, 0, st>>>(N, p.bb.rec, p.bb.ufac, p.bb.lam, level, M);
     ++p.launches;
   }
-  big_down_kernel<NS, NI><<<(unsigned)((size_t)batch * N), 256, 0, st>>>(s, b, p.bb.lam, pack_rhs);
+  big_down_kernel<NS><<<(unsigned)((size_t)batch * N), 256, 0, st>>>(s, b, p.bb.lam, pack_rhs);
   ++p.launches;
   e = cudaGetLastError();
   if (e != cudaSuccess) { err = std::string("big launch: ") + cudaGetErrorString(e); return -3; }
   return 0;
+}
+
+inline int big_launch(BigPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st, std::string& err) {
+  return p.ns == 32 ? big_launch_t<32>(p, s, b, batch, pack_rhs, st, err) : big_launch_t<64>(p, s, b, batch, pack_rhs, st, err);
 }
 
 }  // namespace rslqr

@@ -58,7 +58,7 @@ struct rslqr_cuda_solver {
   FusedPlan fused; int force_dfma;
   ScanPlan scan; int g0_pref;
   bool pdl;   // latency mode (batch < 64): kernels are chained by programmatic dependent launch (kernels_staged.cuh)
-  BigPlan big{};  // dual-form path for large blocks (n = 64, m = 16): buffers allocated on the first solve
+  BigPlan big{};  // dual-form path for large blocks (n <= 64, m <= 16 without an instance of the warp kernels): buffers allocated on the first solve
   int factored = 0;  // `fact` holds a finished staged factorization of the uploaded problems
   bool prof_keep = false;  // keep the profile spans across enqueues (the chunks of solve_host)
   double* ric_gain = nullptr;  // [batch][N][K | dv | P | p] of the Riccati comparison solver (allocated on first use)
@@ -541,9 +541,9 @@ extern "C" int rslqr_cuda_solve_async(rslqr_cuda_solver* h, int pack_rhs) {
     b.knots += f * s.N * s.stride; b.x0 += f * s.n; b.soln += f * s.N * s.zs;
     b.status += f * 3 * s.N; b.flags += f;
     BigPlan q = h->big;
-    q.bb.entA += f * s.N * BigDim<64>::ENT; q.bb.entB += f * (s.N / 2) * BigDim<64>::ENT;
-    q.bb.rec += f * s.N * BigDim<64>::WSZ; q.bb.lam += f * (s.N + 1) * s.n;
-    q.bb.ufac += f * s.N * BigFac<64>::SIZE;
+    q.bb.entA += f * s.N * big_ent_doubles(q.ns); q.bb.entB += f * (s.N / 2) * big_ent_doubles(q.ns);
+    q.bb.rec += f * s.N * big_rec_doubles(q.ns); q.bb.lam += f * (s.N + 1) * q.ns;
+    q.bb.ufac += f * s.N * big_fac_doubles(q.ns);
     int rc = big_launch(q, s, b, h->r_count, pack_rhs, h->stream, g_err);
     if (rc) return rc;
     h->launches = q.launches;

@@ -261,6 +261,44 @@ def test_dual_form_scan_path_more_shapes(shape):
             assert O.kkt_residual(n, m, N, kn[p], x0[p], z[p]) < 1e-10 * max(1.0, np.linalg.norm(z[p]))
 
 
+@pytest.mark.parametrize("shape", [(9, 4), (11, 3), (17, 1), (20, 7), (32, 8), (33, 9), (40, 10), (48, 16), (64, 8), (5, 16)])
+@pytest.mark.parametrize("N", [2, 16, 128])
+def test_large_block_path_pads_any_shape(shape, N):
+    # every (n <= 64, m <= 16) without an instance of the warp kernels runs on the large-block dual path (kernels_big.cuh)
+    # with n padded on chip to blocks of 32 or 64: default mode is the scan mode; against the oracle; re-solve bit-identical;
+    # a caller-supplied right-hand side; a non-positive Q entry raises that problem's flag and the leaf's status word
+    n, m = shape
+    B = 3
+    kn, x0 = R.synth_problems(n, m, N, 47, 0, B)
+    s = R.CudaSolver(n, m, N, batch=B, flags=0)
+    assert s.mode == R.MODE_SCAN
+    s.upload(kn, x0)
+    s.solve()
+    z = s.solution().copy()
+    assert not s.flags().any() and np.isfinite(z).all()
+    s.solve()
+    assert np.array_equal(s.solution(), z)
+    for p in range(B):
+        want, _ = O.port_solve(n, m, N, kn[p], x0[p], threads=2)
+        assert max(rel_err_classes(z[p], want, n, m, N)) < TOL, (shape, N, p)
+        assert O.kkt_residual(n, m, N, kn[p], x0[p], z[p]) < 1e-10 * max(1.0, np.linalg.norm(z[p]))
+    rhs = np.zeros((B, N, 2 * n + m))
+    for p in range(B):
+        ps = O.PortSolver(n, m, N)
+        ps.init(kn[p], x0[p])
+        rhs[p] = ps.soln
+        ps.close()
+    s.upload_rhs(rhs)
+    s.solve(pack_rhs=False)
+    assert np.linalg.norm(s.solution() - z) <= 1e-12 * np.linalg.norm(z)
+    bad = kn.copy()
+    bad[1, N // 2, 0] = -1.0
+    s.upload(bad, x0)
+    s.solve()
+    assert list(s.flags()) == [0, 1, 0] and s.status(1)[2 * (N // 2)] == -1
+    s.close()
+
+
 def test_shipped_n6_problem_runs_in_scan_mode():
     # lqr_prob_256.json (n=6, m=3: the only shape the reference ships) takes the scan path by default
     n, m, N, kn, x0 = R.load_problem_json(os.path.join(GOLDEN, "lqr_prob_256.json"))
