@@ -1,5 +1,6 @@
-// kernels_big.cuh -- the dual-form nested dissection (see kernels_dual.cuh for the formulation) for LARGE blocks,
-// n = 64, m = 16 (BASELINE configs[4]): an element [Saa | Sab | Sbb | sa | sb] is 99 KB and a merge touches three of
+// kernels_big.cuh -- the dual-form nested dissection (see kernels_dual.cuh for the formulation) for LARGE blocks:
+// n = 64, m = 16 (BASELINE configs[4]) and, with n padded on chip to blocks of NS = 32 or 64, every other n <= 64, m <= 16
+// that has no instance of the warp kernels. At n = 64 an element [Saa | Sab | Sbb | sa | sb] is 99 KB and a merge touches three of
 // them plus a 66 KB record, so elements live in HBM / L2 and a CTA (not a warp) owns a merge.
 //
 // Per level, three launches over all (problem, merge) pairs, all block arithmetic on mma.sync.m8n8k4.f64:
