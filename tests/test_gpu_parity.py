@@ -299,6 +299,22 @@ def test_large_block_path_pads_any_shape(shape, N):
     s.close()
 
 
+@pytest.mark.parametrize("shape", [(20, 7, 64), (33, 9, 32), (9, 4, 128), (13, 4, 256)])
+def test_host_api_takes_the_fast_paths_on_any_shape(shape):
+    # ndlqr_NewNdLqrSolver + Initialize + Solve on shapes outside the reference's fixtures: the default solve runs the
+    # scan mode (large-block path with on-chip padding, or a warp-kernel instance), solution layout as src/solve.h:47-53
+    n, m, N = shape
+    pp = R.LIB.rslqr_synth_problem(n, m, N, 77, 3)
+    s = R.NdLqrSolver(n, m, N)
+    assert s.initialize(pp) == 0 and s.solve() == 0
+    assert R.LIB.rslqr_cuda_get_mode(s.c.device) == R.MODE_SCAN
+    z = s.solution().copy()
+    kn, x0 = R.synth_problems(n, m, N, 77, 3, 1)
+    want, _ = O.port_solve(n, m, N, kn[0], x0[0])
+    nv = (2 * n + m) * N - m
+    assert np.linalg.norm(z[:nv] - want[:nv]) <= TOL * np.linalg.norm(want[:nv])
+
+
 def test_shipped_n6_problem_runs_in_scan_mode():
     # lqr_prob_256.json (n=6, m=3: the only shape the reference ships) takes the scan path by default
     n, m, N, kn, x0 = R.load_problem_json(os.path.join(GOLDEN, "lqr_prob_256.json"))
