@@ -1,5 +1,5 @@
 // kernels_big.cuh -- the dual-form nested dissection (see kernels_dual.cuh for the formulation) for LARGE blocks:
-// n = 64, m = 16 (BASELINE configs[4]) and, with n padded on chip to blocks of NS = 32 or 64, every other n <= 64, m <= 16
+// n = 64, m = 16 (BASELINE configs[4]) and, with n padded on chip to blocks of NS = 32 or 64, every other n <= 64, m <= 32
 // that has no instance of the warp kernels. At n = 64 an element [Saa | Sab | Sbb | sa | sb] is 99 KB and a merge touches three of
 // them plus a 66 KB record, so elements live in HBM / L2 and a CTA (not a warp) owns a merge.
 //
@@ -45,14 +45,14 @@ struct BigBufs {
   double* ufac;  // [batch][N][BigFac::SIZE] factor U, block inverses and 1/d of the separator after knot i at slot i
 };
 
-constexpr int BIG_NI = 16;  // inputs the large-block kernels are laid out for (m <= BIG_NI)
+constexpr int BIG_NI_MAX = 32;  // the leaf and down kernels are laid out for NI = 16 or 32 input columns (m <= NI)
 
 // G output tiles of Sbb = [A | B] D [A | B]^T for one warp: tiles warp, warp + 8, ... of the lower block triangle in row-major
 // order (tile i = (t, j), j <= t, i = t (t + 1) / 2 + j). AB: [A | B] in shared memory (column-major, ld NS + 4), dv: D.
 // Rows / columns >= n are padding: 0.5 on the diagonal there (the S of a merge, SbbL + SaaR, gets the identity).
-template <int NS, int G>
+template <int NS, int NI, int G>
 __device__ __forceinline__ void big_leaf_sbb(const double* AB, const double* dv, double* Sbb, int warp, int lane, int n) {
-  constexpr int XU = NS + BIG_NI, LDA = NS + 4, KS = XU / 4;
+  constexpr int XU = NS + NI, LDA = NS + 4, KS = XU / 4;
   const int q = lane & 3, rr = lane >> 2;
   const double *pa[G], *pb[G];
   double* po[G];
@@ -91,18 +91,18 @@ __device__ __forceinline__ void big_leaf_sbb(const double* AB, const double* dv,
 //   Saa = Q^-1, Sab = -Q^-1 A^T, Sbb = A Q^-1 A^T + B R^-1 B^T, sa = -z_x - z_lambda, sb = A z_x + B z_u
 //   knot 0: x_0 is fixed (z_x = x0) and lambda_0 is no unknown: Q^-1 -> 0 in the blocks; last knot: only Saa, sa.
 // The blocks are NS x NS with NS = 32 or 64 >= n = s.n: a smaller n is padded on chip (zero rows / columns, 0.5 on the
-// padded diagonal of Saa and Sbb), m = s.m <= BIG_NI; everything above the leaves works on NS x NS blocks.
-// dynamic smem: big_leaf_smem_doubles<NS>()
+// padded diagonal of Saa and Sbb), m = s.m <= NI (16 or 32 columns of B); everything above the leaves works on NS x NS blocks.
+// dynamic smem: big_leaf_smem_doubles<NS, NI>()
 // ---------------------------------------------------------------------------------------------------------
-template <int NS>
+template <int NS, int NI>
 __host__ __device__ constexpr int big_leaf_smem_doubles() {
-  return (NS + 4) * (NS + BIG_NI) + 2 * (NS + BIG_NI) + 2 * NS + (256 / NS - 1) * NS;
+  return (NS + 4) * (NS + NI) + 2 * (NS + NI) + 2 * NS + (256 / NS - 1) * NS;
 }
 
-template <int NS>
+template <int NS, int NI>
 __global__ void __launch_bounds__(256, 3) big_leaf_kernel(Shape s, Bufs b, BigBufs bb, int pack_rhs) {
   using D = BigDim<NS>;
-  constexpr int XU = NS + BIG_NI, LDA = NS + 4;  // (LDA = 4 mod 16: the DMMA fragments of a warp fall into two wavefronts)
+  constexpr int XU = NS + NI, LDA = NS + 4;  // (LDA = 4 mod 16: the DMMA fragments of a warp fall into two wavefronts)
   constexpr int NT = NS / 8, NTASK = NT * (NT + 1) / 2, PARTS = 256 / NS;
   static_assert(NS % 32 == 0 && 256 % NS == 0 && XU % 4 == 0 && XU % PARTS == 0 && NTASK >= 8, "8 warps; k-steps of 4");
   extern __shared__ __align__(16) double smf[];
@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(256, 3) big_leaf_kernel(Shape s, Bufs b, BigBu
   const bool first = k == 0, last = k == N - 1;
   // [A | B] -> shared memory by 8-byte asynchronous copies (the knot block is only 8-byte aligned), in flight while the
   // diagonal / right-hand-side part below is computed; padding is zero
-  if (n == NS && m == BIG_NI) {  // nothing to pad: [A | B] is one contiguous run of the knot block
+  if (n == NS && m == NI) {  // nothing to pad: [A | B] is one contiguous run of the knot block
     for (int e = tid; e < NS * XU; e += nthr) {
       const int l = e / NS, r = e - l * NS;
       if (last) AB[r + LDA * l] = 0.0;
@@ -182,8 +182,8 @@ __global__ void __launch_bounds__(256, 3) big_leaf_kernel(Shape s, Bufs b, BigBu
   {
     const int warp = tid >> 5;
     constexpr int GLO = NTASK / 8, REM = NTASK % 8;
-    if (warp < REM) big_leaf_sbb<NS, GLO + 1>(AB, dv, E + D::OBB, warp, tid & 31, n);
-    else big_leaf_sbb<NS, GLO>(AB, dv, E + D::OBB, warp, tid & 31, n);
+    if (warp < REM) big_leaf_sbb<NS, NI, GLO + 1>(AB, dv, E + D::OBB, warp, tid & 31, n);
+    else big_leaf_sbb<NS, NI, GLO>(AB, dv, E + D::OBB, warp, tid & 31, n);
   }
   {  // sb = [A | B] z: PARTS threads per row, a share of the XU terms each (thread = NS part + row)
     const int r = tid & (NS - 1), part = tid / NS;
@@ -607,9 +607,9 @@ __global__ void __launch_bounds__(NS) big_topdown_kernel(int N, const double* re
 // equations (the reference's rhs propagation src/solve.c:175-180 telescoped); knot 0: x_0 = x0 and
 // lambda_0 = Q_0 x0 + q_0 + A_0^T lambda_1 (src/nested_dissection.c:24-59). One CTA per (problem, knot), one thread per row.
 // ---------------------------------------------------------------------------------------------------------
-template <int NS>
+template <int NS, int NI>
 __global__ void __launch_bounds__(256) big_down_kernel(Shape s, Bufs b, const double* lam_all, int pack_rhs) {
-  constexpr int XU = NS + BIG_NI, CPW = XU / 8, RPL = NS / 32;
+  constexpr int XU = NS + NI, CPW = XU / 8, RPL = NS / 32;
   static_assert(NS % 32 == 0 && XU % 8 == 0, "NS / 32 elements of a column per lane; columns dealt to 8 warps");
   __shared__ double dot[XU];
   const int N = s.N, n = s.n, m = s.m;
@@ -685,8 +685,8 @@ struct BigPlan {
   int launches;
 };
 
-// any n <= 64 with m <= BIG_NI: blocks of 32 or 64 (the smallest that holds n)
-inline bool big_shape_ok(int n, int m, int N) { return n >= 1 && n <= 64 && m >= 1 && m <= BIG_NI && N >= 2; }
+// any n <= 64 with m <= 32: blocks of 32 or 64 (the smallest that holds n), 16 or 32 input columns
+inline bool big_shape_ok(int n, int m, int N) { return n >= 1 && n <= 64 && m >= 1 && m <= BIG_NI_MAX && N >= 2; }
 inline int big_block_size(int n) { return n <= 32 ? 32 : 64; }
 inline size_t big_ent_doubles(int ns) { return (size_t)3 * ns * ns + 2 * ns; }
 inline size_t big_rec_doubles(int ns) { return ((size_t)2 * ns + 1) * ns; }
@@ -723,21 +723,21 @@ inline int big_alloc(const Shape& s, int batch, BigPlan* p, std::string& err) {
 }
 
 // problems [first, first + count) of the handle (the kernels index problems from 0: views start at `first`)
-template <int NS>
+template <int NS, int NI>
 inline int big_launch_t(BigPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st, std::string& err) {
   const int N = s.N;
   p.launches = 0;
   cudaError_t e = cudaMemsetAsync(p.bb.lam, 0, sizeof(double) * (size_t)batch * (N + 1) * NS, st);
   if (e != cudaSuccess) { err = std::string("big launch: ") + cudaGetErrorString(e); return -3; }
-  const int leaf_smem = big_leaf_smem_doubles<NS>() * (int)sizeof(double);
+  const int leaf_smem = big_leaf_smem_doubles<NS, NI>() * (int)sizeof(double);
   const int schur_smem = (2 * NS + 1) * (NS + 4) * (int)sizeof(double);
   const int solve_smem = (NS * (NS + 4) + (NS / 8) * 64) * (int)sizeof(double);
-  if ((e = smem_optin(big_leaf_kernel<NS>, leaf_smem)) != cudaSuccess || (e = smem_optin(big_solve_kernel<NS>, solve_smem)) != cudaSuccess ||
+  if ((e = smem_optin(big_leaf_kernel<NS, NI>, leaf_smem)) != cudaSuccess || (e = smem_optin(big_solve_kernel<NS>, solve_smem)) != cudaSuccess ||
       (e = smem_optin(big_schur_kernel<NS>, schur_smem)) != cudaSuccess) {
     err = std::string("big launch: ") + cudaGetErrorString(e);
     return -3;
   }
-  big_leaf_kernel<NS><<<(unsigned)((size_t)batch * N), 256, leaf_smem, st>>>(s, b, p.bb, pack_rhs);
+  big_leaf_kernel<NS, NI><<<(unsigned)((size_t)batch * N), 256, leaf_smem, st>>>(s, b, p.bb, pack_rhs);
   ++p.launches;
   const double* ein = p.bb.entA;
   for (int level = 0; level < s.K; ++level) {
@@ -759,7 +759,7 @@ inline int big_launch_t(BigPlan& p, const Shape& s, const Bufs& b, int batch, in
     big_topdown_kernel<NS><<<(unsigned)((size_t)batch * M), NS, 0, st>>>(N, p.bb.rec, p.bb.ufac, p.bb.lam, level, M);
     ++p.launches;
   }
-  big_down_kernel<NS><<<(unsigned)((size_t)batch * N), 256, 0, st>>>(s, b, p.bb.lam, pack_rhs);
+  big_down_kernel<NS, NI><<<(unsigned)((size_t)batch * N), 256, 0, st>>>(s, b, p.bb.lam, pack_rhs);
   ++p.launches;
   e = cudaGetLastError();
   if (e != cudaSuccess) { err = std::string("big launch: ") + cudaGetErrorString(e); return -3; }
@@ -767,7 +767,9 @@ inline int big_launch_t(BigPlan& p, const Shape& s, const Bufs& b, int batch, in
 }
 
 inline int big_launch(BigPlan& p, const Shape& s, const Bufs& b, int batch, int pack_rhs, cudaStream_t st, std::string& err) {
-  return p.ns == 32 ? big_launch_t<32>(p, s, b, batch, pack_rhs, st, err) : big_launch_t<64>(p, s, b, batch, pack_rhs, st, err);
+  if (s.m <= 16)
+    return p.ns == 32 ? big_launch_t<32, 16>(p, s, b, batch, pack_rhs, st, err) : big_launch_t<64, 16>(p, s, b, batch, pack_rhs, st, err);
+  return p.ns == 32 ? big_launch_t<32, 32>(p, s, b, batch, pack_rhs, st, err) : big_launch_t<64, 32>(p, s, b, batch, pack_rhs, st, err);
 }
 
 }  // namespace rslqr

@@ -261,10 +261,11 @@ def test_dual_form_scan_path_more_shapes(shape):
             assert O.kkt_residual(n, m, N, kn[p], x0[p], z[p]) < 1e-10 * max(1.0, np.linalg.norm(z[p]))
 
 
-@pytest.mark.parametrize("shape", [(9, 4), (11, 3), (17, 1), (20, 7), (32, 8), (33, 9), (40, 10), (48, 16), (64, 8), (5, 16)])
+@pytest.mark.parametrize("shape", [(9, 4), (11, 3), (17, 1), (20, 7), (32, 8), (33, 9), (40, 10), (48, 16), (64, 8), (5, 16),
+                                   (24, 20), (40, 17), (64, 32)])
 @pytest.mark.parametrize("N", [2, 16, 128])
 def test_large_block_path_pads_any_shape(shape, N):
-    # every (n <= 64, m <= 16) without an instance of the warp kernels runs on the large-block dual path (kernels_big.cuh)
+    # every (n <= 64, m <= 32) without an instance of the warp kernels runs on the large-block dual path (kernels_big.cuh)
     # with n padded on chip to blocks of 32 or 64: default mode is the scan mode; against the oracle; re-solve bit-identical;
     # a caller-supplied right-hand side; a non-positive Q entry raises that problem's flag and the leaf's status word
     n, m = shape
